@@ -1,0 +1,816 @@
+// ba_engine.cu — the CUDA engine behind include/ba_engine.h: host driver of the Levenberg-Marquardt loop.
+//
+// Replaces ceres::Solve at src/adjuster/BundleAdjuster.h:126 (trust-region LM as configured at :167-174; rules restated
+// in SURVEY.md §8 a-LM) with hand-written sm_100a kernels (ba_kernels.cuh).  Map state lives on the device as FP64
+// SoA buffers for the whole solve; the host only sequences kernels and reads one small struct of scalars per decision.
+// There is NO CPU fallback: without a CUDA device every entry point that needs one returns BA_ERR_CUDA.
+//
+// Multi-GPU (one process per GPU): points and their observations are sharded by contiguous range; poses, intrinsics
+// and all PCG vectors are replicated; per-rank partial sums of camera-side quantities are combined with NCCL
+// all-reduces on the compute stream.  NCCL is loaded with dlopen only when world_size > 1.
+#include "../../include/ba_engine.h"
+
+#include <cuda_runtime.h>
+#include <dlfcn.h>
+
+#include <algorithm>
+#include <cfloat>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <limits>
+#include <string>
+#include <vector>
+
+#include "ba_kernels.cuh"
+
+namespace {
+using std::vector;
+thread_local std::string g_create_error;
+
+#define CU_TRY(expr)                                                                                         \
+    do {                                                                                                     \
+        cudaError_t _e = (expr);                                                                             \
+        if (_e != cudaSuccess) {                                                                             \
+            char _b[512];                                                                                    \
+            std::snprintf(_b, sizeof _b, "%s failed at %s:%d: %s", #expr, __FILE__, __LINE__, cudaGetErrorString(_e)); \
+            throw BaFail{BA_ERR_CUDA, _b};                                                                   \
+        }                                                                                                    \
+    } while (0)
+
+struct BaFail { int code; std::string msg; };
+
+// ---- minimal NCCL binding, resolved at run time (torch bundles its own libnccl.so.2; whichever is already loaded wins) ----
+struct Nccl {
+    typedef struct { char internal[128]; } UniqueId;
+    typedef void* Comm;
+    int (*GetUniqueId)(UniqueId*) = nullptr;
+    int (*CommInitRank)(Comm*, int, UniqueId, int) = nullptr;
+    int (*CommDestroy)(Comm) = nullptr;
+    int (*AllReduce)(const void*, void*, size_t, int, int, Comm, cudaStream_t) = nullptr;
+    int (*Broadcast)(const void*, void*, size_t, int, int, Comm, cudaStream_t) = nullptr;
+    int (*GroupStart)() = nullptr;
+    int (*GroupEnd)() = nullptr;
+    const char* (*GetErrorString)(int) = nullptr;
+    void* handle = nullptr;
+    enum { kInt32 = 2, kFloat64 = 8, kSum = 0, kMax = 2 };   // ncclDataType_t / ncclRedOp_t values (stable since NCCL 2.0)
+    bool load(std::string& err) {
+        if (handle) return true;
+        for (const char* n : {"libnccl.so.2", "libnccl.so"}) { handle = dlopen(n, RTLD_NOW | RTLD_GLOBAL); if (handle) break; }
+        if (!handle) { err = std::string("dlopen libnccl.so.2 failed: ") + dlerror(); return false; }
+        auto sym = [&](const char* n) { void* p = dlsym(handle, n); if (!p) err = std::string("missing NCCL symbol ") + n; return p; };
+        GetUniqueId = reinterpret_cast<decltype(GetUniqueId)>(sym("ncclGetUniqueId"));
+        CommInitRank = reinterpret_cast<decltype(CommInitRank)>(sym("ncclCommInitRank"));
+        CommDestroy = reinterpret_cast<decltype(CommDestroy)>(sym("ncclCommDestroy"));
+        AllReduce = reinterpret_cast<decltype(AllReduce)>(sym("ncclAllReduce"));
+        Broadcast = reinterpret_cast<decltype(Broadcast)>(sym("ncclBroadcast"));
+        GroupStart = reinterpret_cast<decltype(GroupStart)>(sym("ncclGroupStart"));
+        GroupEnd = reinterpret_cast<decltype(GroupEnd)>(sym("ncclGroupEnd"));
+        GetErrorString = reinterpret_cast<decltype(GetErrorString)>(sym("ncclGetErrorString"));
+        return GetUniqueId && CommInitRank && CommDestroy && AllReduce && Broadcast && GroupStart && GroupEnd && GetErrorString;
+    }
+};
+Nccl g_nccl;
+
+#define NCCL_TRY(expr)                                                                                       \
+    do {                                                                                                     \
+        int _r = (expr);                                                                                     \
+        if (_r != 0) {                                                                                       \
+            char _b[512];                                                                                    \
+            std::snprintf(_b, sizeof _b, "%s failed at %s:%d: %s", #expr, __FILE__, __LINE__, g_nccl.GetErrorString(_r)); \
+            throw BaFail{BA_ERR_NCCL, _b};                                                                   \
+        }                                                                                                    \
+    } while (0)
+
+template <class T>
+struct DevBuf {
+    T* p = nullptr;
+    size_t n = 0;
+    void alloc(size_t count) {
+        if (count <= n && p) return;
+        release();
+        CU_TRY(cudaMalloc(reinterpret_cast<void**>(&p), std::max<size_t>(count, 1) * sizeof(T)));
+        n = count;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; n = 0; }
+    void upload(const T* h, size_t count, cudaStream_t s) { alloc(count); if (count) CU_TRY(cudaMemcpyAsync(p, h, count * sizeof(T), cudaMemcpyHostToDevice, s)); }
+    void zero(cudaStream_t s) { if (p && n) CU_TRY(cudaMemsetAsync(p, 0, n * sizeof(T), s)); }
+    ~DevBuf() { release(); }
+};
+
+enum KernelId { KID_K0 = 0, KID_K1, KID_K1C, KID_K2C, KID_K3P, KID_K3C, KID_K4, KID_K5, KID_K7, KID_K8, KID_PCGV, KID_MISC, KID_COUNT };
+const char* const kKernelNames[KID_COUNT] = {"K0_camera_precompute", "K1_residual_jacobian", "K1c_candidate_cost", "K2c_camera_blocks",
+                                             "K3p_point_blocks",      "K3c_camera_blocks",    "K4_reduced_rhs",     "K5_schur_matvec",
+                                             "K7_backsub_model",      "K8_candidate",         "PCG_vector_update",  "misc_reductions"};
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------------------------
+struct ba_engine {
+    ba_options opt{};
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    bool has_problem = false;
+    std::string err;
+    // global sizes and this rank's shard
+    int Nc = 0, Ng = 0, NpG = 0, NoG = 0;   // global
+    int pb = 0, pe = 0, ob = 0, oe = 0;     // local point / observation ranges [pb,pe) [ob,oe)
+    int Np = 0, No = 0, ldo = 0, nTiles = 0, nf = 0, fi = 0;
+    // host copies kept for ba_get_structure and ba_reset_state
+    vector<int32_t> h_obs_cam, h_obs_pt;
+    vector<uint8_t> h_cam_fixed, h_cam_free;
+    vector<int32_t> h_shard_pt;   // [world+1] point range boundaries of every rank
+    // device: static problem data
+    DevBuf<int> d_tile_off, d_obs_cam, d_obs_pt, d_pt_off, d_cam_group, d_perm, d_cam_off;
+    DevBuf<double2> d_obs_uv;
+    DevBuf<unsigned char> d_cam_free, d_grp_free;
+    // device: parameters (current, candidate, initial)
+    DevBuf<double> d_pose, d_intr, d_pt, d_cpose, d_cintr, d_cpt, d_pose0, d_intr0, d_pt0, d_ptfull;
+    // device: work arrays
+    DevBuf<double> d_camrec, d_ccamrec;
+    DevBuf<double2> d_J2, d_r2;
+    DevBuf<double> d_Hpp, d_gp, d_Hinv, d_vp, d_yp, d_sc_pt;
+    DevBuf<double> d_red;        // [Hcc 36Nc | gc 6Nc | Hii 16Ng | gi 4Ng] — one all-reduce per evaluation
+    DevBuf<double> d_sc_f, d_Df2, d_Minv, d_b, d_x, d_r, d_z, d_p, d_y;
+    DevBuf<double> d_part0, d_part1;   // per-tile / per-block partials
+    DevBuf<bak::Scalars> d_scal;
+    bak::Scalars* h_scal = nullptr;    // pinned
+    bak::View V{};
+    // multi-GPU
+    Nccl::Comm comm = nullptr;
+    // profiling
+    bool profiling = false;
+    struct Stat { int64_t launches = 0; double ms = 0.0; double bytes = 0.0; } stats[KID_COUNT];
+    struct Pending { int kid; cudaEvent_t a, b; };
+    vector<Pending> pending;
+    vector<cudaEvent_t> ev_pool;
+    cudaEvent_t ev_t0 = nullptr, ev_t1 = nullptr;
+    // results
+    vector<ba_iter_record> traj;
+    ba_summary summary{};
+    bool scales_set = false;
+
+    double* Hcc() { return d_red.p; }
+    double* gc() { return d_red.p + size_t(36) * Nc; }
+    double* Hii() { return d_red.p + size_t(42) * Nc; }
+    double* gi() { return d_red.p + size_t(42) * Nc + size_t(16) * Ng; }
+    size_t red_count() const { return size_t(42) * Nc + size_t(20) * Ng; }
+};
+
+namespace {
+
+int fail(ba_engine* e, int code, const std::string& msg) { if (e) e->err = msg; else g_create_error = msg; return code; }
+
+// Profiling hook around one launch: CUDA events on the engine's stream, resolved after the solve's final sync.
+struct LaunchTimer {
+    ba_engine* e; int kid; cudaEvent_t a = nullptr, b = nullptr;
+    LaunchTimer(ba_engine* e_, int kid_) : e(e_), kid(kid_) {
+        ++e->stats[kid].launches;
+        if (!e->profiling) return;
+        auto get = [&]() { cudaEvent_t ev; if (!e->ev_pool.empty()) { ev = e->ev_pool.back(); e->ev_pool.pop_back(); } else cudaEventCreate(&ev); return ev; };
+        a = get(); b = get();
+        cudaEventRecord(a, e->stream);
+    }
+    ~LaunchTimer() { if (a) { cudaEventRecord(b, e->stream); e->pending.push_back({kid, a, b}); } }
+};
+
+void resolve_timers(ba_engine* e) {
+    for (auto& p : e->pending) {
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, p.a, p.b) == cudaSuccess) e->stats[p.kid].ms += ms;
+        e->ev_pool.push_back(p.a); e->ev_pool.push_back(p.b);
+    }
+    e->pending.clear();
+}
+
+void allreduce_sum(ba_engine* e, double* buf, size_t n) {
+    if (e->opt.world_size <= 1) return;
+    NCCL_TRY(g_nccl.AllReduce(buf, buf, n, Nccl::kFloat64, Nccl::kSum, e->comm, e->stream));
+}
+void allreduce_max(ba_engine* e, double* buf, size_t n) {
+    if (e->opt.world_size <= 1) return;
+    NCCL_TRY(g_nccl.AllReduce(buf, buf, n, Nccl::kFloat64, Nccl::kMax, e->comm, e->stream));
+}
+void allreduce_flags(ba_engine* e, int* buf, size_t n) {
+    if (e->opt.world_size <= 1) return;
+    NCCL_TRY(g_nccl.AllReduce(buf, buf, n, Nccl::kInt32, Nccl::kMax, e->comm, e->stream));
+}
+
+// Cut the point-sorted observation list [0,No) into tiles of whole points with <= TILE_OBS observations; a point with
+// more observations than that becomes a tile of its own (the kernels walk it in chunks).
+void build_tiles(const vector<int32_t>& pt_off, int Np, vector<int32_t>& tile_off) {
+    tile_off.clear();
+    tile_off.push_back(0);
+    int start = 0;   // first observation of the open tile
+    for (int p = 0; p < Np; ++p) {
+        const int a = pt_off[p], b = pt_off[p + 1];
+        if (b == a) continue;
+        if (b - start > bak::TILE_OBS) {          // point p does not fit into the open tile
+            if (a > start) { tile_off.push_back(a); start = a; }
+            if (b - a > bak::TILE_OBS) { tile_off.push_back(b); start = b; }   // long point: closes its own tile
+        }
+    }
+    if (tile_off.back() != pt_off[Np]) tile_off.push_back(pt_off[Np]);
+}
+
+void do_set_problem(ba_engine* e, const ba_problem* P) {
+    const int Nc = P->num_cameras, Ng = P->num_groups, NpG = P->num_points, NoG = P->num_observations;
+    const int W = e->opt.world_size, R = e->opt.rank;
+    CU_TRY(cudaSetDevice(e->device));
+    cudaStream_t s = e->stream;
+    e->Nc = Nc; e->Ng = Ng; e->NpG = NpG; e->NoG = NoG;
+    e->fi = e->opt.intrinsics_free ? 1 : 0;
+    e->nf = 6 * Nc + (e->fi ? 4 * Ng : 0);
+    e->h_obs_cam.assign(P->obs_cam, P->obs_cam + NoG);
+    e->h_obs_pt.assign(P->obs_pt, P->obs_pt + NoG);
+    e->h_cam_fixed.assign(P->cam_fixed, P->cam_fixed + Nc);
+
+    // global CSR by point, global free masks
+    vector<int32_t> gpt_off(size_t(NpG) + 1, 0);
+    vector<int32_t> cam_cnt(Nc, 0);
+    for (int o = 0; o < NoG; ++o) { ++gpt_off[P->obs_pt[o] + 1]; ++cam_cnt[P->obs_cam[o]]; }
+    for (int p = 0; p < NpG; ++p) gpt_off[p + 1] += gpt_off[p];
+    e->h_cam_free.assign(Nc, 0);
+    vector<unsigned char> grp_free(std::max(Ng, 1), 0);
+    for (int c = 0; c < Nc; ++c) {
+        e->h_cam_free[c] = (!P->cam_fixed[c] && cam_cnt[c] > 0) ? 1 : 0;
+        if (e->fi && cam_cnt[c] > 0) grp_free[P->cam_group[c]] = 1;
+    }
+
+    // shard: contiguous point ranges balanced by observation count, cut at point boundaries
+    e->h_shard_pt.assign(W + 1, 0);
+    e->h_shard_pt[W] = NpG;
+    for (int r = 1; r < W; ++r) {
+        const int64_t target = int64_t(NoG) * r / W;
+        int p = int(std::lower_bound(gpt_off.begin(), gpt_off.end(), int32_t(target)) - gpt_off.begin());
+        e->h_shard_pt[r] = std::min(std::max(p, e->h_shard_pt[r - 1]), NpG);
+    }
+    e->pb = e->h_shard_pt[R]; e->pe = e->h_shard_pt[R + 1];
+    e->ob = gpt_off[e->pb]; e->oe = gpt_off[e->pe];
+    const int Np = e->pe - e->pb, No = e->oe - e->ob;
+    e->Np = Np; e->No = No;
+    e->ldo = (No + 31) / 32 * 32 + 32;
+
+    // local index arrays
+    vector<int32_t> pt_off(size_t(Np) + 1), obs_pt(No), tile_off, perm(No), cam_off(size_t(Nc) + 1, 0);
+    for (int p = 0; p <= Np; ++p) pt_off[p] = gpt_off[e->pb + p] - e->ob;
+    for (int o = 0; o < No; ++o) { obs_pt[o] = P->obs_pt[e->ob + o] - e->pb; ++cam_off[P->obs_cam[e->ob + o] + 1]; }
+    for (int c = 0; c < Nc; ++c) cam_off[c + 1] += cam_off[c];
+    {
+        vector<int32_t> cur(cam_off.begin(), cam_off.end() - 1);
+        for (int o = 0; o < No; ++o) perm[cur[P->obs_cam[e->ob + o]]++] = o;
+    }
+    build_tiles(pt_off, Np, tile_off);
+    e->nTiles = int(tile_off.size()) - 1;
+
+    e->d_tile_off.upload(tile_off.data(), tile_off.size(), s);
+    e->d_obs_cam.upload(P->obs_cam + e->ob, No, s);
+    e->d_obs_pt.upload(obs_pt.data(), No, s);
+    e->d_obs_uv.upload(reinterpret_cast<const double2*>(P->obs_uv) + e->ob, No, s);
+    e->d_pt_off.upload(pt_off.data(), pt_off.size(), s);
+    e->d_cam_group.upload(P->cam_group, Nc, s);
+    e->d_perm.upload(perm.data(), No, s);
+    e->d_cam_off.upload(cam_off.data(), cam_off.size(), s);
+    e->d_cam_free.upload(e->h_cam_free.data(), Nc, s);
+    e->d_grp_free.upload(grp_free.data(), std::max(Ng, 1), s);
+    e->d_pose0.upload(P->pose, size_t(6) * Nc, s);
+    e->d_intr0.upload(P->intr, size_t(4) * Ng, s);
+    e->d_pt0.upload(P->pt + size_t(3) * e->pb, size_t(3) * Np, s);
+    for (auto* b : {&e->d_pose, &e->d_cpose}) b->alloc(size_t(6) * Nc);
+    for (auto* b : {&e->d_intr, &e->d_cintr}) b->alloc(size_t(4) * Ng);
+    for (auto* b : {&e->d_pt, &e->d_cpt}) b->alloc(size_t(3) * Np);
+    e->d_camrec.alloc(size_t(bak::CAMREC) * Nc); e->d_ccamrec.alloc(size_t(bak::CAMREC) * Nc);
+    e->d_J2.alloc(size_t(e->fi ? 13 : 9) * e->ldo); e->d_r2.alloc(e->ldo);
+    e->d_Hpp.alloc(size_t(6) * Np); e->d_gp.alloc(size_t(3) * Np); e->d_Hinv.alloc(size_t(6) * Np);
+    e->d_vp.alloc(size_t(3) * Np); e->d_yp.alloc(size_t(3) * Np); e->d_sc_pt.alloc(size_t(3) * Np);
+    e->d_red.alloc(e->red_count());
+    for (auto* b : {&e->d_sc_f, &e->d_Df2, &e->d_b, &e->d_x, &e->d_r, &e->d_z, &e->d_p, &e->d_y}) b->alloc(e->nf);
+    e->d_Minv.alloc(size_t(36) * Nc + size_t(16) * Ng);
+    const size_t nparts = std::max<size_t>(e->nTiles, 2048);
+    e->d_part0.alloc(nparts); e->d_part1.alloc(nparts);
+    e->d_scal.alloc(1);
+    e->d_Hpp.zero(s); e->d_gp.zero(s); e->d_yp.zero(s); e->d_Hinv.zero(s); e->d_vp.zero(s); e->d_scal.zero(s);
+    CU_TRY(cudaMemcpyAsync(e->d_pose.p, e->d_pose0.p, size_t(6) * Nc * sizeof(double), cudaMemcpyDeviceToDevice, s));
+    CU_TRY(cudaMemcpyAsync(e->d_intr.p, e->d_intr0.p, size_t(4) * Ng * sizeof(double), cudaMemcpyDeviceToDevice, s));
+    CU_TRY(cudaMemcpyAsync(e->d_pt.p, e->d_pt0.p, size_t(3) * Np * sizeof(double), cudaMemcpyDeviceToDevice, s));
+
+    bak::View& V = e->V;
+    V.Nc = Nc; V.Ng = Ng; V.Np = Np; V.No = No; V.ldo = e->ldo; V.nTiles = e->nTiles; V.fi = e->fi;
+    V.tile_off = e->d_tile_off.p; V.obs_cam = e->d_obs_cam.p; V.obs_pt = e->d_obs_pt.p; V.obs_uv = e->d_obs_uv.p;
+    V.pt_off = e->d_pt_off.p; V.cam_group = e->d_cam_group.p; V.cam_free = e->d_cam_free.p; V.grp_free = e->d_grp_free.p;
+    V.perm_by_cam = e->d_perm.p; V.cam_off = e->d_cam_off.p;
+    V.J2 = e->d_J2.p; V.r2 = e->d_r2.p; V.Hpp = e->d_Hpp.p; V.gp = e->d_gp.p; V.Hinv = e->d_Hinv.p; V.vp = e->d_vp.p; V.yp = e->d_yp.p;
+    V.sc_pt = e->d_sc_pt.p;
+    CU_TRY(cudaStreamSynchronize(s));   // host staging vectors go out of scope
+    e->traj.clear();
+    e->scales_set = false;
+    e->has_problem = true;
+
+    // algorithmic bytes per launch of each kernel in THIS formulation, for roofline.achieved
+    const double no = No, np = Np, nc = Nc, jb = e->fi ? 208.0 : 144.0;
+    e->stats[KID_K0].bytes = (48 + 160) * nc;
+    e->stats[KID_K1].bytes = no * (24 + jb + 16) + np * (24 + 72) + 160 * nc;
+    e->stats[KID_K1C].bytes = no * 24 + np * 24 + 160 * nc;
+    e->stats[KID_K2C].bytes = no * (96 + (e->fi ? 64 : 0) + 16 + 4) + (288 + 48) * nc;
+    e->stats[KID_K3P].bytes = np * (48 + 24 + 24 + 48 + 24);
+    e->stats[KID_K3C].bytes = nc * (288 + 48 + 48 + 288);
+    e->stats[KID_K4].bytes = no * (jb + 16 + 8) + np * 24 + 48 * nc;
+    e->stats[KID_K5].bytes = no * (jb + 8) + np * (48 + 4) + 96 * nc;
+    e->stats[KID_K7].bytes = no * (jb + 8 + 16) + np * (48 + 24 + 24 + 4) + 48 * nc;
+    e->stats[KID_K8].bytes = np * 72 + nc * 144;
+    e->stats[KID_PCGV].bytes = double(e->nf) * 8 * 12 + 288 * nc;
+    e->stats[KID_MISC].bytes = 0;
+}
+
+}  // namespace
+
+namespace {
+
+// ---- kernel sequences ----------------------------------------------------------------------------------------
+inline int cdiv(int a, int b) { return (a + b - 1) / b; }
+constexpr int kNormBlocks = 592;   // 4 x 148 SMs for the grid-stride vector kernels
+
+void read_scalars(ba_engine* e) {
+    CU_TRY(cudaMemcpyAsync(e->h_scal, e->d_scal.p, sizeof(bak::Scalars), cudaMemcpyDeviceToHost, e->stream));
+    CU_TRY(cudaStreamSynchronize(e->stream));
+}
+
+// Evaluate residuals, Jacobian, cost and the block Hessian / gradient at the CURRENT parameters (K0, K1, K2c).
+void evaluate_full(ba_engine* e) {
+    cudaStream_t s = e->stream;
+    bak::Scalars* sc = e->d_scal.p;
+    const bak::RobustParams rp{e->opt.robust_kind, e->opt.robust_a};
+    CU_TRY(cudaMemsetAsync(&sc->bad_eval, 0, sizeof(int), s));
+    { LaunchTimer t(e, KID_K0);
+      bak::k0_camera_precompute<<<cdiv(e->Nc, 128), 128, 0, s>>>(e->Nc, e->d_pose.p, e->d_camrec.p, e->opt.taylor_rule); }
+    if (e->nTiles > 0) {
+        LaunchTimer t(e, KID_K1);
+        bak::k1_residual_jacobian<<<e->nTiles, bak::TILE_OBS, 0, s>>>(e->V, e->d_camrec.p, e->d_intr.p, e->d_pt.p, rp, e->d_part0.p, &sc->bad_eval);
+    }
+    { LaunchTimer t(e, KID_MISC);
+      bak::k_reduce_partials<<<1, 1024, 0, s>>>(e->d_part0.p, e->nTiles, &sc->cost); }
+    if (e->fi) CU_TRY(cudaMemsetAsync(e->Hii(), 0, size_t(20) * e->Ng * sizeof(double), s));
+    if (e->Nc > 0) {
+        LaunchTimer t(e, KID_K2C);
+        if (e->fi) bak::k2c_camera_blocks<true><<<e->Nc, 128, 0, s>>>(e->V, e->Hcc(), e->gc(), e->Hii(), e->gi());
+        else bak::k2c_camera_blocks<false><<<e->Nc, 128, 0, s>>>(e->V, e->Hcc(), e->gc(), e->Hii(), e->gi());
+    }
+    if (e->opt.world_size > 1) {
+        NCCL_TRY(g_nccl.GroupStart());
+        allreduce_sum(e, e->d_red.p, e->red_count());
+        allreduce_sum(e, &sc->cost, 1);
+        allreduce_flags(e, &sc->bad_eval, 1);
+        NCCL_TRY(g_nccl.GroupEnd());
+    }
+}
+
+void gradient_max(ba_engine* e) {
+    cudaStream_t s = e->stream;
+    LaunchTimer t(e, KID_MISC);
+    bak::k_gradmax_points<<<kNormBlocks, 256, 0, s>>>(e->V, e->d_pt.p, e->d_part1.p);
+    bak::k_gradmax_final<<<1, 1024, 0, s>>>(e->Nc, e->Ng, e->fi, e->d_cam_free.p, e->d_grp_free.p, e->d_pose.p, e->d_intr.p, e->gc(), e->gi(),
+                                            e->d_part1.p, kNormBlocks, e->d_scal.p);
+    allreduce_max(e, &e->d_scal.p->gmax_pt, 1);
+}
+
+// x+ = x - y and the norms of K8; yf = PCG solution (pose | intrinsics part), yp in V.yp.
+void make_candidate(ba_engine* e, const double* yf) {
+    cudaStream_t s = e->stream;
+    bak::Scalars* sc = e->d_scal.p;
+    LaunchTimer t(e, KID_K8);
+    bak::k8_candidate_points<<<kNormBlocks, 256, 0, s>>>(e->V, e->d_pt.p, e->d_cpt.p, e->d_part0.p, e->d_part1.p);
+    bak::k_reduce_partials<<<1, 1024, 0, s>>>(e->d_part0.p, kNormBlocks, &sc->step2_pt);
+    bak::k_reduce_partials<<<1, 1024, 0, s>>>(e->d_part1.p, kNormBlocks, &sc->xn2_pt);
+    bak::k8_candidate_cameras<<<1, 1024, 0, s>>>(e->Nc, e->Ng, e->fi, e->d_cam_free.p, e->d_grp_free.p, e->d_pose.p, e->d_intr.p, yf,
+                                                 e->d_cpose.p, e->d_cintr.p, sc);
+}
+
+void candidate_cost(ba_engine* e) {
+    cudaStream_t s = e->stream;
+    bak::Scalars* sc = e->d_scal.p;
+    const bak::RobustParams rp{e->opt.robust_kind, e->opt.robust_a};
+    CU_TRY(cudaMemsetAsync(&sc->bad_cand, 0, sizeof(int), s));
+    { LaunchTimer t(e, KID_K0);
+      bak::k0_camera_precompute<<<cdiv(e->Nc, 128), 128, 0, s>>>(e->Nc, e->d_cpose.p, e->d_ccamrec.p, e->opt.taylor_rule); }
+    if (e->nTiles > 0) {
+        LaunchTimer t(e, KID_K1C);
+        bak::k1c_candidate_cost<<<e->nTiles, bak::TILE_OBS, 0, s>>>(e->V, e->d_ccamrec.p, e->d_cintr.p, e->d_cpt.p, rp, e->d_part0.p, &sc->bad_cand);
+    }
+    { LaunchTimer t(e, KID_MISC);
+      bak::k_reduce_partials<<<1, 1024, 0, s>>>(e->d_part0.p, e->nTiles, &sc->ccost); }
+}
+
+template <int MODE>
+void launch_sweep(ba_engine* e, int kid, const double* xin, double* yout, const int* done, double* partial) {
+    if (e->nTiles == 0) return;
+    LaunchTimer t(e, kid);
+    if (e->fi) bak::k_schur_sweep<MODE, true><<<e->nTiles, bak::TILE_OBS, 0, e->stream>>>(e->V, xin, yout, done, partial);
+    else bak::k_schur_sweep<MODE, false><<<e->nTiles, bak::TILE_OBS, 0, e->stream>>>(e->V, xin, yout, done, partial);
+}
+
+// One linear solve of the LM step at trust-region radius `radius` (K3, K4, PCG with K5, K7).  Leaves the step in
+// d_x (pose|intrinsics part) and V.yp (points), the model cost change in scal.mcc.  Returns PCG iterations, or -1.
+int solve_linear(ba_engine* e, double radius, double* rel_out) {
+    cudaStream_t s = e->stream;
+    bak::Scalars* sc = e->d_scal.p;
+    const bak::LmParams lm{radius, e->opt.min_lm_diagonal, e->opt.max_lm_diagonal};
+    CU_TRY(cudaMemsetAsync(&sc->bad_lin, 0, sizeof(int), s));
+    if (e->Np > 0) { LaunchTimer t(e, KID_K3P); bak::k3_point_blocks<<<cdiv(e->Np, 256), 256, 0, s>>>(e->V, lm, &sc->bad_lin); }
+    { LaunchTimer t(e, KID_K3C);
+      bak::k3_camera_blocks<<<cdiv(e->Nc + e->Ng, 128), 128, 0, s>>>(e->Nc, e->Ng, e->fi, e->Hcc(), e->Hii(), e->d_sc_f.p, lm, e->d_Df2.p, e->d_Minv.p, &sc->bad_lin); }
+    // reduced right-hand side b = gc - F^T E vp:  start from zero, sweep adds F^T (r - E vp) = gc - F^T E vp
+    e->d_b.zero(s);
+    launch_sweep<bak::SWEEP_RHS>(e, KID_K4, nullptr, e->d_b.p, nullptr, nullptr);
+    allreduce_sum(e, e->d_b.p, e->nf);
+    const bak::PcgParams pp{e->opt.pcg_max_iterations, e->opt.pcg_forcing, e->opt.pcg_rel_tolerance, e->opt.eta};
+    { LaunchTimer t(e, KID_PCGV);
+      bak::k_pcg_init<<<1, 1024, 0, s>>>(e->nf, e->Nc, e->d_Minv.p, e->d_b.p, e->d_x.p, e->d_r.p, e->d_z.p, e->d_p.p, e->d_y.p, &sc->pcg); }
+    const int batch = 8;
+    for (;;) {
+        for (int i = 0; i < batch; ++i) {
+            launch_sweep<bak::SWEEP_MATVEC>(e, KID_K5, e->d_p.p, e->d_y.p, &sc->pcg.done, nullptr);
+            allreduce_sum(e, e->d_y.p, e->nf);
+            LaunchTimer t(e, KID_PCGV);
+            bak::k_pcg_update<<<1, 1024, 0, s>>>(e->nf, e->Nc, e->d_Df2.p, e->d_Minv.p, e->d_b.p, e->d_x.p, e->d_r.p, e->d_z.p, e->d_p.p, e->d_y.p, &sc->pcg, pp);
+        }
+        read_scalars(e);
+        if (e->h_scal->pcg.done) break;
+    }
+    *rel_out = e->h_scal->pcg.rel;
+    if (e->h_scal->bad_lin || e->h_scal->pcg.done == 3) return -1;
+    // back-substitution and model cost change
+    launch_sweep<bak::SWEEP_BACKSUB>(e, KID_K7, e->d_x.p, nullptr, nullptr, e->d_part0.p);
+    { LaunchTimer t(e, KID_MISC);
+      bak::k_reduce_partials<<<1, 1024, 0, s>>>(e->d_part0.p, e->nTiles, &sc->mcc); }
+    return e->h_scal->pcg.k;
+}
+
+void swap_params(ba_engine* e) {
+    std::swap(e->d_pose.p, e->d_cpose.p); std::swap(e->d_intr.p, e->d_cintr.p); std::swap(e->d_pt.p, e->d_cpt.p);
+}
+
+}  // namespace
+
+namespace {
+
+// ---- the Levenberg-Marquardt loop: Ceres 2.2 TrustRegionMinimizer + LevenbergMarquardtStrategy (SURVEY §8 a-LM) ----
+void lm_solve(ba_engine* e) {
+    const ba_options& O = e->opt;
+    cudaStream_t s = e->stream;
+    bak::Scalars* sc = e->d_scal.p;
+    bak::Scalars* H = e->h_scal;
+    ba_summary& S = e->summary;
+    std::memset(&S, 0, sizeof S);
+    S.num_residuals = 2 * e->NoG;
+    e->traj.clear();
+    CU_TRY(cudaEventRecord(e->ev_t0, s));
+    auto finish = [&](int term, const char* msg, double cost) {
+        S.termination = term; S.usable = (term != BA_TERM_FAILURE); S.final_cost = cost; S.num_iterations = int(e->traj.size());
+        std::snprintf(S.message, sizeof S.message, "%s", msg);
+        CU_TRY(cudaEventRecord(e->ev_t1, s));
+        CU_TRY(cudaEventSynchronize(e->ev_t1));
+        float ms = 0.f;
+        CU_TRY(cudaEventElapsedTime(&ms, e->ev_t0, e->ev_t1));
+        S.solve_seconds = ms * 1e-3;
+        resolve_timers(e);
+    };
+
+    // ---- iteration 0: evaluate, Jacobi scales, gradient norm, ||x|| ----
+    e->d_yp.zero(s); e->d_x.zero(s);
+    evaluate_full(e);
+    {   // s_j = 1/(1 + sqrt(H_jj)) from the iteration-0 diagonals, frozen for the solve
+        LaunchTimer t(e, KID_MISC);
+        if (e->Np > 0) bak::k_scales_points<<<cdiv(3 * e->Np, 256), 256, 0, s>>>(e->V, O.jacobi_scaling);
+        bak::k_scales_cameras<<<cdiv(e->nf, 256), 256, 0, s>>>(e->Nc, e->Ng, e->fi, e->Hcc(), e->Hii(), e->d_sc_f.p, O.jacobi_scaling);
+    }
+    gradient_max(e);
+    make_candidate(e, e->d_x.p);   // y = 0: gives ||x|| of the free parameters
+    allreduce_sum(e, &sc->ccost, 4);
+    read_scalars(e);
+    double cost = H->cost;
+    S.initial_cost = cost;
+    if (H->bad_eval || !std::isfinite(cost)) { finish(BA_TERM_FAILURE, "initial residual/Jacobian evaluation failed (non-finite)", cost); return; }
+    double gmax = std::max(H->gmax_pt, H->gmax_f);
+    double x_norm = std::sqrt(H->xn2_pt + H->xn2_f);
+    double radius = O.initial_trust_region_radius, decrease_factor = 2.0;
+    int num_invalid = 0;
+    {
+        ba_iter_record R{}; R.step_is_valid = 1; R.step_is_successful = 1; R.cost = cost; R.radius = radius; R.radius_used = radius; R.gradient_max_norm = gmax;
+        e->traj.push_back(R); S.num_successful_steps = 1;
+    }
+    int iteration = 0;
+    for (;;) {
+        const ba_iter_record last = e->traj.back();
+        if (iteration >= O.max_num_iterations) { finish(BA_TERM_NO_CONVERGENCE, "maximum number of iterations reached", cost); return; }
+        if (last.step_is_successful && gmax <= O.gradient_tolerance) { finish(BA_TERM_CONVERGENCE, "gradient tolerance reached", cost); return; }
+        if (radius <= O.min_trust_region_radius) { finish(BA_TERM_CONVERGENCE, "minimum trust region radius reached", cost); return; }
+        if (O.target_chi2 > 0.0 && 2.0 * cost <= O.target_chi2) { finish(BA_TERM_TARGET_REACHED, "target chi2 reached", cost); return; }
+        ++iteration;
+        ba_iter_record R{}; R.iteration = iteration; R.radius_used = radius; R.gradient_max_norm = gmax; R.cost = cost;
+
+        double rel = 0.0;
+        const int its = solve_linear(e, radius, &rel);
+        R.pcg_iterations = std::max(its, 0); R.pcg_rel_residual = rel; S.total_pcg_iterations += std::max(its, 0);
+        bool valid = its >= 0;
+        if (valid) {   // launch candidate + its cost right away; one read-back serves model change, norms and candidate cost
+            make_candidate(e, e->d_x.p);
+            candidate_cost(e);
+            if (O.world_size > 1) {
+                NCCL_TRY(g_nccl.GroupStart());
+                allreduce_sum(e, &sc->ccost, 4);
+                allreduce_flags(e, &sc->bad_cand, 1);
+                NCCL_TRY(g_nccl.GroupEnd());
+            }
+            read_scalars(e);
+            R.model_cost_change = -H->mcc;
+            valid = std::isfinite(R.model_cost_change) && R.model_cost_change > 0.0;
+        }
+        R.step_is_valid = valid;
+        if (!valid) {   // HandleInvalidStep
+            if (++num_invalid >= O.max_num_consecutive_invalid_steps) { e->traj.push_back(R); ++S.num_unsuccessful_steps; finish(BA_TERM_FAILURE, "too many consecutive invalid steps", cost); return; }
+            radius /= decrease_factor; decrease_factor *= 2.0;
+            R.radius = radius; e->traj.push_back(R); ++S.num_unsuccessful_steps;
+            continue;
+        }
+        num_invalid = 0;
+        double ccost = H->ccost;
+        if (H->bad_cand || !std::isfinite(ccost)) ccost = std::numeric_limits<double>::max();
+        R.candidate_cost = ccost;
+        R.step_norm = std::sqrt(H->step2_pt + H->step2_f);
+        if (R.step_norm <= O.parameter_tolerance * (x_norm + O.parameter_tolerance)) { finish(BA_TERM_CONVERGENCE, "parameter tolerance reached", cost); return; }
+        if (std::fabs(cost - ccost) <= O.function_tolerance * cost) { finish(BA_TERM_CONVERGENCE, "function tolerance reached", cost); return; }
+        R.relative_decrease = (ccost >= std::numeric_limits<double>::max()) ? std::numeric_limits<double>::lowest() : (cost - ccost) / R.model_cost_change;
+        if (R.relative_decrease > O.min_relative_decrease) {   // HandleSuccessfulStep
+            swap_params(e);
+            x_norm = std::sqrt(H->xn2_pt + H->xn2_f);
+            evaluate_full(e);
+            gradient_max(e);
+            read_scalars(e);
+            cost = H->cost;
+            if (H->bad_eval || !std::isfinite(cost)) { finish(BA_TERM_FAILURE, "residual/Jacobian evaluation failed after an accepted step", cost); return; }
+            gmax = std::max(H->gmax_pt, H->gmax_f);
+            radius = std::min(O.max_trust_region_radius, radius / std::max(1.0 / 3.0, 1.0 - std::pow(2.0 * R.relative_decrease - 1.0, 3)));
+            decrease_factor = 2.0;
+            R.step_is_successful = 1; R.cost = cost; R.gradient_max_norm = gmax; ++S.num_successful_steps;
+        } else {
+            radius /= decrease_factor; decrease_factor *= 2.0; ++S.num_unsuccessful_steps;
+        }
+        R.radius = radius;
+        e->traj.push_back(R);
+    }
+}
+
+template <class F>
+int guarded(ba_engine* e, F&& f) {
+    try { f(); return BA_OK; }
+    catch (const BaFail& x) { return fail(e, x.code, x.msg); }
+    catch (const std::exception& x) { return fail(e, BA_ERR_INTERNAL, x.what()); }
+    catch (...) { return fail(e, BA_ERR_INTERNAL, "unknown exception"); }
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------------------------
+// C-ABI
+extern "C" {
+
+int ba_options_default(ba_options* o) {
+    if (!o) return BA_ERR_INVALID_ARGUMENT;
+    std::memset(o, 0, sizeof *o);
+    o->abi_version = BA_ABI_VERSION;
+    o->model = BA_MODEL_PINHOLE;
+    o->robust_kind = BA_ROBUST_HUBER; o->robust_a = 4.0;          // BundleAdjuster.h:109
+    o->intrinsics_free = 1;                                        // :106-107
+    o->taylor_rule = BA_TAYLOR_THETA2_LE_EPS;
+    o->max_num_iterations = 50; o->initial_trust_region_radius = 1e4; o->max_trust_region_radius = 1e16; o->min_trust_region_radius = 1e-32;
+    o->min_relative_decrease = 1e-3; o->min_lm_diagonal = 1e-6; o->max_lm_diagonal = 1e32; o->max_num_consecutive_invalid_steps = 5;
+    o->function_tolerance = 1e-6; o->gradient_tolerance = 1e-10; o->parameter_tolerance = 1e-8; o->jacobi_scaling = 1;
+    o->linear_solver = BA_LINEAR_PCG;                              // the engine's solver; EXACT exists only in the oracle
+    o->preconditioner = BA_PRECOND_JACOBI;                         // :171
+    o->pcg_max_iterations = 2000; o->pcg_rel_tolerance = 1e-12; o->pcg_forcing = 0; o->eta = 0.1;
+    o->target_chi2 = 0.0; o->device = 0; o->num_threads = 1;
+    o->rank = 0; o->world_size = 1; o->nccl_unique_id = nullptr; o->stream = nullptr; o->scatter_mode = 0;
+    return BA_OK;
+}
+
+int ba_create(const ba_options* opt, ba_engine** out) {
+    if (!opt || !out) return fail(nullptr, BA_ERR_INVALID_ARGUMENT, "null argument");
+    if (opt->abi_version != BA_ABI_VERSION) return fail(nullptr, BA_ERR_INVALID_ARGUMENT, "abi_version mismatch");
+    if (opt->linear_solver != BA_LINEAR_PCG) return fail(nullptr, BA_ERR_UNSUPPORTED, "the CUDA engine solves the reduced system by PCG only (linear_solver = BA_LINEAR_PCG)");
+    if (opt->model != BA_MODEL_PINHOLE) return fail(nullptr, BA_ERR_UNSUPPORTED, "model not implemented by the CUDA engine yet");
+    if (opt->preconditioner != BA_PRECOND_JACOBI) return fail(nullptr, BA_ERR_UNSUPPORTED, "preconditioner not implemented by the CUDA engine yet");
+    if (opt->world_size < 1 || opt->rank < 0 || opt->rank >= opt->world_size) return fail(nullptr, BA_ERR_INVALID_ARGUMENT, "bad rank/world_size");
+    if (opt->world_size > 1 && !opt->nccl_unique_id) return fail(nullptr, BA_ERR_INVALID_ARGUMENT, "world_size > 1 needs nccl_unique_id");
+    int ndev = 0;
+    cudaError_t ce = cudaGetDeviceCount(&ndev);
+    if (ce != cudaSuccess || ndev == 0)
+        return fail(nullptr, BA_ERR_CUDA, std::string("no usable CUDA device (") + cudaGetErrorString(ce) + ") — this engine has no CPU fallback");
+    if (opt->device < 0 || opt->device >= ndev) return fail(nullptr, BA_ERR_INVALID_ARGUMENT, "device ordinal out of range");
+    ba_engine* e = new (std::nothrow) ba_engine();
+    if (!e) return fail(nullptr, BA_ERR_INTERNAL, "out of memory");
+    e->opt = *opt; e->opt.nccl_unique_id = nullptr;
+    e->device = opt->device;
+    const int rc = guarded(e, [&] {
+        CU_TRY(cudaSetDevice(e->device));
+        cudaDeviceProp prop{};
+        CU_TRY(cudaGetDeviceProperties(&prop, e->device));
+        if (prop.major < 10) throw BaFail{BA_ERR_CUDA, std::string("device ") + prop.name + " is not sm_100-class; this library holds sm_100a code only"};
+        if (opt->stream) e->stream = static_cast<cudaStream_t>(opt->stream);
+        else { CU_TRY(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking)); e->own_stream = true; }
+        CU_TRY(cudaMallocHost(reinterpret_cast<void**>(&e->h_scal), sizeof(bak::Scalars)));
+        CU_TRY(cudaEventCreate(&e->ev_t0)); CU_TRY(cudaEventCreate(&e->ev_t1));
+        if (opt->world_size > 1) {
+            std::string err;
+            if (!g_nccl.load(err)) throw BaFail{BA_ERR_NCCL, err};
+            Nccl::UniqueId id; std::memcpy(&id, opt->nccl_unique_id, sizeof id);
+            NCCL_TRY(g_nccl.CommInitRank(&e->comm, opt->world_size, id, opt->rank));
+        }
+    });
+    if (rc != BA_OK) { g_create_error = e->err; ba_destroy(e); return rc; }
+    *out = e;
+    return BA_OK;
+}
+
+int ba_set_problem(ba_engine* e, const ba_problem* p) {
+    if (!e || !p) return fail(e, BA_ERR_INVALID_ARGUMENT, "null argument");
+    if (p->num_cameras < 0 || p->num_groups < 0 || p->num_points < 0 || p->num_observations < 0) return fail(e, BA_ERR_INVALID_ARGUMENT, "negative size");
+    const int Nc = p->num_cameras, Ng = p->num_groups, Np = p->num_points, No = p->num_observations;
+    if ((Nc && (!p->pose || !p->cam_group || !p->cam_fixed)) || (Ng && !p->intr) || (Np && !p->pt) || (No && (!p->obs_cam || !p->obs_pt || !p->obs_uv)))
+        return fail(e, BA_ERR_INVALID_ARGUMENT, "null array");
+    for (int c = 0; c < Nc; ++c) if (p->cam_group[c] < 0 || p->cam_group[c] >= Ng) return fail(e, BA_ERR_INVALID_ARGUMENT, "cam_group out of range");
+    for (int o = 0; o < No; ++o) {
+        if (p->obs_cam[o] < 0 || p->obs_cam[o] >= Nc || p->obs_pt[o] < 0 || p->obs_pt[o] >= Np) return fail(e, BA_ERR_INVALID_ARGUMENT, "observation index out of range");
+        if (o && p->obs_pt[o] < p->obs_pt[o - 1]) return fail(e, BA_ERR_INVALID_ARGUMENT, "observations must be sorted by point id");
+    }
+    e->has_problem = false;
+    return guarded(e, [&] { do_set_problem(e, p); });
+}
+
+int ba_reset_state(ba_engine* e) {
+    if (!e) return BA_ERR_INVALID_ARGUMENT;
+    if (!e->has_problem) return fail(e, BA_ERR_NO_PROBLEM, "no problem set");
+    return guarded(e, [&] {
+        CU_TRY(cudaSetDevice(e->device));
+        cudaStream_t s = e->stream;
+        CU_TRY(cudaMemcpyAsync(e->d_pose.p, e->d_pose0.p, size_t(6) * e->Nc * sizeof(double), cudaMemcpyDeviceToDevice, s));
+        CU_TRY(cudaMemcpyAsync(e->d_intr.p, e->d_intr0.p, size_t(4) * e->Ng * sizeof(double), cudaMemcpyDeviceToDevice, s));
+        CU_TRY(cudaMemcpyAsync(e->d_pt.p, e->d_pt0.p, size_t(3) * e->Np * sizeof(double), cudaMemcpyDeviceToDevice, s));
+        e->traj.clear();
+    });
+}
+
+int ba_solve(ba_engine* e, ba_summary* out) {
+    if (!e) return BA_ERR_INVALID_ARGUMENT;
+    if (!e->has_problem) return fail(e, BA_ERR_NO_PROBLEM, "no problem set");
+    const int rc = guarded(e, [&] { CU_TRY(cudaSetDevice(e->device)); lm_solve(e); });
+    if (out) *out = e->summary;
+    return rc;
+}
+
+int ba_get_state(ba_engine* e, double* pose, double* intr, double* pt) {
+    if (!e) return BA_ERR_INVALID_ARGUMENT;
+    if (!e->has_problem) return fail(e, BA_ERR_NO_PROBLEM, "no problem set");
+    return guarded(e, [&] {
+        CU_TRY(cudaSetDevice(e->device));
+        cudaStream_t s = e->stream;
+        if (pose) CU_TRY(cudaMemcpyAsync(pose, e->d_pose.p, size_t(6) * e->Nc * sizeof(double), cudaMemcpyDeviceToHost, s));
+        if (intr) CU_TRY(cudaMemcpyAsync(intr, e->d_intr.p, size_t(4) * e->Ng * sizeof(double), cudaMemcpyDeviceToHost, s));
+        if (pt) {
+            if (e->opt.world_size == 1) CU_TRY(cudaMemcpyAsync(pt, e->d_pt.p, size_t(3) * e->Np * sizeof(double), cudaMemcpyDeviceToHost, s));
+            else {   // every rank ends with the full point array: one broadcast per shard (collective: all ranks must call)
+                e->d_ptfull.alloc(size_t(3) * e->NpG);
+                CU_TRY(cudaMemcpyAsync(e->d_ptfull.p + size_t(3) * e->pb, e->d_pt.p, size_t(3) * e->Np * sizeof(double), cudaMemcpyDeviceToDevice, s));
+                NCCL_TRY(g_nccl.GroupStart());
+                for (int r = 0; r < e->opt.world_size; ++r) {
+                    double* seg = e->d_ptfull.p + size_t(3) * e->h_shard_pt[r];
+                    const size_t cnt = size_t(3) * (e->h_shard_pt[r + 1] - e->h_shard_pt[r]);
+                    if (cnt) NCCL_TRY(g_nccl.Broadcast(seg, seg, cnt, Nccl::kFloat64, r, e->comm, s));
+                }
+                NCCL_TRY(g_nccl.GroupEnd());
+                CU_TRY(cudaMemcpyAsync(pt, e->d_ptfull.p, size_t(3) * e->NpG * sizeof(double), cudaMemcpyDeviceToHost, s));
+            }
+        }
+        CU_TRY(cudaStreamSynchronize(s));
+    });
+}
+
+int ba_get_trajectory(ba_engine* e, ba_iter_record* out, int32_t cap, int32_t* n) {
+    if (!e || !n) return BA_ERR_INVALID_ARGUMENT;
+    *n = int32_t(e->traj.size());
+    if (out) for (int i = 0; i < std::min<int>(cap, *n); ++i) out[i] = e->traj[i];
+    return BA_OK;
+}
+
+int ba_get_structure(ba_engine* e, int32_t* perm_by_cam, int32_t* cam_off, int32_t* pt_off, int32_t* schur_pairs, int64_t pairs_cap, int64_t* n_pairs) {
+    if (!e) return BA_ERR_INVALID_ARGUMENT;
+    if (!e->has_problem) return fail(e, BA_ERR_NO_PROBLEM, "no problem set");
+    // Global canonical structure (independent of sharding), rebuilt on the host from the index arrays kept at set_problem.
+    const int Nc = e->Nc, Np = e->NpG, No = e->NoG;
+    vector<int32_t> po(size_t(Np) + 1, 0), co(size_t(Nc) + 1, 0);
+    for (int o = 0; o < No; ++o) { ++po[e->h_obs_pt[o] + 1]; ++co[e->h_obs_cam[o] + 1]; }
+    for (int p = 0; p < Np; ++p) po[p + 1] += po[p];
+    for (int c = 0; c < Nc; ++c) co[c + 1] += co[c];
+    if (pt_off) std::copy(po.begin(), po.end(), pt_off);
+    if (cam_off) std::copy(co.begin(), co.end(), cam_off);
+    if (perm_by_cam) { vector<int32_t> cur(co.begin(), co.end() - 1); for (int o = 0; o < No; ++o) perm_by_cam[cur[e->h_obs_cam[o]]++] = o; }
+    if (schur_pairs || n_pairs) {
+        // co-visibility bitset, one row per pose: bit j of row i set iff i<j are both free and share a point
+        const size_t words = (size_t(Nc) + 63) / 64;
+        vector<uint64_t> bits(size_t(Nc) * words, 0);
+        for (int p = 0; p < Np; ++p)
+            for (int a = po[p]; a < po[p + 1]; ++a) {
+                const int i = e->h_obs_cam[a];
+                if (!e->h_cam_free[i]) continue;
+                for (int b = po[p]; b < po[p + 1]; ++b) { const int j = e->h_obs_cam[b]; if (j > i && e->h_cam_free[j]) bits[size_t(i) * words + (j >> 6)] |= uint64_t(1) << (j & 63); }
+            }
+        int64_t n = 0;
+        for (int i = 0; i < Nc; ++i)
+            for (size_t w = 0; w < words; ++w) {
+                uint64_t v = bits[size_t(i) * words + w];
+                while (v) { const int j = int(w * 64) + __builtin_ctzll(v); v &= v - 1; if (schur_pairs && n < pairs_cap) { schur_pairs[2 * n] = i; schur_pairs[2 * n + 1] = j; } ++n; }
+            }
+        if (n_pairs) *n_pairs = n;
+    }
+    return BA_OK;
+}
+
+int ba_evaluate(ba_engine* e, double* cost, double* r, double* Jc, double* Jp, double* Ji, double* g) {
+    if (!e) return BA_ERR_INVALID_ARGUMENT;
+    if (!e->has_problem) return fail(e, BA_ERR_NO_PROBLEM, "no problem set");
+    if (e->opt.world_size != 1) return fail(e, BA_ERR_UNSUPPORTED, "ba_evaluate is a single-GPU debugging entry point");
+    int bad = 0;
+    const int rc = guarded(e, [&] {
+        CU_TRY(cudaSetDevice(e->device));
+        evaluate_full(e);
+        read_scalars(e);
+        bad = e->h_scal->bad_eval;
+        if (cost) *cost = e->h_scal->cost;
+        const int No = e->No, ld = e->ldo, ncol = e->fi ? 13 : 9;
+        vector<double2> hJ(size_t(ncol) * ld), hr(ld);
+        CU_TRY(cudaMemcpy(hJ.data(), e->d_J2.p, hJ.size() * sizeof(double2), cudaMemcpyDeviceToHost));
+        CU_TRY(cudaMemcpy(hr.data(), e->d_r2.p, hr.size() * sizeof(double2), cudaMemcpyDeviceToHost));
+        for (int o = 0; o < No; ++o) {
+            if (r) { r[2 * o] = hr[o].x; r[2 * o + 1] = hr[o].y; }
+            if (Jc) for (int k = 0; k < 6; ++k) { Jc[(2 * o) * 6 + k] = hJ[size_t(k) * ld + o].x; Jc[(2 * o + 1) * 6 + k] = hJ[size_t(k) * ld + o].y; }
+            if (Jp) for (int k = 0; k < 3; ++k) { Jp[(2 * o) * 3 + k] = hJ[size_t(6 + k) * ld + o].x; Jp[(2 * o + 1) * 3 + k] = hJ[size_t(6 + k) * ld + o].y; }
+            if (Ji) for (int k = 0; k < 4; ++k) { Ji[(2 * o) * 4 + k] = e->fi ? hJ[size_t(9 + k) * ld + o].x : 0.0; Ji[(2 * o + 1) * 4 + k] = e->fi ? hJ[size_t(9 + k) * ld + o].y : 0.0; }
+        }
+        if (g) {
+            CU_TRY(cudaMemcpy(g, e->gc(), size_t(6) * e->Nc * sizeof(double), cudaMemcpyDeviceToHost));
+            if (e->fi) CU_TRY(cudaMemcpy(g + size_t(6) * e->Nc, e->gi(), size_t(4) * e->Ng * sizeof(double), cudaMemcpyDeviceToHost));
+            else std::fill(g + size_t(6) * e->Nc, g + size_t(6) * e->Nc + size_t(4) * e->Ng, 0.0);
+            CU_TRY(cudaMemcpy(g + size_t(6) * e->Nc + size_t(4) * e->Ng, e->d_gp.p, size_t(3) * e->Np * sizeof(double), cudaMemcpyDeviceToHost));
+        }
+    });
+    if (rc != BA_OK) return rc;
+    return bad ? fail(e, BA_ERR_EVAL_FAILED, "non-finite residual or Jacobian") : BA_OK;
+}
+
+int ba_set_profiling(ba_engine* e, int32_t enabled) {
+    if (!e) return BA_ERR_INVALID_ARGUMENT;
+    e->profiling = enabled != 0;
+    for (auto& st : e->stats) { st.launches = 0; st.ms = 0.0; }
+    return BA_OK;
+}
+
+int ba_get_kernel_stats(ba_engine* e, ba_kernel_stat* out, int32_t cap, int32_t* n) {
+    if (!e || !n) return BA_ERR_INVALID_ARGUMENT;
+    *n = KID_COUNT;
+    if (out) for (int i = 0; i < std::min<int>(cap, KID_COUNT); ++i) {
+        std::memset(&out[i], 0, sizeof out[i]);
+        std::snprintf(out[i].name, sizeof out[i].name, "%s", kKernelNames[i]);
+        out[i].launches = e->stats[i].launches; out[i].total_ms = e->stats[i].ms; out[i].bytes_per_launch = e->stats[i].bytes;
+    }
+    return BA_OK;
+}
+
+int ba_nccl_unique_id(void* out128) {
+    if (!out128) return BA_ERR_INVALID_ARGUMENT;
+    std::string err;
+    if (!g_nccl.load(err)) return fail(nullptr, BA_ERR_NCCL, err);
+    Nccl::UniqueId id;
+    const int r = g_nccl.GetUniqueId(&id);
+    if (r != 0) return fail(nullptr, BA_ERR_NCCL, std::string("ncclGetUniqueId: ") + g_nccl.GetErrorString(r));
+    std::memcpy(out128, &id, sizeof id);
+    return BA_OK;
+}
+
+const char* ba_last_error(const ba_engine* e) { return e ? e->err.c_str() : g_create_error.c_str(); }
+const char* ba_backend(void) { return "cuda-sm100a"; }
+
+void ba_destroy(ba_engine* e) {
+    if (!e) return;
+    cudaSetDevice(e->device);
+    if (e->stream) cudaStreamSynchronize(e->stream);
+    if (e->comm) g_nccl.CommDestroy(e->comm);
+    for (auto& p : e->pending) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
+    for (auto ev : e->ev_pool) cudaEventDestroy(ev);
+    if (e->ev_t0) cudaEventDestroy(e->ev_t0);
+    if (e->ev_t1) cudaEventDestroy(e->ev_t1);
+    if (e->h_scal) cudaFreeHost(e->h_scal);
+    if (e->own_stream && e->stream) cudaStreamDestroy(e->stream);
+    delete e;
+}
+
+}  // extern "C"

@@ -1,0 +1,893 @@
+// ba_kernels.cuh — hand-written sm_100a kernels of the Levenberg-Marquardt inner loop (SURVEY.md §8 a-K).
+//
+// Everything is IEEE double (the reference's arithmetic type, BundleAdjuster.h:74-76); these are small-block streaming
+// kernels bounded by HBM bandwidth, so no tensor cores.  Layout:
+//   observations are sorted by point and cut into TILES of <= TILE_OBS observations holding whole points, one CTA per tile,
+//   one thread per observation; a point's 3x3 work is done by one thread per point after a shared-memory exchange;
+//   J is stored SoA as double2 column pairs  J2[k][o] = (dr0/dx_k, dr1/dx_k), k = 0..5 pose, 6..8 point, 9..12 intrinsics,
+//   so every warp load is a fully coalesced 512-byte LDG.128 run;
+//   per-camera data is a 160-byte record (R, t, aa and the Rodrigues-derivative coefficients) gathered through L1/L2.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace bak {
+
+constexpr int TILE_OBS = 256;     // observations per tile == threads per CTA of the observation sweeps
+constexpr int CAMREC = 20;        // doubles per camera record
+constexpr int NJC = 6, NJP = 3, NJI = 4;
+
+// camera record offsets
+constexpr int CR_R = 0, CR_T = 9, CR_AA = 12, CR_A = 15, CR_B = 16, CR_C1 = 17, CR_C2 = 18, CR_C3 = 19;
+
+struct RobustParams { int kind; double a; };
+
+// Device-resident view of (this rank's shard of) the problem.  Point-indexed arrays are LOCAL to the shard.
+struct View {
+    int Nc, Ng, Np, No;          // cameras (global), groups (global), local points, local observations
+    int ldo;                     // leading dimension (observations) of J2 / r2
+    int nTiles;
+    int fi;                      // 1: intrinsics blocks are free (J2 has 13 column pairs)
+    const int* tile_off;         // [nTiles+1] first observation of each tile
+    const int* obs_cam;          // [No]
+    const int* obs_pt;           // [No] local point id, non-decreasing
+    const double2* obs_uv;       // [No]
+    const int* pt_off;           // [Np+1]
+    const int* cam_group;        // [Nc]
+    const unsigned char* cam_free;  // [Nc] not constant and referenced
+    const unsigned char* grp_free;  // [Ng]
+    // camera-sorted view (for the by-camera segmented reductions)
+    const int* perm_by_cam;      // [No] local observation ids, stable by camera
+    const int* cam_off;          // [Nc+1]
+    double2* J2;                 // [9 or 13][ldo]
+    double2* r2;                 // [ldo] robustified residual
+    double* Hpp;                 // [Np][6] upper triangle xx xy xz yy yz zz of sum Jp^T Jp
+    double* gp;                  // [Np][3] sum Jp^T r
+    double* Hinv;                // [Np][6] (Hpp + Dp^2)^-1
+    double* vp;                  // [Np][3] Hinv gp
+    double* yp;                  // [Np][3] point part of the LM step
+    double* sc_pt;               // [Np][3] Jacobi column scales
+};
+
+__device__ __forceinline__ double2 ldg2(const double2* p) { return __ldg(p); }
+
+__device__ __forceinline__ void red_add(double* addr, double v) {
+    // fire-and-forget L2 reduction (RED.E.ADD.F64), no return value
+    asm volatile("red.global.add.f64 [%0], %1;" ::"l"(addr), "d"(v) : "memory");
+}
+
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// Block-wide sum for blockDim.x <= 1024 (multiple of 32); result valid in thread 0. `scratch` holds >= 32 doubles.
+__device__ __forceinline__ double block_sum(double v, double* scratch) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+    v = warp_sum(v);
+    __syncthreads();
+    if (lane == 0) scratch[wid] = v;
+    __syncthreads();
+    double s = 0.0;
+    if (wid == 0) {
+        s = lane < nw ? scratch[lane] : 0.0;
+        s = warp_sum(s);
+    }
+    return s;
+}
+
+// Robust kernel on s = ||r||^2: returns rho(s), sets w = sqrt(rho'(s))   (ceres::HuberLoss / CauchyLoss)
+__device__ __forceinline__ double robust(const RobustParams rp, double s, double& w) {
+    const double b = rp.a * rp.a;
+    if (rp.kind == 1) {
+        if (s > b) {
+            const double r = sqrt(s);
+            const double rho1 = fmax(2.2250738585072014e-308, rp.a / r);
+            w = sqrt(rho1);
+            return 2.0 * rp.a * r - b;
+        }
+        w = 1.0;
+        return s;
+    } else if (rp.kind == 2) {
+        const double sum = 1.0 + s / b;   // s * c with c = 1/b in Ceres; identical to rounding
+        const double inv = 1.0 / sum;
+        w = sqrt(fmax(2.2250738585072014e-308, inv));
+        return b * log(sum);
+    }
+    w = 1.0;
+    return s;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// K0 — camera precompute: R(aa), and the coefficients of d(R(aa)X)/d(aa) in closed form:
+//   R X = cos(th) X + a (aa x X) + b (aa.X) aa,  a = sin(th)/th, b = (1-cos th)/th^2
+//   d(RX)/d(aa) = h aa^T - a [X]x + b ((aa.X) I + aa X^T),  h = c1 X + c2 (aa x X) + c3 (aa.X) aa
+//   c1 = -a, c2 = (th cos th - sin th)/th^3, c3 = (th sin th - 2(1-cos th))/th^4   (power series below th^2 < 1e-2)
+// Cameras on Ceres' first-order branch (AngleAxisRotatePoint) get R = I + [aa]x and d/daa = -[X]x exactly.
+__global__ void k0_camera_precompute(int Nc, const double* __restrict__ pose, double* __restrict__ camrec, int taylor_rule) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= Nc) return;
+    const double ax = pose[6 * c], ay = pose[6 * c + 1], az = pose[6 * c + 2];
+    double* o = camrec + size_t(c) * CAMREC;
+    const double th2 = ax * ax + ay * ay + az * az;
+    bool taylor;
+    if (taylor_rule == 0) taylor = !(th2 > 2.220446049250313e-16);
+    else taylor = (ax == 0.0 && ay == 0.0 && az == 0.0);
+    double a, b, c1, c2, c3, ct;
+    if (taylor) {
+        a = 1.0; b = 0.0; c1 = 0.0; c2 = 0.0; c3 = 0.0; ct = 1.0;
+    } else {
+        const double th = sqrt(th2);
+        double sn, cs;
+        sincos(th, &sn, &cs);
+        ct = cs;
+        if (th2 < 1e-2) {
+            a = 1.0 + th2 * (-1.0 / 6 + th2 * (1.0 / 120 + th2 * (-1.0 / 5040 + th2 * (1.0 / 362880))));
+            b = 0.5 + th2 * (-1.0 / 24 + th2 * (1.0 / 720 + th2 * (-1.0 / 40320 + th2 * (1.0 / 3628800))));
+            c2 = -1.0 / 3 + th2 * (1.0 / 30 + th2 * (-1.0 / 840 + th2 * (1.0 / 45360 + th2 * (-1.0 / 3991680))));
+            c3 = -1.0 / 12 + th2 * (1.0 / 180 + th2 * (-1.0 / 6720 + th2 * (1.0 / 453600 + th2 * (-1.0 / 47900160))));
+        } else {
+            a = sn / th;
+            b = (1.0 - cs) / th2;
+            c2 = (th * cs - sn) / (th2 * th);
+            c3 = (th * sn - 2.0 * (1.0 - cs)) / (th2 * th2);
+        }
+        c1 = -a;
+    }
+    // R = ct I + a [aa]x + b aa aa^T
+    o[CR_R + 0] = ct + b * ax * ax; o[CR_R + 1] = -a * az + b * ax * ay; o[CR_R + 2] = a * ay + b * ax * az;
+    o[CR_R + 3] = a * az + b * ay * ax; o[CR_R + 4] = ct + b * ay * ay; o[CR_R + 5] = -a * ax + b * ay * az;
+    o[CR_R + 6] = -a * ay + b * az * ax; o[CR_R + 7] = a * ax + b * az * ay; o[CR_R + 8] = ct + b * az * az;
+    o[CR_T] = pose[6 * c + 3]; o[CR_T + 1] = pose[6 * c + 4]; o[CR_T + 2] = pose[6 * c + 5];
+    o[CR_AA] = ax; o[CR_AA + 1] = ay; o[CR_AA + 2] = az;
+    o[CR_A] = a; o[CR_B] = b; o[CR_C1] = c1; o[CR_C2] = c2; o[CR_C3] = c3;
+}
+
+
+// ---------------------------------------------------------------------------------------------------------
+// Projection shared by K1 and K1': ReprojectCost::operator() (BundleAdjuster.h:38-68), trig-free thanks to K0.
+struct Proj { double X[3]; double P[3]; double iz, xn, yn, r0, r1; };
+
+__device__ __forceinline__ void project_obs(const double* __restrict__ cr, const double* __restrict__ X, const double* __restrict__ in,
+                                            double2 uv, Proj& q) {
+    q.X[0] = X[0]; q.X[1] = X[1]; q.X[2] = X[2];
+    q.P[0] = cr[CR_R + 0] * X[0] + cr[CR_R + 1] * X[1] + cr[CR_R + 2] * X[2] + cr[CR_T + 0];
+    q.P[1] = cr[CR_R + 3] * X[0] + cr[CR_R + 4] * X[1] + cr[CR_R + 5] * X[2] + cr[CR_T + 1];
+    q.P[2] = cr[CR_R + 6] * X[0] + cr[CR_R + 7] * X[1] + cr[CR_R + 8] * X[2] + cr[CR_T + 2];
+    q.iz = 1.0 / q.P[2];
+    q.xn = q.P[0] / q.P[2];
+    q.yn = q.P[1] / q.P[2];
+    q.r0 = in[0] * q.xn + in[2] - uv.x;   // u - observation.x   (:61,:64)
+    q.r1 = in[1] * q.yn + in[3] - uv.y;   // v - observation.y   (:62,:65)
+}
+
+// K1 — residual + analytic Jacobian + robust weight + cost, fused with the by-point half of K2 (Hpp, g_p).
+// One CTA per tile, one thread per observation; then one thread per point of the tile sums its observations'
+// Jp^T Jp and Jp^T r from shared memory (observations are sorted by point, so a point's are contiguous).
+// Algorithmic bytes: reads 24 No (uv, cam, pt ids) + 24 Np + 160 Nc; writes (144 [+64] + 16) No + 72 Np.
+__global__ void __launch_bounds__(TILE_OBS)
+k1_residual_jacobian(View V, const double* __restrict__ camrec, const double* __restrict__ intr, const double* __restrict__ pt,
+                     RobustParams rp, double* __restrict__ cost_partial, int* __restrict__ bad_flag) {
+    __shared__ double sJp[TILE_OBS][9];   // per observation: Jp (2x3) , r (2)  [+1 pad: stride 9 is conflict-free]
+    __shared__ double sred[32];
+    const int t = blockIdx.x;
+    const int o0 = V.tile_off[t], o1 = V.tile_off[t + 1];
+    double cost = 0.0;
+    int bad = 0;
+    // Tiles normally hold <= TILE_OBS observations; a single point with more observations than that forms its own
+    // tile and is walked in chunks (its Hpp/g_p are then accumulated across chunks by thread 0's running sums).
+    double Hl[6] = {0, 0, 0, 0, 0, 0}, gl[3] = {0, 0, 0};   // long-point accumulators (thread 0 only)
+    const bool longpt = (o1 - o0) > TILE_OBS;
+    for (int base = o0; base < o1; base += TILE_OBS) {
+        const int o = base + threadIdx.x;
+        const bool act = o < o1;
+        if (act) {
+            const int c = V.obs_cam[o], p = V.obs_pt[o], g = V.cam_group[c];
+            const double* cr = camrec + size_t(c) * CAMREC;
+            const double* in = intr + 4 * g;
+            Proj q;
+            project_obs(cr, pt + 3 * size_t(p), in, ldg2(V.obs_uv + o), q);
+            const double s = q.r0 * q.r0 + q.r1 * q.r1;
+            double w;
+            const double rho = robust(rp, s, w);
+            cost += 0.5 * rho;
+            // A = d(u,v)/dP
+            const double fx = in[0], fy = in[1];
+            const double A0[3] = {fx * q.iz, 0.0, -fx * q.xn * q.iz};
+            const double A1[3] = {0.0, fy * q.iz, -fy * q.yn * q.iz};
+            // J_X = A R
+            double JX0[3], JX1[3];
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                JX0[k] = A0[0] * cr[CR_R + k] + A0[2] * cr[CR_R + 6 + k];
+                JX1[k] = A1[1] * cr[CR_R + 3 + k] + A1[2] * cr[CR_R + 6 + k];
+            }
+            // J_aa = A G, row i: (A_i.h) aa - a (A_i x X) + b (d A_i + (A_i.aa) X)
+            const double ax = cr[CR_AA], ay = cr[CR_AA + 1], az = cr[CR_AA + 2];
+            const double X0 = q.X[0], X1 = q.X[1], X2 = q.X[2];
+            const double d = ax * X0 + ay * X1 + az * X2;
+            const double qx = ay * X2 - az * X1, qy = az * X0 - ax * X2, qz = ax * X1 - ay * X0;   // aa x X
+            const double ca = cr[CR_A], cb = cr[CR_B], c1 = cr[CR_C1], c2 = cr[CR_C2], c3 = cr[CR_C3];
+            const double hx = c1 * X0 + c2 * qx + c3 * d * ax, hy = c1 * X1 + c2 * qy + c3 * d * ay, hz = c1 * X2 + c2 * qz + c3 * d * az;
+            double Ja0[3], Ja1[3];
+            {
+                const double Ah = A0[0] * hx + A0[2] * hz, Aa = A0[0] * ax + A0[2] * az;
+                const double cx0 = A0[1] * X2 - A0[2] * X1, cx1 = A0[2] * X0 - A0[0] * X2, cx2 = A0[0] * X1 - A0[1] * X0;  // A0 x X
+                Ja0[0] = Ah * ax - ca * cx0 + cb * (d * A0[0] + Aa * X0);
+                Ja0[1] = Ah * ay - ca * cx1 + cb * (d * A0[1] + Aa * X1);
+                Ja0[2] = Ah * az - ca * cx2 + cb * (d * A0[2] + Aa * X2);
+            }
+            {
+                const double Ah = A1[1] * hy + A1[2] * hz, Aa = A1[1] * ay + A1[2] * az;
+                const double cx0 = A1[1] * X2 - A1[2] * X1, cx1 = A1[2] * X0 - A1[0] * X2, cx2 = A1[0] * X1 - A1[1] * X0;
+                Ja1[0] = Ah * ax - ca * cx0 + cb * (d * A1[0] + Aa * X0);
+                Ja1[1] = Ah * ay - ca * cx1 + cb * (d * A1[1] + Aa * X1);
+                Ja1[2] = Ah * az - ca * cx2 + cb * (d * A1[2] + Aa * X2);
+            }
+            const double wc = V.cam_free[c] ? w : 0.0;   // constant pose: its Jacobian columns vanish (SetParameterBlockConstant, :105)
+            double2* J = V.J2 + o;
+            const size_t ld = V.ldo;
+            J[0 * ld] = make_double2(wc * Ja0[0], wc * Ja1[0]);
+            J[1 * ld] = make_double2(wc * Ja0[1], wc * Ja1[1]);
+            J[2 * ld] = make_double2(wc * Ja0[2], wc * Ja1[2]);
+            J[3 * ld] = make_double2(wc * A0[0], wc * A1[0]);
+            J[4 * ld] = make_double2(wc * A0[1], wc * A1[1]);
+            J[5 * ld] = make_double2(wc * A0[2], wc * A1[2]);
+            const double p0[3] = {w * JX0[0], w * JX0[1], w * JX0[2]}, p1[3] = {w * JX1[0], w * JX1[1], w * JX1[2]};
+            J[6 * ld] = make_double2(p0[0], p1[0]);
+            J[7 * ld] = make_double2(p0[1], p1[1]);
+            J[8 * ld] = make_double2(p0[2], p1[2]);
+            if (V.fi) {   // d(u,v)/d(fx,fy,cx,cy) = [x 0 1 0; 0 y 0 1]
+                const double wi = V.grp_free[g] ? w : 0.0;
+                J[9 * ld] = make_double2(wi * q.xn, 0.0);
+                J[10 * ld] = make_double2(0.0, wi * q.yn);
+                J[11 * ld] = make_double2(wi, 0.0);
+                J[12 * ld] = make_double2(0.0, wi);
+            }
+            const double rr0 = w * q.r0, rr1 = w * q.r1;
+            V.r2[o] = make_double2(rr0, rr1);
+            double chk = rr0 + rr1 + rho;
+#pragma unroll
+            for (int k = 0; k < 3; ++k) chk += Ja0[k] + Ja1[k] + p0[k] + p1[k] + A0[k] + A1[k];
+            if (!isfinite(chk)) bad = 1;
+            double* sj = sJp[threadIdx.x];
+            sj[0] = p0[0]; sj[1] = p0[1]; sj[2] = p0[2]; sj[3] = p1[0]; sj[4] = p1[1]; sj[5] = p1[2]; sj[6] = rr0; sj[7] = rr1;
+        }
+        __syncthreads();
+        // by-point half of K2: thread j takes the j-th point of this chunk
+        const int lim = min(o1, base + TILE_OBS);
+        const int pfirst = V.obs_pt[base];
+        const int plast = V.obs_pt[lim - 1];
+        const int p = pfirst + threadIdx.x;
+        if (p <= plast) {
+            const int a = max(V.pt_off[p], base), b = min(V.pt_off[p + 1], lim);
+            double H[6] = {0, 0, 0, 0, 0, 0}, gg[3] = {0, 0, 0};
+            for (int i = a; i < b; ++i) {
+                const double* sj = sJp[i - base];
+#pragma unroll
+                for (int rrow = 0; rrow < 2; ++rrow) {
+                    const double j0 = sj[3 * rrow], j1 = sj[3 * rrow + 1], j2 = sj[3 * rrow + 2], rv = sj[6 + rrow];
+                    H[0] += j0 * j0; H[1] += j0 * j1; H[2] += j0 * j2; H[3] += j1 * j1; H[4] += j1 * j2; H[5] += j2 * j2;
+                    gg[0] += j0 * rv; gg[1] += j1 * rv; gg[2] += j2 * rv;
+                }
+            }
+            if (!longpt) {
+#pragma unroll
+                for (int k = 0; k < 6; ++k) V.Hpp[6 * size_t(p) + k] = H[k];
+#pragma unroll
+                for (int k = 0; k < 3; ++k) V.gp[3 * size_t(p) + k] = gg[k];
+            } else {   // single long point: only thread 0 is active here
+#pragma unroll
+                for (int k = 0; k < 6; ++k) Hl[k] += H[k];
+#pragma unroll
+                for (int k = 0; k < 3; ++k) gl[k] += gg[k];
+            }
+        }
+        __syncthreads();
+    }
+    if (longpt && threadIdx.x == 0) {
+        const int p = V.obs_pt[o0];
+#pragma unroll
+        for (int k = 0; k < 6; ++k) V.Hpp[6 * size_t(p) + k] = Hl[k];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) V.gp[3 * size_t(p) + k] = gl[k];
+    }
+    if (bad) atomicOr(bad_flag, 1);
+    const double cs = block_sum(cost, sred);
+    if (threadIdx.x == 0) cost_partial[t] = cs;
+}
+
+// K1' — candidate cost: residual + rho only.  Reads 24 No + 24 Np + 160 Nc, writes one partial per tile.
+__global__ void __launch_bounds__(TILE_OBS)
+k1c_candidate_cost(View V, const double* __restrict__ camrec, const double* __restrict__ intr, const double* __restrict__ pt,
+                   RobustParams rp, double* __restrict__ cost_partial, int* __restrict__ bad_flag) {
+    __shared__ double sred[32];
+    const int t = blockIdx.x;
+    const int o0 = V.tile_off[t], o1 = V.tile_off[t + 1];
+    double cost = 0.0;
+    int bad = 0;
+    for (int o = o0 + threadIdx.x; o < o1; o += TILE_OBS) {
+        const int c = V.obs_cam[o], p = V.obs_pt[o];
+        Proj q;
+        project_obs(camrec + size_t(c) * CAMREC, pt + 3 * size_t(p), intr + 4 * V.cam_group[c], ldg2(V.obs_uv + o), q);
+        const double s = q.r0 * q.r0 + q.r1 * q.r1;
+        double w;
+        const double rho = robust(rp, s, w);
+        if (!isfinite(rho)) bad = 1;
+        cost += 0.5 * rho;
+    }
+    if (bad) atomicOr(bad_flag, 1);
+    const double cs = block_sum(cost, sred);
+    if (threadIdx.x == 0) cost_partial[t] = cs;
+}
+
+// Deterministic final reduction of per-tile partials (fixed order for a fixed launch shape).
+__global__ void k_reduce_partials(const double* __restrict__ partial, int n, double* __restrict__ out) {
+    __shared__ double sred[32];
+    double s = 0.0;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) s += partial[i];
+    s = block_sum(s, sred);
+    if (threadIdx.x == 0) *out = s;
+}
+
+
+// ---------------------------------------------------------------------------------------------------------
+// K4 / K5 / K7 — one sweep over the point-sorted Jacobian, three uses:
+//   SWEEP_MATVEC : y += F^T (I - E (E^T E + Dp^2)^-1 E^T) F x      implicit Schur product, PCG inner loop (K5)
+//   SWEEP_RHS    : b += F^T (r - E vp),  vp = (E^T E + Dp^2)^-1 E^T r   reduced right-hand side (K4)
+//   SWEEP_BACKSUB: yp = vp - Hinv E^T F y;  partial of sum m.(r + m/2), m = -(F y + E yp)   (K7)
+// F = [Jc | Ji] (pose and intrinsics columns), E = Jp.  J is read exactly once per sweep (144 [+64] B/observation);
+// the camera-side scatter is a fire-and-forget L2 reduction (red.global.add.f64) per pose component.
+// The damping term Df^2 x of the matvec is added by the PCG vector kernel, not here.
+enum { SWEEP_MATVEC = 0, SWEEP_RHS = 1, SWEEP_BACKSUB = 2 };
+
+template <int MODE, bool FI>
+__global__ void __launch_bounds__(TILE_OBS)
+k_schur_sweep(View V, const double* __restrict__ xin, double* __restrict__ yout, const int* __restrict__ done_flag,
+              double* __restrict__ partial) {
+    __shared__ double sW[TILE_OBS][3];
+    __shared__ double sV[TILE_OBS][3];
+    __shared__ double sred[32];
+    __shared__ double sI[4];
+    if (done_flag && *done_flag) return;   // PCG already converged: batched launches become no-ops
+    const int t = blockIdx.x;
+    const int o0 = V.tile_off[t], o1 = V.tile_off[t + 1];
+    const size_t ld = V.ldo;
+    const int ioff = 6 * V.Nc;
+    double acc = 0.0;                      // BACKSUB: model-cost partial
+    double yi[4] = {0, 0, 0, 0};           // FI: intrinsics-side scatter, reduced per CTA when there is one group
+
+    if (o1 - o0 <= TILE_OBS) {
+        const int o = o0 + threadIdx.x;
+        const bool act = o < o1;
+        double2 jc[6], jp[3], ji[4];
+        double2 u = make_double2(0.0, 0.0);
+        int c = 0, p = 0, g = 0;
+        if (act) {
+            c = V.obs_cam[o]; p = V.obs_pt[o];
+            const double2* J = V.J2 + o;
+#pragma unroll
+            for (int k = 0; k < 6; ++k) jc[k] = ldg2(J + k * ld);
+#pragma unroll
+            for (int k = 0; k < 3; ++k) jp[k] = ldg2(J + (6 + k) * ld);
+            if (FI) {
+                g = V.cam_group[c];
+#pragma unroll
+                for (int k = 0; k < 4; ++k) ji[k] = ldg2(J + (9 + k) * ld);
+            }
+            if (MODE != SWEEP_RHS) {
+                const double* xc = xin + 6 * c;
+#pragma unroll
+                for (int k = 0; k < 6; ++k) { const double xv = __ldg(xc + k); u.x += jc[k].x * xv; u.y += jc[k].y * xv; }
+                if (FI) {
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) { const double xv = __ldg(xin + ioff + 4 * g + k); u.x += ji[k].x * xv; u.y += ji[k].y * xv; }
+                }
+#pragma unroll
+                for (int a = 0; a < 3; ++a) sW[threadIdx.x][a] = jp[a].x * u.x + jp[a].y * u.y;
+            }
+        }
+        double2 tt = make_double2(0.0, 0.0);
+        if (MODE != SWEEP_RHS) {
+            __syncthreads();
+            const int pfirst = V.obs_pt[o0], plast = V.obs_pt[o1 - 1];
+            const int pj = pfirst + threadIdx.x;
+            if (pj <= plast) {
+                double W[3] = {0, 0, 0};
+                for (int i = V.pt_off[pj] - o0, e = V.pt_off[pj + 1] - o0; i < e; ++i) { W[0] += sW[i][0]; W[1] += sW[i][1]; W[2] += sW[i][2]; }
+                const double* H = V.Hinv + 6 * size_t(pj);
+                double v0 = H[0] * W[0] + H[1] * W[1] + H[2] * W[2];
+                double v1 = H[1] * W[0] + H[3] * W[1] + H[4] * W[2];
+                double v2 = H[2] * W[0] + H[4] * W[1] + H[5] * W[2];
+                if (MODE == SWEEP_BACKSUB) {
+                    v0 = V.vp[3 * size_t(pj)] - v0; v1 = V.vp[3 * size_t(pj) + 1] - v1; v2 = V.vp[3 * size_t(pj) + 2] - v2;
+                    V.yp[3 * size_t(pj)] = v0; V.yp[3 * size_t(pj) + 1] = v1; V.yp[3 * size_t(pj) + 2] = v2;
+                }
+                sV[threadIdx.x][0] = v0; sV[threadIdx.x][1] = v1; sV[threadIdx.x][2] = v2;
+            }
+            __syncthreads();
+            if (act) {
+                const double* v = sV[p - pfirst];
+                const double e0 = jp[0].x * v[0] + jp[1].x * v[1] + jp[2].x * v[2];
+                const double e1 = jp[0].y * v[0] + jp[1].y * v[1] + jp[2].y * v[2];
+                if (MODE == SWEEP_MATVEC) { tt.x = u.x - e0; tt.y = u.y - e1; }
+                else {   // BACKSUB: m = -(F y + E yp)
+                    const double m0 = -(u.x + e0), m1 = -(u.y + e1);
+                    const double2 r = V.r2[o];
+                    acc += m0 * (r.x + 0.5 * m0) + m1 * (r.y + 0.5 * m1);
+                }
+            }
+        } else if (act) {
+            const double* v = V.vp + 3 * size_t(p);
+            const double2 r = V.r2[o];
+            tt.x = r.x - (jp[0].x * v[0] + jp[1].x * v[1] + jp[2].x * v[2]);
+            tt.y = r.y - (jp[0].y * v[0] + jp[1].y * v[1] + jp[2].y * v[2]);
+        }
+        if (MODE != SWEEP_BACKSUB && act) {
+            double* yc = yout + 6 * c;
+#pragma unroll
+            for (int k = 0; k < 6; ++k) red_add(yc + k, jc[k].x * tt.x + jc[k].y * tt.y);
+            if (FI) {
+#pragma unroll
+                for (int k = 0; k < 4; ++k) yi[k] = ji[k].x * tt.x + ji[k].y * tt.y;
+                if (V.Ng > 1) {
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) red_add(yout + ioff + 4 * g + k, yi[k]);
+                }
+            }
+        }
+    } else {
+        // ---- one point with more than TILE_OBS observations: two passes over its observations ----
+        const int p = V.obs_pt[o0];
+        double W[3] = {0, 0, 0};
+        if (MODE != SWEEP_RHS) {
+            for (int o = o0 + threadIdx.x; o < o1; o += TILE_OBS) {
+                const int c = V.obs_cam[o];
+                const double2* J = V.J2 + o;
+                double2 u = make_double2(0.0, 0.0);
+#pragma unroll
+                for (int k = 0; k < 6; ++k) { const double2 j = ldg2(J + k * ld); const double xv = __ldg(xin + 6 * c + k); u.x += j.x * xv; u.y += j.y * xv; }
+                if (FI) {
+                    const int g = V.cam_group[c];
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) { const double2 j = ldg2(J + (9 + k) * ld); const double xv = __ldg(xin + ioff + 4 * g + k); u.x += j.x * xv; u.y += j.y * xv; }
+                }
+#pragma unroll
+                for (int a = 0; a < 3; ++a) { const double2 j = ldg2(J + (6 + a) * ld); W[a] += j.x * u.x + j.y * u.y; }
+            }
+#pragma unroll
+            for (int a = 0; a < 3; ++a) { const double s = block_sum(W[a], sred); if (threadIdx.x == 0) sV[0][a] = s; }
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                const double* H = V.Hinv + 6 * size_t(p);
+                const double w0 = sV[0][0], w1 = sV[0][1], w2 = sV[0][2];
+                double v0 = H[0] * w0 + H[1] * w1 + H[2] * w2, v1 = H[1] * w0 + H[3] * w1 + H[4] * w2, v2 = H[2] * w0 + H[4] * w1 + H[5] * w2;
+                if (MODE == SWEEP_BACKSUB) {
+                    v0 = V.vp[3 * size_t(p)] - v0; v1 = V.vp[3 * size_t(p) + 1] - v1; v2 = V.vp[3 * size_t(p) + 2] - v2;
+                    V.yp[3 * size_t(p)] = v0; V.yp[3 * size_t(p) + 1] = v1; V.yp[3 * size_t(p) + 2] = v2;
+                }
+                sV[1][0] = v0; sV[1][1] = v1; sV[1][2] = v2;
+            }
+            __syncthreads();
+        }
+        double v[3];
+        if (MODE == SWEEP_RHS) { v[0] = V.vp[3 * size_t(p)]; v[1] = V.vp[3 * size_t(p) + 1]; v[2] = V.vp[3 * size_t(p) + 2]; }
+        else { v[0] = sV[1][0]; v[1] = sV[1][1]; v[2] = sV[1][2]; }
+        for (int o = o0 + threadIdx.x; o < o1; o += TILE_OBS) {
+            const int c = V.obs_cam[o];
+            const int g = FI ? V.cam_group[c] : 0;
+            const double2* J = V.J2 + o;
+            double2 jc[6], ji[4];
+            double2 u = make_double2(0.0, 0.0);
+#pragma unroll
+            for (int k = 0; k < 6; ++k) jc[k] = ldg2(J + k * ld);
+            if (FI) {
+#pragma unroll
+                for (int k = 0; k < 4; ++k) ji[k] = ldg2(J + (9 + k) * ld);
+            }
+            if (MODE != SWEEP_RHS) {
+#pragma unroll
+                for (int k = 0; k < 6; ++k) { const double xv = __ldg(xin + 6 * c + k); u.x += jc[k].x * xv; u.y += jc[k].y * xv; }
+                if (FI) {
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) { const double xv = __ldg(xin + ioff + 4 * g + k); u.x += ji[k].x * xv; u.y += ji[k].y * xv; }
+                }
+            }
+            double e0 = 0.0, e1 = 0.0;
+#pragma unroll
+            for (int a = 0; a < 3; ++a) { const double2 j = ldg2(J + (6 + a) * ld); e0 += j.x * v[a]; e1 += j.y * v[a]; }
+            double2 tt;
+            if (MODE == SWEEP_MATVEC) { tt.x = u.x - e0; tt.y = u.y - e1; }
+            else if (MODE == SWEEP_RHS) { const double2 r = V.r2[o]; tt.x = r.x - e0; tt.y = r.y - e1; }
+            else {
+                const double m0 = -(u.x + e0), m1 = -(u.y + e1);
+                const double2 r = V.r2[o];
+                acc += m0 * (r.x + 0.5 * m0) + m1 * (r.y + 0.5 * m1);
+                continue;
+            }
+#pragma unroll
+            for (int k = 0; k < 6; ++k) red_add(yout + 6 * c + k, jc[k].x * tt.x + jc[k].y * tt.y);
+            if (FI) {
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const double contrib = ji[k].x * tt.x + ji[k].y * tt.y;
+                    if (V.Ng > 1) red_add(yout + ioff + 4 * g + k, contrib); else yi[k] += contrib;
+                }
+            }
+        }
+    }
+    if (FI && MODE != SWEEP_BACKSUB && V.Ng == 1) {   // one shared intrinsics group: reduce over the CTA, one RED per component
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { const double s = block_sum(yi[k], sred); if (threadIdx.x == 0) sI[k] = s; }
+        if (threadIdx.x == 0) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) red_add(yout + ioff + k, sI[k]);
+        }
+    }
+    if (MODE == SWEEP_BACKSUB) {
+        const double s = block_sum(acc, sred);
+        if (threadIdx.x == 0) partial[t] = s;
+    }
+}
+
+
+// ---------------------------------------------------------------------------------------------------------
+// K2c — by-camera half of K2: Hcc[c] = sum Jc^T Jc (6x6, stored full), gc[c] = sum Jc^T r, over the camera-sorted
+// observation list (one CTA per camera, fixed summation order => deterministic).  With free intrinsics also the
+// per-group 4x4 block and gradient (RED into Hii/gi, one per CTA and component).
+// v1 formulation: gathers Jc through perm_by_cam — 6 x 16 B + 16 B per observation, each in its own 32-byte sector,
+// i.e. DRAM traffic ~2x the 112 No algorithmic bytes.  
+template <bool FI>
+__global__ void __launch_bounds__(128)
+k2c_camera_blocks(View V, double* __restrict__ Hcc, double* __restrict__ gc, double* __restrict__ Hii, double* __restrict__ gi) {
+    constexpr int NV = FI ? (21 + 6 + 10 + 4) : (21 + 6);   // Hcc upper, gc, [Hii upper, gi]
+    __shared__ double sm[4][NV];
+    const int c = blockIdx.x;
+    const int a0 = V.cam_off[c], a1 = V.cam_off[c + 1];
+    const size_t ld = V.ldo;
+    double acc[NV];
+#pragma unroll
+    for (int k = 0; k < NV; ++k) acc[k] = 0.0;
+    for (int i = a0 + threadIdx.x; i < a1; i += blockDim.x) {
+        const int o = V.perm_by_cam[i];
+        const double2* J = V.J2 + o;
+        double2 j[FI ? 10 : 6];
+#pragma unroll
+        for (int k = 0; k < 6; ++k) j[k] = ldg2(J + k * ld);
+        if (FI) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) j[6 + k] = ldg2(J + (9 + k) * ld);
+        }
+        const double2 r = V.r2[o];
+        int n = 0;
+#pragma unroll
+        for (int a = 0; a < 6; ++a)
+#pragma unroll
+            for (int b = a; b < 6; ++b) acc[n++] += j[a].x * j[b].x + j[a].y * j[b].y;
+#pragma unroll
+        for (int a = 0; a < 6; ++a) acc[n++] += j[a].x * r.x + j[a].y * r.y;
+        if (FI) {
+#pragma unroll
+            for (int a = 0; a < 4; ++a)
+#pragma unroll
+                for (int b = a; b < 4; ++b) acc[n++] += j[6 + a].x * j[6 + b].x + j[6 + a].y * j[6 + b].y;
+#pragma unroll
+            for (int a = 0; a < 4; ++a) acc[n++] += j[6 + a].x * r.x + j[6 + a].y * r.y;
+        }
+    }
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+#pragma unroll
+    for (int k = 0; k < NV; ++k) { const double s = warp_sum(acc[k]); if (lane == 0) sm[wid][k] = s; }
+    __syncthreads();
+    if (threadIdx.x < NV) {
+        const int k = threadIdx.x;
+        const double s = sm[0][k] + sm[1][k] + sm[2][k] + sm[3][k];
+        if (k < 21) {   // unpack upper-triangle index k -> (a,b)
+            int a = 0, rem = k;
+            while (rem >= 6 - a) { rem -= 6 - a; ++a; }
+            const int b = a + rem;
+            Hcc[36 * size_t(c) + 6 * a + b] = s;
+            Hcc[36 * size_t(c) + 6 * b + a] = s;
+        } else if (k < 27) {
+            gc[6 * size_t(c) + (k - 21)] = s;
+        } else if (FI) {
+            const int g = V.cam_group[c];
+            if (k < 37) {
+                int a = 0, rem = k - 27;
+                while (rem >= 4 - a) { rem -= 4 - a; ++a; }
+                const int b = a + rem;
+                red_add(Hii + 16 * size_t(g) + 4 * a + b, s);
+                if (a != b) red_add(Hii + 16 * size_t(g) + 4 * b + a, s);
+            } else {
+                red_add(gi + 4 * size_t(g) + (k - 37), s);
+            }
+        }
+    }
+}
+
+// Symmetric positive-definite n x n inverse by Cholesky on a thread-local array (n = 3, 4 or 6). false if not PD.
+template <int N>
+__device__ __forceinline__ bool spd_inverse(const double* A, double* Ainv) {
+    double L[N * N];
+#pragma unroll
+    for (int i = 0; i < N; ++i)
+#pragma unroll
+        for (int j = 0; j <= i; ++j) {
+            double s = A[i * N + j];
+#pragma unroll
+            for (int k = 0; k < j; ++k) s -= L[i * N + k] * L[j * N + k];
+            if (i == j) { if (!(s > 0.0)) return false; L[i * N + i] = sqrt(s); }
+            else L[i * N + j] = s / L[j * N + j];
+        }
+#pragma unroll
+    for (int c = 0; c < N; ++c) {
+        double y[N];
+#pragma unroll
+        for (int i = 0; i < N; ++i) { double s = (i == c) ? 1.0 : 0.0;
+#pragma unroll
+            for (int k = 0; k < i; ++k) s -= L[i * N + k] * y[k];
+            y[i] = s / L[i * N + i]; }
+#pragma unroll
+        for (int i = N - 1; i >= 0; --i) { double s = y[i];
+#pragma unroll
+            for (int k = i + 1; k < N; ++k) s -= L[k * N + i] * Ainv[k * N + c];
+            Ainv[i * N + c] = s / L[i * N + i]; }
+    }
+    return true;
+}
+
+struct LmParams { double radius, min_diag, max_diag; };
+
+// Damping in unscaled coordinates: Ceres solves in Jacobi-scaled space with D^2 = clamp(diag(Js^T Js))/radius;
+// substituting Js = J diag(s) gives the identical step from (J^T J + D'^2) y = J^T r with
+//   D'^2_j = clamp(s_j^2 H_jj, min, max) / (s_j^2 radius).
+__device__ __forceinline__ double damping(double Hjj, double s, const LmParams lm) {
+    const double s2 = s * s;
+    return fmin(fmax(s2 * Hjj, lm.min_diag), lm.max_diag) / (s2 * lm.radius);
+}
+
+// K3p — per point: Hinv = (Hpp + Dp'^2)^-1 (closed form through Cholesky), vp = Hinv gp.  168 Np bytes.
+__global__ void k3_point_blocks(View V, LmParams lm, int* __restrict__ bad_flag) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= V.Np) return;
+    const double* H = V.Hpp + 6 * size_t(p);
+    const double* s = V.sc_pt + 3 * size_t(p);
+    double A[9];
+    A[0] = H[0] + damping(H[0], s[0], lm); A[1] = H[1]; A[2] = H[2];
+    A[3] = H[1]; A[4] = H[3] + damping(H[3], s[1], lm); A[5] = H[4];
+    A[6] = H[2]; A[7] = H[4]; A[8] = H[5] + damping(H[5], s[2], lm);
+    double I[9];
+    if (!spd_inverse<3>(A, I)) { atomicOr(bad_flag, 2); for (int k = 0; k < 9; ++k) I[k] = 0.0; }
+    double* o = V.Hinv + 6 * size_t(p);
+    o[0] = I[0]; o[1] = I[1]; o[2] = I[2]; o[3] = I[4]; o[4] = I[5]; o[5] = I[8];
+    const double* g = V.gp + 3 * size_t(p);
+    V.vp[3 * size_t(p)] = I[0] * g[0] + I[1] * g[1] + I[2] * g[2];
+    V.vp[3 * size_t(p) + 1] = I[3] * g[0] + I[4] * g[1] + I[5] * g[2];
+    V.vp[3 * size_t(p) + 2] = I[6] * g[0] + I[7] * g[1] + I[8] * g[2];
+}
+
+// K3c — per pose (and per intrinsics group): damping diagonal Df2 and block-Jacobi preconditioner
+// Minv = (Hcc + Dc'^2)^-1.  Block b < Nc is a pose (6x6 at Minv[36 b]); block Nc+g is a group (4x4 at Minv[36 Nc + 16 g]).
+__global__ void k3_camera_blocks(int Nc, int Ng, int fi, const double* __restrict__ Hcc, const double* __restrict__ Hii,
+                                 const double* __restrict__ sc_f, LmParams lm, double* __restrict__ Df2, double* __restrict__ Minv,
+                                 int* __restrict__ bad_flag) {
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b < Nc) {
+        double A[36], I[36];
+        for (int k = 0; k < 36; ++k) A[k] = Hcc[36 * size_t(b) + k];
+        for (int k = 0; k < 6; ++k) { const double d = damping(A[7 * k], sc_f[6 * b + k], lm); Df2[6 * b + k] = d; A[7 * k] += d; }
+        if (!spd_inverse<6>(A, I)) { atomicOr(bad_flag, 4); for (int k = 0; k < 36; ++k) I[k] = 0.0; }
+        for (int k = 0; k < 36; ++k) Minv[36 * size_t(b) + k] = I[k];
+    } else if (fi && b < Nc + Ng) {
+        const int g = b - Nc;
+        double A[16], I[16];
+        for (int k = 0; k < 16; ++k) A[k] = Hii[16 * size_t(g) + k];
+        for (int k = 0; k < 4; ++k) { const double d = damping(A[5 * k], sc_f[6 * Nc + 4 * g + k], lm); Df2[6 * Nc + 4 * g + k] = d; A[5 * k] += d; }
+        if (!spd_inverse<4>(A, I)) { atomicOr(bad_flag, 4); for (int k = 0; k < 16; ++k) I[k] = 0.0; }
+        for (int k = 0; k < 16; ++k) Minv[36 * size_t(Nc) + 16 * size_t(g) + k] = I[k];
+    }
+}
+
+// Jacobi column scales s_j = 1/(1 + sqrt(H_jj)) from the iteration-0 Hessian diagonals (frozen afterwards).
+__global__ void k_scales_points(View V, int enabled) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= 3 * V.Np) return;
+    const int p = i / 3, a = i % 3;
+    const int d = (a == 0) ? 0 : (a == 1 ? 3 : 5);
+    V.sc_pt[i] = enabled ? 1.0 / (1.0 + sqrt(V.Hpp[6 * size_t(p) + d])) : 1.0;
+}
+__global__ void k_scales_cameras(int Nc, int Ng, int fi, const double* __restrict__ Hcc, const double* __restrict__ Hii,
+                                 double* __restrict__ sc_f, int enabled) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < 6 * Nc) sc_f[i] = enabled ? 1.0 / (1.0 + sqrt(Hcc[36 * size_t(i / 6) + 7 * (i % 6)])) : 1.0;
+    else if (fi && i < 6 * Nc + 4 * Ng) { const int j = i - 6 * Nc; sc_f[i] = enabled ? 1.0 / (1.0 + sqrt(Hii[16 * size_t(j / 4) + 5 * (j % 4)])) : 1.0; }
+}
+
+
+// ---------------------------------------------------------------------------------------------------------
+// PCG on the reduced camera system (block-Jacobi preconditioner, implicit Schur product by k_schur_sweep<MATVEC>).
+// All vectors have nf = 6 Nc (+ 4 Ng) entries (85 KB on Venice) and are replicated on every rank, so the vector
+// algebra of one iteration is a single one-CTA kernel: no scalar ever travels to the host inside the loop.
+struct PcgState { double rho, rho0, rel, Q0; int k, done, pad0, pad1; };   // done: 0 running, 1 converged, 2 iteration cap, 3 breakdown
+struct PcgParams { int max_iterations; int forcing; double rel_tolerance; double eta; };
+
+struct Scalars {   // everything the host reads back, one D2H copy
+    double cost, ccost, mcc, step2_pt, xn2_pt, step2_f, xn2_f, gmax_pt, gmax_f;
+    PcgState pcg;
+    int bad_eval, bad_cand, bad_lin, pad;
+};
+
+__device__ __forceinline__ double apply_minv(int j, int Nc, const double* __restrict__ Minv, const double* __restrict__ r) {
+    if (j < 6 * Nc) {
+        const int c = j / 6, a = j - 6 * c;
+        const double* M = Minv + 36 * size_t(c) + 6 * a;
+        const double* rc = r + 6 * c;
+        return M[0] * rc[0] + M[1] * rc[1] + M[2] * rc[2] + M[3] * rc[3] + M[4] * rc[4] + M[5] * rc[5];
+    }
+    const int jj = j - 6 * Nc, g = jj / 4, a = jj - 4 * g;
+    const double* M = Minv + 36 * size_t(Nc) + 16 * size_t(g) + 4 * a;
+    const double* rg = r + 6 * Nc + 4 * g;
+    return M[0] * rg[0] + M[1] * rg[1] + M[2] * rg[2] + M[3] * rg[3];
+}
+
+__global__ void __launch_bounds__(1024)
+k_pcg_init(int nf, int Nc, const double* __restrict__ Minv, const double* __restrict__ b, double* __restrict__ x,
+           double* __restrict__ r, double* __restrict__ z, double* __restrict__ p, double* __restrict__ y, PcgState* __restrict__ st) {
+    __shared__ double sred[32];
+    double acc = 0.0;
+    for (int j = threadIdx.x; j < nf; j += blockDim.x) {
+        x[j] = 0.0; y[j] = 0.0;
+        const double zj = apply_minv(j, Nc, Minv, b);
+        r[j] = b[j]; z[j] = zj; p[j] = zj;
+        acc += b[j] * zj;
+    }
+    acc = block_sum(acc, sred);
+    if (threadIdx.x == 0) {
+        st->rho = acc; st->rho0 = acc; st->rel = acc > 0.0 ? 1.0 : 0.0; st->Q0 = 0.0; st->k = 0;
+        st->done = (acc > 0.0 && isfinite(acc)) ? 0 : (acc == 0.0 ? 1 : 3);
+    }
+}
+
+__global__ void __launch_bounds__(1024)
+k_pcg_update(int nf, int Nc, const double* __restrict__ Df2, const double* __restrict__ Minv, const double* __restrict__ b,
+             double* __restrict__ x, double* __restrict__ r, double* __restrict__ z, double* __restrict__ p, double* __restrict__ y,
+             PcgState* __restrict__ st, PcgParams pp) {
+    __shared__ double sred[32];
+    __shared__ double sb[2];
+    if (st->done) return;
+    const double rho = st->rho;
+    // q = S p = y + Df^2 p ;  pq = p.q
+    double acc = 0.0;
+    for (int j = threadIdx.x; j < nf; j += blockDim.x) {
+        const double q = y[j] + Df2[j] * p[j];
+        y[j] = q;
+        acc += p[j] * q;
+    }
+    acc = block_sum(acc, sred);
+    if (threadIdx.x == 0) sb[0] = acc;
+    __syncthreads();
+    const double pq = sb[0];
+    if (!(pq > 0.0) || !isfinite(pq)) {
+        for (int j = threadIdx.x; j < nf; j += blockDim.x) y[j] = 0.0;
+        if (threadIdx.x == 0) st->done = 3;
+        return;
+    }
+    const double alpha = rho / pq;
+    for (int j = threadIdx.x; j < nf; j += blockDim.x) { x[j] += alpha * p[j]; r[j] -= alpha * y[j]; }
+    __syncthreads();
+    double acc2 = 0.0, accq = 0.0;
+    for (int j = threadIdx.x; j < nf; j += blockDim.x) {
+        const double zj = apply_minv(j, Nc, Minv, r);
+        z[j] = zj;
+        acc2 += r[j] * zj;
+        accq += x[j] * (b[j] + r[j]);
+    }
+    acc2 = block_sum(acc2, sred);
+    if (threadIdx.x == 0) sb[0] = acc2;
+    accq = block_sum(accq, sred);
+    if (threadIdx.x == 0) sb[1] = accq;
+    __syncthreads();
+    const double rho_new = sb[0];
+    const double beta = rho_new / rho;
+    for (int j = threadIdx.x; j < nf; j += blockDim.x) { p[j] = z[j] + beta * p[j]; y[j] = 0.0; }
+    if (threadIdx.x == 0) {
+        const int k = st->k + 1;
+        const double rel = sqrt(fmax(rho_new, 0.0) / st->rho0);
+        int done = 0;
+        if (pp.forcing) {   // Ceres' Q-criterion (inexact Newton): Q = -1/2 x.(b + r); stop when k (Q1 - Q0)/Q1 < eta
+            const double Q1 = -0.5 * sb[1];
+            const double zeta = k * (Q1 - st->Q0) / Q1;
+            st->Q0 = Q1;
+            if (zeta < pp.eta) done = 1;
+        }
+        if (rel <= pp.rel_tolerance) done = 1;
+        if (!done && k >= pp.max_iterations) done = 2;
+        if (!isfinite(rho_new)) done = 3;
+        st->k = k; st->rel = rel; st->rho = rho_new; st->done = done;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// K8 — candidate x+ = x - y (the step is delta = -y), with the norms the minimizer needs:
+//   step2 = sum (x - x+)^2 formed from the rounded difference exactly as Ceres does, xn2 = sum (x+)^2, free scalars only.
+__global__ void __launch_bounds__(256)
+k8_candidate_points(View V, const double* __restrict__ pt, double* __restrict__ cpt, double* __restrict__ step2_partial,
+                    double* __restrict__ xn2_partial) {
+    __shared__ double sred[32];
+    double s2 = 0.0, x2 = 0.0;
+    const int n = 3 * V.Np;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const int p = i / 3;
+        const bool fr = V.pt_off[p + 1] > V.pt_off[p];
+        const double xo = pt[i];
+        const double xc = xo - V.yp[i];
+        cpt[i] = xc;
+        if (fr) { const double d = xo - xc; s2 += d * d; x2 += xc * xc; }
+    }
+    s2 = block_sum(s2, sred);
+    if (threadIdx.x == 0) step2_partial[blockIdx.x] = s2;
+    x2 = block_sum(x2, sred);
+    if (threadIdx.x == 0) xn2_partial[blockIdx.x] = x2;
+}
+
+__global__ void __launch_bounds__(1024)
+k8_candidate_cameras(int Nc, int Ng, int fi, const unsigned char* __restrict__ cam_free, const unsigned char* __restrict__ grp_free,
+                     const double* __restrict__ pose, const double* __restrict__ intr, const double* __restrict__ yf,
+                     double* __restrict__ cpose, double* __restrict__ cintr, Scalars* __restrict__ sc) {
+    __shared__ double sred[32];
+    double s2 = 0.0, x2 = 0.0;
+    for (int j = threadIdx.x; j < 6 * Nc; j += blockDim.x) {
+        const double xo = pose[j];
+        if (cam_free[j / 6]) { const double xc = xo - yf[j]; cpose[j] = xc; const double d = xo - xc; s2 += d * d; x2 += xc * xc; }
+        else cpose[j] = xo;
+    }
+    for (int j = threadIdx.x; j < 4 * Ng; j += blockDim.x) {
+        const double xo = intr[j];
+        if (fi && grp_free[j / 4]) { const double xc = xo - yf[6 * Nc + j]; cintr[j] = xc; const double d = xo - xc; s2 += d * d; x2 += xc * xc; }
+        else cintr[j] = xo;
+    }
+    s2 = block_sum(s2, sred);
+    if (threadIdx.x == 0) sc->step2_f = s2;
+    x2 = block_sum(x2, sred);
+    if (threadIdx.x == 0) sc->xn2_f = x2;
+}
+
+// max |x - (x + (-g))| over free scalars — the minimizer's gradient_max_norm (Plus(x, -g) lifted back, SURVEY a-LM).
+__global__ void __launch_bounds__(256)
+k_gradmax_points(View V, const double* __restrict__ pt, double* __restrict__ max_partial) {
+    __shared__ double smax[32];
+    double m = 0.0;
+    const int n = 3 * V.Np;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const int p = i / 3;
+        if (V.pt_off[p + 1] > V.pt_off[p]) { const double x = pt[i]; m = fmax(m, fabs(x - (x + (-V.gp[i])))); }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if ((threadIdx.x & 31) == 0) smax[threadIdx.x >> 5] = m;
+    __syncthreads();
+    if (threadIdx.x == 0) { double r = 0.0; for (int w = 0; w < (blockDim.x >> 5); ++w) r = fmax(r, smax[w]); max_partial[blockIdx.x] = r; }
+}
+
+__global__ void __launch_bounds__(1024)
+k_gradmax_final(int Nc, int Ng, int fi, const unsigned char* __restrict__ cam_free, const unsigned char* __restrict__ grp_free,
+                const double* __restrict__ pose, const double* __restrict__ intr, const double* __restrict__ gc, const double* __restrict__ gi,
+                const double* __restrict__ max_partial, int npartial, Scalars* __restrict__ sc) {
+    __shared__ double smax[32];
+    double m = 0.0, mp = 0.0;
+    for (int j = threadIdx.x; j < 6 * Nc; j += blockDim.x) if (cam_free[j / 6]) { const double x = pose[j]; m = fmax(m, fabs(x - (x + (-gc[j])))); }
+    if (fi) for (int j = threadIdx.x; j < 4 * Ng; j += blockDim.x) if (grp_free[j / 4]) { const double x = intr[j]; m = fmax(m, fabs(x - (x + (-gi[j])))); }
+    for (int j = threadIdx.x; j < npartial; j += blockDim.x) mp = fmax(mp, max_partial[j]);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) { m = fmax(m, __shfl_xor_sync(0xffffffffu, m, o)); mp = fmax(mp, __shfl_xor_sync(0xffffffffu, mp, o)); }
+    if ((threadIdx.x & 31) == 0) smax[threadIdx.x >> 5] = m;
+    __syncthreads();
+    if (threadIdx.x == 0) { double r = 0.0; for (int w = 0; w < 32; ++w) r = fmax(r, smax[w]); sc->gmax_f = r; }
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) smax[threadIdx.x >> 5] = mp;
+    __syncthreads();
+    if (threadIdx.x == 0) { double r = 0.0; for (int w = 0; w < 32; ++w) r = fmax(r, smax[w]); sc->gmax_pt = r; }
+}
+
+}  // namespace bak

@@ -1,0 +1,200 @@
+/*
+ * ba_engine.h — C-ABI of the B200 bundle-adjustment engine.
+ *
+ * This is the drop-in boundary for the reference's src/adjuster optimisation path.
+ * The reference has no FFI: its "operator API" is the C++ functor
+ *     BundleAdjuster::BundleAdjuster()                       src/adjuster/BundleAdjuster.h:167-174
+ *     void BundleAdjuster::operator()(WorldStructure::Ptr&)  src/adjuster/BundleAdjuster.h:176-186
+ * which gathers parameters from the map (loadDataFromWorld, :82-98), hands raw double*
+ * blocks to the solver (bundleAdjustment, :100-141; ceres::Solve at :126) and scatters
+ * the result back (updateWorld, :143-156).  The boundary sits exactly at :126 — the
+ * functions below replace that call (plus the SoA form of the gather/scatter either side).
+ * The host adapter that keeps the functor's shape lives in
+ * 3dreconstruction_b200/host/adjuster/BundleAdjuster.h and calls only this header.
+ *
+ * Two shared libraries implement this header with identical symbols:
+ *   3dreconstruction_b200/csrc/libba_engine.so   sm_100a CUDA engine (the product; no CPU fallback)
+ *   oracle/libba_oracle.so                       CPU restatement of the reference's solver (test infrastructure only)
+ *
+ * Conventions: every function returns 0 on success and a negative
+ * ba_status on error; ba_last_error() gives the message; no C++ exception crosses the
+ * boundary; host arrays are borrowed for the duration of a call only; a handle is used
+ * by one host thread at a time.  All reals are IEEE double (the reference's arithmetic
+ * type: cv::Matx..d, BundleAdjuster.h:74-76); all indices are int32.
+ */
+#ifndef BA_ENGINE_H
+#define BA_ENGINE_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define BA_ABI_VERSION 1
+
+typedef struct ba_engine ba_engine; /* opaque */
+
+typedef enum ba_status {
+    BA_OK = 0,
+    BA_ERR_INVALID_ARGUMENT = -1,
+    BA_ERR_NO_PROBLEM = -2,
+    BA_ERR_CUDA = -3,        /* CUDA runtime/driver failure, or no usable device (the engine never falls back to the CPU) */
+    BA_ERR_NCCL = -4,
+    BA_ERR_UNSUPPORTED = -5, /* option combination this library does not implement */
+    BA_ERR_EVAL_FAILED = -6, /* non-finite residual/Jacobian at the initial point (Ceres: "initial evaluation failed") */
+    BA_ERR_INTERNAL = -7
+} ba_status;
+
+/* Robust kernel applied to s = ||r||^2 of each 2-vector residual.
+ * Reference: one shared ceres::HuberLoss(4), BundleAdjuster.h:109.  Cauchy is the north star's second kernel. */
+typedef enum ba_robust_kind { BA_ROBUST_NONE = 0, BA_ROBUST_HUBER = 1, BA_ROBUST_CAUCHY = 2 } ba_robust_kind;
+
+/* Residual model. PINHOLE = ReprojectCost (BundleAdjuster.h:38-68): +z forward, intrinsics group = (fx,fy,cx,cy).
+ * SNAVELY = SnavelyReprojectionError (SnavelyReprojectionError.h:16-48): -z, intrinsics group = (f,l1,l2). */
+typedef enum ba_model { BA_MODEL_PINHOLE = 0, BA_MODEL_SNAVELY = 1 } ba_model;
+
+/* How the reduced camera system is solved.
+ * EXACT is what the reference configures (SPARSE_SCHUR + EIGEN_SPARSE, BundleAdjuster.h:172-173): a direct
+ * factorisation of S — implemented by the oracle only.  PCG is the engine's block-preconditioned conjugate
+ * gradients on the implicit Schur complement (what Ceres calls ITERATIVE_SCHUR; the reference even sets
+ * preconditioner_type = JACOBI at :171, which only ITERATIVE_SCHUR would read). */
+typedef enum ba_linear_solver { BA_LINEAR_EXACT = 0, BA_LINEAR_PCG = 1 } ba_linear_solver;
+typedef enum ba_preconditioner { BA_PRECOND_JACOBI = 0 /* blockdiag(Hcc + Dc^2) */, BA_PRECOND_SCHUR_JACOBI = 1 /* blockdiag(S) */ } ba_preconditioner;
+
+/* Which rule selects the first-order branch of AngleAxisRotatePoint. */
+typedef enum ba_taylor_rule { BA_TAYLOR_THETA2_LE_EPS = 0 /* theta^2 <= DBL_EPSILON */, BA_TAYLOR_THETA_IS_ZERO = 1 /* hypot()==0 */ } ba_taylor_rule;
+
+typedef enum ba_termination {
+    BA_TERM_CONVERGENCE = 0,    /* function / parameter / gradient tolerance or minimum radius reached */
+    BA_TERM_NO_CONVERGENCE = 1, /* iteration cap */
+    BA_TERM_FAILURE = 2,        /* too many consecutive invalid steps, or evaluation failure */
+    BA_TERM_TARGET_REACHED = 3  /* chi2 <= target_chi2 (bench-only stop rule, off by default) */
+} ba_termination;
+
+/* Options. Call ba_options_default() first; the defaults are the reference's configuration:
+ * Ceres 2.2 trust-region LM defaults + what BundleAdjuster() sets (BundleAdjuster.h:167-174), see SURVEY §8 (a-LM). */
+typedef struct ba_options {
+    int32_t abi_version;                 /* BA_ABI_VERSION */
+    /* --- problem semantics --- */
+    int32_t model;                       /* ba_model */
+    int32_t robust_kind;                 /* ba_robust_kind; reference: HUBER */
+    double  robust_a;                    /* reference: 4.0 */
+    int32_t intrinsics_free;             /* 1: every intrinsics group is a free block (reference, :106-107); 0: held constant (north star's 2x6/2x3 form) */
+    int32_t taylor_rule;                 /* ba_taylor_rule */
+    /* --- Levenberg-Marquardt (Ceres names) --- */
+    int32_t max_num_iterations;          /* 50 */
+    double  initial_trust_region_radius; /* 1e4 */
+    double  max_trust_region_radius;     /* 1e16 */
+    double  min_trust_region_radius;     /* 1e-32 */
+    double  min_relative_decrease;       /* 1e-3 */
+    double  min_lm_diagonal;             /* 1e-6 */
+    double  max_lm_diagonal;             /* 1e32 */
+    int32_t max_num_consecutive_invalid_steps; /* 5 */
+    double  function_tolerance;          /* 1e-6 */
+    double  gradient_tolerance;          /* 1e-10 */
+    double  parameter_tolerance;         /* 1e-8 */
+    int32_t jacobi_scaling;              /* 1 */
+    /* --- reduced-system solve --- */
+    int32_t linear_solver;               /* ba_linear_solver; engine: PCG only */
+    int32_t preconditioner;              /* ba_preconditioner */
+    int32_t pcg_max_iterations;          /* parity mode 2000 */
+    double  pcg_rel_tolerance;           /* stop when sqrt(r'M^-1 r / b'M^-1 b) <= tol; parity mode 1e-12 */
+    int32_t pcg_forcing;                 /* 0: fixed tolerance above; 1: Ceres inexact-Newton rule (eta, Q-criterion, r_tolerance off) */
+    double  eta;                         /* 0.1 */
+    /* --- extra stop rule for time-to-converge measurements --- */
+    double  target_chi2;                 /* >0: stop as soon as chi2 (= 2*cost) <= target_chi2; 0: off */
+    /* --- execution --- */
+    int32_t device;                      /* CUDA ordinal (engine) */
+    int32_t num_threads;                 /* oracle: OpenMP threads; reference sets 1 (:170) */
+    int32_t rank;                        /* multi-GPU: this process' rank, one process per GPU */
+    int32_t world_size;                  /* 1 = single GPU */
+    const void* nccl_unique_id;          /* world_size>1: 128-byte ncclUniqueId from ba_nccl_unique_id() on rank 0, broadcast by the caller */
+    void*   stream;                      /* engine: cudaStream_t to run on (NULL: the engine creates its own) */
+    int32_t scatter_mode;                /* engine: 0 = auto, 1 = red.global atomics, 2 = tile-aggregated atomics */
+    int32_t reserved[7];
+} ba_options;
+
+/* Problem in canonical indexing: observations sorted by point id (non-decreasing obs_pt),
+ * point id = rank of WorldPoint::idx_, pose id = rank of Image::idx_, group id = Camera object. */
+typedef struct ba_problem {
+    int32_t num_cameras;      /* Nc poses: 6 doubles each (angle-axis, translation) — image_extrinsic_, BundleAdjuster.h:93-94 */
+    int32_t num_groups;       /* Ng intrinsics groups — camera_intrinsics_, :95-96 */
+    int32_t num_points;       /* Np — world_points_pos_, :84-86 */
+    int32_t num_observations; /* No residual blocks, :110-121 */
+    const double*  pose;      /* [Nc][6] */
+    const double*  intr;      /* [Ng][4] (pinhole: fx,fy,cx,cy; snavely: f,l1,l2,unused) */
+    const int32_t* cam_group; /* [Nc] */
+    const uint8_t* cam_fixed; /* [Nc] 1 = SetParameterBlockConstant (:105); any subset */
+    const double*  pt;        /* [Np][3] */
+    const int32_t* obs_cam;   /* [No] */
+    const int32_t* obs_pt;    /* [No] non-decreasing */
+    const double*  obs_uv;    /* [No][2] */
+} ba_problem;
+
+typedef struct ba_summary {
+    int32_t termination;       /* ba_termination */
+    int32_t usable;            /* mirrors Summary::IsSolutionUsable(), BundleAdjuster.h:128 */
+    int32_t num_iterations;    /* records in the trajectory, including iteration 0 */
+    int32_t num_successful_steps;
+    int32_t num_unsuccessful_steps;
+    int32_t num_residuals;     /* 2*No */
+    int64_t total_pcg_iterations;
+    double  initial_cost;      /* cost = 1/2 sum rho(||r||^2); chi2 = 2*cost */
+    double  final_cost;
+    double  solve_seconds;     /* engine: device time of ba_solve from CUDA events on its stream; oracle: wall clock */
+    char    message[160];
+} ba_summary;
+
+/* One record per LM iteration — the parity artefact of SURVEY §8 (a-LM). */
+typedef struct ba_iter_record {
+    int32_t iteration;
+    int32_t step_is_valid;
+    int32_t step_is_successful;
+    int32_t pcg_iterations;
+    double  cost;               /* cost of the current x after this iteration */
+    double  candidate_cost;     /* cost at x+delta (DBL_MAX if evaluation failed; 0 for iteration 0) */
+    double  model_cost_change;
+    double  relative_decrease;  /* rho_k */
+    double  radius_used;        /* trust-region radius the step was computed with */
+    double  radius;             /* radius after accept/reject */
+    double  step_norm;
+    double  gradient_max_norm;
+    double  pcg_rel_residual;
+} ba_iter_record;
+
+/* Per-kernel device timing for the roofline report. */
+typedef struct ba_kernel_stat {
+    char    name[32];
+    int64_t launches;
+    double  total_ms;           /* CUDA-event time summed over launches (only when profiling is enabled) */
+    double  bytes_per_launch;   /* algorithmic bytes, DESIGN.md formula for this kernel's formulation */
+} ba_kernel_stat;
+
+int  ba_options_default(ba_options* opt);
+int  ba_create(const ba_options* opt, ba_engine** out);
+int  ba_set_problem(ba_engine* e, const ba_problem* p);       /* copies (engine: host->device) and builds index structure */
+int  ba_reset_state(ba_engine* e);                            /* restore the parameters given to ba_set_problem (engine: device-to-device) */
+int  ba_solve(ba_engine* e, ba_summary* out);                 /* blocking; whole LM loop */
+int  ba_get_state(ba_engine* e, double* pose, double* intr, double* pt); /* any may be NULL */
+int  ba_get_trajectory(ba_engine* e, ba_iter_record* out, int32_t cap, int32_t* n);
+/* Index structure for the bit-exact check: perm_by_cam[No] (stable sort of observation ids by camera),
+ * cam_off[Nc+1], pt_off[Np+1], schur_pairs[2*n_pairs] (i<j, both free, co-observing >=1 point; lexicographic).
+ * Any pointer may be NULL; *n_pairs is always set when non-NULL. */
+int  ba_get_structure(ba_engine* e, int32_t* perm_by_cam, int32_t* cam_off, int32_t* pt_off,
+                      int32_t* schur_pairs, int64_t pairs_cap, int64_t* n_pairs);
+/* One evaluation at the current parameters without solving: cost, residuals r[No][2] (robustified),
+ * Jacobian blocks Jc[No][2][6], Jp[No][2][3], Ji[No][2][4] (robustified, NOT column-scaled), gradient
+ * g[6Nc+4Ng+3Np] (pose, intrinsics, point order).  Any output may be NULL. For the K1/K2 parity tests. */
+int  ba_evaluate(ba_engine* e, double* cost, double* r, double* Jc, double* Jp, double* Ji, double* g);
+int  ba_set_profiling(ba_engine* e, int32_t enabled);          /* per-kernel CUDA-event timing on/off (off by default) */
+int  ba_get_kernel_stats(ba_engine* e, ba_kernel_stat* out, int32_t cap, int32_t* n);
+int  ba_nccl_unique_id(void* out128);                          /* rank 0 only; engine library only */
+const char* ba_last_error(const ba_engine* e);                /* e may be NULL: last error of a failed ba_create on this thread */
+const char* ba_backend(void);                                 /* "cuda-sm100a" or "cpu-oracle" */
+void ba_destroy(ba_engine* e);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BA_ENGINE_H */

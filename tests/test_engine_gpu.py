@@ -1,0 +1,149 @@
+"""GPU parity tests: the CUDA engine against the CPU oracle on the same seeded inputs, through the C-ABI.
+
+Bars (BASELINE.json north_star / SURVEY §8d): per-iteration chi2 within 1e-6 relative with identical accept/reject
+flags; final poses and points within 1e-5 relative; index structure bit-exact.
+"""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+CHI2_RTOL = 1e-6
+STATE_RTOL = 1e-5
+
+
+def solve_both(ba, oracle, P, **opts):
+    oopts = dict(opts)
+    threads = oopts.pop("oracle_threads", 4)
+    with ba.Engine(**opts) as eng:
+        eng.set_problem(P)
+        se = eng.solve()
+        te = eng.trajectory()
+        xe = eng.get_state()
+    with oracle.create(oracle.default_options(num_threads=threads, **oopts)) as h:
+        h.set_problem(P)
+        so = h.solve()
+        to = h.trajectory()
+        xo = h.get_state()
+    return (se, te, xe), (so, to, xo)
+
+
+def assert_trajectory_parity(te, to, upto=None):
+    n = min(len(te), len(to)) if upto is None else upto
+    assert n > 1
+    for a, b in zip(te[:n], to[:n]):
+        assert a.iteration == b.iteration
+        assert a.step_is_valid == b.step_is_valid, f"iteration {a.iteration}: valid flag differs"
+        assert a.step_is_successful == b.step_is_successful, f"iteration {a.iteration}: accept/reject differs"
+        assert abs(a.cost - b.cost) <= CHI2_RTOL * abs(b.cost), f"iteration {a.iteration}: chi2 {2*a.cost!r} vs oracle {2*b.cost!r}"
+        assert abs(a.radius - b.radius) <= 1e-6 * abs(b.radius)
+
+
+def rel_err(a, b):
+    return np.linalg.norm(a - b) / max(np.linalg.norm(b), 1e-300)
+
+
+def test_backend_is_cuda(engine_lib):
+    assert engine_lib.backend() == "cuda-sm100a"
+
+
+@pytest.mark.parametrize("name", ["tiny", "ladybug"])
+def test_evaluate_parity(ba, oracle, name):
+    """K0+K1+K2: residuals, analytic Jacobian blocks, cost and gradient against the Jet-differentiated oracle."""
+    P = ba.synth(name)
+    for fi in (0, 1):
+        with ba.Engine(intrinsics_free=fi) as eng, oracle.create(oracle.default_options(intrinsics_free=fi)) as h:
+            eng.set_problem(P)
+            h.set_problem(P)
+            a, b = eng.evaluate(), h.evaluate()
+        assert abs(a["cost"] - b["cost"]) <= 1e-12 * abs(b["cost"])
+        for k in ("r", "Jc", "Jp", "Ji"):
+            scale = max(np.abs(b[k]).max(), 1e-300)
+            assert np.abs(a[k] - b[k]).max() <= 1e-10 * scale, k
+        assert np.abs(a["g"] - b["g"]).max() <= 1e-10 * np.abs(b["g"]).max()
+
+
+@pytest.mark.parametrize("name,fi", [("tiny", 0), ("tiny", 1), ("ladybug", 0), ("ladybug", 1), ("trafalgar", 0)])
+def test_trajectory_parity(ba, oracle, name, fi):
+    P = ba.synth(name)
+    (se, te, xe), (so, to, xo) = solve_both(ba, oracle, P, intrinsics_free=fi, max_num_iterations=12)
+    assert se.usable and so.usable
+    assert len(te) == len(to)
+    assert_trajectory_parity(te, to)
+    assert se.termination == so.termination
+    assert rel_err(xe[0], xo[0]) <= STATE_RTOL
+    assert rel_err(xe[2], xo[2]) <= STATE_RTOL
+    assert rel_err(xe[1], xo[1]) <= STATE_RTOL
+
+
+@pytest.mark.parametrize("kind", [0, 1, 2])
+def test_robust_kernels(ba, oracle, kind):
+    P = ba.synth("ladybug", seed=77)
+    (se, te, xe), (so, to, xo) = solve_both(ba, oracle, P, intrinsics_free=0, robust_kind=kind, robust_a=4.0, max_num_iterations=8)
+    assert_trajectory_parity(te, to)
+
+
+def test_structure_bit_exact(ba, oracle):
+    P = ba.synth("ladybug")
+    with ba.Engine(intrinsics_free=0) as eng, oracle.create(oracle.default_options(intrinsics_free=0)) as h:
+        eng.set_problem(P)
+        h.set_problem(P)
+        for x, y in zip(eng.structure(), h.structure()):
+            assert x.dtype == y.dtype and x.shape == y.shape and np.array_equal(x, y)
+
+
+def test_reset_state_reproduces(ba):
+    P = ba.synth("ladybug")
+    with ba.Engine(intrinsics_free=0, max_num_iterations=5) as eng:
+        eng.set_problem(P)
+        s1 = eng.solve()
+        eng.reset_state()
+        s2 = eng.solve()
+    assert abs(s1.final_cost - s2.final_cost) <= 1e-9 * s1.final_cost
+    assert s1.num_iterations == s2.num_iterations
+
+
+def test_long_track_and_ragged(ba, oracle):
+    """A point seen by more cameras than one tile holds (long-point path), empty points and an unobserved camera."""
+    P = ba.synth(num_cameras=300, num_points=60, num_observations=60 * 2 + 298 + 100, seed=5, max_track=300)
+    # make point 0 visible from every camera: rebuild the observation list by hand
+    rng = np.random.default_rng(3)
+    Nc, Np = 300, 60
+    cams, pts = [], []
+    for p in range(Np):
+        k = Nc if p == 0 else int(rng.integers(2, 6))
+        cs = np.sort(rng.choice(Nc - 1, size=min(k, Nc - 1), replace=False))   # camera Nc-1 is never observed
+        if p in (7, 8):
+            continue                                                            # points 7 and 8 have no observation
+        cams.append(cs); pts.append(np.full(cs.size, p))
+    obs_cam = np.concatenate(cams).astype(np.int32); obs_pt = np.concatenate(pts).astype(np.int32)
+    # exact projections of the true scene + noise
+    from math import sqrt
+    def rot(aa):
+        th = np.linalg.norm(aa)
+        if th < 1e-300: return np.eye(3)
+        k = aa / th; K = np.array([[0, -k[2], k[1]], [k[2], 0, -k[0]], [-k[1], k[0], 0]])
+        return np.eye(3) + np.sin(th) * K + (1 - np.cos(th)) * K @ K
+    uv = np.empty((obs_cam.size, 2))
+    for i, (c, p) in enumerate(zip(obs_cam, obs_pt)):
+        Pc = rot(P.pose_true[c, :3]) @ P.pt_true[p] + P.pose_true[c, 3:]
+        uv[i] = [P.intr[0, 0] * Pc[0] / Pc[2] + P.intr[0, 2], P.intr[0, 1] * Pc[1] / Pc[2] + P.intr[0, 3]]
+    uv += rng.normal(0, 0.5, uv.shape)
+    Q = ba.Problem(pose=P.pose, intr=P.intr, cam_group=P.cam_group, cam_fixed=P.cam_fixed, pt=P.pt, obs_cam=obs_cam, obs_pt=obs_pt, obs_uv=uv)
+    (se, te, xe), (so, to, xo) = solve_both(ba, oracle, Q, intrinsics_free=1, max_num_iterations=6)
+    assert_trajectory_parity(te, to)
+    # untouched parameters stay bit-identical
+    assert np.array_equal(xe[2][7], Q.pt[7]) and np.array_equal(xe[2][8], Q.pt[8])
+    assert np.array_equal(xe[0][Nc - 1], Q.pose[Nc - 1])
+
+
+def test_evaluation_failure_is_reported(ba):
+    """A point on a camera's principal plane (Pz = 0) makes the evaluation non-finite: FAILURE, not usable."""
+    P = ba.synth("tiny")
+    c, p = int(P.obs_cam[0]), int(P.obs_pt[0])
+    P.pose[c] = 0.0
+    P.pt[p] = [1.0, 2.0, 0.0]
+    with ba.Engine(intrinsics_free=0) as eng:
+        eng.set_problem(P)
+        s = eng.solve()
+    assert s.termination == 2 and not s.usable
