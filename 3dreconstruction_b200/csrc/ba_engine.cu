@@ -23,6 +23,7 @@
 #include <vector>
 
 #include "ba_kernels.cuh"
+#include "ba_scatter.cuh"
 
 namespace {
 using std::vector;
@@ -134,6 +135,13 @@ struct ba_engine {
     DevBuf<double> d_red;        // [Hcc 36Nc | gc 6Nc | Hii 16Ng | gi 4Ng] — one all-reduce per evaluation
     DevBuf<double> d_sc_f, d_Df2, d_Minv, d_b, d_x, d_r, d_z, d_p, d_y;
     DevBuf<double> d_part0, d_part1;   // per-tile / per-block partials
+    // static scatter schedule + private accumulators (ba_scatter.cuh)
+    DevBuf<unsigned char> d_slot;
+    DevBuf<int> d_spack;
+    DevBuf<double> d_scratch;
+    bak::ScatterSched Sch{};
+    int scatter_mode = 2;              // 1 = red.global atomics, 2 = private accumulators (default)
+    int num_sms = 148;
     DevBuf<bak::Scalars> d_scal;
     bak::Scalars* h_scal = nullptr;    // pinned
     bak::View V{};
@@ -263,6 +271,36 @@ void do_set_problem(ba_engine* e, const ba_problem* P) {
     }
     build_tiles(pt_off, Np, tile_off);
     e->nTiles = int(tile_off.size()) - 1;
+    // static scatter schedule: within each tile, the rank of every observation in camera-sorted (stable) order, and per
+    // sorted position the camera + segment length at segment heads (ba_scatter.cuh)
+    vector<unsigned char> slot(No, 0);
+    vector<int32_t> spack(No, -1);
+    {
+        vector<int32_t> idx(bak::TILE_OBS);
+        for (int t = 0; t < e->nTiles; ++t) {
+            const int o0 = tile_off[t], n = tile_off[t + 1] - o0;
+            if (n > bak::TILE_OBS) continue;   // long-point tile: handled with atomics, no schedule
+            for (int i = 0; i < n; ++i) idx[i] = i;
+            std::stable_sort(idx.begin(), idx.begin() + n, [&](int a, int b) { return P->obs_cam[e->ob + o0 + a] < P->obs_cam[e->ob + o0 + b]; });
+            for (int j = 0; j < n;) {
+                const int cam = P->obs_cam[e->ob + o0 + idx[j]];
+                int k = j;
+                while (k < n && P->obs_cam[e->ob + o0 + idx[k]] == cam) { slot[o0 + idx[k]] = static_cast<unsigned char>(k); ++k; }
+                spack[o0 + j] = cam | ((k - j) << 22);
+                j = k;
+            }
+        }
+    }
+    if (Nc >= (1 << 22)) throw BaFail{BA_ERR_UNSUPPORTED, "more than 4M cameras"};
+    e->d_slot.upload(slot.data(), No, s);
+    e->d_spack.upload(spack.data(), No, s);
+    {
+        const int G = std::max(1, std::min(e->nTiles, e->num_sms * bak::SCAT_CTAS_PER_SM));
+        const int ldf = (e->nf + 15) / 16 * 16;
+        e->d_scratch.alloc(size_t(G) * ldf);
+        e->d_scratch.zero(s);
+        e->Sch.slot = e->d_slot.p; e->Sch.spack = e->d_spack.p; e->Sch.scratch = e->d_scratch.p; e->Sch.ldf = ldf; e->Sch.G = G;
+    }
 
     e->d_tile_off.upload(tile_off.data(), tile_off.size(), s);
     e->d_obs_cam.upload(P->obs_cam + e->ob, No, s);
@@ -315,11 +353,11 @@ void do_set_problem(ba_engine* e, const ba_problem* P) {
     e->stats[KID_K2C].bytes = no * (96 + (e->fi ? 64 : 0) + 16 + 4) + (288 + 48) * nc;
     e->stats[KID_K3P].bytes = np * (48 + 24 + 24 + 48 + 24);
     e->stats[KID_K3C].bytes = nc * (288 + 48 + 48 + 288);
-    e->stats[KID_K4].bytes = no * (jb + 16 + 8) + np * 24 + 48 * nc;
-    e->stats[KID_K5].bytes = no * (jb + 8) + np * (48 + 4) + 96 * nc;
+    e->stats[KID_K4].bytes = no * (jb + 16 + 8 + 5) + np * 24 + 48 * nc;
+    e->stats[KID_K5].bytes = no * (jb + 8 + 5) + np * (48 + 4) + 96 * nc;
     e->stats[KID_K7].bytes = no * (jb + 8 + 16) + np * (48 + 24 + 24 + 4) + 48 * nc;
     e->stats[KID_K8].bytes = np * 72 + nc * 144;
-    e->stats[KID_PCGV].bytes = double(e->nf) * 8 * 12 + 288 * nc;
+    e->stats[KID_PCGV].bytes = double(e->nf) * 8 * (14 + e->Sch.G * 2) + 288 * nc;
     e->stats[KID_MISC].bytes = 0;
 }
 
@@ -409,30 +447,55 @@ void launch_sweep(ba_engine* e, int kid, const double* xin, double* yout, const 
     else bak::k_schur_sweep<MODE, false><<<e->nTiles, bak::TILE_OBS, 0, e->stream>>>(e->V, xin, yout, done, partial);
 }
 
+// Camera-side product y = F^T(...) by the configured scatter: private accumulators (default) or L2 atomics into yout.
+template <int MODE>
+void launch_scatter(ba_engine* e, int kid, const double* xin, double* yout, const int* done) {
+    if (e->nTiles == 0) return;
+    if (e->scatter_mode == 1) { launch_sweep<MODE>(e, kid, xin, yout, done, nullptr); return; }
+    LaunchTimer t(e, kid);
+    if (e->fi) bak::k_schur_scatter<MODE, true><<<e->Sch.G, bak::TILE_OBS, 0, e->stream>>>(e->V, e->Sch, xin, done);
+    else bak::k_schur_scatter<MODE, false><<<e->Sch.G, bak::TILE_OBS, 0, e->stream>>>(e->V, e->Sch, xin, done);
+}
+
 // One linear solve of the LM step at trust-region radius `radius` (K3, K4, PCG with K5, K7).  Leaves the step in
 // d_x (pose|intrinsics part) and V.yp (points), the model cost change in scal.mcc.  Returns PCG iterations, or -1.
 int solve_linear(ba_engine* e, double radius, double* rel_out) {
     cudaStream_t s = e->stream;
     bak::Scalars* sc = e->d_scal.p;
     const bak::LmParams lm{radius, e->opt.min_lm_diagonal, e->opt.max_lm_diagonal};
+    const bool priv = e->scatter_mode != 1;
+    const int vblocks = std::max(1, std::min(cdiv(e->nf, bak::PCG_BLOCK), 2 * e->num_sms));
+    const int cblocks = std::max(1, cdiv(e->Nc + e->Ng, bak::PCG_BLOCK));
     CU_TRY(cudaMemsetAsync(&sc->bad_lin, 0, sizeof(int), s));
     if (e->Np > 0) { LaunchTimer t(e, KID_K3P); bak::k3_point_blocks<<<cdiv(e->Np, 256), 256, 0, s>>>(e->V, lm, &sc->bad_lin); }
     { LaunchTimer t(e, KID_K3C);
       bak::k3_camera_blocks<<<cdiv(e->Nc + e->Ng, 128), 128, 0, s>>>(e->Nc, e->Ng, e->fi, e->Hcc(), e->Hii(), e->d_sc_f.p, lm, e->d_Df2.p, e->d_Minv.p, &sc->bad_lin); }
-    // reduced right-hand side b = gc - F^T E vp:  start from zero, sweep adds F^T (r - E vp) = gc - F^T E vp
-    e->d_b.zero(s);
-    launch_sweep<bak::SWEEP_RHS>(e, KID_K4, nullptr, e->d_b.p, nullptr, nullptr);
+    // reduced right-hand side b = F^T (r - E vp) = gc - F^T E vp
+    if (!priv) e->d_b.zero(s);
+    launch_scatter<bak::SWEEP_RHS>(e, KID_K4, nullptr, e->d_b.p, nullptr);
+    if (priv) { LaunchTimer t(e, KID_PCGV);
+        bak::k_pcg_q<<<vblocks, bak::PCG_BLOCK, 0, s>>>(e->nf, e->Sch.G, e->Sch.ldf, e->d_scratch.p, nullptr, nullptr, e->d_b.p, nullptr, nullptr, 1, 0); }
     allreduce_sum(e, e->d_b.p, e->nf);
     const bak::PcgParams pp{e->opt.pcg_max_iterations, e->opt.pcg_forcing, e->opt.pcg_rel_tolerance, e->opt.eta};
     { LaunchTimer t(e, KID_PCGV);
-      bak::k_pcg_init<<<1, 1024, 0, s>>>(e->nf, e->Nc, e->d_Minv.p, e->d_b.p, e->d_x.p, e->d_r.p, e->d_z.p, e->d_p.p, e->d_y.p, &sc->pcg); }
+      bak::k_pcg_init2<<<1, 1024, 0, s>>>(e->nf, e->Nc, e->d_Minv.p, e->d_b.p, e->d_x.p, e->d_r.p, e->d_z.p, e->d_p.p, &sc->pcg); }
+    if (!priv) e->d_y.zero(s);
     const int batch = 8;
+    const bool multi = e->opt.world_size > 1;
     for (;;) {
         for (int i = 0; i < batch; ++i) {
-            launch_sweep<bak::SWEEP_MATVEC>(e, KID_K5, e->d_p.p, e->d_y.p, &sc->pcg.done, nullptr);
-            allreduce_sum(e, e->d_y.p, e->nf);
+            launch_scatter<bak::SWEEP_MATVEC>(e, KID_K5, e->d_p.p, e->d_y.p, &sc->pcg.done);
             LaunchTimer t(e, KID_PCGV);
-            bak::k_pcg_update<<<1, 1024, 0, s>>>(e->nf, e->Nc, e->d_Df2.p, e->d_Minv.p, e->d_b.p, e->d_x.p, e->d_r.p, e->d_z.p, e->d_p.p, e->d_y.p, &sc->pcg, pp);
+            if (multi) {   // reduce the private copies, all-reduce across ranks, then the dot product
+                if (priv) bak::k_pcg_q<<<vblocks, bak::PCG_BLOCK, 0, s>>>(e->nf, e->Sch.G, e->Sch.ldf, e->d_scratch.p, nullptr, nullptr, e->d_y.p, nullptr, nullptr, 1, 0);
+                allreduce_sum(e, e->d_y.p, e->nf);
+                bak::k_pcg_q<<<vblocks, bak::PCG_BLOCK, 0, s>>>(e->nf, e->Sch.G, e->Sch.ldf, e->d_scratch.p, e->d_Df2.p, e->d_p.p, e->d_y.p, e->d_part1.p, &sc->pcg, 0, 1);
+            } else {
+                bak::k_pcg_q<<<vblocks, bak::PCG_BLOCK, 0, s>>>(e->nf, e->Sch.G, e->Sch.ldf, e->d_scratch.p, e->d_Df2.p, e->d_p.p, e->d_y.p, e->d_part1.p, &sc->pcg, priv ? 1 : 0, 1);
+            }
+            bak::k_pcg_xr<<<cblocks, bak::PCG_BLOCK, 0, s>>>(e->Nc, e->Ng, e->fi, e->d_Minv.p, e->d_b.p, e->d_y.p, e->d_p.p, e->d_x.p, e->d_r.p, e->d_z.p, e->d_part1.p, &sc->pcg, pp);
+            bak::k_pcg_p<<<vblocks, bak::PCG_BLOCK, 0, s>>>(e->nf, e->d_z.p, e->d_p.p, &sc->pcg);
+            if (!priv) e->d_y.zero(s);
         }
         read_scalars(e);
         if (e->h_scal->pcg.done) break;
@@ -615,6 +678,8 @@ int ba_create(const ba_options* opt, ba_engine** out) {
         CU_TRY(cudaSetDevice(e->device));
         cudaDeviceProp prop{};
         CU_TRY(cudaGetDeviceProperties(&prop, e->device));
+        e->num_sms = prop.multiProcessorCount;
+        e->scatter_mode = (opt->scatter_mode == 1) ? 1 : 2;
         if (prop.major < 10) throw BaFail{BA_ERR_CUDA, std::string("device ") + prop.name + " is not sm_100-class; this library holds sm_100a code only"};
         if (opt->stream) e->stream = static_cast<cudaStream_t>(opt->stream);
         else { CU_TRY(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking)); e->own_stream = true; }

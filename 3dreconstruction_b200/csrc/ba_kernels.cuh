@@ -706,15 +706,19 @@ __global__ void k_scales_cameras(int Nc, int Ng, int fi, const double* __restric
 
 
 // ---------------------------------------------------------------------------------------------------------
-// PCG on the reduced camera system (block-Jacobi preconditioner, implicit Schur product by k_schur_sweep<MATVEC>).
-// All vectors have nf = 6 Nc (+ 4 Ng) entries (85 KB on Venice) and are replicated on every rank, so the vector
-// algebra of one iteration is a single one-CTA kernel: no scalar ever travels to the host inside the loop.
-struct PcgState { double rho, rho0, rel, Q0; int k, done, pad0, pad1; };   // done: 0 running, 1 converged, 2 iteration cap, 3 breakdown
+// PCG on the reduced camera system (block-Jacobi preconditioner, implicit Schur product by the K5 sweep).
+// All vectors have nf = 6 Nc (+ 4 Ng) entries (85 KB on Venice) and are replicated on every rank; the kernels are in
+// ba_scatter.cuh.  No scalar travels to the host inside the loop: the stop test lives in PcgState2.done.
+struct PcgState2 {
+    double rho, rho0, rel, Q0, alpha, beta;
+    int k, done;                  // done: 0 running, 1 converged, 2 iteration cap, 3 breakdown
+    unsigned int ticket_q, ticket_r;
+};
 struct PcgParams { int max_iterations; int forcing; double rel_tolerance; double eta; };
 
 struct Scalars {   // everything the host reads back, one D2H copy
     double cost, ccost, mcc, step2_pt, xn2_pt, step2_f, xn2_f, gmax_pt, gmax_f;
-    PcgState pcg;
+    PcgState2 pcg;
     int bad_eval, bad_cand, bad_lin, pad;
 };
 
@@ -729,83 +733,6 @@ __device__ __forceinline__ double apply_minv(int j, int Nc, const double* __rest
     const double* M = Minv + 36 * size_t(Nc) + 16 * size_t(g) + 4 * a;
     const double* rg = r + 6 * Nc + 4 * g;
     return M[0] * rg[0] + M[1] * rg[1] + M[2] * rg[2] + M[3] * rg[3];
-}
-
-__global__ void __launch_bounds__(1024)
-k_pcg_init(int nf, int Nc, const double* __restrict__ Minv, const double* __restrict__ b, double* __restrict__ x,
-           double* __restrict__ r, double* __restrict__ z, double* __restrict__ p, double* __restrict__ y, PcgState* __restrict__ st) {
-    __shared__ double sred[32];
-    double acc = 0.0;
-    for (int j = threadIdx.x; j < nf; j += blockDim.x) {
-        x[j] = 0.0; y[j] = 0.0;
-        const double zj = apply_minv(j, Nc, Minv, b);
-        r[j] = b[j]; z[j] = zj; p[j] = zj;
-        acc += b[j] * zj;
-    }
-    acc = block_sum(acc, sred);
-    if (threadIdx.x == 0) {
-        st->rho = acc; st->rho0 = acc; st->rel = acc > 0.0 ? 1.0 : 0.0; st->Q0 = 0.0; st->k = 0;
-        st->done = (acc > 0.0 && isfinite(acc)) ? 0 : (acc == 0.0 ? 1 : 3);
-    }
-}
-
-__global__ void __launch_bounds__(1024)
-k_pcg_update(int nf, int Nc, const double* __restrict__ Df2, const double* __restrict__ Minv, const double* __restrict__ b,
-             double* __restrict__ x, double* __restrict__ r, double* __restrict__ z, double* __restrict__ p, double* __restrict__ y,
-             PcgState* __restrict__ st, PcgParams pp) {
-    __shared__ double sred[32];
-    __shared__ double sb[2];
-    if (st->done) return;
-    const double rho = st->rho;
-    // q = S p = y + Df^2 p ;  pq = p.q
-    double acc = 0.0;
-    for (int j = threadIdx.x; j < nf; j += blockDim.x) {
-        const double q = y[j] + Df2[j] * p[j];
-        y[j] = q;
-        acc += p[j] * q;
-    }
-    acc = block_sum(acc, sred);
-    if (threadIdx.x == 0) sb[0] = acc;
-    __syncthreads();
-    const double pq = sb[0];
-    if (!(pq > 0.0) || !isfinite(pq)) {
-        for (int j = threadIdx.x; j < nf; j += blockDim.x) y[j] = 0.0;
-        if (threadIdx.x == 0) st->done = 3;
-        return;
-    }
-    const double alpha = rho / pq;
-    for (int j = threadIdx.x; j < nf; j += blockDim.x) { x[j] += alpha * p[j]; r[j] -= alpha * y[j]; }
-    __syncthreads();
-    double acc2 = 0.0, accq = 0.0;
-    for (int j = threadIdx.x; j < nf; j += blockDim.x) {
-        const double zj = apply_minv(j, Nc, Minv, r);
-        z[j] = zj;
-        acc2 += r[j] * zj;
-        accq += x[j] * (b[j] + r[j]);
-    }
-    acc2 = block_sum(acc2, sred);
-    if (threadIdx.x == 0) sb[0] = acc2;
-    accq = block_sum(accq, sred);
-    if (threadIdx.x == 0) sb[1] = accq;
-    __syncthreads();
-    const double rho_new = sb[0];
-    const double beta = rho_new / rho;
-    for (int j = threadIdx.x; j < nf; j += blockDim.x) { p[j] = z[j] + beta * p[j]; y[j] = 0.0; }
-    if (threadIdx.x == 0) {
-        const int k = st->k + 1;
-        const double rel = sqrt(fmax(rho_new, 0.0) / st->rho0);
-        int done = 0;
-        if (pp.forcing) {   // Ceres' Q-criterion (inexact Newton): Q = -1/2 x.(b + r); stop when k (Q1 - Q0)/Q1 < eta
-            const double Q1 = -0.5 * sb[1];
-            const double zeta = k * (Q1 - st->Q0) / Q1;
-            st->Q0 = Q1;
-            if (zeta < pp.eta) done = 1;
-        }
-        if (rel <= pp.rel_tolerance) done = 1;
-        if (!done && k >= pp.max_iterations) done = 2;
-        if (!isfinite(rho_new)) done = 3;
-        st->k = k; st->rel = rel; st->rho = rho_new; st->done = done;
-    }
 }
 
 // ---------------------------------------------------------------------------------------------------------
