@@ -24,6 +24,7 @@
 
 #include "ba_kernels.cuh"
 #include "ba_scatter.cuh"
+#include "ba_pipe.cuh"
 
 namespace {
 using std::vector;
@@ -99,6 +100,7 @@ struct DevBuf {
     ~DevBuf() { release(); }
 };
 
+constexpr int kRedSlices = 8;      // stage-1 slices of the private-copy reduction (ba_pipe.cuh)
 enum KernelId { KID_K0 = 0, KID_K1, KID_K1C, KID_K2C, KID_K3P, KID_K3C, KID_K4, KID_K5, KID_K7, KID_K8, KID_PCGV, KID_MISC, KID_COUNT };
 const char* const kKernelNames[KID_COUNT] = {"K0_camera_precompute", "K1_residual_jacobian", "K1c_candidate_cost", "K2c_camera_blocks",
                                              "K3p_point_blocks",      "K3c_camera_blocks",    "K4_reduced_rhs",     "K5_schur_matvec",
@@ -140,7 +142,8 @@ struct ba_engine {
     DevBuf<int> d_spack;
     DevBuf<double> d_scratch;
     bak::ScatterSched Sch{};
-    int scatter_mode = 2;              // 1 = red.global atomics, 2 = private accumulators (default)
+    DevBuf<double> d_redpart;          // [kRedSlices][ldf] stage-1 output of the copy reduction
+    int scatter_mode = 3;              // 1 = red.global atomics, 2 = private accumulators, 3 = + bulk-copy pipeline (default)
     int num_sms = 148;
     DevBuf<bak::Scalars> d_scal;
     bak::Scalars* h_scal = nullptr;    // pinned
@@ -295,11 +298,12 @@ void do_set_problem(ba_engine* e, const ba_problem* P) {
     e->d_slot.upload(slot.data(), No, s);
     e->d_spack.upload(spack.data(), No, s);
     {
-        const int G = std::max(1, std::min(e->nTiles, e->num_sms * bak::SCAT_CTAS_PER_SM));
+        const int G = std::max(1, std::min(e->nTiles, e->num_sms * 2));
         const int ldf = (e->nf + 15) / 16 * 16;
         e->d_scratch.alloc(size_t(G) * ldf);
         e->d_scratch.zero(s);
         e->Sch.slot = e->d_slot.p; e->Sch.spack = e->d_spack.p; e->Sch.scratch = e->d_scratch.p; e->Sch.ldf = ldf; e->Sch.G = G;
+        e->d_redpart.alloc(size_t(kRedSlices) * ldf);
     }
 
     e->d_tile_off.upload(tile_off.data(), tile_off.size(), s);
@@ -367,7 +371,7 @@ namespace {
 
 // ---- kernel sequences ----------------------------------------------------------------------------------------
 inline int cdiv(int a, int b) { return (a + b - 1) / b; }
-constexpr int kNormBlocks = 592;   // 4 x 148 SMs for the grid-stride vector kernels
+constexpr int kNormBlocks = 592;
 
 void read_scalars(ba_engine* e) {
     CU_TRY(cudaMemcpyAsync(e->h_scal, e->d_scal.p, sizeof(bak::Scalars), cudaMemcpyDeviceToHost, e->stream));
@@ -447,14 +451,32 @@ void launch_sweep(ba_engine* e, int kid, const double* xin, double* yout, const 
     else bak::k_schur_sweep<MODE, false><<<e->nTiles, bak::TILE_OBS, 0, e->stream>>>(e->V, xin, yout, done, partial);
 }
 
-// Camera-side product y = F^T(...) by the configured scatter: private accumulators (default) or L2 atomics into yout.
+// Camera-side product F^T(...) by the configured scatter.  Result: in `yout` for mode 1 (L2 atomics), otherwise in the
+// private copies e->d_scratch[0..*G_out) to be reduced by reduce_copies().
+template <int MODE, bool FI>
+void launch_pipe(ba_engine* e, const double* xin, const int* done, int* G_out) {
+    using Cfg = bak::PipeCfg<MODE, FI>;
+    static bool attr_set = false;
+    if (!attr_set) { CU_TRY(cudaFuncSetAttribute(bak::k_schur_pipe<MODE, FI>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(Cfg::SMEM))); attr_set = true; }
+    const int G = std::max(1, std::min(e->nTiles, e->num_sms * Cfg::CTAS_PER_SM));
+    bak::k_schur_pipe<MODE, FI><<<G, Cfg::THREADS, Cfg::SMEM, e->stream>>>(e->V, e->Sch, xin, done);
+    *G_out = G;
+}
+
 template <int MODE>
-void launch_scatter(ba_engine* e, int kid, const double* xin, double* yout, const int* done) {
+void launch_scatter(ba_engine* e, int kid, const double* xin, double* yout, const int* done, int* G_out) {
+    *G_out = 0;
     if (e->nTiles == 0) return;
     if (e->scatter_mode == 1) { launch_sweep<MODE>(e, kid, xin, yout, done, nullptr); return; }
     LaunchTimer t(e, kid);
-    if (e->fi) bak::k_schur_scatter<MODE, true><<<e->Sch.G, bak::TILE_OBS, 0, e->stream>>>(e->V, e->Sch, xin, done);
-    else bak::k_schur_scatter<MODE, false><<<e->Sch.G, bak::TILE_OBS, 0, e->stream>>>(e->V, e->Sch, xin, done);
+    if (e->scatter_mode == 2) {
+        if (e->fi) bak::k_schur_scatter<MODE, true><<<e->Sch.G, bak::TILE_OBS, 0, e->stream>>>(e->V, e->Sch, xin, done);
+        else bak::k_schur_scatter<MODE, false><<<e->Sch.G, bak::TILE_OBS, 0, e->stream>>>(e->V, e->Sch, xin, done);
+        *G_out = e->Sch.G;
+    } else {
+        if (e->fi) launch_pipe<MODE, true>(e, xin, done, G_out);
+        else launch_pipe<MODE, false>(e, xin, done, G_out);
+    }
 }
 
 // One linear solve of the LM step at trust-region radius `radius` (K3, K4, PCG with K5, K7).  Leaves the step in
@@ -470,11 +492,23 @@ int solve_linear(ba_engine* e, double radius, double* rel_out) {
     if (e->Np > 0) { LaunchTimer t(e, KID_K3P); bak::k3_point_blocks<<<cdiv(e->Np, 256), 256, 0, s>>>(e->V, lm, &sc->bad_lin); }
     { LaunchTimer t(e, KID_K3C);
       bak::k3_camera_blocks<<<cdiv(e->Nc + e->Ng, 128), 128, 0, s>>>(e->Nc, e->Ng, e->fi, e->Hcc(), e->Hii(), e->d_sc_f.p, lm, e->d_Df2.p, e->d_Minv.p, &sc->bad_lin); }
+    // Source of k_pcg_q's reduction: mode 2 sums the G private copies directly (and re-zeroes them); mode 3 first folds
+    // them into kRedSlices slices with a wide grid (k_reduce_copies), the pipe kernel clears its own copy on entry.
+    auto reduce_src = [&](int G, const int* done, double*& src, int& nsrc) {
+        src = e->d_scratch.p; nsrc = G;
+        if (e->scatter_mode == 3 && G > 0) {
+            dim3 grid(cdiv(e->nf, 256), kRedSlices);
+            bak::k_reduce_copies<<<grid, 256, 0, s>>>(e->nf, G, e->Sch.ldf, e->d_scratch.p, kRedSlices, e->d_redpart.p, done);
+            src = e->d_redpart.p; nsrc = kRedSlices;
+        }
+    };
     // reduced right-hand side b = F^T (r - E vp) = gc - F^T E vp
     if (!priv) e->d_b.zero(s);
-    launch_scatter<bak::SWEEP_RHS>(e, KID_K4, nullptr, e->d_b.p, nullptr);
+    int G = 0;
+    launch_scatter<bak::SWEEP_RHS>(e, KID_K4, nullptr, e->d_b.p, nullptr, &G);
     if (priv) { LaunchTimer t(e, KID_PCGV);
-        bak::k_pcg_q<<<vblocks, bak::PCG_BLOCK, 0, s>>>(e->nf, e->Sch.G, e->Sch.ldf, e->d_scratch.p, nullptr, nullptr, e->d_b.p, nullptr, nullptr, 1, 0); }
+        double* src; int nsrc; reduce_src(G, nullptr, src, nsrc);
+        bak::k_pcg_q<<<vblocks, bak::PCG_BLOCK, 0, s>>>(e->nf, nsrc, e->Sch.ldf, src, nullptr, nullptr, e->d_b.p, nullptr, nullptr, 1, 0); }
     allreduce_sum(e, e->d_b.p, e->nf);
     const bak::PcgParams pp{e->opt.pcg_max_iterations, e->opt.pcg_forcing, e->opt.pcg_rel_tolerance, e->opt.eta};
     { LaunchTimer t(e, KID_PCGV);
@@ -484,14 +518,16 @@ int solve_linear(ba_engine* e, double radius, double* rel_out) {
     const bool multi = e->opt.world_size > 1;
     for (;;) {
         for (int i = 0; i < batch; ++i) {
-            launch_scatter<bak::SWEEP_MATVEC>(e, KID_K5, e->d_p.p, e->d_y.p, &sc->pcg.done);
+            launch_scatter<bak::SWEEP_MATVEC>(e, KID_K5, e->d_p.p, e->d_y.p, &sc->pcg.done, &G);
             LaunchTimer t(e, KID_PCGV);
+            double* src = nullptr; int nsrc = 0;
+            if (priv) reduce_src(G, &sc->pcg.done, src, nsrc);
             if (multi) {   // reduce the private copies, all-reduce across ranks, then the dot product
-                if (priv) bak::k_pcg_q<<<vblocks, bak::PCG_BLOCK, 0, s>>>(e->nf, e->Sch.G, e->Sch.ldf, e->d_scratch.p, nullptr, nullptr, e->d_y.p, nullptr, nullptr, 1, 0);
+                if (priv) bak::k_pcg_q<<<vblocks, bak::PCG_BLOCK, 0, s>>>(e->nf, nsrc, e->Sch.ldf, src, nullptr, nullptr, e->d_y.p, nullptr, nullptr, 1, 0);
                 allreduce_sum(e, e->d_y.p, e->nf);
-                bak::k_pcg_q<<<vblocks, bak::PCG_BLOCK, 0, s>>>(e->nf, e->Sch.G, e->Sch.ldf, e->d_scratch.p, e->d_Df2.p, e->d_p.p, e->d_y.p, e->d_part1.p, &sc->pcg, 0, 1);
+                bak::k_pcg_q<<<vblocks, bak::PCG_BLOCK, 0, s>>>(e->nf, 0, e->Sch.ldf, nullptr, e->d_Df2.p, e->d_p.p, e->d_y.p, e->d_part1.p, &sc->pcg, 0, 1);
             } else {
-                bak::k_pcg_q<<<vblocks, bak::PCG_BLOCK, 0, s>>>(e->nf, e->Sch.G, e->Sch.ldf, e->d_scratch.p, e->d_Df2.p, e->d_p.p, e->d_y.p, e->d_part1.p, &sc->pcg, priv ? 1 : 0, 1);
+                bak::k_pcg_q<<<vblocks, bak::PCG_BLOCK, 0, s>>>(e->nf, nsrc, e->Sch.ldf, src, e->d_Df2.p, e->d_p.p, e->d_y.p, e->d_part1.p, &sc->pcg, priv ? 1 : 0, 1);
             }
             bak::k_pcg_xr<<<cblocks, bak::PCG_BLOCK, 0, s>>>(e->Nc, e->Ng, e->fi, e->d_Minv.p, e->d_b.p, e->d_y.p, e->d_p.p, e->d_x.p, e->d_r.p, e->d_z.p, e->d_part1.p, &sc->pcg, pp);
             bak::k_pcg_p<<<vblocks, bak::PCG_BLOCK, 0, s>>>(e->nf, e->d_z.p, e->d_p.p, &sc->pcg);
@@ -679,7 +715,7 @@ int ba_create(const ba_options* opt, ba_engine** out) {
         cudaDeviceProp prop{};
         CU_TRY(cudaGetDeviceProperties(&prop, e->device));
         e->num_sms = prop.multiProcessorCount;
-        e->scatter_mode = (opt->scatter_mode == 1) ? 1 : 2;
+        e->scatter_mode = (opt->scatter_mode >= 1 && opt->scatter_mode <= 3) ? opt->scatter_mode : 3;
         if (prop.major < 10) throw BaFail{BA_ERR_CUDA, std::string("device ") + prop.name + " is not sm_100-class; this library holds sm_100a code only"};
         if (opt->stream) e->stream = static_cast<cudaStream_t>(opt->stream);
         else { CU_TRY(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking)); e->own_stream = true; }
