@@ -25,6 +25,7 @@
 #include "ba_kernels.cuh"
 #include "ba_scatter.cuh"
 #include "ba_pipe.cuh"
+#include "ba_rows.cuh"
 
 namespace {
 using std::vector;
@@ -143,7 +144,12 @@ struct ba_engine {
     DevBuf<double> d_scratch;
     bak::ScatterSched Sch{};
     DevBuf<double> d_redpart;          // [kRedSlices][ldf] stage-1 output of the copy reduction
-    int scatter_mode = 3;              // 1 = red.global atomics, 2 = private accumulators, 3 = + bulk-copy pipeline (default)
+    // mode 4: per-(tile, camera) partial rows + by-camera gather (ba_rows.cuh)
+    DevBuf<unsigned char> d_lvl1, d_hrank;
+    DevBuf<int> d_tile_hbase, d_cam_row_off, d_cam_rows;
+    DevBuf<double> d_rows, d_tile_intr;
+    bak::RowSched RS{};
+    int scatter_mode = 4;              // 1 = red.global atomics, 2 = private accumulators, 3 = 2 + bulk-copy pipeline, 4 = partial rows (default)
     int num_sms = 148;
     DevBuf<bak::Scalars> d_scal;
     bak::Scalars* h_scal = nullptr;    // pinned
@@ -295,6 +301,45 @@ void do_set_problem(ba_engine* e, const ba_problem* P) {
         }
     }
     if (Nc >= (1 << 22)) throw BaFail{BA_ERR_UNSUPPORTED, "more than 4M cameras"};
+    // mode-4 schedule: level-1 chunk counts, head ranks, compact row numbering and the by-camera row lists
+    {
+        vector<unsigned char> lvl1(No, 0), hrank(No, 0);
+        vector<int32_t> hbase(size_t(e->nTiles) + 1, 0), row_cam;
+        row_cam.reserve(No / 2 + 16);
+        for (int t = 0; t < e->nTiles; ++t) {
+            const int o0 = tile_off[t], n = tile_off[t + 1] - o0;
+            hbase[t] = int(row_cam.size());
+            if (n > bak::TILE_OBS) { for (int i = 0; i < n; ++i) row_cam.push_back(P->obs_cam[e->ob + o0 + i]); continue; }
+            int rank = 0;
+            for (int j = 0; j < n;) {
+                const int pk = spack[o0 + j];            // head at sorted position j
+                const int cam = pk & 0x3fffff, len = pk >> 22, end = j + len;
+                hrank[o0 + j] = static_cast<unsigned char>(rank++);
+                row_cam.push_back(cam);
+                for (int q = j; q < end;) {               // chunk leaders: the head, then every multiple of L1_CHUNK inside the segment
+                    const int nxt = std::min((q / bak::L1_CHUNK + 1) * bak::L1_CHUNK, end);
+                    lvl1[o0 + q] = static_cast<unsigned char>(nxt - q);
+                    q = nxt;
+                }
+                j = end;
+            }
+        }
+        hbase[e->nTiles] = int(row_cam.size());
+        const int nRows = int(row_cam.size());
+        vector<int32_t> cro(size_t(Nc) + 1, 0), crows(nRows);
+        for (int r = 0; r < nRows; ++r) ++cro[row_cam[r] + 1];
+        for (int c = 0; c < Nc; ++c) cro[c + 1] += cro[c];
+        { vector<int32_t> cur(cro.begin(), cro.end() - 1); for (int r = 0; r < nRows; ++r) crows[cur[row_cam[r]]++] = r; }
+        e->d_lvl1.upload(lvl1.data(), No, s); e->d_hrank.upload(hrank.data(), No, s);
+        e->d_tile_hbase.upload(hbase.data(), hbase.size(), s);
+        e->d_cam_row_off.upload(cro.data(), cro.size(), s); e->d_cam_rows.upload(crows.data(), nRows, s);
+        e->d_rows.alloc(size_t(nRows) * bak::ROW_DOUBLES); e->d_rows.zero(s);
+        e->d_tile_intr.alloc(size_t(4) * std::max(e->nTiles, 1)); e->d_tile_intr.zero(s);
+        CU_TRY(cudaStreamSynchronize(s));
+        bak::RowSched& RS = e->RS;
+        RS.lvl1 = e->d_lvl1.p; RS.hrank = e->d_hrank.p; RS.tile_hbase = e->d_tile_hbase.p;
+        RS.rows = e->d_rows.p; RS.tile_intr = e->d_tile_intr.p; RS.cam_row_off = e->d_cam_row_off.p; RS.cam_rows = e->d_cam_rows.p; RS.nRows = nRows;
+    }
     e->d_slot.upload(slot.data(), No, s);
     e->d_spack.upload(spack.data(), No, s);
     {
@@ -304,6 +349,7 @@ void do_set_problem(ba_engine* e, const ba_problem* P) {
         e->d_scratch.zero(s);
         e->Sch.slot = e->d_slot.p; e->Sch.spack = e->d_spack.p; e->Sch.scratch = e->d_scratch.p; e->Sch.ldf = ldf; e->Sch.G = G;
         e->d_redpart.alloc(size_t(kRedSlices) * ldf);
+        e->RS.slot = e->d_slot.p; e->RS.spack = e->d_spack.p;
     }
 
     e->d_tile_off.upload(tile_off.data(), tile_off.size(), s);
@@ -329,7 +375,7 @@ void do_set_problem(ba_engine* e, const ba_problem* P) {
     e->d_red.alloc(e->red_count());
     for (auto* b : {&e->d_sc_f, &e->d_Df2, &e->d_b, &e->d_x, &e->d_r, &e->d_z, &e->d_p, &e->d_y}) b->alloc(e->nf);
     e->d_Minv.alloc(size_t(36) * Nc + size_t(16) * Ng);
-    const size_t nparts = std::max<size_t>(e->nTiles, 2048);
+    const size_t nparts = std::max<size_t>(std::max(e->nTiles, Nc + 8), 2048);
     e->d_part0.alloc(nparts); e->d_part1.alloc(nparts);
     e->d_scal.alloc(1);
     e->d_Hpp.zero(s); e->d_gp.zero(s); e->d_yp.zero(s); e->d_Hinv.zero(s); e->d_vp.zero(s); e->d_scal.zero(s);
@@ -363,6 +409,12 @@ void do_set_problem(ba_engine* e, const ba_problem* P) {
     e->stats[KID_K8].bytes = np * 72 + nc * 144;
     e->stats[KID_PCGV].bytes = double(e->nf) * 8 * (14 + e->Sch.G * 2) + 288 * nc;
     e->stats[KID_MISC].bytes = 0;
+    if (e->scatter_mode == 4) {   // partial-row formulation: + 7 B/obs of schedule, 64 B written per (tile, camera) row, read back by the gather
+        const double nr = e->RS.nRows;
+        e->stats[KID_K4].bytes = no * (jb + 16 + 8 + 7) + np * 24 + 64 * nr;
+        e->stats[KID_K5].bytes = no * (jb + 8 + 7) + np * (48 + 4) + 48 * nc + 64 * nr;
+        e->stats[KID_PCGV].bytes = 68 * nr + double(e->nf) * 8 * 12 + 288 * nc;
+    }
 }
 
 }  // namespace
@@ -469,6 +521,12 @@ void launch_scatter(ba_engine* e, int kid, const double* xin, double* yout, cons
     if (e->nTiles == 0) return;
     if (e->scatter_mode == 1) { launch_sweep<MODE>(e, kid, xin, yout, done, nullptr); return; }
     LaunchTimer t(e, kid);
+    if (e->scatter_mode == 4) {
+        if (e->fi && e->Ng > 1) CU_TRY(cudaMemsetAsync(yout + 6 * e->Nc, 0, size_t(4) * e->Ng * sizeof(double), e->stream));
+        if (e->fi) bak::k_schur_rows<MODE, true><<<e->nTiles, bak::TILE_OBS, 0, e->stream>>>(e->V, e->RS, xin, yout, done);
+        else bak::k_schur_rows<MODE, false><<<e->nTiles, bak::TILE_OBS, 0, e->stream>>>(e->V, e->RS, xin, yout, done);
+        return;
+    }
     if (e->scatter_mode == 2) {
         if (e->fi) bak::k_schur_scatter<MODE, true><<<e->Sch.G, bak::TILE_OBS, 0, e->stream>>>(e->V, e->Sch, xin, done);
         else bak::k_schur_scatter<MODE, false><<<e->Sch.G, bak::TILE_OBS, 0, e->stream>>>(e->V, e->Sch, xin, done);
@@ -485,7 +543,7 @@ int solve_linear(ba_engine* e, double radius, double* rel_out) {
     cudaStream_t s = e->stream;
     bak::Scalars* sc = e->d_scal.p;
     const bak::LmParams lm{radius, e->opt.min_lm_diagonal, e->opt.max_lm_diagonal};
-    const bool priv = e->scatter_mode != 1;
+    const bool priv = e->scatter_mode == 2 || e->scatter_mode == 3;
     const int vblocks = std::max(1, std::min(cdiv(e->nf, bak::PCG_BLOCK), 2 * e->num_sms));
     const int cblocks = std::max(1, cdiv(e->Nc + e->Ng, bak::PCG_BLOCK));
     CU_TRY(cudaMemsetAsync(&sc->bad_lin, 0, sizeof(int), s));
@@ -503,17 +561,21 @@ int solve_linear(ba_engine* e, double radius, double* rel_out) {
         }
     };
     // reduced right-hand side b = F^T (r - E vp) = gc - F^T E vp
-    if (!priv) e->d_b.zero(s);
+    if (e->scatter_mode == 1) e->d_b.zero(s);
     int G = 0;
     launch_scatter<bak::SWEEP_RHS>(e, KID_K4, nullptr, e->d_b.p, nullptr, &G);
-    if (priv) { LaunchTimer t(e, KID_PCGV);
+    const bool rowsm = e->scatter_mode == 4;
+    const int gblocks = cdiv(e->Nc, bak::GATHER_WARPS) + 1;
+    if (rowsm) { LaunchTimer t(e, KID_PCGV);
+        bak::k_camera_gather<<<gblocks, bak::GATHER_WARPS * 32, 0, s>>>(e->Nc, e->Ng, e->fi, e->nTiles, e->RS, nullptr, nullptr, e->d_b.p, nullptr, nullptr, 0);
+    } else if (priv) { LaunchTimer t(e, KID_PCGV);
         double* src; int nsrc; reduce_src(G, nullptr, src, nsrc);
         bak::k_pcg_q<<<vblocks, bak::PCG_BLOCK, 0, s>>>(e->nf, nsrc, e->Sch.ldf, src, nullptr, nullptr, e->d_b.p, nullptr, nullptr, 1, 0); }
     allreduce_sum(e, e->d_b.p, e->nf);
     const bak::PcgParams pp{e->opt.pcg_max_iterations, e->opt.pcg_forcing, e->opt.pcg_rel_tolerance, e->opt.eta};
     { LaunchTimer t(e, KID_PCGV);
       bak::k_pcg_init2<<<1, 1024, 0, s>>>(e->nf, e->Nc, e->d_Minv.p, e->d_b.p, e->d_x.p, e->d_r.p, e->d_z.p, e->d_p.p, &sc->pcg); }
-    if (!priv) e->d_y.zero(s);
+    if (e->scatter_mode == 1) e->d_y.zero(s);
     const int batch = 8;
     const bool multi = e->opt.world_size > 1;
     for (;;) {
@@ -521,6 +583,15 @@ int solve_linear(ba_engine* e, double radius, double* rel_out) {
             launch_scatter<bak::SWEEP_MATVEC>(e, KID_K5, e->d_p.p, e->d_y.p, &sc->pcg.done, &G);
             LaunchTimer t(e, KID_PCGV);
             double* src = nullptr; int nsrc = 0;
+            if (rowsm) {
+                if (multi) {
+                    bak::k_camera_gather<<<gblocks, bak::GATHER_WARPS * 32, 0, s>>>(e->Nc, e->Ng, e->fi, e->nTiles, e->RS, nullptr, nullptr, e->d_y.p, nullptr, nullptr, 0);
+                    allreduce_sum(e, e->d_y.p, e->nf);
+                    bak::k_pcg_q<<<vblocks, bak::PCG_BLOCK, 0, s>>>(e->nf, 0, e->Sch.ldf, nullptr, e->d_Df2.p, e->d_p.p, e->d_y.p, e->d_part1.p, &sc->pcg, 0, 1);
+                } else {
+                    bak::k_camera_gather<<<gblocks, bak::GATHER_WARPS * 32, 0, s>>>(e->Nc, e->Ng, e->fi, e->nTiles, e->RS, e->d_Df2.p, e->d_p.p, e->d_y.p, e->d_part1.p, &sc->pcg, 1);
+                }
+            } else {
             if (priv) reduce_src(G, &sc->pcg.done, src, nsrc);
             if (multi) {   // reduce the private copies, all-reduce across ranks, then the dot product
                 if (priv) bak::k_pcg_q<<<vblocks, bak::PCG_BLOCK, 0, s>>>(e->nf, nsrc, e->Sch.ldf, src, nullptr, nullptr, e->d_y.p, nullptr, nullptr, 1, 0);
@@ -529,9 +600,10 @@ int solve_linear(ba_engine* e, double radius, double* rel_out) {
             } else {
                 bak::k_pcg_q<<<vblocks, bak::PCG_BLOCK, 0, s>>>(e->nf, nsrc, e->Sch.ldf, src, e->d_Df2.p, e->d_p.p, e->d_y.p, e->d_part1.p, &sc->pcg, priv ? 1 : 0, 1);
             }
+            }
             bak::k_pcg_xr<<<cblocks, bak::PCG_BLOCK, 0, s>>>(e->Nc, e->Ng, e->fi, e->d_Minv.p, e->d_b.p, e->d_y.p, e->d_p.p, e->d_x.p, e->d_r.p, e->d_z.p, e->d_part1.p, &sc->pcg, pp);
             bak::k_pcg_p<<<vblocks, bak::PCG_BLOCK, 0, s>>>(e->nf, e->d_z.p, e->d_p.p, &sc->pcg);
-            if (!priv) e->d_y.zero(s);
+            if (e->scatter_mode == 1) e->d_y.zero(s);
         }
         read_scalars(e);
         if (e->h_scal->pcg.done) break;
@@ -715,7 +787,7 @@ int ba_create(const ba_options* opt, ba_engine** out) {
         cudaDeviceProp prop{};
         CU_TRY(cudaGetDeviceProperties(&prop, e->device));
         e->num_sms = prop.multiProcessorCount;
-        e->scatter_mode = (opt->scatter_mode >= 1 && opt->scatter_mode <= 3) ? opt->scatter_mode : 3;
+        e->scatter_mode = (opt->scatter_mode >= 1 && opt->scatter_mode <= 4) ? opt->scatter_mode : 4;
         if (prop.major < 10) throw BaFail{BA_ERR_CUDA, std::string("device ") + prop.name + " is not sm_100-class; this library holds sm_100a code only"};
         if (opt->stream) e->stream = static_cast<cudaStream_t>(opt->stream);
         else { CU_TRY(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking)); e->own_stream = true; }

@@ -78,7 +78,7 @@ def test_trajectory_parity(ba, oracle, name, fi):
     assert rel_err(xe[1], xo[1]) <= STATE_RTOL
 
 
-@pytest.mark.parametrize("mode", [1, 2, 3])
+@pytest.mark.parametrize("mode", [1, 2, 3, 4])
 @pytest.mark.parametrize("fi", [0, 1])
 def test_scatter_modes(ba, oracle, mode, fi):
     """All three camera-side scatter implementations (L2 atomics, private accumulators, bulk-copy pipeline) agree with the oracle."""
@@ -92,7 +92,7 @@ def test_private_scatter_is_bit_reproducible(ba):
     P = ba.synth("ladybug", seed=9)
     states = []
     for _ in range(2):
-        with ba.Engine(intrinsics_free=0, max_num_iterations=5, scatter_mode=3) as eng:
+        with ba.Engine(intrinsics_free=0, max_num_iterations=5) as eng:
             eng.set_problem(P)
             eng.solve()
             states.append(eng.get_state())
