@@ -145,8 +145,8 @@ struct ba_engine {
     bak::ScatterSched Sch{};
     DevBuf<double> d_redpart;          // [kRedSlices][ldf] stage-1 output of the copy reduction
     // mode 4: per-(tile, camera) partial rows + by-camera gather (ba_rows.cuh)
-    DevBuf<unsigned char> d_lvl1, d_hrank;
-    DevBuf<int> d_tile_hbase, d_cam_row_off, d_cam_rows;
+    DevBuf<int4> d_tmeta, d_tile_info;
+    DevBuf<int> d_cam_row_off, d_cam_rows;
     DevBuf<double> d_rows, d_tile_intr;
     bak::RowSched RS{};
     int scatter_mode = 4;              // 1 = red.global atomics, 2 = private accumulators, 3 = 2 + bulk-copy pipeline, 4 = partial rows (default)
@@ -330,14 +330,29 @@ void do_set_problem(ba_engine* e, const ba_problem* P) {
         for (int r = 0; r < nRows; ++r) ++cro[row_cam[r] + 1];
         for (int c = 0; c < Nc; ++c) cro[c + 1] += cro[c];
         { vector<int32_t> cur(cro.begin(), cro.end() - 1); for (int r = 0; r < nRows; ++r) crows[cur[row_cam[r]]++] = r; }
-        e->d_lvl1.upload(lvl1.data(), No, s); e->d_hrank.upload(hrank.data(), No, s);
-        e->d_tile_hbase.upload(hbase.data(), hbase.size(), s);
+        // pack the per-position records (RowSched::tmeta) and per-tile records (RowSched::tile_info)
+        vector<int4> tmeta(No), tinfo(std::max(e->nTiles, 1));
+        for (int t = 0; t < e->nTiles; ++t) {
+            const int o0 = tile_off[t], n = tile_off[t + 1] - o0;
+            const int pfirst = obs_pt[o0];
+            tinfo[t] = make_int4(o0, n, hbase[t], pfirst);
+            if (n > bak::TILE_OBS) { for (int i = 0; i < n; ++i) tmeta[o0 + i] = make_int4(P->obs_cam[e->ob + o0 + i], 0, -1, 0); continue; }
+            const int plast = obs_pt[o0 + n - 1];
+            for (int i = 0; i < n; ++i) {
+                const int lpt = obs_pt[o0 + i] - pfirst;
+                const unsigned packA = unsigned(slot[o0 + i]) | unsigned(lvl1[o0 + i]) << 8 | unsigned(hrank[o0 + i]) << 16 | unsigned(lpt) << 24;
+                int pw = 0;
+                if (pfirst + i <= plast) { const int a = pt_off[pfirst + i] - o0, cnt = pt_off[pfirst + i + 1] - pt_off[pfirst + i]; pw = cnt > 0 ? (a | cnt << 16) : 0; }
+                tmeta[o0 + i] = make_int4(P->obs_cam[e->ob + o0 + i], int(packA), spack[o0 + i], pw);
+            }
+        }
+        e->d_tmeta.upload(tmeta.data(), No, s); e->d_tile_info.upload(tinfo.data(), tinfo.size(), s);
         e->d_cam_row_off.upload(cro.data(), cro.size(), s); e->d_cam_rows.upload(crows.data(), nRows, s);
         e->d_rows.alloc(size_t(nRows) * bak::ROW_DOUBLES); e->d_rows.zero(s);
         e->d_tile_intr.alloc(size_t(4) * std::max(e->nTiles, 1)); e->d_tile_intr.zero(s);
         CU_TRY(cudaStreamSynchronize(s));
         bak::RowSched& RS = e->RS;
-        RS.lvl1 = e->d_lvl1.p; RS.hrank = e->d_hrank.p; RS.tile_hbase = e->d_tile_hbase.p;
+        RS.tmeta = e->d_tmeta.p; RS.tile_info = e->d_tile_info.p;
         RS.rows = e->d_rows.p; RS.tile_intr = e->d_tile_intr.p; RS.cam_row_off = e->d_cam_row_off.p; RS.cam_rows = e->d_cam_rows.p; RS.nRows = nRows;
     }
     e->d_slot.upload(slot.data(), No, s);
@@ -349,7 +364,6 @@ void do_set_problem(ba_engine* e, const ba_problem* P) {
         e->d_scratch.zero(s);
         e->Sch.slot = e->d_slot.p; e->Sch.spack = e->d_spack.p; e->Sch.scratch = e->d_scratch.p; e->Sch.ldf = ldf; e->Sch.G = G;
         e->d_redpart.alloc(size_t(kRedSlices) * ldf);
-        e->RS.slot = e->d_slot.p; e->RS.spack = e->d_spack.p;
     }
 
     e->d_tile_off.upload(tile_off.data(), tile_off.size(), s);
@@ -411,8 +425,8 @@ void do_set_problem(ba_engine* e, const ba_problem* P) {
     e->stats[KID_MISC].bytes = 0;
     if (e->scatter_mode == 4) {   // partial-row formulation: + 7 B/obs of schedule, 64 B written per (tile, camera) row, read back by the gather
         const double nr = e->RS.nRows;
-        e->stats[KID_K4].bytes = no * (jb + 16 + 8 + 7) + np * 24 + 64 * nr;
-        e->stats[KID_K5].bytes = no * (jb + 8 + 7) + np * (48 + 4) + 48 * nc + 64 * nr;
+        e->stats[KID_K4].bytes = no * (jb + 16 + 16) + np * 24 + 64 * nr + 16.0 * e->nTiles;
+        e->stats[KID_K5].bytes = no * (jb + 16) + np * 48 + 48 * nc + 64 * nr + 16.0 * e->nTiles;
         e->stats[KID_PCGV].bytes = 68 * nr + double(e->nf) * 8 * 12 + 288 * nc;
     }
 }
@@ -565,7 +579,7 @@ int solve_linear(ba_engine* e, double radius, double* rel_out) {
     int G = 0;
     launch_scatter<bak::SWEEP_RHS>(e, KID_K4, nullptr, e->d_b.p, nullptr, &G);
     const bool rowsm = e->scatter_mode == 4;
-    const int gblocks = cdiv(e->Nc, bak::GATHER_WARPS) + 1;
+    const int gblocks = e->Nc + 1;
     if (rowsm) { LaunchTimer t(e, KID_PCGV);
         bak::k_camera_gather<<<gblocks, bak::GATHER_WARPS * 32, 0, s>>>(e->Nc, e->Ng, e->fi, e->nTiles, e->RS, nullptr, nullptr, e->d_b.p, nullptr, nullptr, 0);
     } else if (priv) { LaunchTimer t(e, KID_PCGV);

@@ -17,11 +17,14 @@ constexpr int ROW_DOUBLES = 8;    // 6 used; 64-byte rows = two full 32-byte sec
 constexpr int L1_CHUNK = 8;       // level-1 chunk of the in-tile segmented sum
 
 struct RowSched {
-    const unsigned char* slot;    // [No] rank of the observation in its tile's camera-sorted order
-    const unsigned char* lvl1;    // [No] per sorted position: rows this thread adds up in level 1 (0: none)
-    const unsigned char* hrank;   // [No] per sorted position: index of this segment head among the tile's heads
-    const int* spack;             // [No] per sorted position: camera | (segment length << 22) at segment heads, -1 elsewhere
-    const int* tile_hbase;        // [nTiles+1] first compact row of each tile
+    // One 16-byte record per tile position i = o0 + tid, read with a single LDG.128 at kernel entry:
+    //   .x  camera of observation i
+    //   .y  slot | lvl1 << 8 | hrank << 16 | lpt << 24   (observation i: rank in the tile's camera-sorted order; sorted position
+    //       tid: rows to fold in level 1, index of this segment head among the tile's heads; observation i: tile-local point)
+    //   .z  sorted position tid: camera | segment length << 22 at segment heads, -1 elsewhere
+    //   .w  tile-local point tid: first observation | observation count << 16 (0 when tid >= points in tile)
+    const int4* tmeta;            // [No]
+    const int4* tile_info;        // [nTiles] {o0, n, first compact row, first local point}
     double* rows;                 // [nRows][ROW_DOUBLES]
     double* tile_intr;            // [nTiles][4] per-tile intrinsics-side partials (free intrinsics, one group)
     // by-camera view of the rows
@@ -39,33 +42,49 @@ k_schur_rows(View V, RowSched S, const double* __restrict__ xin, double* __restr
     __shared__ double sred[32];
     if (done_flag && *done_flag) return;
     const int t = blockIdx.x;
-    const int o0 = V.tile_off[t], o1 = V.tile_off[t + 1];
+    const int4 ti = __ldg(S.tile_info + t);
+    const int o0 = ti.x, n = ti.y, hbase = ti.z, pfirst = ti.w;
     const size_t ld = V.ldo;
     const int ioff = 6 * V.Nc;
     double yi[4] = {0, 0, 0, 0};
 
-    if (o1 - o0 <= TILE_OBS) {
+    if (n <= TILE_OBS) {
+        // ---- every global load of this tile is issued here, before the first use (one latency, not five) ----
         const int o = o0 + threadIdx.x;
-        const bool act = o < o1;
-        double2 jc[6], jp[3], ji[4];
-        double2 u = make_double2(0.0, 0.0);
-        int c = 0, p = 0, g = 0;
+        const bool act = threadIdx.x < n;
+        int4 tm = make_int4(0, 0, -1, 0);
+        double2 jc[6], jp[3], ji[4], rr = make_double2(0.0, 0.0);
         if (act) {
-            c = V.obs_cam[o]; p = V.obs_pt[o];
+            tm = __ldg(S.tmeta + o);
             const double2* J = V.J2 + o;
 #pragma unroll
             for (int k = 0; k < 6; ++k) jc[k] = ldg2(J + k * ld);
 #pragma unroll
             for (int k = 0; k < 3; ++k) jp[k] = ldg2(J + (6 + k) * ld);
             if (FI) {
-                g = V.cam_group[c];
 #pragma unroll
                 for (int k = 0; k < 4; ++k) ji[k] = ldg2(J + (9 + k) * ld);
             }
-            if (MODE == SWEEP_MATVEC) {
-                const double* xc = xin + 6 * c;
-#pragma unroll
-                for (int k = 0; k < 6; ++k) { const double xv = __ldg(xc + k); u.x += jc[k].x * xv; u.y += jc[k].y * xv; }
+            if (MODE == SWEEP_RHS) rr = V.r2[o];
+        }
+        const int npt_obs = tm.w >> 16, pstart = tm.w & 0xffff;   // this thread as a point thread
+        double2 h0 = make_double2(0, 0), h1 = h0, h2 = h0;
+        if (MODE == SWEEP_MATVEC && npt_obs > 0) {
+            const double2* H = reinterpret_cast<const double2*>(V.Hinv + 6 * size_t(pfirst + threadIdx.x));
+            h0 = __ldg(H); h1 = __ldg(H + 1); h2 = __ldg(H + 2);      // (H0,H1) (H2,H3) (H4,H5)
+        }
+        const int c = tm.x;
+        const int slot = tm.y & 0xff, n1 = (tm.y >> 8) & 0xff, hrank = (tm.y >> 16) & 0xff, lpt = (tm.y >> 24) & 0xff;
+        const int pk = tm.z;
+        const int g = (FI && act) ? V.cam_group[c] : 0;
+        double2 u = make_double2(0.0, 0.0);
+        double2 tt = make_double2(0.0, 0.0);
+        if (MODE == SWEEP_MATVEC) {
+            if (act) {
+                const double2* xc = reinterpret_cast<const double2*>(xin + 6 * c);
+                const double2 x0 = __ldg(xc), x1 = __ldg(xc + 1), x2 = __ldg(xc + 2);
+                u.x = jc[0].x * x0.x + jc[1].x * x0.y + jc[2].x * x1.x + jc[3].x * x1.y + jc[4].x * x2.x + jc[5].x * x2.y;
+                u.y = jc[0].y * x0.x + jc[1].y * x0.y + jc[2].y * x1.x + jc[3].y * x1.y + jc[4].y * x2.x + jc[5].y * x2.y;
                 if (FI) {
 #pragma unroll
                     for (int k = 0; k < 4; ++k) { const double xv = __ldg(xin + ioff + 4 * g + k); u.x += ji[k].x * xv; u.y += ji[k].y * xv; }
@@ -73,35 +92,27 @@ k_schur_rows(View V, RowSched S, const double* __restrict__ xin, double* __restr
 #pragma unroll
                 for (int a = 0; a < 3; ++a) sW[threadIdx.x][a] = jp[a].x * u.x + jp[a].y * u.y;
             }
-        }
-        double2 tt = make_double2(0.0, 0.0);
-        if (MODE == SWEEP_MATVEC) {
             __syncthreads();
-            const int pfirst = V.obs_pt[o0], plast = V.obs_pt[o1 - 1];
-            const int pj = pfirst + threadIdx.x;
-            if (pj <= plast) {
+            if (npt_obs > 0) {
                 double W0 = 0, W1 = 0, W2 = 0;
-                for (int i = V.pt_off[pj] - o0, e = V.pt_off[pj + 1] - o0; i < e; ++i) { W0 += sW[i][0]; W1 += sW[i][1]; W2 += sW[i][2]; }
-                const double* H = V.Hinv + 6 * size_t(pj);
-                sV[threadIdx.x][0] = H[0] * W0 + H[1] * W1 + H[2] * W2;
-                sV[threadIdx.x][1] = H[1] * W0 + H[3] * W1 + H[4] * W2;
-                sV[threadIdx.x][2] = H[2] * W0 + H[4] * W1 + H[5] * W2;
+                for (int i = pstart, e = pstart + npt_obs; i < e; ++i) { W0 += sW[i][0]; W1 += sW[i][1]; W2 += sW[i][2]; }
+                sV[threadIdx.x][0] = h0.x * W0 + h0.y * W1 + h1.x * W2;
+                sV[threadIdx.x][1] = h0.y * W0 + h1.y * W1 + h2.x * W2;
+                sV[threadIdx.x][2] = h1.x * W0 + h2.x * W1 + h2.y * W2;
             }
             __syncthreads();
             if (act) {
-                const double* v = sV[p - pfirst];
+                const double* v = sV[lpt];
                 tt.x = u.x - (jp[0].x * v[0] + jp[1].x * v[1] + jp[2].x * v[2]);
                 tt.y = u.y - (jp[0].y * v[0] + jp[1].y * v[1] + jp[2].y * v[2]);
             }
         } else if (act) {   // SWEEP_RHS: t = r - E vp
-            const double* v = V.vp + 3 * size_t(p);
-            const double2 r = V.r2[o];
-            tt.x = r.x - (jp[0].x * v[0] + jp[1].x * v[1] + jp[2].x * v[2]);
-            tt.y = r.y - (jp[0].y * v[0] + jp[1].y * v[1] + jp[2].y * v[2]);
+            const double* v = V.vp + 3 * size_t(pfirst + lpt);
+            tt.x = rr.x - (jp[0].x * v[0] + jp[1].x * v[1] + jp[2].x * v[2]);
+            tt.y = rr.y - (jp[0].y * v[0] + jp[1].y * v[1] + jp[2].y * v[2]);
         }
-        int n1 = 0, pk = -1;
         if (act) {
-            double2* sc = reinterpret_cast<double2*>(sC[S.slot[o]]);
+            double2* sc = reinterpret_cast<double2*>(sC[slot]);
             sc[0] = make_double2(jc[0].x * tt.x + jc[0].y * tt.y, jc[1].x * tt.x + jc[1].y * tt.y);
             sc[1] = make_double2(jc[2].x * tt.x + jc[2].y * tt.y, jc[3].x * tt.x + jc[3].y * tt.y);
             sc[2] = make_double2(jc[4].x * tt.x + jc[4].y * tt.y, jc[5].x * tt.x + jc[5].y * tt.y);
@@ -113,8 +124,6 @@ k_schur_rows(View V, RowSched S, const double* __restrict__ xin, double* __restr
                     for (int k = 0; k < 4; ++k) red_add(atomic_out + ioff + 4 * g + k, yi[k]);
                 }
             }
-            n1 = S.lvl1[o];
-            pk = S.spack[o];
         }
         __syncthreads();
         // level 1: chunk leaders (segment heads and every 8th sorted position) fold their <= 8 rows into their own row
@@ -139,12 +148,13 @@ k_schur_rows(View V, RowSched S, const double* __restrict__ xin, double* __restr
                 const double2 a2 = r2[0], b2 = r2[1], c2 = r2[2];
                 a.x += a2.x; a.y += a2.y; bq.x += b2.x; bq.y += b2.y; cq.x += c2.x; cq.y += c2.y;
             }
-            double2* dst = reinterpret_cast<double2*>(S.rows + size_t(ROW_DOUBLES) * (S.tile_hbase[t] + S.hrank[o]));
+            double2* dst = reinterpret_cast<double2*>(S.rows + size_t(ROW_DOUBLES) * (hbase + hrank));
             __stcg(dst, a); __stcg(dst + 1, bq); __stcg(dst + 2, cq);
         }
     } else {
         // ---- one point with more than TILE_OBS observations (rare): two passes, every observation is its own row ----
-        const int p = V.obs_pt[o0];
+        const int o1 = o0 + n;
+        const int p = pfirst;
         double v[3];
         if (MODE == SWEEP_MATVEC) {
             double W[3] = {0, 0, 0};
@@ -169,7 +179,6 @@ k_schur_rows(View V, RowSched S, const double* __restrict__ xin, double* __restr
             const double w0 = sV[0][0], w1 = sV[0][1], w2 = sV[0][2];
             v[0] = H[0] * w0 + H[1] * w1 + H[2] * w2; v[1] = H[1] * w0 + H[3] * w1 + H[4] * w2; v[2] = H[2] * w0 + H[4] * w1 + H[5] * w2;
         } else { v[0] = V.vp[3 * size_t(p)]; v[1] = V.vp[3 * size_t(p) + 1]; v[2] = V.vp[3 * size_t(p) + 2]; }
-        const int hb = S.tile_hbase[t];
         for (int o = o0 + threadIdx.x; o < o1; o += TILE_OBS) {
             const int c = V.obs_cam[o];
             const int g = FI ? V.cam_group[c] : 0;
@@ -196,7 +205,7 @@ k_schur_rows(View V, RowSched S, const double* __restrict__ xin, double* __restr
             double2 tt;
             if (MODE == SWEEP_MATVEC) { tt.x = u.x - e0; tt.y = u.y - e1; }
             else { const double2 r = V.r2[o]; tt.x = r.x - e0; tt.y = r.y - e1; }
-            double2* dst = reinterpret_cast<double2*>(S.rows + size_t(ROW_DOUBLES) * (hb + (o - o0)));
+            double2* dst = reinterpret_cast<double2*>(S.rows + size_t(ROW_DOUBLES) * (hbase + (o - o0)));
             __stcg(dst, make_double2(jc[0].x * tt.x + jc[0].y * tt.y, jc[1].x * tt.x + jc[1].y * tt.y));
             __stcg(dst + 1, make_double2(jc[2].x * tt.x + jc[2].y * tt.y, jc[3].x * tt.x + jc[3].y * tt.y));
             __stcg(dst + 2, make_double2(jc[4].x * tt.x + jc[4].y * tt.y, jc[5].x * tt.x + jc[5].y * tt.y));
@@ -215,37 +224,37 @@ k_schur_rows(View V, RowSched S, const double* __restrict__ xin, double* __restr
     }
 }
 
-// K5b — y[c] = sum of camera c's partial rows (one warp per camera, lanes stride the static row list, fixed shuffle tree);
-// with do_dot: q = y + Df2 p stored in y, block partials of p.q, last block forms alpha = rho / p.q  (PcgState2).
-// Block `gridDim.x - 1` additionally reduces the per-tile intrinsics partials (free intrinsics, single group).
+// K5b — y[c] = sum of camera c's partial rows: one 4-warp CTA per camera, lanes stride the static row list, fixed combine
+// order; with do_dot: q = y + Df2 p stored in y, one p.q partial per CTA, last CTA forms alpha = rho / p.q  (PcgState2).
+// CTA `Nc` (the last) reduces the per-tile intrinsics partials instead (free intrinsics, single group).
 constexpr int GATHER_WARPS = 4;
 __global__ void __launch_bounds__(GATHER_WARPS * 32)
 k_camera_gather(int Nc, int Ng, int fi, int nTiles, RowSched S, const double* __restrict__ Df2, const double* __restrict__ p,
                 double* __restrict__ y, double* __restrict__ partial, PcgState2* __restrict__ st, int do_dot) {
-    __shared__ double sw[GATHER_WARPS];
-    __shared__ double sred[32];
+    __shared__ double sw[GATHER_WARPS][6];
     __shared__ bool last;
     if (do_dot && st->done) return;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int ioff = 6 * Nc;
     double dot = 0.0;
-    const bool intr_block = (blockIdx.x == gridDim.x - 1);
-    if (!intr_block) {
-        const int c = blockIdx.x * GATHER_WARPS + wid;
-        if (c < Nc) {
-            double s0 = 0, s1 = 0, s2 = 0, s3 = 0, s4 = 0, s5 = 0;
-            for (int i = S.cam_row_off[c] + lane, e = S.cam_row_off[c + 1]; i < e; i += 32) {
-                const double2* row = reinterpret_cast<const double2*>(S.rows + size_t(ROW_DOUBLES) * S.cam_rows[i]);
-                const double2 a = __ldcg(row), bq = __ldcg(row + 1), cq = __ldcg(row + 2);
-                s0 += a.x; s1 += a.y; s2 += bq.x; s3 += bq.y; s4 += cq.x; s5 += cq.y;
-            }
-            s0 = warp_sum(s0); s1 = warp_sum(s1); s2 = warp_sum(s2); s3 = warp_sum(s3); s4 = warp_sum(s4); s5 = warp_sum(s5);
-            if (lane < 6) {
-                double v = lane == 0 ? s0 : lane == 1 ? s1 : lane == 2 ? s2 : lane == 3 ? s3 : lane == 4 ? s4 : s5;
-                const int j = 6 * c + lane;
-                if (do_dot) { const double pj = p[j]; v += Df2[j] * pj; dot = pj * v; }
-                y[j] = v;
-            }
+    const int c = blockIdx.x;
+    if (c < Nc) {
+        double s0 = 0, s1 = 0, s2 = 0, s3 = 0, s4 = 0, s5 = 0;
+        for (int i = S.cam_row_off[c] + threadIdx.x, e = S.cam_row_off[c + 1]; i < e; i += GATHER_WARPS * 32) {
+            const double2* row = reinterpret_cast<const double2*>(S.rows + size_t(ROW_DOUBLES) * S.cam_rows[i]);
+            const double2 a = __ldcg(row), bq = __ldcg(row + 1), cq = __ldcg(row + 2);
+            s0 += a.x; s1 += a.y; s2 += bq.x; s3 += bq.y; s4 += cq.x; s5 += cq.y;
+        }
+        s0 = warp_sum(s0); s1 = warp_sum(s1); s2 = warp_sum(s2); s3 = warp_sum(s3); s4 = warp_sum(s4); s5 = warp_sum(s5);
+        if (lane == 0) { sw[wid][0] = s0; sw[wid][1] = s1; sw[wid][2] = s2; sw[wid][3] = s3; sw[wid][4] = s4; sw[wid][5] = s5; }
+        __syncthreads();
+        if (threadIdx.x < 6) {
+            double v = 0.0;
+#pragma unroll
+            for (int w = 0; w < GATHER_WARPS; ++w) v += sw[w][threadIdx.x];
+            const int j = 6 * c + threadIdx.x;
+            if (do_dot) { const double pj = p[j]; v += Df2[j] * pj; dot = pj * v; }
+            y[j] = v;
         }
     } else if (fi) {
         // intrinsics entries: single group -> ordered sum of the per-tile partials; several groups -> RED-accumulated in y already
@@ -262,34 +271,31 @@ k_camera_gather(int Nc, int Ng, int fi, int nTiles, RowSched S, const double* __
                 y[j] = v;
             }
         }
+        // fold the per-warp dots of this CTA into warp 0 lane 0 below
+        __syncthreads();
     }
     if (!do_dot) return;
+    // CTA partial of p.q: camera CTAs hold it in threads 0..5 (warp 0); the intrinsics CTA in lane 0 of each warp
     dot = warp_sum(dot);
-    if (lane == 0) sw[wid] = dot;
-    __syncthreads();
+    if (c >= Nc) { if (lane == 0) sw[wid][0] = dot; __syncthreads(); if (threadIdx.x == 0) { dot = 0.0; for (int w = 0; w < GATHER_WARPS; ++w) dot += sw[w][0]; } }
     if (threadIdx.x == 0) {
-        double bsum = 0.0;
-        for (int w = 0; w < GATHER_WARPS; ++w) bsum += sw[w];
-        partial[blockIdx.x] = bsum;
+        partial[blockIdx.x] = dot;
         __threadfence();
         const unsigned int tk = atomicAdd(&st->ticket_q, 1u);
         last = (tk == gridDim.x - 1);
     }
     __syncthreads();
-    if (last) {   // fixed-order sum of the block partials by one warp
+    if (last && wid == 0) {   // fixed-order sum of the CTA partials by one warp
         __threadfence();
         double pq = 0.0;
-        if (wid == 0) {
-            for (int i = lane; i < int(gridDim.x); i += 32) pq += __ldcg(partial + i);
-            pq = warp_sum(pq);
-            if (lane == 0) {
-                if (!(pq > 0.0) || !isfinite(pq)) { st->done = 3; st->alpha = 0.0; }
-                else st->alpha = st->rho / pq;
-                st->ticket_q = 0;
-            }
+        for (int i = lane; i < int(gridDim.x); i += 32) pq += __ldcg(partial + i);
+        pq = warp_sum(pq);
+        if (lane == 0) {
+            if (!(pq > 0.0) || !isfinite(pq)) { st->done = 3; st->alpha = 0.0; }
+            else st->alpha = st->rho / pq;
+            st->ticket_q = 0;
         }
     }
-    (void)sred;
 }
 
 }  // namespace bak
