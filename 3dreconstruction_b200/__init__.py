@@ -89,6 +89,18 @@ class Library:
     def backend(self):
         return self.lib.ba_backend().decode()
 
+    def io_bytes(self):
+        a, b = C.c_int64(0), C.c_int64(0)
+        self.lib.ba_get_io_bytes(C.byref(a), C.byref(b))
+        return a.value, b.value
+
+    def nccl_unique_id(self):
+        buf = C.create_string_buffer(128)
+        rc = self.lib.ba_nccl_unique_id(buf)
+        if rc != 0:
+            raise BAError(f"ba_nccl_unique_id failed ({rc}): {self.lib.ba_last_error(None).decode()}")
+        return buf.raw
+
     def default_options(self, **kw):
         o = BAOptions()
         rc = self.lib.ba_options_default(C.byref(o))
@@ -186,8 +198,9 @@ class Handle:
             self._check(rc, "ba_evaluate")
         return dict(rc=rc, cost=cost.value, r=r, Jc=Jc, Jp=Jp, Ji=Ji, g=g)
 
-    def set_profiling(self, on):
-        self._check(self.lib.ba_set_profiling(self.h, 1 if on else 0), "ba_set_profiling")
+    def set_profiling(self, mask):
+        """mask: False/0 off, True/1 every kernel, else a bit mask over kernel_stats() order."""
+        self._check(self.lib.ba_set_profiling(self.h, int(mask)), "ba_set_profiling")
 
     def kernel_stats(self):
         n = C.c_int32(0)

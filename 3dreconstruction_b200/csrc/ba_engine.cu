@@ -42,6 +42,7 @@ thread_local std::string g_create_error;
     } while (0)
 
 struct BaFail { int code; std::string msg; };
+#define KL(eng) (++(eng)->kernel_launches)   // every kernel launch is counted (reported in ba_summary.kernel_launches)
 
 // ---- minimal NCCL binding, resolved at run time (torch bundles its own libnccl.so.2; whichever is already loaded wins) ----
 struct Nccl {
@@ -85,6 +86,8 @@ Nccl g_nccl;
         }                                                                                                    \
     } while (0)
 
+int64_t g_h2d_bytes = 0, g_d2h_bytes = 0;   // cumulative host<->device traffic of this library (ba_get_io_bytes)
+
 template <class T>
 struct DevBuf {
     T* p = nullptr;
@@ -96,7 +99,7 @@ struct DevBuf {
         n = count;
     }
     void release() { if (p) cudaFree(p); p = nullptr; n = 0; }
-    void upload(const T* h, size_t count, cudaStream_t s) { alloc(count); if (count) CU_TRY(cudaMemcpyAsync(p, h, count * sizeof(T), cudaMemcpyHostToDevice, s)); }
+    void upload(const T* h, size_t count, cudaStream_t s) { alloc(count); if (count) { CU_TRY(cudaMemcpyAsync(p, h, count * sizeof(T), cudaMemcpyHostToDevice, s)); g_h2d_bytes += int64_t(count * sizeof(T)); } }
     void zero(cudaStream_t s) { if (p && n) CU_TRY(cudaMemsetAsync(p, 0, n * sizeof(T), s)); }
     ~DevBuf() { release(); }
 };
@@ -157,7 +160,8 @@ struct ba_engine {
     // multi-GPU
     Nccl::Comm comm = nullptr;
     // profiling
-    bool profiling = false;
+    int64_t kernel_launches = 0;
+    unsigned profiling = 0;           // bit k set: time kernel id k with CUDA events
     struct Stat { int64_t launches = 0; double ms = 0.0; double bytes = 0.0; } stats[KID_COUNT];
     struct Pending { int kid; cudaEvent_t a, b; };
     vector<Pending> pending;
@@ -184,7 +188,7 @@ struct LaunchTimer {
     ba_engine* e; int kid; cudaEvent_t a = nullptr, b = nullptr;
     LaunchTimer(ba_engine* e_, int kid_) : e(e_), kid(kid_) {
         ++e->stats[kid].launches;
-        if (!e->profiling) return;
+        if (!((e->profiling >> kid) & 1u)) return;
         auto get = [&]() { cudaEvent_t ev; if (!e->ev_pool.empty()) { ev = e->ev_pool.back(); e->ev_pool.pop_back(); } else cudaEventCreate(&ev); return ev; };
         a = get(); b = get();
         cudaEventRecord(a, e->stream);
@@ -441,6 +445,7 @@ constexpr int kNormBlocks = 592;
 
 void read_scalars(ba_engine* e) {
     CU_TRY(cudaMemcpyAsync(e->h_scal, e->d_scal.p, sizeof(bak::Scalars), cudaMemcpyDeviceToHost, e->stream));
+    g_d2h_bytes += int64_t(sizeof(bak::Scalars));
     CU_TRY(cudaStreamSynchronize(e->stream));
 }
 
@@ -451,18 +456,18 @@ void evaluate_full(ba_engine* e) {
     const bak::RobustParams rp{e->opt.robust_kind, e->opt.robust_a};
     CU_TRY(cudaMemsetAsync(&sc->bad_eval, 0, sizeof(int), s));
     { LaunchTimer t(e, KID_K0);
-      bak::k0_camera_precompute<<<cdiv(e->Nc, 128), 128, 0, s>>>(e->Nc, e->d_pose.p, e->d_camrec.p, e->opt.taylor_rule); }
+      KL(e), bak::k0_camera_precompute<<<cdiv(e->Nc, 128), 128, 0, s>>>(e->Nc, e->d_pose.p, e->d_camrec.p, e->opt.taylor_rule); }
     if (e->nTiles > 0) {
         LaunchTimer t(e, KID_K1);
-        bak::k1_residual_jacobian<<<e->nTiles, bak::TILE_OBS, 0, s>>>(e->V, e->d_camrec.p, e->d_intr.p, e->d_pt.p, rp, e->d_part0.p, &sc->bad_eval);
+        KL(e), bak::k1_residual_jacobian<<<e->nTiles, bak::TILE_OBS, 0, s>>>(e->V, e->d_camrec.p, e->d_intr.p, e->d_pt.p, rp, e->d_part0.p, &sc->bad_eval);
     }
     { LaunchTimer t(e, KID_MISC);
-      bak::k_reduce_partials<<<1, 1024, 0, s>>>(e->d_part0.p, e->nTiles, &sc->cost); }
+      KL(e), bak::k_reduce_partials<<<1, 1024, 0, s>>>(e->d_part0.p, e->nTiles, &sc->cost); }
     if (e->fi) CU_TRY(cudaMemsetAsync(e->Hii(), 0, size_t(20) * e->Ng * sizeof(double), s));
     if (e->Nc > 0) {
         LaunchTimer t(e, KID_K2C);
-        if (e->fi) bak::k2c_camera_blocks<true><<<e->Nc, 128, 0, s>>>(e->V, e->Hcc(), e->gc(), e->Hii(), e->gi());
-        else bak::k2c_camera_blocks<false><<<e->Nc, 128, 0, s>>>(e->V, e->Hcc(), e->gc(), e->Hii(), e->gi());
+        if (e->fi) KL(e), bak::k2c_camera_blocks<true><<<e->Nc, 128, 0, s>>>(e->V, e->Hcc(), e->gc(), e->Hii(), e->gi());
+        else KL(e), bak::k2c_camera_blocks<false><<<e->Nc, 128, 0, s>>>(e->V, e->Hcc(), e->gc(), e->Hii(), e->gi());
     }
     if (e->opt.world_size > 1) {
         NCCL_TRY(g_nccl.GroupStart());
@@ -476,8 +481,8 @@ void evaluate_full(ba_engine* e) {
 void gradient_max(ba_engine* e) {
     cudaStream_t s = e->stream;
     LaunchTimer t(e, KID_MISC);
-    bak::k_gradmax_points<<<kNormBlocks, 256, 0, s>>>(e->V, e->d_pt.p, e->d_part1.p);
-    bak::k_gradmax_final<<<1, 1024, 0, s>>>(e->Nc, e->Ng, e->fi, e->d_cam_free.p, e->d_grp_free.p, e->d_pose.p, e->d_intr.p, e->gc(), e->gi(),
+    KL(e), bak::k_gradmax_points<<<kNormBlocks, 256, 0, s>>>(e->V, e->d_pt.p, e->d_part1.p);
+    KL(e), bak::k_gradmax_final<<<1, 1024, 0, s>>>(e->Nc, e->Ng, e->fi, e->d_cam_free.p, e->d_grp_free.p, e->d_pose.p, e->d_intr.p, e->gc(), e->gi(),
                                             e->d_part1.p, kNormBlocks, e->d_scal.p);
     allreduce_max(e, &e->d_scal.p->gmax_pt, 1);
 }
@@ -487,10 +492,10 @@ void make_candidate(ba_engine* e, const double* yf) {
     cudaStream_t s = e->stream;
     bak::Scalars* sc = e->d_scal.p;
     LaunchTimer t(e, KID_K8);
-    bak::k8_candidate_points<<<kNormBlocks, 256, 0, s>>>(e->V, e->d_pt.p, e->d_cpt.p, e->d_part0.p, e->d_part1.p);
-    bak::k_reduce_partials<<<1, 1024, 0, s>>>(e->d_part0.p, kNormBlocks, &sc->step2_pt);
-    bak::k_reduce_partials<<<1, 1024, 0, s>>>(e->d_part1.p, kNormBlocks, &sc->xn2_pt);
-    bak::k8_candidate_cameras<<<1, 1024, 0, s>>>(e->Nc, e->Ng, e->fi, e->d_cam_free.p, e->d_grp_free.p, e->d_pose.p, e->d_intr.p, yf,
+    KL(e), bak::k8_candidate_points<<<kNormBlocks, 256, 0, s>>>(e->V, e->d_pt.p, e->d_cpt.p, e->d_part0.p, e->d_part1.p);
+    KL(e), bak::k_reduce_partials<<<1, 1024, 0, s>>>(e->d_part0.p, kNormBlocks, &sc->step2_pt);
+    KL(e), bak::k_reduce_partials<<<1, 1024, 0, s>>>(e->d_part1.p, kNormBlocks, &sc->xn2_pt);
+    KL(e), bak::k8_candidate_cameras<<<1, 1024, 0, s>>>(e->Nc, e->Ng, e->fi, e->d_cam_free.p, e->d_grp_free.p, e->d_pose.p, e->d_intr.p, yf,
                                                  e->d_cpose.p, e->d_cintr.p, sc);
 }
 
@@ -500,21 +505,21 @@ void candidate_cost(ba_engine* e) {
     const bak::RobustParams rp{e->opt.robust_kind, e->opt.robust_a};
     CU_TRY(cudaMemsetAsync(&sc->bad_cand, 0, sizeof(int), s));
     { LaunchTimer t(e, KID_K0);
-      bak::k0_camera_precompute<<<cdiv(e->Nc, 128), 128, 0, s>>>(e->Nc, e->d_cpose.p, e->d_ccamrec.p, e->opt.taylor_rule); }
+      KL(e), bak::k0_camera_precompute<<<cdiv(e->Nc, 128), 128, 0, s>>>(e->Nc, e->d_cpose.p, e->d_ccamrec.p, e->opt.taylor_rule); }
     if (e->nTiles > 0) {
         LaunchTimer t(e, KID_K1C);
-        bak::k1c_candidate_cost<<<e->nTiles, bak::TILE_OBS, 0, s>>>(e->V, e->d_ccamrec.p, e->d_cintr.p, e->d_cpt.p, rp, e->d_part0.p, &sc->bad_cand);
+        KL(e), bak::k1c_candidate_cost<<<e->nTiles, bak::TILE_OBS, 0, s>>>(e->V, e->d_ccamrec.p, e->d_cintr.p, e->d_cpt.p, rp, e->d_part0.p, &sc->bad_cand);
     }
     { LaunchTimer t(e, KID_MISC);
-      bak::k_reduce_partials<<<1, 1024, 0, s>>>(e->d_part0.p, e->nTiles, &sc->ccost); }
+      KL(e), bak::k_reduce_partials<<<1, 1024, 0, s>>>(e->d_part0.p, e->nTiles, &sc->ccost); }
 }
 
 template <int MODE>
 void launch_sweep(ba_engine* e, int kid, const double* xin, double* yout, const int* done, double* partial) {
     if (e->nTiles == 0) return;
     LaunchTimer t(e, kid);
-    if (e->fi) bak::k_schur_sweep<MODE, true><<<e->nTiles, bak::TILE_OBS, 0, e->stream>>>(e->V, xin, yout, done, partial);
-    else bak::k_schur_sweep<MODE, false><<<e->nTiles, bak::TILE_OBS, 0, e->stream>>>(e->V, xin, yout, done, partial);
+    if (e->fi) KL(e), bak::k_schur_sweep<MODE, true><<<e->nTiles, bak::TILE_OBS, 0, e->stream>>>(e->V, xin, yout, done, partial);
+    else KL(e), bak::k_schur_sweep<MODE, false><<<e->nTiles, bak::TILE_OBS, 0, e->stream>>>(e->V, xin, yout, done, partial);
 }
 
 // Camera-side product F^T(...) by the configured scatter.  Result: in `yout` for mode 1 (L2 atomics), otherwise in the
@@ -525,7 +530,7 @@ void launch_pipe(ba_engine* e, const double* xin, const int* done, int* G_out) {
     static bool attr_set = false;
     if (!attr_set) { CU_TRY(cudaFuncSetAttribute(bak::k_schur_pipe<MODE, FI>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(Cfg::SMEM))); attr_set = true; }
     const int G = std::max(1, std::min(e->nTiles, e->num_sms * Cfg::CTAS_PER_SM));
-    bak::k_schur_pipe<MODE, FI><<<G, Cfg::THREADS, Cfg::SMEM, e->stream>>>(e->V, e->Sch, xin, done);
+    KL(e), bak::k_schur_pipe<MODE, FI><<<G, Cfg::THREADS, Cfg::SMEM, e->stream>>>(e->V, e->Sch, xin, done);
     *G_out = G;
 }
 
@@ -537,13 +542,13 @@ void launch_scatter(ba_engine* e, int kid, const double* xin, double* yout, cons
     LaunchTimer t(e, kid);
     if (e->scatter_mode == 4) {
         if (e->fi && e->Ng > 1) CU_TRY(cudaMemsetAsync(yout + 6 * e->Nc, 0, size_t(4) * e->Ng * sizeof(double), e->stream));
-        if (e->fi) bak::k_schur_rows<MODE, true><<<e->nTiles, bak::TILE_OBS, 0, e->stream>>>(e->V, e->RS, xin, yout, done);
-        else bak::k_schur_rows<MODE, false><<<e->nTiles, bak::TILE_OBS, 0, e->stream>>>(e->V, e->RS, xin, yout, done);
+        if (e->fi) KL(e), bak::k_schur_rows<MODE, true><<<e->nTiles, bak::TILE_OBS, 0, e->stream>>>(e->V, e->RS, xin, yout, done);
+        else KL(e), bak::k_schur_rows<MODE, false><<<e->nTiles, bak::TILE_OBS, 0, e->stream>>>(e->V, e->RS, xin, yout, done);
         return;
     }
     if (e->scatter_mode == 2) {
-        if (e->fi) bak::k_schur_scatter<MODE, true><<<e->Sch.G, bak::TILE_OBS, 0, e->stream>>>(e->V, e->Sch, xin, done);
-        else bak::k_schur_scatter<MODE, false><<<e->Sch.G, bak::TILE_OBS, 0, e->stream>>>(e->V, e->Sch, xin, done);
+        if (e->fi) KL(e), bak::k_schur_scatter<MODE, true><<<e->Sch.G, bak::TILE_OBS, 0, e->stream>>>(e->V, e->Sch, xin, done);
+        else KL(e), bak::k_schur_scatter<MODE, false><<<e->Sch.G, bak::TILE_OBS, 0, e->stream>>>(e->V, e->Sch, xin, done);
         *G_out = e->Sch.G;
     } else {
         if (e->fi) launch_pipe<MODE, true>(e, xin, done, G_out);
@@ -561,16 +566,16 @@ int solve_linear(ba_engine* e, double radius, double* rel_out) {
     const int vblocks = std::max(1, std::min(cdiv(e->nf, bak::PCG_BLOCK), 2 * e->num_sms));
     const int cblocks = std::max(1, cdiv(e->Nc + e->Ng, bak::PCG_BLOCK));
     CU_TRY(cudaMemsetAsync(&sc->bad_lin, 0, sizeof(int), s));
-    if (e->Np > 0) { LaunchTimer t(e, KID_K3P); bak::k3_point_blocks<<<cdiv(e->Np, 256), 256, 0, s>>>(e->V, lm, &sc->bad_lin); }
+    if (e->Np > 0) { LaunchTimer t(e, KID_K3P); KL(e), bak::k3_point_blocks<<<cdiv(e->Np, 256), 256, 0, s>>>(e->V, lm, &sc->bad_lin); }
     { LaunchTimer t(e, KID_K3C);
-      bak::k3_camera_blocks<<<cdiv(e->Nc + e->Ng, 128), 128, 0, s>>>(e->Nc, e->Ng, e->fi, e->Hcc(), e->Hii(), e->d_sc_f.p, lm, e->d_Df2.p, e->d_Minv.p, &sc->bad_lin); }
+      KL(e), bak::k3_camera_blocks<<<cdiv(e->Nc + e->Ng, 128), 128, 0, s>>>(e->Nc, e->Ng, e->fi, e->Hcc(), e->Hii(), e->d_sc_f.p, lm, e->d_Df2.p, e->d_Minv.p, &sc->bad_lin); }
     // Source of k_pcg_q's reduction: mode 2 sums the G private copies directly (and re-zeroes them); mode 3 first folds
     // them into kRedSlices slices with a wide grid (k_reduce_copies), the pipe kernel clears its own copy on entry.
     auto reduce_src = [&](int G, const int* done, double*& src, int& nsrc) {
         src = e->d_scratch.p; nsrc = G;
         if (e->scatter_mode == 3 && G > 0) {
             dim3 grid(cdiv(e->nf, 256), kRedSlices);
-            bak::k_reduce_copies<<<grid, 256, 0, s>>>(e->nf, G, e->Sch.ldf, e->d_scratch.p, kRedSlices, e->d_redpart.p, done);
+            KL(e), bak::k_reduce_copies<<<grid, 256, 0, s>>>(e->nf, G, e->Sch.ldf, e->d_scratch.p, kRedSlices, e->d_redpart.p, done);
             src = e->d_redpart.p; nsrc = kRedSlices;
         }
     };
@@ -581,14 +586,14 @@ int solve_linear(ba_engine* e, double radius, double* rel_out) {
     const bool rowsm = e->scatter_mode == 4;
     const int gblocks = e->Nc + 1;
     if (rowsm) { LaunchTimer t(e, KID_PCGV);
-        bak::k_camera_gather<<<gblocks, bak::GATHER_WARPS * 32, 0, s>>>(e->Nc, e->Ng, e->fi, e->nTiles, e->RS, nullptr, nullptr, e->d_b.p, nullptr, nullptr, 0);
+        KL(e), bak::k_camera_gather<<<gblocks, bak::GATHER_WARPS * 32, 0, s>>>(e->Nc, e->Ng, e->fi, e->nTiles, e->RS, nullptr, nullptr, e->d_b.p, nullptr, nullptr, 0);
     } else if (priv) { LaunchTimer t(e, KID_PCGV);
         double* src; int nsrc; reduce_src(G, nullptr, src, nsrc);
-        bak::k_pcg_q<<<vblocks, bak::PCG_BLOCK, 0, s>>>(e->nf, nsrc, e->Sch.ldf, src, nullptr, nullptr, e->d_b.p, nullptr, nullptr, 1, 0); }
+        KL(e), bak::k_pcg_q<<<vblocks, bak::PCG_BLOCK, 0, s>>>(e->nf, nsrc, e->Sch.ldf, src, nullptr, nullptr, e->d_b.p, nullptr, nullptr, 1, 0); }
     allreduce_sum(e, e->d_b.p, e->nf);
     const bak::PcgParams pp{e->opt.pcg_max_iterations, e->opt.pcg_forcing, e->opt.pcg_rel_tolerance, e->opt.eta};
     { LaunchTimer t(e, KID_PCGV);
-      bak::k_pcg_init2<<<1, 1024, 0, s>>>(e->nf, e->Nc, e->d_Minv.p, e->d_b.p, e->d_x.p, e->d_r.p, e->d_z.p, e->d_p.p, &sc->pcg); }
+      KL(e), bak::k_pcg_init2<<<1, 1024, 0, s>>>(e->nf, e->Nc, e->d_Minv.p, e->d_b.p, e->d_x.p, e->d_r.p, e->d_z.p, e->d_p.p, &sc->pcg); }
     if (e->scatter_mode == 1) e->d_y.zero(s);
     const int batch = 8;
     const bool multi = e->opt.world_size > 1;
@@ -599,24 +604,24 @@ int solve_linear(ba_engine* e, double radius, double* rel_out) {
             double* src = nullptr; int nsrc = 0;
             if (rowsm) {
                 if (multi) {
-                    bak::k_camera_gather<<<gblocks, bak::GATHER_WARPS * 32, 0, s>>>(e->Nc, e->Ng, e->fi, e->nTiles, e->RS, nullptr, nullptr, e->d_y.p, nullptr, nullptr, 0);
+                    KL(e), bak::k_camera_gather<<<gblocks, bak::GATHER_WARPS * 32, 0, s>>>(e->Nc, e->Ng, e->fi, e->nTiles, e->RS, nullptr, nullptr, e->d_y.p, nullptr, nullptr, 0);
                     allreduce_sum(e, e->d_y.p, e->nf);
-                    bak::k_pcg_q<<<vblocks, bak::PCG_BLOCK, 0, s>>>(e->nf, 0, e->Sch.ldf, nullptr, e->d_Df2.p, e->d_p.p, e->d_y.p, e->d_part1.p, &sc->pcg, 0, 1);
+                    KL(e), bak::k_pcg_q<<<vblocks, bak::PCG_BLOCK, 0, s>>>(e->nf, 0, e->Sch.ldf, nullptr, e->d_Df2.p, e->d_p.p, e->d_y.p, e->d_part1.p, &sc->pcg, 0, 1);
                 } else {
-                    bak::k_camera_gather<<<gblocks, bak::GATHER_WARPS * 32, 0, s>>>(e->Nc, e->Ng, e->fi, e->nTiles, e->RS, e->d_Df2.p, e->d_p.p, e->d_y.p, e->d_part1.p, &sc->pcg, 1);
+                    KL(e), bak::k_camera_gather<<<gblocks, bak::GATHER_WARPS * 32, 0, s>>>(e->Nc, e->Ng, e->fi, e->nTiles, e->RS, e->d_Df2.p, e->d_p.p, e->d_y.p, e->d_part1.p, &sc->pcg, 1);
                 }
             } else {
             if (priv) reduce_src(G, &sc->pcg.done, src, nsrc);
             if (multi) {   // reduce the private copies, all-reduce across ranks, then the dot product
-                if (priv) bak::k_pcg_q<<<vblocks, bak::PCG_BLOCK, 0, s>>>(e->nf, nsrc, e->Sch.ldf, src, nullptr, nullptr, e->d_y.p, nullptr, nullptr, 1, 0);
+                if (priv) KL(e), bak::k_pcg_q<<<vblocks, bak::PCG_BLOCK, 0, s>>>(e->nf, nsrc, e->Sch.ldf, src, nullptr, nullptr, e->d_y.p, nullptr, nullptr, 1, 0);
                 allreduce_sum(e, e->d_y.p, e->nf);
-                bak::k_pcg_q<<<vblocks, bak::PCG_BLOCK, 0, s>>>(e->nf, 0, e->Sch.ldf, nullptr, e->d_Df2.p, e->d_p.p, e->d_y.p, e->d_part1.p, &sc->pcg, 0, 1);
+                KL(e), bak::k_pcg_q<<<vblocks, bak::PCG_BLOCK, 0, s>>>(e->nf, 0, e->Sch.ldf, nullptr, e->d_Df2.p, e->d_p.p, e->d_y.p, e->d_part1.p, &sc->pcg, 0, 1);
             } else {
-                bak::k_pcg_q<<<vblocks, bak::PCG_BLOCK, 0, s>>>(e->nf, nsrc, e->Sch.ldf, src, e->d_Df2.p, e->d_p.p, e->d_y.p, e->d_part1.p, &sc->pcg, priv ? 1 : 0, 1);
+                KL(e), bak::k_pcg_q<<<vblocks, bak::PCG_BLOCK, 0, s>>>(e->nf, nsrc, e->Sch.ldf, src, e->d_Df2.p, e->d_p.p, e->d_y.p, e->d_part1.p, &sc->pcg, priv ? 1 : 0, 1);
             }
             }
-            bak::k_pcg_xr<<<cblocks, bak::PCG_BLOCK, 0, s>>>(e->Nc, e->Ng, e->fi, e->d_Minv.p, e->d_b.p, e->d_y.p, e->d_p.p, e->d_x.p, e->d_r.p, e->d_z.p, e->d_part1.p, &sc->pcg, pp);
-            bak::k_pcg_p<<<vblocks, bak::PCG_BLOCK, 0, s>>>(e->nf, e->d_z.p, e->d_p.p, &sc->pcg);
+            KL(e), bak::k_pcg_xr<<<cblocks, bak::PCG_BLOCK, 0, s>>>(e->Nc, e->Ng, e->fi, e->d_Minv.p, e->d_b.p, e->d_y.p, e->d_p.p, e->d_x.p, e->d_r.p, e->d_z.p, e->d_part1.p, &sc->pcg, pp);
+            KL(e), bak::k_pcg_p<<<vblocks, bak::PCG_BLOCK, 0, s>>>(e->nf, e->d_z.p, e->d_p.p, &sc->pcg);
             if (e->scatter_mode == 1) e->d_y.zero(s);
         }
         read_scalars(e);
@@ -627,7 +632,7 @@ int solve_linear(ba_engine* e, double radius, double* rel_out) {
     // back-substitution and model cost change
     launch_sweep<bak::SWEEP_BACKSUB>(e, KID_K7, e->d_x.p, nullptr, nullptr, e->d_part0.p);
     { LaunchTimer t(e, KID_MISC);
-      bak::k_reduce_partials<<<1, 1024, 0, s>>>(e->d_part0.p, e->nTiles, &sc->mcc); }
+      KL(e), bak::k_reduce_partials<<<1, 1024, 0, s>>>(e->d_part0.p, e->nTiles, &sc->mcc); }
     return e->h_scal->pcg.k;
 }
 
@@ -649,6 +654,7 @@ void lm_solve(ba_engine* e) {
     std::memset(&S, 0, sizeof S);
     S.num_residuals = 2 * e->NoG;
     e->traj.clear();
+    e->kernel_launches = 0;
     CU_TRY(cudaEventRecord(e->ev_t0, s));
     auto finish = [&](int term, const char* msg, double cost) {
         S.termination = term; S.usable = (term != BA_TERM_FAILURE); S.final_cost = cost; S.num_iterations = int(e->traj.size());
@@ -658,6 +664,7 @@ void lm_solve(ba_engine* e) {
         float ms = 0.f;
         CU_TRY(cudaEventElapsedTime(&ms, e->ev_t0, e->ev_t1));
         S.solve_seconds = ms * 1e-3;
+        S.kernel_launches = e->kernel_launches;
         resolve_timers(e);
     };
 
@@ -666,8 +673,8 @@ void lm_solve(ba_engine* e) {
     evaluate_full(e);
     {   // s_j = 1/(1 + sqrt(H_jj)) from the iteration-0 diagonals, frozen for the solve
         LaunchTimer t(e, KID_MISC);
-        if (e->Np > 0) bak::k_scales_points<<<cdiv(3 * e->Np, 256), 256, 0, s>>>(e->V, O.jacobi_scaling);
-        bak::k_scales_cameras<<<cdiv(e->nf, 256), 256, 0, s>>>(e->Nc, e->Ng, e->fi, e->Hcc(), e->Hii(), e->d_sc_f.p, O.jacobi_scaling);
+        if (e->Np > 0) KL(e), bak::k_scales_points<<<cdiv(3 * e->Np, 256), 256, 0, s>>>(e->V, O.jacobi_scaling);
+        KL(e), bak::k_scales_cameras<<<cdiv(e->nf, 256), 256, 0, s>>>(e->Nc, e->Ng, e->fi, e->Hcc(), e->Hii(), e->d_sc_f.p, O.jacobi_scaling);
     }
     gradient_max(e);
     make_candidate(e, e->d_x.p);   // y = 0: gives ||x|| of the free parameters
@@ -861,8 +868,9 @@ int ba_get_state(ba_engine* e, double* pose, double* intr, double* pt) {
     return guarded(e, [&] {
         CU_TRY(cudaSetDevice(e->device));
         cudaStream_t s = e->stream;
-        if (pose) CU_TRY(cudaMemcpyAsync(pose, e->d_pose.p, size_t(6) * e->Nc * sizeof(double), cudaMemcpyDeviceToHost, s));
-        if (intr) CU_TRY(cudaMemcpyAsync(intr, e->d_intr.p, size_t(4) * e->Ng * sizeof(double), cudaMemcpyDeviceToHost, s));
+        if (pose) { CU_TRY(cudaMemcpyAsync(pose, e->d_pose.p, size_t(6) * e->Nc * sizeof(double), cudaMemcpyDeviceToHost, s)); g_d2h_bytes += int64_t(48) * e->Nc; }
+        if (intr) { CU_TRY(cudaMemcpyAsync(intr, e->d_intr.p, size_t(4) * e->Ng * sizeof(double), cudaMemcpyDeviceToHost, s)); g_d2h_bytes += int64_t(32) * e->Ng; }
+        if (pt) g_d2h_bytes += int64_t(24) * e->NpG;
         if (pt) {
             if (e->opt.world_size == 1) CU_TRY(cudaMemcpyAsync(pt, e->d_pt.p, size_t(3) * e->Np * sizeof(double), cudaMemcpyDeviceToHost, s));
             else {   // every rank ends with the full point array: one broadcast per shard (collective: all ranks must call)
@@ -956,7 +964,8 @@ int ba_evaluate(ba_engine* e, double* cost, double* r, double* Jc, double* Jp, d
 
 int ba_set_profiling(ba_engine* e, int32_t enabled) {
     if (!e) return BA_ERR_INVALID_ARGUMENT;
-    e->profiling = enabled != 0;
+    e->profiling = enabled < 0 ? 0xffffffffu : unsigned(enabled);   // bit mask of kernel ids (ba_kernel_stat order); 1 keeps meaning "all" for convenience
+    if (enabled == 1) e->profiling = 0xffffffffu;
     for (auto& st : e->stats) { st.launches = 0; st.ms = 0.0; }
     return BA_OK;
 }
@@ -983,6 +992,7 @@ int ba_nccl_unique_id(void* out128) {
     return BA_OK;
 }
 
+int ba_get_io_bytes(int64_t* h2d, int64_t* d2h) { if (h2d) *h2d = g_h2d_bytes; if (d2h) *d2h = g_d2h_bytes; return BA_OK; }
 const char* ba_last_error(const ba_engine* e) { return e ? e->err.c_str() : g_create_error.c_str(); }
 const char* ba_backend(void) { return "cuda-sm100a"; }
 

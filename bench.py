@@ -1,0 +1,284 @@
+#!/usr/bin/env python
+"""bench.py — Venice-shape bundle adjustment: LM iterations/s, time-to-converge and HBM roofline fraction on B200.
+
+    python bench.py --gpus N --steps K --warmup W            # our arm (CUDA engine); N>1 is launched by torchrun
+    python bench.py --impl reference --gpus N --steps K --warmup W   # the reference's CPU solver path (oracle port) on host cores
+
+One "step" = one full BA solve (Levenberg-Marquardt from the same initial guess to termination with the reference's
+Ceres options) of the Venice-shape synthetic problem (1778 cameras, 993 923 points, 5 001 946 observations).
+`value` = LM iterations per second with the problem resident in HBM when the timed region starts;
+`e2e`   = the same metric through the C-ABI with HOST buffers: ba_set_problem (H2D) + ba_solve + ba_get_state (D2H) every step.
+The CPU oracle (oracle/) is used here only for the `cpu_baseline` leg and for `--impl reference`.
+"""
+import argparse
+import importlib
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "LM iterations/sec and time-to-converge (Venice-shape BA), % HBM roofline"
+UNIT = "LM iterations/s"
+KID_K5 = 7  # index of K5_schur_matvec in ba_get_kernel_stats
+
+
+def load_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+    Q = "index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200", "-i", str(self.index)],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[1])); mx.append(float(r[2]))
+            except (ValueError, IndexError):
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def solver_options(args):
+    """The reference's configuration (Ceres defaults + BundleAdjuster.h:167-174) with the north star's 2x6/2x3 problem form."""
+    return dict(intrinsics_free=0, robust_kind=1, robust_a=4.0, max_num_iterations=args.max_lm_iterations,
+                pcg_rel_tolerance=args.pcg_tol, pcg_max_iterations=2000)
+
+
+def workload_name(P, args):
+    Nc, Ng, Np, No = P.sizes
+    return f"{args.workload}-shape synthetic BA: {Nc} cameras, {Np} points, {No} observations, pinhole, intrinsics fixed, Huber(4)"
+
+
+def cpu_solve_sample(ba, P, args, lm_iterations, threads):
+    """Time the CPU oracle (port of the reference's solver path) on a bounded sample: the first `lm_iterations` LM iterations."""
+    orc = ba.Library(os.path.join(ROOT, "oracle", "libba_oracle.so"))
+    opts = solver_options(args)
+    opts.update(max_num_iterations=lm_iterations, num_threads=threads, linear_solver=args.cpu_linear_solver)
+    with orc.create(orc.default_options(**opts)) as h:
+        h.set_problem(P)
+        t0 = time.perf_counter()
+        s = h.solve()
+        dt = time.perf_counter() - t0
+    its = max(s.num_iterations - 1, 1)
+    return its, dt, s
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the reference's CPU solver path (oracle port; Ceres itself cannot be built here) on all host threads."""
+    if rank != 0:
+        return
+    ba = importlib.import_module("3dreconstruction_b200")
+    P = ba.synth(args.workload)
+    threads = os.cpu_count() or 1
+    times, its_total = [], 0
+    for i in range(args.warmup + args.steps):
+        its, dt, s = cpu_solve_sample(ba, P, args, args.cpu_lm_iterations, threads)
+        if i >= args.warmup:
+            times.append(dt); its_total += its
+    total = sum(times)
+    value = its_total / total
+    sample = (f"first {args.cpu_lm_iterations} LM iteration(s) of the {args.workload} solve per step "
+              f"({'exact dense Cholesky on S' if args.cpu_linear_solver == 0 else 'block-Jacobi PCG on the implicit Schur complement, rel tol %g' % args.pcg_tol}), OpenMP")
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": 1e3 * total / max(len(times), 1), "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic", "config": {"workload": workload_name(P, args), "step": sample},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def pinned_problem(ba, P):
+    """Host copies of the inputs in page-locked memory (what the e2e leg uploads every step)."""
+    import torch
+    def pin(a):
+        return torch.from_numpy(a).pin_memory().numpy()
+    return ba.Problem(pose=pin(P.pose), intr=pin(P.intr), cam_group=pin(P.cam_group), cam_fixed=pin(P.cam_fixed), pt=pin(P.pt),
+                      obs_cam=pin(P.obs_cam), obs_pt=pin(P.obs_pt), obs_uv=pin(P.obs_uv))
+
+
+def run_ours(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    ba = importlib.import_module("3dreconstruction_b200")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    lib = ba.engine_library()   # raises if the CUDA extension is missing: no fallback
+    nccl_id = None
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+        idt = torch.zeros(128, dtype=torch.uint8, device=dev)
+        if rank == 0:
+            idt.copy_(torch.frombuffer(bytearray(lib.nccl_unique_id()), dtype=torch.uint8))
+        dist.broadcast(idt, 0)
+        nccl_id = bytes(idt.cpu().numpy().tobytes())
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    P = ba.synth(args.workload)
+    Ph = pinned_problem(ba, P)
+    stream = torch.cuda.current_stream()
+    import ctypes
+    idbuf = ctypes.create_string_buffer(nccl_id, 128) if nccl_id else None
+    opts = solver_options(args)
+    opts.update(device=local_rank, rank=rank, world_size=world, stream=ctypes.c_void_p(stream.cuda_stream),
+                nccl_unique_id=ctypes.cast(idbuf, ctypes.c_void_p) if idbuf else None)
+    eng = lib.create(lib.default_options(**opts))
+    eng.set_problem(Ph)
+    summaries = []
+    for _ in range(args.warmup):
+        eng.reset_state()
+        summaries.append(eng.solve())
+
+    # ---- timed region 1: inputs resident in HBM ----
+    sampler = ClockSampler(local_rank)
+    eng.set_profiling(1 << KID_K5)     # CUDA events around the dominant kernel only
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    if rank == 0:
+        sampler.start()
+    ev0.record(stream)
+    lm_its = pcg_its = launches = 0
+    for _ in range(args.steps):
+        eng.reset_state()
+        s = eng.solve()
+        lm_its += s.num_iterations - 1; pcg_its += s.total_pcg_iterations; launches += s.kernel_launches
+    ev1.record(stream)
+    barrier()
+    t_dev = max_over_ranks(ev0.elapsed_time(ev1) * 1e-3)
+    clocks = sampler.stop() if rank == 0 else None
+    stats = {k["name"]: k for k in eng.kernel_stats()}
+    eng.set_profiling(0)
+    final = s
+    traj = eng.trajectory()
+
+    # ---- timed region 2: end to end through the C-ABI with host buffers ----
+    h2d0, d2h0 = lib.io_bytes()
+    barrier()
+    t0 = time.perf_counter()
+    e2e_its = 0
+    for _ in range(args.steps):
+        eng.set_problem(Ph)            # host -> device: parameters, observations and the index structure built from them
+        s2 = eng.solve()
+        pose, intr, pt = eng.get_state()   # device -> host: the write-back the adapter needs
+        e2e_its += s2.num_iterations - 1
+    barrier()
+    t_e2e = max_over_ranks(time.perf_counter() - t0)
+    h2d1, d2h1 = lib.io_bytes()
+
+    if rank == 0:
+        peak_gbs, peak_src = load_peaks()
+        k5 = stats["K5_schur_matvec"]
+        k5_avg_s = (k5["total_ms"] / max(k5["launches"], 1)) * 1e-3
+        achieved = k5["bytes_per_launch"] / k5_avg_s / 1e9 if k5_avg_s > 0 else 0.0
+        traffic = None
+        tpath = os.path.join(ROOT, "profiles", "k5_dram_bytes_per_launch.json")
+        if os.path.exists(tpath) and world == 1:
+            with open(tpath) as f:
+                traffic = json.load(f).get("dram_bytes_per_launch")
+        line = {
+            "metric": METRIC, "value": lm_its / t_dev, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": 1e3 * t_dev / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic",
+            "config": {"workload": workload_name(P, args),
+                       "step": "one full BA solve: LM with the reference's Ceres options (max 50 iterations, tolerances 1e-6/1e-8/1e-10), "
+                               f"PCG on the implicit Schur complement to rel. residual {args.pcg_tol:g} (trajectory-parity mode)",
+                       "l2": "inputs larger than L2 (J = 720 MB per sweep vs 126 MB L2)",
+                       "parallelism": f"points sharded over {world} GPU(s), camera-side vectors all-reduced with NCCL" if world > 1 else "single GPU"},
+            "e2e": {"value": e2e_its / t_e2e, "unit": UNIT, "h2d_bytes_per_step": (h2d1 - h2d0) // args.steps, "d2h_bytes_per_step": (d2h1 - d2h0) // args.steps,
+                    "ms_per_step": 1e3 * t_e2e / args.steps},
+            "gpu_launches": int(launches),
+            "clocks": clocks,
+            "roofline": {"bound": "hbm", "kernel": "K5_schur_matvec (k_schur_rows, one PCG iteration's J sweep)", "achieved": achieved, "peak": peak_gbs,
+                         "unit": "GB/s", "frac": achieved / peak_gbs, "traffic": traffic, "peak_source": peak_src,
+                         "bytes_per_launch": k5["bytes_per_launch"], "launches": k5["launches"], "avg_us": k5_avg_s * 1e6},
+            "solve": {"lm_iterations_per_step": lm_its / args.steps, "pcg_iterations_per_step": pcg_its / args.steps, "time_to_converge_s": t_dev / args.steps,
+                      "termination": final.message.decode(), "initial_chi2": 2 * final.initial_cost, "final_chi2": 2 * final.final_cost},
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            threads = os.cpu_count() or 1
+            its, dt, so = cpu_solve_sample(ba, P, args, args.cpu_lm_iterations, threads)
+            ok = abs(so.final_cost - traj[its].cost) <= 1e-6 * abs(so.final_cost) if len(traj) > its else None
+            line["cpu_baseline"] = {"value": its / dt, "unit": UNIT, "cores": threads, "kind": "port",
+                                    "sample": f"first {its} LM iteration(s) of the same solve on the CPU oracle "
+                                              f"({'exact dense Cholesky' if args.cpu_linear_solver == 0 else 'PCG rel tol %g' % args.pcg_tol}), {dt:.1f} s",
+                                    "chi2_matches_gpu_trajectory": ok}
+        print(json.dumps(line), flush=True)
+    eng.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="venice")
+    ap.add_argument("--max-lm-iterations", type=int, default=50)
+    ap.add_argument("--pcg-tol", type=float, default=1e-12)
+    ap.add_argument("--cpu-lm-iterations", type=int, default=1)
+    ap.add_argument("--cpu-linear-solver", type=int, default=1, help="0 exact dense Cholesky (the reference's SPARSE_SCHUR semantics), 1 PCG")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank, world, local_rank = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+    if world != args.gpus and not (world == 1 and args.gpus == 1):
+        print(f"warning: --gpus {args.gpus} but WORLD_SIZE={world}; launch with torchrun for multi-GPU", file=sys.stderr)
+    run_ours(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

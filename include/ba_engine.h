@@ -143,6 +143,7 @@ typedef struct ba_summary {
     double  initial_cost;      /* cost = 1/2 sum rho(||r||^2); chi2 = 2*cost */
     double  final_cost;
     double  solve_seconds;     /* engine: device time of ba_solve from CUDA events on its stream; oracle: wall clock */
+    int64_t kernel_launches;   /* engine: CUDA kernels launched by this ba_solve; oracle: 0 */
     char    message[160];
 } ba_summary;
 
@@ -187,8 +188,9 @@ int  ba_get_structure(ba_engine* e, int32_t* perm_by_cam, int32_t* cam_off, int3
  * Jacobian blocks Jc[No][2][6], Jp[No][2][3], Ji[No][2][4] (robustified, NOT column-scaled), gradient
  * g[6Nc+4Ng+3Np] (pose, intrinsics, point order).  Any output may be NULL. For the K1/K2 parity tests. */
 int  ba_evaluate(ba_engine* e, double* cost, double* r, double* Jc, double* Jp, double* Ji, double* g);
-int  ba_set_profiling(ba_engine* e, int32_t enabled);          /* per-kernel CUDA-event timing on/off (off by default) */
+int  ba_set_profiling(ba_engine* e, int32_t mask);             /* per-kernel CUDA-event timing: 0 off (default), 1 or -1 all kernels, else bit k = kernel k of ba_get_kernel_stats */
 int  ba_get_kernel_stats(ba_engine* e, ba_kernel_stat* out, int32_t cap, int32_t* n);
+int  ba_get_io_bytes(int64_t* h2d, int64_t* d2h);              /* cumulative host->device / device->host bytes moved by this library in this process */
 int  ba_nccl_unique_id(void* out128);                          /* rank 0 only; engine library only */
 const char* ba_last_error(const ba_engine* e);                /* e may be NULL: last error of a failed ba_create on this thread */
 const char* ba_backend(void);                                 /* "cuda-sm100a" or "cpu-oracle" */
