@@ -101,6 +101,16 @@ class Library:
             raise BAError(f"ba_nccl_unique_id failed ({rc}): {self.lib.ba_last_error(None).decode()}")
         return buf.raw
 
+    def shard_points(self, obs_pt, num_points, world_size):
+        """Point ranges [shard_pt[r], shard_pt[r+1]) of the multi-GPU sharding (host-only; needs no device)."""
+        obs_pt = _as(obs_pt, np.int32)
+        out = np.zeros(world_size + 1, np.int32)
+        rc = self.lib.ba_shard_points(int(num_points), int(obs_pt.size), obs_pt.ctypes.data_as(_capi.c_int32_p), int(world_size),
+                                      out.ctypes.data_as(_capi.c_int32_p))
+        if rc != 0:
+            raise BAError(f"ba_shard_points failed ({rc})")
+        return out
+
     def default_options(self, **kw):
         o = BAOptions()
         rc = self.lib.ba_options_default(C.byref(o))

@@ -235,6 +235,18 @@ void build_tiles(const vector<int32_t>& pt_off, int Np, vector<int32_t>& tile_of
     if (tile_off.back() != pt_off[Np]) tile_off.push_back(pt_off[Np]);
 }
 
+// Point ranges of the W shards from the global CSR-by-point offsets: rank r starts at the first point whose first
+// observation is >= r*No/W (ba_shard_points).
+void shard_points(const vector<int32_t>& gpt_off, int NpG, int NoG, int W, vector<int32_t>& shard_pt) {
+    shard_pt.assign(size_t(W) + 1, 0);
+    shard_pt[W] = NpG;
+    for (int r = 1; r < W; ++r) {
+        const int64_t target = int64_t(NoG) * r / W;
+        const int p = int(std::lower_bound(gpt_off.begin(), gpt_off.end(), int32_t(target)) - gpt_off.begin());
+        shard_pt[r] = std::min(std::max(p, shard_pt[r - 1]), NpG);
+    }
+}
+
 void do_set_problem(ba_engine* e, const ba_problem* P) {
     const int Nc = P->num_cameras, Ng = P->num_groups, NpG = P->num_points, NoG = P->num_observations;
     const int W = e->opt.world_size, R = e->opt.rank;
@@ -260,13 +272,7 @@ void do_set_problem(ba_engine* e, const ba_problem* P) {
     }
 
     // shard: contiguous point ranges balanced by observation count, cut at point boundaries
-    e->h_shard_pt.assign(W + 1, 0);
-    e->h_shard_pt[W] = NpG;
-    for (int r = 1; r < W; ++r) {
-        const int64_t target = int64_t(NoG) * r / W;
-        int p = int(std::lower_bound(gpt_off.begin(), gpt_off.end(), int32_t(target)) - gpt_off.begin());
-        e->h_shard_pt[r] = std::min(std::max(p, e->h_shard_pt[r - 1]), NpG);
-    }
+    shard_points(gpt_off, NpG, NoG, W, e->h_shard_pt);
     e->pb = e->h_shard_pt[R]; e->pe = e->h_shard_pt[R + 1];
     e->ob = gpt_off[e->pb]; e->oe = gpt_off[e->pe];
     const int Np = e->pe - e->pb, No = e->oe - e->ob;
@@ -978,6 +984,19 @@ int ba_get_kernel_stats(ba_engine* e, ba_kernel_stat* out, int32_t cap, int32_t*
         std::snprintf(out[i].name, sizeof out[i].name, "%s", kKernelNames[i]);
         out[i].launches = e->stats[i].launches; out[i].total_ms = e->stats[i].ms; out[i].bytes_per_launch = e->stats[i].bytes;
     }
+    return BA_OK;
+}
+
+int ba_shard_points(int32_t num_points, int32_t num_observations, const int32_t* obs_pt, int32_t world_size, int32_t* shard_pt) {
+    if (num_points < 0 || num_observations < 0 || world_size < 1 || !shard_pt || (num_observations && !obs_pt)) return BA_ERR_INVALID_ARGUMENT;
+    vector<int32_t> off(size_t(num_points) + 1, 0), sp;
+    for (int o = 0; o < num_observations; ++o) {
+        if (obs_pt[o] < 0 || obs_pt[o] >= num_points || (o && obs_pt[o] < obs_pt[o - 1])) return BA_ERR_INVALID_ARGUMENT;
+        ++off[obs_pt[o] + 1];
+    }
+    for (int p = 0; p < num_points; ++p) off[p + 1] += off[p];
+    shard_points(off, num_points, num_observations, world_size, sp);
+    std::copy(sp.begin(), sp.end(), shard_pt);
     return BA_OK;
 }
 

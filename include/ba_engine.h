@@ -191,6 +191,10 @@ int  ba_evaluate(ba_engine* e, double* cost, double* r, double* Jc, double* Jp, 
 int  ba_set_profiling(ba_engine* e, int32_t mask);             /* per-kernel CUDA-event timing: 0 off (default), 1 or -1 all kernels, else bit k = kernel k of ba_get_kernel_stats */
 int  ba_get_kernel_stats(ba_engine* e, ba_kernel_stat* out, int32_t cap, int32_t* n);
 int  ba_get_io_bytes(int64_t* h2d, int64_t* d2h);              /* cumulative host->device / device->host bytes moved by this library in this process */
+/* Host-only (no device needed): the point ranges of the multi-GPU sharding. Rank r owns points
+ * [shard_pt[r], shard_pt[r+1]) and all their observations; ranges are contiguous, cut at point boundaries and
+ * balanced by observation count.  obs_pt[No] non-decreasing; shard_pt has world_size+1 entries. */
+int  ba_shard_points(int32_t num_points, int32_t num_observations, const int32_t* obs_pt, int32_t world_size, int32_t* shard_pt);
 int  ba_nccl_unique_id(void* out128);                          /* rank 0 only; engine library only */
 const char* ba_last_error(const ba_engine* e);                /* e may be NULL: last error of a failed ba_create on this thread */
 const char* ba_backend(void);                                 /* "cuda-sm100a" or "cpu-oracle" */

@@ -740,6 +740,7 @@ int ba_evaluate(ba_engine* e, double* cost, double* r, double* Jc, double* Jp, d
 
 int ba_set_profiling(ba_engine* e, int32_t) { return e ? BA_OK : BA_ERR_INVALID_ARGUMENT; }
 int ba_get_kernel_stats(ba_engine* e, ba_kernel_stat*, int32_t, int32_t* n) { if (!e || !n) return BA_ERR_INVALID_ARGUMENT; *n = 0; return BA_OK; }
+int ba_shard_points(int32_t, int32_t, const int32_t*, int32_t, int32_t*) { return BA_ERR_UNSUPPORTED; }   // engine-side host logic; the oracle is single-process
 int ba_nccl_unique_id(void*) { return BA_ERR_UNSUPPORTED; }
 int ba_get_io_bytes(int64_t* h2d, int64_t* d2h) { if (h2d) *h2d = 0; if (d2h) *d2h = 0; return BA_OK; }
 const char* ba_last_error(const ba_engine* e) { return e ? e->err.c_str() : g_create_error.c_str(); }
