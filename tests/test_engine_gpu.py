@@ -171,3 +171,19 @@ def test_evaluation_failure_is_reported(ba):
         eng.set_problem(P)
         s = eng.solve()
     assert s.termination == 2 and not s.usable
+
+
+def test_multi_gpu_matches_single_gpu():
+    """Sharded NCCL solve == single-GPU solve (needs >= 2 GPUs on the box; skipped otherwise). tools/multi_gpu_check.py under torchrun."""
+    import os
+    import subprocess
+    import sys
+    import torch
+    n = torch.cuda.device_count()
+    if n < 2:
+        pytest.skip("needs at least 2 GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+                        "--master-port", "29517", os.path.join(root, "tools", "multi_gpu_check.py"), "ladybug"], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert "MISMATCH" not in r.stdout and "OK" in r.stdout
