@@ -47,7 +47,7 @@ def check_trajectories(ba, make_handle, rtol):
         d = np.load(f)
         P = ba.synth(name)
         assert int(P.obs_cam.astype(np.int64).sum() * 31 + P.obs_pt.astype(np.int64).sum()) == int(d["obs_checksum"])   # generator is bit-stable
-        with make_handle(intrinsics_free=fi) as h:
+        with make_handle(intrinsics_free=fi, max_num_iterations=15) as h:
             h.set_problem(P)
             s = h.solve()
             t = h.trajectory()
