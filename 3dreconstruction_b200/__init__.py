@@ -18,7 +18,8 @@ from . import _capi
 from ._capi import (BAIterRecord, BAKernelStat, BAOptions, BAProblem, BASummary, SynthProblem, SynthSpec)  # noqa: F401
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-ENGINE_LIB = os.path.join(_HERE, "csrc", "libba_engine.so")
+# BA_ENGINE_LIB selects another build of the SAME CUDA engine (kernel-tuning experiments: csrc/libba_engine_<variant>.so)
+ENGINE_LIB = os.environ.get("BA_ENGINE_LIB") or os.path.join(_HERE, "csrc", "libba_engine.so")
 SYNTH_LIB = os.path.join(_HERE, "host", "libba_synth.so")
 
 

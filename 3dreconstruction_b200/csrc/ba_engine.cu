@@ -17,6 +17,7 @@
 #include <cfloat>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
 #include <string>
@@ -26,6 +27,7 @@
 #include "ba_scatter.cuh"
 #include "ba_pipe.cuh"
 #include "ba_rows.cuh"
+#include "ba_rows_pipe.cuh"
 
 namespace {
 using std::vector;
@@ -152,7 +154,7 @@ struct ba_engine {
     DevBuf<int> d_cam_row_off, d_cam_rows;
     DevBuf<double> d_rows, d_tile_intr;
     bak::RowSched RS{};
-    int scatter_mode = 4;              // 1 = red.global atomics, 2 = private accumulators, 3 = 2 + bulk-copy pipeline, 4 = partial rows (default)
+    int scatter_mode = 4;              // 1 = red.global atomics, 2 = private accumulators, 3 = 2 + bulk-copy pipeline, 4 = partial rows (default), 5 = 4 as a persistent cp.async pipeline
     int num_sms = 148;
     DevBuf<bak::Scalars> d_scal;
     bak::Scalars* h_scal = nullptr;    // pinned
@@ -433,7 +435,7 @@ void do_set_problem(ba_engine* e, const ba_problem* P) {
     e->stats[KID_K8].bytes = np * 72 + nc * 144;
     e->stats[KID_PCGV].bytes = double(e->nf) * 8 * (14 + e->Sch.G * 2) + 288 * nc;
     e->stats[KID_MISC].bytes = 0;
-    if (e->scatter_mode == 4) {   // partial-row formulation: + 7 B/obs of schedule, 64 B written per (tile, camera) row, read back by the gather
+    if (e->scatter_mode >= 4) {   // partial-row formulation: + 7 B/obs of schedule, 64 B written per (tile, camera) row, read back by the gather
         const double nr = e->RS.nRows;
         e->stats[KID_K4].bytes = no * (jb + 16 + 16) + np * 24 + 64 * nr + 16.0 * e->nTiles;
         e->stats[KID_K5].bytes = no * (jb + 16) + np * 48 + 48 * nc + 64 * nr + 16.0 * e->nTiles;
@@ -499,10 +501,8 @@ void make_candidate(ba_engine* e, const double* yf) {
     bak::Scalars* sc = e->d_scal.p;
     LaunchTimer t(e, KID_K8);
     KL(e), bak::k8_candidate_points<<<kNormBlocks, 256, 0, s>>>(e->V, e->d_pt.p, e->d_cpt.p, e->d_part0.p, e->d_part1.p);
-    KL(e), bak::k_reduce_partials<<<1, 1024, 0, s>>>(e->d_part0.p, kNormBlocks, &sc->step2_pt);
-    KL(e), bak::k_reduce_partials<<<1, 1024, 0, s>>>(e->d_part1.p, kNormBlocks, &sc->xn2_pt);
     KL(e), bak::k8_candidate_cameras<<<1, 1024, 0, s>>>(e->Nc, e->Ng, e->fi, e->d_cam_free.p, e->d_grp_free.p, e->d_pose.p, e->d_intr.p, yf,
-                                                 e->d_cpose.p, e->d_cintr.p, sc);
+                                                 e->d_cpose.p, e->d_cintr.p, e->d_part0.p, e->d_part1.p, kNormBlocks, sc);
 }
 
 void candidate_cost(ba_engine* e) {
@@ -540,12 +540,28 @@ void launch_pipe(ba_engine* e, const double* xin, const int* done, int* G_out) {
     *G_out = G;
 }
 
+// Persistent software-pipelined K4/K5a (ba_rows_pipe.cuh): G = CTAs that are co-resident, each walking tiles b, b+G, ...
+template <int MODE, bool FI>
+void launch_rows_pipe(ba_engine* e, const double* xin, double* yout, const int* done) {
+    using Cfg = bak::RowsPipeCfg<MODE, FI>;
+    static bool attr_set = false;
+    if (!attr_set) { CU_TRY(cudaFuncSetAttribute(bak::k_schur_rows_pipe<MODE, FI>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(Cfg::SMEM))); attr_set = true; }
+    const int G = std::max(1, std::min(e->nTiles, e->num_sms * Cfg::CTAS_PER_SM));
+    KL(e), bak::k_schur_rows_pipe<MODE, FI><<<G, bak::TILE_OBS, Cfg::SMEM, e->stream>>>(e->V, e->RS, xin, yout, done);
+}
+
 template <int MODE>
 void launch_scatter(ba_engine* e, int kid, const double* xin, double* yout, const int* done, int* G_out) {
     *G_out = 0;
     if (e->nTiles == 0) return;
     if (e->scatter_mode == 1) { launch_sweep<MODE>(e, kid, xin, yout, done, nullptr); return; }
     LaunchTimer t(e, kid);
+    if (e->scatter_mode == 5) {
+        if (e->fi && e->Ng > 1) CU_TRY(cudaMemsetAsync(yout + 6 * e->Nc, 0, size_t(4) * e->Ng * sizeof(double), e->stream));
+        if (e->fi) launch_rows_pipe<MODE, true>(e, xin, yout, done);
+        else launch_rows_pipe<MODE, false>(e, xin, yout, done);
+        return;
+    }
     if (e->scatter_mode == 4) {
         if (e->fi && e->Ng > 1) CU_TRY(cudaMemsetAsync(yout + 6 * e->Nc, 0, size_t(4) * e->Ng * sizeof(double), e->stream));
         if (e->fi) KL(e), bak::k_schur_rows<MODE, true><<<e->nTiles, bak::TILE_OBS, 0, e->stream>>>(e->V, e->RS, xin, yout, done);
@@ -570,7 +586,7 @@ int solve_linear(ba_engine* e, double radius, double* rel_out) {
     const bak::LmParams lm{radius, e->opt.min_lm_diagonal, e->opt.max_lm_diagonal};
     const bool priv = e->scatter_mode == 2 || e->scatter_mode == 3;
     const int vblocks = std::max(1, std::min(cdiv(e->nf, bak::PCG_BLOCK), 2 * e->num_sms));
-    const int cblocks = std::max(1, cdiv(e->Nc + e->Ng, bak::PCG_BLOCK));
+    const int cblocks = std::max(1, cdiv((e->Nc + e->Ng) * 8, bak::PCG_BLOCK));
     CU_TRY(cudaMemsetAsync(&sc->bad_lin, 0, sizeof(int), s));
     if (e->Np > 0) { LaunchTimer t(e, KID_K3P); KL(e), bak::k3_point_blocks<<<cdiv(e->Np, 256), 256, 0, s>>>(e->V, lm, &sc->bad_lin); }
     { LaunchTimer t(e, KID_K3C);
@@ -589,7 +605,7 @@ int solve_linear(ba_engine* e, double radius, double* rel_out) {
     if (e->scatter_mode == 1) e->d_b.zero(s);
     int G = 0;
     launch_scatter<bak::SWEEP_RHS>(e, KID_K4, nullptr, e->d_b.p, nullptr, &G);
-    const bool rowsm = e->scatter_mode == 4;
+    const bool rowsm = e->scatter_mode >= 4;
     const int gblocks = e->Nc + 1;
     if (rowsm) { LaunchTimer t(e, KID_PCGV);
         KL(e), bak::k_camera_gather<<<gblocks, bak::GATHER_WARPS * 32, 0, s>>>(e->Nc, e->Ng, e->fi, e->nTiles, e->RS, nullptr, nullptr, e->d_b.p, nullptr, nullptr, 0);
@@ -814,7 +830,8 @@ int ba_create(const ba_options* opt, ba_engine** out) {
         cudaDeviceProp prop{};
         CU_TRY(cudaGetDeviceProperties(&prop, e->device));
         e->num_sms = prop.multiProcessorCount;
-        e->scatter_mode = (opt->scatter_mode >= 1 && opt->scatter_mode <= 4) ? opt->scatter_mode : 4;
+        e->scatter_mode = (opt->scatter_mode >= 1 && opt->scatter_mode <= 5) ? opt->scatter_mode : 4;
+        if (const char* g = std::getenv("BA_L2_FETCH")) CU_TRY(cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, size_t(std::atoi(g))));   // experiment knob: 32 / 64 / 128
         if (prop.major < 10) throw BaFail{BA_ERR_CUDA, std::string("device ") + prop.name + " is not sm_100-class; this library holds sm_100a code only"};
         if (opt->stream) e->stream = static_cast<cudaStream_t>(opt->stream);
         else { CU_TRY(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking)); e->own_stream = true; }

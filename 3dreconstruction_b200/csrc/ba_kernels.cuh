@@ -166,7 +166,10 @@ __device__ __forceinline__ void project_obs(const double* __restrict__ cr, const
 // One CTA per tile, one thread per observation; then one thread per point of the tile sums its observations'
 // Jp^T Jp and Jp^T r from shared memory (observations are sorted by point, so a point's are contiguous).
 // Algorithmic bytes: reads 24 No (uv, cam, pt ids) + 24 Np + 160 Nc; writes (144 [+64] + 16) No + 72 Np.
-__global__ void __launch_bounds__(TILE_OBS)
+#ifndef K1_CTAS_PER_SM
+#define K1_CTAS_PER_SM 1
+#endif
+__global__ void __launch_bounds__(TILE_OBS, K1_CTAS_PER_SM)
 k1_residual_jacobian(View V, const double* __restrict__ camrec, const double* __restrict__ intr, const double* __restrict__ pt,
                      RobustParams rp, double* __restrict__ cost_partial, int* __restrict__ bad_flag) {
     __shared__ double sJp[TILE_OBS][9];   // per observation: Jp (2x3) , r (2)  [+1 pad: stride 9 is conflict-free]
@@ -182,8 +185,15 @@ k1_residual_jacobian(View V, const double* __restrict__ camrec, const double* __
     for (int base = o0; base < o1; base += TILE_OBS) {
         const int o = base + threadIdx.x;
         const bool act = o < o1;
+        // by-point half, issued first so these dependent loads overlap the observation math: thread j takes the j-th point of the chunk
+        const int lim = min(o1, base + TILE_OBS);
+        const int pfirst = V.obs_pt[base];
+        const int plast = V.obs_pt[lim - 1];
+        const int pj = pfirst + threadIdx.x;
+        int pa = 0, pb = 0;
+        if (pj <= plast) { pa = max(V.pt_off[pj], base); pb = min(V.pt_off[pj + 1], lim); }
         if (act) {
-            const int c = V.obs_cam[o], p = V.obs_pt[o], g = V.cam_group[c];
+            const int c = V.obs_cam[o], p = V.obs_pt[o], g = V.Ng == 1 ? 0 : V.cam_group[c];   // one shared Camera: no dependent group load
             const double* cr = camrec + size_t(c) * CAMREC;
             const double* in = intr + 4 * g;
             Proj q;
@@ -255,13 +265,10 @@ k1_residual_jacobian(View V, const double* __restrict__ camrec, const double* __
             sj[0] = p0[0]; sj[1] = p0[1]; sj[2] = p0[2]; sj[3] = p1[0]; sj[4] = p1[1]; sj[5] = p1[2]; sj[6] = rr0; sj[7] = rr1;
         }
         __syncthreads();
-        // by-point half of K2: thread j takes the j-th point of this chunk
-        const int lim = min(o1, base + TILE_OBS);
-        const int pfirst = V.obs_pt[base];
-        const int plast = V.obs_pt[lim - 1];
-        const int p = pfirst + threadIdx.x;
+        // by-point half of K2
+        const int p = pj;
         if (p <= plast) {
-            const int a = max(V.pt_off[p], base), b = min(V.pt_off[p + 1], lim);
+            const int a = pa, b = pb;
             double H[6] = {0, 0, 0, 0, 0, 0}, gg[3] = {0, 0, 0};
             for (int i = a; i < b; ++i) {
                 const double* sj = sJp[i - base];
@@ -310,7 +317,7 @@ k1c_candidate_cost(View V, const double* __restrict__ camrec, const double* __re
     for (int o = o0 + threadIdx.x; o < o1; o += TILE_OBS) {
         const int c = V.obs_cam[o], p = V.obs_pt[o];
         Proj q;
-        project_obs(camrec + size_t(c) * CAMREC, pt + 3 * size_t(p), intr + 4 * V.cam_group[c], ldg2(V.obs_uv + o), q);
+        project_obs(camrec + size_t(c) * CAMREC, pt + 3 * size_t(p), intr + (V.Ng == 1 ? 0 : 4 * V.cam_group[c]), ldg2(V.obs_uv + o), q);
         const double s = q.r0 * q.r0 + q.r1 * q.r1;
         double w;
         const double rho = robust(rp, s, w);
@@ -743,14 +750,16 @@ k8_candidate_points(View V, const double* __restrict__ pt, double* __restrict__ 
                     double* __restrict__ xn2_partial) {
     __shared__ double sred[32];
     double s2 = 0.0, x2 = 0.0;
-    const int n = 3 * V.Np;
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        const int p = i / 3;
+    for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < V.Np; p += gridDim.x * blockDim.x) {   // one point per thread and trip
         const bool fr = V.pt_off[p + 1] > V.pt_off[p];
-        const double xo = pt[i];
-        const double xc = xo - V.yp[i];
-        cpt[i] = xc;
-        if (fr) { const double d = xo - xc; s2 += d * d; x2 += xc * xc; }
+        const size_t i = 3 * size_t(p);
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            const double xo = pt[i + a];
+            const double xc = xo - V.yp[i + a];
+            cpt[i + a] = xc;
+            if (fr) { const double d = xo - xc; s2 += d * d; x2 += xc * xc; }
+        }
     }
     s2 = block_sum(s2, sred);
     if (threadIdx.x == 0) step2_partial[blockIdx.x] = s2;
@@ -761,9 +770,10 @@ k8_candidate_points(View V, const double* __restrict__ pt, double* __restrict__ 
 __global__ void __launch_bounds__(1024)
 k8_candidate_cameras(int Nc, int Ng, int fi, const unsigned char* __restrict__ cam_free, const unsigned char* __restrict__ grp_free,
                      const double* __restrict__ pose, const double* __restrict__ intr, const double* __restrict__ yf,
-                     double* __restrict__ cpose, double* __restrict__ cintr, Scalars* __restrict__ sc) {
+                     double* __restrict__ cpose, double* __restrict__ cintr, const double* __restrict__ step2_partial,
+                     const double* __restrict__ xn2_partial, int npartial, Scalars* __restrict__ sc) {
     __shared__ double sred[32];
-    double s2 = 0.0, x2 = 0.0;
+    double s2 = 0.0, x2 = 0.0, ps = 0.0, px = 0.0;
     for (int j = threadIdx.x; j < 6 * Nc; j += blockDim.x) {
         const double xo = pose[j];
         if (cam_free[j / 6]) { const double xc = xo - yf[j]; cpose[j] = xc; const double d = xo - xc; s2 += d * d; x2 += xc * xc; }
@@ -774,10 +784,15 @@ k8_candidate_cameras(int Nc, int Ng, int fi, const unsigned char* __restrict__ c
         if (fi && grp_free[j / 4]) { const double xc = xo - yf[6 * Nc + j]; cintr[j] = xc; const double d = xo - xc; s2 += d * d; x2 += xc * xc; }
         else cintr[j] = xo;
     }
+    for (int j = threadIdx.x; j < npartial; j += blockDim.x) { ps += step2_partial[j]; px += xn2_partial[j]; }   // point-side partials (fixed order)
     s2 = block_sum(s2, sred);
     if (threadIdx.x == 0) sc->step2_f = s2;
     x2 = block_sum(x2, sred);
     if (threadIdx.x == 0) sc->xn2_f = x2;
+    ps = block_sum(ps, sred);
+    if (threadIdx.x == 0) sc->step2_pt = ps;
+    px = block_sum(px, sred);
+    if (threadIdx.x == 0) sc->xn2_pt = px;
 }
 
 // max |x - (x + (-g))| over free scalars — the minimizer's gradient_max_norm (Plus(x, -g) lifted back, SURVEY a-LM).

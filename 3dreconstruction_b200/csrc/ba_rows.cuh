@@ -240,7 +240,25 @@ k_camera_gather(int Nc, int Ng, int fi, int nTiles, RowSched S, const double* __
     const int c = blockIdx.x;
     if (c < Nc) {
         double s0 = 0, s1 = 0, s2 = 0, s3 = 0, s4 = 0, s5 = 0;
-        for (int i = S.cam_row_off[c] + threadIdx.x, e = S.cam_row_off[c + 1]; i < e; i += GATHER_WARPS * 32) {
+        // four independent rows per thread and trip: 4 index loads, then 12 row loads in flight
+        constexpr int NT = GATHER_WARPS * 32;
+        const int e = S.cam_row_off[c + 1];
+        int i = S.cam_row_off[c] + threadIdx.x;
+        for (; i + 3 * NT < e; i += 4 * NT) {
+            const int i0 = S.cam_rows[i], i1 = S.cam_rows[i + NT], i2 = S.cam_rows[i + 2 * NT], i3 = S.cam_rows[i + 3 * NT];
+            const double2* r0 = reinterpret_cast<const double2*>(S.rows + size_t(ROW_DOUBLES) * i0);
+            const double2* r1 = reinterpret_cast<const double2*>(S.rows + size_t(ROW_DOUBLES) * i1);
+            const double2* r2 = reinterpret_cast<const double2*>(S.rows + size_t(ROW_DOUBLES) * i2);
+            const double2* r3 = reinterpret_cast<const double2*>(S.rows + size_t(ROW_DOUBLES) * i3);
+            const double2 a0 = __ldcg(r0), b0 = __ldcg(r0 + 1), c0 = __ldcg(r0 + 2);
+            const double2 a1 = __ldcg(r1), b1 = __ldcg(r1 + 1), c1 = __ldcg(r1 + 2);
+            const double2 a2 = __ldcg(r2), b2 = __ldcg(r2 + 1), c2 = __ldcg(r2 + 2);
+            const double2 a3 = __ldcg(r3), b3 = __ldcg(r3 + 1), c3 = __ldcg(r3 + 2);
+            s0 += (a0.x + a1.x) + (a2.x + a3.x); s1 += (a0.y + a1.y) + (a2.y + a3.y);
+            s2 += (b0.x + b1.x) + (b2.x + b3.x); s3 += (b0.y + b1.y) + (b2.y + b3.y);
+            s4 += (c0.x + c1.x) + (c2.x + c3.x); s5 += (c0.y + c1.y) + (c2.y + c3.y);
+        }
+        for (; i < e; i += NT) {
             const double2* row = reinterpret_cast<const double2*>(S.rows + size_t(ROW_DOUBLES) * S.cam_rows[i]);
             const double2 a = __ldcg(row), bq = __ldcg(row + 1), cq = __ldcg(row + 2);
             s0 += a.x; s1 += a.y; s2 += bq.x; s3 += bq.y; s4 += cq.x; s5 += cq.y;
@@ -285,11 +303,18 @@ k_camera_gather(int Nc, int Ng, int fi, int nTiles, RowSched S, const double* __
         last = (tk == gridDim.x - 1);
     }
     __syncthreads();
-    if (last && wid == 0) {   // fixed-order sum of the CTA partials by one warp
+    if (last) {   // fixed-order sum of the CTA partials by the whole last CTA (strided per thread, warp trees, then warp 0)
         __threadfence();
         double pq = 0.0;
-        for (int i = lane; i < int(gridDim.x); i += 32) pq += __ldcg(partial + i);
+        for (int i = threadIdx.x; i < int(gridDim.x); i += GATHER_WARPS * 32) pq += __ldcg(partial + i);
         pq = warp_sum(pq);
+        __syncthreads();
+        if (lane == 0) sw[wid][0] = pq;
+        __syncthreads();
+        pq = 0.0;
+#pragma unroll
+        for (int w = 0; w < GATHER_WARPS; ++w) pq += sw[w][0];
+        if (wid == 0)
         if (lane == 0) {
             if (!(pq > 0.0) || !isfinite(pq)) { st->done = 3; st->alpha = 0.0; }
             else st->alpha = st->rho / pq;

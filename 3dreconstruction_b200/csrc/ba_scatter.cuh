@@ -259,24 +259,30 @@ k_pcg_xr(int Nc, int Ng, int fi, const double* __restrict__ Minv, const double* 
     const double alpha = st->alpha;
     const int nblk = Nc + (fi ? Ng : 0);
     double rz = 0.0, xq = 0.0;
-    for (int blk = blockIdx.x * blockDim.x + threadIdx.x; blk < nblk; blk += gridDim.x * blockDim.x) {
+    // 8 lanes per diagonal block (6 or 4 active): lane a owns row a; the block's residual travels by width-8 shuffles
+    const int sub = threadIdx.x & 7;
+    const int nblk8 = (nblk + 15) / 16 * 16;   // whole warps stay together for the shuffles
+    for (int blk = (blockIdx.x * blockDim.x + threadIdx.x) >> 3; blk < nblk8; blk += (gridDim.x * blockDim.x) >> 3) {
+        const bool valid = blk < nblk;
         const bool cam = blk < Nc;
         const int n = cam ? 6 : 4;
         const int off = cam ? 6 * blk : 6 * Nc + 4 * (blk - Nc);
-        const double* M = cam ? Minv + 36 * size_t(blk) : Minv + 36 * size_t(Nc) + 16 * size_t(blk - Nc);
-        double rr[6];
-        for (int a = 0; a < n; ++a) {
-            const double xv = x[off + a] + alpha * p[off + a];
-            rr[a] = r[off + a] - alpha * q[off + a];
-            x[off + a] = xv; r[off + a] = rr[a];
-            xq += xv * (b[off + a] + rr[a]);
+        const bool act = valid && sub < n;
+        double rra = 0.0;
+        if (act) {
+            const double xv = x[off + sub] + alpha * p[off + sub];
+            rra = r[off + sub] - alpha * q[off + sub];
+            x[off + sub] = xv; r[off + sub] = rra;
+            xq += xv * (b[off + sub] + rra);
         }
-        for (int a = 0; a < n; ++a) {
-            double zz = 0.0;
-            for (int k = 0; k < n; ++k) zz += M[a * n + k] * rr[k];
-            z[off + a] = zz;
-            rz += rr[a] * zz;
+        double zz = 0.0;
+        const double* M = cam ? Minv + 36 * size_t(blk) + n * sub : Minv + 36 * size_t(Nc) + 16 * size_t(blk - Nc) + n * sub;
+#pragma unroll
+        for (int k = 0; k < 6; ++k) {
+            const double rk = __shfl_sync(0xffffffffu, rra, k, 8);
+            if (act && k < n) zz += M[k] * rk;
         }
+        if (act) { z[off + sub] = zz; rz += rra * zz; }
     }
     rz = block_sum(rz, sred);
     if (threadIdx.x == 0) partial[blockIdx.x] = rz;
@@ -288,10 +294,14 @@ k_pcg_xr(int Nc, int Ng, int fi, const double* __restrict__ Minv, const double* 
         last = (tk == gridDim.x - 1);
     }
     __syncthreads();
-    if (last && threadIdx.x == 0) {
+    double rho_new = 0.0, xb = 0.0;
+    if (last) {   // fixed-order sum of the block partials by the whole CTA (strided per thread, then the block tree)
         __threadfence();
-        double rho_new = 0.0, xb = 0.0;
-        for (int i = 0; i < int(gridDim.x); ++i) { rho_new += __ldcg(partial + i); xb += __ldcg(partial + gridDim.x + i); }
+        for (int i = threadIdx.x; i < int(gridDim.x); i += blockDim.x) { rho_new += __ldcg(partial + i); xb += __ldcg(partial + gridDim.x + i); }
+        rho_new = block_sum(rho_new, sred);
+        xb = block_sum(xb, sred);
+    }
+    if (last && threadIdx.x == 0) {
         const int k = st->k + 1;
         const double rel = sqrt(fmax(rho_new, 0.0) / st->rho0);
         int done = 0;

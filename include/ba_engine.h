@@ -111,7 +111,7 @@ typedef struct ba_options {
     int32_t world_size;                  /* 1 = single GPU */
     const void* nccl_unique_id;          /* world_size>1: 128-byte ncclUniqueId from ba_nccl_unique_id() on rank 0, broadcast by the caller */
     void*   stream;                      /* engine: cudaStream_t to run on (NULL: the engine creates its own) */
-    int32_t scatter_mode;                /* engine camera-side scatter: 0 = default (3), 1 = red.global.add.f64, 2 = private accumulators, 3 = 2 + bulk-copy pipeline */
+    int32_t scatter_mode;                /* engine camera-side scatter: 0 = default (4), 1 = red.global.add.f64, 2 = private accumulators, 3 = 2 + bulk-copy pipeline, 4 = partial rows, 5 = 4 as a persistent cp.async pipeline (measured slower) */
     int32_t reserved[7];
 } ba_options;
 

@@ -78,7 +78,7 @@ def test_trajectory_parity(ba, oracle, name, fi):
     assert rel_err(xe[1], xo[1]) <= STATE_RTOL
 
 
-@pytest.mark.parametrize("mode", [1, 2, 3, 4])
+@pytest.mark.parametrize("mode", [1, 2, 3, 4, 5])
 @pytest.mark.parametrize("fi", [0, 1])
 def test_scatter_modes(ba, oracle, mode, fi):
     """All three camera-side scatter implementations (L2 atomics, private accumulators, bulk-copy pipeline) agree with the oracle."""
