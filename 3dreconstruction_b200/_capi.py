@@ -48,7 +48,8 @@ class BAOptions(C.Structure):
         ("nccl_unique_id", C.c_void_p),
         ("stream", C.c_void_p),
         ("scatter_mode", C.c_int32),
-        ("reserved", C.c_int32 * 7),
+        ("p2p_allreduce", C.c_int32),
+        ("reserved", C.c_int32 * 6),
     ]
 
 

@@ -28,6 +28,7 @@
 #include "ba_pipe.cuh"
 #include "ba_rows.cuh"
 #include "ba_rows_pipe.cuh"
+#include "ba_p2p.cuh"
 
 namespace {
 using std::vector;
@@ -55,11 +56,12 @@ struct Nccl {
     int (*CommDestroy)(Comm) = nullptr;
     int (*AllReduce)(const void*, void*, size_t, int, int, Comm, cudaStream_t) = nullptr;
     int (*Broadcast)(const void*, void*, size_t, int, int, Comm, cudaStream_t) = nullptr;
+    int (*AllGather)(const void*, void*, size_t, int, Comm, cudaStream_t) = nullptr;
     int (*GroupStart)() = nullptr;
     int (*GroupEnd)() = nullptr;
     const char* (*GetErrorString)(int) = nullptr;
     void* handle = nullptr;
-    enum { kInt32 = 2, kFloat64 = 8, kSum = 0, kMax = 2 };   // ncclDataType_t / ncclRedOp_t values (stable since NCCL 2.0)
+    enum { kInt8 = 0, kInt32 = 2, kFloat64 = 8, kSum = 0, kMax = 2 };   // ncclDataType_t / ncclRedOp_t values (stable since NCCL 2.0)
     bool load(std::string& err) {
         if (handle) return true;
         for (const char* n : {"libnccl.so.2", "libnccl.so"}) { handle = dlopen(n, RTLD_NOW | RTLD_GLOBAL); if (handle) break; }
@@ -70,10 +72,11 @@ struct Nccl {
         CommDestroy = reinterpret_cast<decltype(CommDestroy)>(sym("ncclCommDestroy"));
         AllReduce = reinterpret_cast<decltype(AllReduce)>(sym("ncclAllReduce"));
         Broadcast = reinterpret_cast<decltype(Broadcast)>(sym("ncclBroadcast"));
+        AllGather = reinterpret_cast<decltype(AllGather)>(sym("ncclAllGather"));
         GroupStart = reinterpret_cast<decltype(GroupStart)>(sym("ncclGroupStart"));
         GroupEnd = reinterpret_cast<decltype(GroupEnd)>(sym("ncclGroupEnd"));
         GetErrorString = reinterpret_cast<decltype(GetErrorString)>(sym("ncclGetErrorString"));
-        return GetUniqueId && CommInitRank && CommDestroy && AllReduce && Broadcast && GroupStart && GroupEnd && GetErrorString;
+        return GetUniqueId && CommInitRank && CommDestroy && AllReduce && Broadcast && AllGather && GroupStart && GroupEnd && GetErrorString;
     }
 };
 Nccl g_nccl;
@@ -161,6 +164,16 @@ struct ba_engine {
     bak::View V{};
     // multi-GPU
     Nccl::Comm comm = nullptr;
+    struct P2P {   // one-shot peer-memory all-reduce of the PCG matvec (ba_p2p.cuh)
+        bool on = false;
+        size_t cap = 0;                       // doubles in the local receive buffer
+        double* local = nullptr;
+        unsigned int* lflags = nullptr;
+            void* opened[2 * bak::P2P_MAX_RANKS] = {};   // IPC mappings to close
+        int nopened = 0;
+        bak::PeerView view{};
+        unsigned int seq = 0;
+    } p2p;
     // profiling
     int64_t kernel_launches = 0;
     unsigned profiling = 0;           // bit k set: time kernel id k with CUDA events
@@ -235,6 +248,70 @@ void build_tiles(const vector<int32_t>& pt_off, int Np, vector<int32_t>& tile_of
         }
     }
     if (tile_off.back() != pt_off[Np]) tile_off.push_back(pt_off[Np]);
+}
+
+void teardown_p2p(ba_engine* e) {
+    for (int i = 0; i < e->p2p.nopened; ++i) cudaIpcCloseMemHandle(e->p2p.opened[i]);
+    if (e->p2p.local) cudaFree(e->p2p.local);
+    if (e->p2p.lflags) cudaFree(e->p2p.lflags);
+    e->p2p = ba_engine::P2P{};
+}
+
+// Map every rank's receive buffer and flag array into this process (CUDA IPC; handles travel through one ncclAllGather).
+// Collective: every rank calls it with the same nf.  On any failure anywhere all ranks fall back to the NCCL all-reduce
+// (or fail, when p2p_allreduce = 2).
+void setup_p2p(ba_engine* e) {
+    const int W = e->opt.world_size, R = e->opt.rank;
+    if (W <= 1 || e->opt.p2p_allreduce == 1) return;
+    if (W > bak::P2P_MAX_RANKS) { if (e->opt.p2p_allreduce == 2) throw BaFail{BA_ERR_UNSUPPORTED, "peer-memory all-reduce supports at most 8 ranks"}; return; }
+    const int ldf = (e->nf + 15) / 16 * 16;
+    const size_t need = size_t(2) * W * ldf;
+    cudaStream_t s = e->stream;
+    if (e->p2p.on && e->p2p.cap >= need) { e->p2p.view.ldf = ldf; return; }
+    teardown_p2p(e);
+    ba_engine::P2P& Q = e->p2p;
+    CU_TRY(cudaMalloc(reinterpret_cast<void**>(&Q.local), need * sizeof(double)));
+    CU_TRY(cudaMalloc(reinterpret_cast<void**>(&Q.lflags), 64 * sizeof(unsigned int)));
+    CU_TRY(cudaMemsetAsync(Q.local, 0, need * sizeof(double), s));
+    CU_TRY(cudaMemsetAsync(Q.lflags, 0, 64 * sizeof(unsigned int), s));
+    Q.cap = need;
+    struct Rec { cudaIpcMemHandle_t data, flags; };
+    static_assert(sizeof(Rec) == 128, "two 64-byte IPC handles");
+    vector<Rec> all(W);
+    int fail_local = 0;
+    if (cudaIpcGetMemHandle(&all[R].data, Q.local) != cudaSuccess || cudaIpcGetMemHandle(&all[R].flags, Q.lflags) != cudaSuccess) { fail_local = 1; cudaGetLastError(); }
+    DevBuf<char> d_all; d_all.alloc(size_t(W) * sizeof(Rec));
+    CU_TRY(cudaMemcpyAsync(d_all.p + size_t(R) * sizeof(Rec), &all[R], sizeof(Rec), cudaMemcpyHostToDevice, s));
+    NCCL_TRY(g_nccl.AllGather(d_all.p + size_t(R) * sizeof(Rec), d_all.p, sizeof(Rec), Nccl::kInt8, e->comm, s));
+    CU_TRY(cudaMemcpyAsync(all.data(), d_all.p, size_t(W) * sizeof(Rec), cudaMemcpyDeviceToHost, s));
+    CU_TRY(cudaStreamSynchronize(s));
+    bak::PeerView& V = Q.view;
+    V = bak::PeerView{};
+    V.W = W; V.rank = R; V.ldf = ldf; V.timeout_flag = &e->d_scal.p->bad_lin;
+    V.data[R] = Q.local; V.flags[R] = Q.lflags;
+    for (int r = 0; r < W && !fail_local; ++r) {
+        if (r == R) continue;
+        void *pd = nullptr, *pf = nullptr;
+        if (cudaIpcOpenMemHandle(&pd, all[r].data, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { fail_local = 1; cudaGetLastError(); break; }
+        Q.opened[Q.nopened++] = pd;
+        if (cudaIpcOpenMemHandle(&pf, all[r].flags, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { fail_local = 1; cudaGetLastError(); break; }
+        Q.opened[Q.nopened++] = pf;
+        V.data[r] = static_cast<double*>(pd); V.flags[r] = static_cast<unsigned int*>(pf);
+    }
+    // agree: one failure anywhere disables the path everywhere
+    DevBuf<int> d_fail; d_fail.alloc(1);
+    CU_TRY(cudaMemcpyAsync(d_fail.p, &fail_local, sizeof(int), cudaMemcpyHostToDevice, s));
+    NCCL_TRY(g_nccl.AllReduce(d_fail.p, d_fail.p, 1, Nccl::kInt32, Nccl::kMax, e->comm, s));
+    int fail_any = 0;
+    CU_TRY(cudaMemcpyAsync(&fail_any, d_fail.p, sizeof(int), cudaMemcpyDeviceToHost, s));
+    CU_TRY(cudaStreamSynchronize(s));
+    if (fail_any) {
+        teardown_p2p(e);
+        if (e->opt.p2p_allreduce == 2) throw BaFail{BA_ERR_NCCL, "peer-memory all-reduce required (p2p_allreduce = 2) but CUDA IPC mapping of a peer buffer failed"};
+        return;
+    }
+    Q.on = true;
+    Q.seq = 0;
 }
 
 // Point ranges of the W shards from the global CSR-by-point offsets: rank r starts at the first point whose first
@@ -408,6 +485,8 @@ void do_set_problem(ba_engine* e, const ba_problem* P) {
     CU_TRY(cudaMemcpyAsync(e->d_pose.p, e->d_pose0.p, size_t(6) * Nc * sizeof(double), cudaMemcpyDeviceToDevice, s));
     CU_TRY(cudaMemcpyAsync(e->d_intr.p, e->d_intr0.p, size_t(4) * Ng * sizeof(double), cudaMemcpyDeviceToDevice, s));
     CU_TRY(cudaMemcpyAsync(e->d_pt.p, e->d_pt0.p, size_t(3) * Np * sizeof(double), cudaMemcpyDeviceToDevice, s));
+
+    setup_p2p(e);
 
     bak::View& V = e->V;
     V.Nc = Nc; V.Ng = Ng; V.Np = Np; V.No = No; V.ldo = e->ldo; V.nTiles = e->nTiles; V.fi = e->fi;
@@ -625,7 +704,11 @@ int solve_linear(ba_engine* e, double radius, double* rel_out) {
             LaunchTimer t(e, KID_PCGV);
             double* src = nullptr; int nsrc = 0;
             if (rowsm) {
-                if (multi) {
+                if (multi && e->p2p.on) {   // one-shot NVLink all-reduce fused into the gather and the dot-product kernel (ba_p2p.cuh)
+                    const unsigned int seq = ++e->p2p.seq;
+                    KL(e), bak::k_camera_gather_push<<<gblocks, bak::GATHER_WARPS * 32, 0, s>>>(e->Nc, e->Ng, e->fi, e->nTiles, e->RS, e->d_y.p, e->p2p.view, seq, &sc->pcg, 1);
+                    KL(e), bak::k_pcg_q_p2p<<<vblocks, 128, 0, s>>>(e->nf, e->p2p.view, seq, e->d_Df2.p, e->d_p.p, e->d_y.p, e->d_part1.p, &sc->pcg, 1, 1);
+                } else if (multi) {
                     KL(e), bak::k_camera_gather<<<gblocks, bak::GATHER_WARPS * 32, 0, s>>>(e->Nc, e->Ng, e->fi, e->nTiles, e->RS, nullptr, nullptr, e->d_y.p, nullptr, nullptr, 0);
                     allreduce_sum(e, e->d_y.p, e->nf);
                     KL(e), bak::k_pcg_q<<<vblocks, bak::PCG_BLOCK, 0, s>>>(e->nf, 0, e->Sch.ldf, nullptr, e->d_Df2.p, e->d_p.p, e->d_y.p, e->d_part1.p, &sc->pcg, 0, 1);
@@ -647,6 +730,7 @@ int solve_linear(ba_engine* e, double radius, double* rel_out) {
             if (e->scatter_mode == 1) e->d_y.zero(s);
         }
         read_scalars(e);
+        if (e->h_scal->bad_lin & 8) throw BaFail{BA_ERR_NCCL, "peer-memory all-reduce timed out waiting for another rank"};
         if (e->h_scal->pcg.done) break;
     }
     *rel_out = e->h_scal->pcg.rel;
@@ -804,7 +888,7 @@ int ba_options_default(ba_options* o) {
     o->preconditioner = BA_PRECOND_JACOBI;                         // :171
     o->pcg_max_iterations = 2000; o->pcg_rel_tolerance = 1e-12; o->pcg_forcing = 0; o->eta = 0.1;
     o->target_chi2 = 0.0; o->device = 0; o->num_threads = 1;
-    o->rank = 0; o->world_size = 1; o->nccl_unique_id = nullptr; o->stream = nullptr; o->scatter_mode = 0;
+    o->rank = 0; o->world_size = 1; o->nccl_unique_id = nullptr; o->stream = nullptr; o->scatter_mode = 0; o->p2p_allreduce = 0;
     return BA_OK;
 }
 
@@ -1036,6 +1120,7 @@ void ba_destroy(ba_engine* e) {
     if (!e) return;
     cudaSetDevice(e->device);
     if (e->stream) cudaStreamSynchronize(e->stream);
+    teardown_p2p(e);
     if (e->comm) g_nccl.CommDestroy(e->comm);
     for (auto& p : e->pending) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
     for (auto ev : e->ev_pool) cudaEventDestroy(ev);

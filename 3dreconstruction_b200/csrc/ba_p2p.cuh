@@ -1,0 +1,134 @@
+// ba_p2p.cuh — multi-GPU: the per-PCG-iteration all-reduce of the matvec result y (6 Nc doubles, 85 KB on Venice) as a ONE-SHOT
+// peer-memory all-reduce over NVLink/NVSwitch, fused into the K5b gather and the PCG dot-product kernel ("B200-native step
+// beyond NCCL").  NCCL's all-reduce of this payload is latency-bound (tens of microseconds, comparable to the local matvec at 8 GPUs).
+//
+//   k_camera_gather_push : K5b on every rank — sums camera c's partial rows (fixed order) and stores the 6-vector straight into slot
+//                          [parity][my rank] of EVERY rank's receive buffer (peer pointers mapped with CUDA IPC; plain 16-byte st.global
+//                          over NVLink).  The last CTA to finish (ticket) publishes flag[my rank] = seq on every rank (st.release.sys).
+//   k_pcg_q_p2p          : waits (ld.acquire.sys on LOCAL memory) until all W flags show seq, then y = sum over ranks IN RANK ORDER of the
+//                          W slots — the same order on every rank, so all ranks hold bit-identical y and take identical decisions —
+//                          and continues with q = y + Df2 p, p.q, alpha as k_pcg_q.
+// Slots are double-buffered by the parity of seq: a rank can be at most one all-reduce ahead of the slowest rank (it needs that rank's
+// slot of the current sequence number to finish), so parity p is never overwritten while someone still reads it.
+// One rank per GPU only: the wait spins on flags another GPU writes (never emulate several ranks on one GPU with this path).
+#pragma once
+#include "ba_rows.cuh"
+
+namespace bak {
+
+constexpr int P2P_MAX_RANKS = 8;
+
+struct PeerView {
+    double* data[P2P_MAX_RANKS];        // rank r's receive buffer: [2][W][ldf] doubles (data[rank] is the local one)
+    unsigned int* flags[P2P_MAX_RANKS]; // rank r's flag array [W]: flags[r][s] = last sequence number rank s has fully delivered to r
+    int W, rank, ldf;
+    int* timeout_flag;                  // local Scalars::bad_lin: bit 8 set if a wait gave up (the host turns it into BA_ERR_NCCL)
+};
+
+__device__ __forceinline__ void st_release_sys(unsigned int* p, unsigned int v) { asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
+__device__ __forceinline__ unsigned int ld_acquire_sys(const unsigned int* p) {
+    unsigned int v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+__global__ void __launch_bounds__(GATHER_WARPS * 32)
+k_camera_gather_push(int Nc, int Ng, int fi, int nTiles, RowSched S, const double* __restrict__ ylocal_rw, PeerView P, unsigned int seq,
+                     PcgState2* __restrict__ st, int check_done) {
+    __shared__ double sw[GATHER_WARPS][6];
+    __shared__ bool last;
+    if (check_done && st->done) return;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int ioff = 6 * Nc;
+    const size_t slot = (size_t(seq & 1u) * P.W + P.rank) * P.ldf;
+    const int c = blockIdx.x;
+    if (c < Nc) {
+        double s0 = 0, s1 = 0, s2 = 0, s3 = 0, s4 = 0, s5 = 0;
+        for (int i = S.cam_row_off[c] + threadIdx.x, e = S.cam_row_off[c + 1]; i < e; i += GATHER_WARPS * 32) {
+            const double2* row = reinterpret_cast<const double2*>(S.rows + size_t(ROW_DOUBLES) * S.cam_rows[i]);
+            const double2 a = __ldcg(row), bq = __ldcg(row + 1), cq = __ldcg(row + 2);
+            s0 += a.x; s1 += a.y; s2 += bq.x; s3 += bq.y; s4 += cq.x; s5 += cq.y;
+        }
+        s0 = warp_sum(s0); s1 = warp_sum(s1); s2 = warp_sum(s2); s3 = warp_sum(s3); s4 = warp_sum(s4); s5 = warp_sum(s5);
+        if (lane == 0) { sw[wid][0] = s0; sw[wid][1] = s1; sw[wid][2] = s2; sw[wid][3] = s3; sw[wid][4] = s4; sw[wid][5] = s5; }
+        __syncthreads();
+        // thread (r, h): half-row h (16 bytes) of this camera's 6-vector to rank r
+        if (threadIdx.x < 3 * P.W) {
+            const int r = threadIdx.x / 3, h = threadIdx.x - 3 * r;
+            double2 v = make_double2(0.0, 0.0);
+#pragma unroll
+            for (int w = 0; w < GATHER_WARPS; ++w) { v.x += sw[w][2 * h]; v.y += sw[w][2 * h + 1]; }
+            *reinterpret_cast<double2*>(P.data[r] + slot + 6 * size_t(c) + 2 * h) = v;
+        }
+    } else if (fi) {
+        // intrinsics entries: single group -> ordered sum of the per-tile partials; several groups -> RED-accumulated in ylocal_rw already
+        for (int k = wid; k < 4 * Ng; k += GATHER_WARPS) {
+            double v;
+            if (Ng == 1) {
+                double s = 0.0;
+                for (int t = lane; t < nTiles; t += 32) s += __ldcg(S.tile_intr + 4 * size_t(t) + k);
+                v = warp_sum(s);
+            } else v = ylocal_rw[ioff + k];
+            if (lane < P.W) P.data[lane][slot + ioff + k] = v;
+        }
+    }
+    // publish: every CTA fences its remote stores at system scope before taking a ticket; the last one raises the flags
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence_system();
+        const unsigned int tk = atomicAdd(&st->ticket_q, 1u);
+        last = (tk == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (last) {
+        if (threadIdx.x == 0) st->ticket_q = 0;
+        if (threadIdx.x < P.W) { __threadfence_system(); st_release_sys(P.flags[threadIdx.x] + P.rank, seq); }
+    }
+}
+
+// y = sum_r slot[r] in rank order (after all W ranks delivered sequence number seq); with do_dot: q = y + Df2 p in y, p.q, alpha.
+__global__ void __launch_bounds__(128)
+k_pcg_q_p2p(int nf, PeerView P, unsigned int seq, const double* __restrict__ Df2, const double* __restrict__ p, double* __restrict__ y,
+            double* __restrict__ partial, PcgState2* __restrict__ st, int do_dot, int check_done) {
+    __shared__ double sred[32];
+    __shared__ bool last;
+    if (check_done && st->done) return;
+    if (threadIdx.x < P.W) {
+        const unsigned int* f = P.flags[P.rank] + threadIdx.x;
+        const long long t0 = clock64();
+        while (int(ld_acquire_sys(f) - seq) < 0) {
+            if ((*reinterpret_cast<volatile int*>(P.timeout_flag) & 8) || clock64() - t0 > 4000000000LL) { atomicOr(P.timeout_flag, 8); break; }   // ~2 s: a peer died; never hang the GPU
+        }
+    }
+    __syncthreads();
+    const double* base = P.data[P.rank] + size_t(seq & 1u) * P.W * P.ldf;
+    double acc = 0.0;
+    for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < nf; j += gridDim.x * blockDim.x) {
+        double s = 0.0;
+        for (int r = 0; r < P.W; ++r) s += __ldcg(base + size_t(r) * P.ldf + j);
+        if (do_dot) { const double pj = p[j]; s += Df2[j] * pj; acc += pj * s; }
+        y[j] = s;
+    }
+    if (!do_dot) return;
+    acc = block_sum(acc, sred);
+    if (threadIdx.x == 0) {
+        partial[blockIdx.x] = acc;
+        __threadfence();
+        const unsigned int tk = atomicAdd(&st->ticket_r, 1u);
+        last = (tk == gridDim.x - 1);
+    }
+    __syncthreads();
+    double pq = 0.0;
+    if (last) {
+        __threadfence();
+        for (int i = threadIdx.x; i < int(gridDim.x); i += blockDim.x) pq += __ldcg(partial + i);
+        pq = block_sum(pq, sred);
+    }
+    if (last && threadIdx.x == 0) {
+        if (!(pq > 0.0) || !isfinite(pq)) { st->done = 3; st->alpha = 0.0; }
+        else st->alpha = st->rho / pq;
+        st->ticket_r = 0;
+    }
+}
+
+}  // namespace bak

@@ -170,7 +170,7 @@ def run_ours(args, rank, world, local_rank):
     import ctypes
     idbuf = ctypes.create_string_buffer(nccl_id, 128) if nccl_id else None
     opts = solver_options(args)
-    opts.update(device=local_rank, rank=rank, world_size=world, stream=ctypes.c_void_p(stream.cuda_stream),
+    opts.update(device=local_rank, rank=rank, world_size=world, stream=ctypes.c_void_p(stream.cuda_stream), p2p_allreduce=args.p2p,
                 nccl_unique_id=ctypes.cast(idbuf, ctypes.c_void_p) if idbuf else None)
     eng = lib.create(lib.default_options(**opts))
     eng.set_problem(Ph)
@@ -233,7 +233,7 @@ def run_ours(args, rank, world, local_rank):
                        "step": "one full BA solve: LM with the reference's Ceres options (max 50 iterations, tolerances 1e-6/1e-8/1e-10), "
                                f"PCG on the implicit Schur complement to rel. residual {args.pcg_tol:g} (trajectory-parity mode)",
                        "l2": "inputs larger than L2 (J = 720 MB per sweep vs 126 MB L2)",
-                       "parallelism": f"points sharded over {world} GPU(s), camera-side vectors all-reduced with NCCL" if world > 1 else "single GPU"},
+                       "parallelism": (f"points sharded over {world} GPU(s); per-PCG-iteration all-reduce of the matvec: " + {0: "auto (one-shot NVLink peer-memory all-reduce fused into the gather kernel when mappable, else NCCL)", 1: "NCCL", 2: "one-shot NVLink peer-memory all-reduce fused into the gather kernel"}[args.p2p] + "; other reductions NCCL") if world > 1 else "single GPU"},
             "e2e": {"value": e2e_its / t_e2e, "unit": UNIT, "h2d_bytes_per_step": (h2d1 - h2d0) // args.steps, "d2h_bytes_per_step": (d2h1 - d2h0) // args.steps,
                     "ms_per_step": 1e3 * t_e2e / args.steps},
             "gpu_launches": int(launches),
@@ -270,6 +270,7 @@ def main():
     ap.add_argument("--cpu-lm-iterations", type=int, default=1)
     ap.add_argument("--cpu-linear-solver", type=int, default=1, help="0 exact dense Cholesky (the reference's SPARSE_SCHUR semantics), 1 PCG")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--p2p", type=int, default=0, help="multi-GPU matvec all-reduce: 0 auto (NVLink peer memory if mappable, else NCCL), 1 NCCL only, 2 peer memory required")
     args = ap.parse_args()
     rank, world, local_rank = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
     if args.impl == "reference":

@@ -112,7 +112,9 @@ typedef struct ba_options {
     const void* nccl_unique_id;          /* world_size>1: 128-byte ncclUniqueId from ba_nccl_unique_id() on rank 0, broadcast by the caller */
     void*   stream;                      /* engine: cudaStream_t to run on (NULL: the engine creates its own) */
     int32_t scatter_mode;                /* engine camera-side scatter: 0 = default (4), 1 = red.global.add.f64, 2 = private accumulators, 3 = 2 + bulk-copy pipeline, 4 = partial rows, 5 = 4 as a persistent cp.async pipeline (measured slower) */
-    int32_t reserved[7];
+    int32_t p2p_allreduce;               /* multi-GPU all-reduce of the PCG matvec: 0 = auto (one-shot NVLink peer-memory all-reduce fused into the
+                                            K5b gather when every peer buffer can be mapped with CUDA IPC, else NCCL), 1 = NCCL only, 2 = peer memory required */
+    int32_t reserved[6];
 } ba_options;
 
 /* Problem in canonical indexing: observations sorted by point id (non-decreasing obs_pt),

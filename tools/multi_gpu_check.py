@@ -22,7 +22,7 @@ def main():
     lib = ba.engine_library()
     ok = True
     for shape in (sys.argv[1:] or ["ladybug", "trafalgar"]):
-        for fi in (0, 1):
+        for fi, p2p in ((0, 2), (1, 2), (0, 1)):   # p2p 2: peer-memory all-reduce required; 1: NCCL only
             idt = torch.zeros(128, dtype=torch.uint8, device=dev)
             if rank == 0:
                 idt.copy_(torch.frombuffer(bytearray(lib.nccl_unique_id()), dtype=torch.uint8))
@@ -30,7 +30,7 @@ def main():
             idbuf = ctypes.create_string_buffer(bytes(idt.cpu().numpy().tobytes()), 128)
             P = ba.synth(shape)
             common = dict(intrinsics_free=fi, max_num_iterations=10, device=local)
-            with lib.create(lib.default_options(rank=rank, world_size=world, nccl_unique_id=ctypes.cast(idbuf, ctypes.c_void_p), **common)) as eng:
+            with lib.create(lib.default_options(rank=rank, world_size=world, p2p_allreduce=p2p, nccl_unique_id=ctypes.cast(idbuf, ctypes.c_void_p), **common)) as eng:
                 eng.set_problem(P)
                 s = eng.solve()
                 t = eng.trajectory()
@@ -48,7 +48,7 @@ def main():
                     pose1, intr1, pt1 = one.get_state()
                 good = same and len(t) == len(t1) and all(a.step_is_successful == b.step_is_successful and abs(a.cost - b.cost) <= 1e-6 * abs(b.cost) for a, b in zip(t, t1))
                 good = good and np.linalg.norm(pt - pt1) <= 1e-5 * np.linalg.norm(pt1) and np.linalg.norm(pose - pose1) <= 1e-5 * np.linalg.norm(pose1)
-                print(f"{shape} fi={fi} world={world}: {'OK' if good else 'MISMATCH'} iters {len(t)} vs {len(t1)} final cost {s.final_cost:.12e} vs {s1.final_cost:.12e} "
+                print(f"{shape} fi={fi} p2p={p2p} world={world}: {'OK' if good else 'MISMATCH'} iters {len(t)} vs {len(t1)} final cost {s.final_cost:.12e} vs {s1.final_cost:.12e} "
                       f"ranks identical: {same}; device time {s.solve_seconds*1e3:.1f} ms vs {s1.solve_seconds*1e3:.1f} ms single", flush=True)
                 ok = ok and good
     flag = torch.tensor([0 if ok else 1], device=dev)
