@@ -141,7 +141,8 @@ struct ba_engine {
     DevBuf<double> d_pose, d_intr, d_pt, d_cpose, d_cintr, d_cpt, d_pose0, d_intr0, d_pt0, d_ptfull;
     // device: work arrays
     DevBuf<double> d_camrec, d_ccamrec;
-    DevBuf<double2> d_J2, d_r2;
+    DevBuf<double2> d_J2, d_r2, d_JcA;
+    int k1_grid = 1;
     DevBuf<double> d_Hpp, d_gp, d_Hinv, d_vp, d_yp, d_sc_pt;
     DevBuf<double> d_red;        // [Hcc 36Nc | gc 6Nc | Hii 16Ng | gi 4Ng] — one all-reduce per evaluation
     DevBuf<double> d_sc_f, d_Df2, d_Minv, d_b, d_x, d_r, d_z, d_p, d_y;
@@ -473,6 +474,8 @@ void do_set_problem(ba_engine* e, const ba_problem* P) {
     for (auto* b : {&e->d_pt, &e->d_cpt}) b->alloc(size_t(3) * Np);
     e->d_camrec.alloc(size_t(bak::CAMREC) * Nc); e->d_ccamrec.alloc(size_t(bak::CAMREC) * Nc);
     e->d_J2.alloc(size_t(e->fi ? 13 : 9) * e->ldo); e->d_r2.alloc(e->ldo);
+    e->d_JcA.alloc(size_t(e->fi ? 12 : 8) * std::max(No, 1));
+    e->k1_grid = std::max(1, std::min(e->nTiles, e->num_sms * K1_CTAS_PER_SM));
     e->d_Hpp.alloc(size_t(6) * Np); e->d_gp.alloc(size_t(3) * Np); e->d_Hinv.alloc(size_t(6) * Np);
     e->d_vp.alloc(size_t(3) * Np); e->d_yp.alloc(size_t(3) * Np); e->d_sc_pt.alloc(size_t(3) * Np);
     e->d_red.alloc(e->red_count());
@@ -493,7 +496,7 @@ void do_set_problem(ba_engine* e, const ba_problem* P) {
     V.tile_off = e->d_tile_off.p; V.obs_cam = e->d_obs_cam.p; V.obs_pt = e->d_obs_pt.p; V.obs_uv = e->d_obs_uv.p;
     V.pt_off = e->d_pt_off.p; V.cam_group = e->d_cam_group.p; V.cam_free = e->d_cam_free.p; V.grp_free = e->d_grp_free.p;
     V.perm_by_cam = e->d_perm.p; V.cam_off = e->d_cam_off.p;
-    V.J2 = e->d_J2.p; V.r2 = e->d_r2.p; V.Hpp = e->d_Hpp.p; V.gp = e->d_gp.p; V.Hinv = e->d_Hinv.p; V.vp = e->d_vp.p; V.yp = e->d_yp.p;
+    V.J2 = e->d_J2.p; V.r2 = e->d_r2.p; V.JcA = e->d_JcA.p; V.jca_stride = e->fi ? 12 : 8; V.Hpp = e->d_Hpp.p; V.gp = e->d_gp.p; V.Hinv = e->d_Hinv.p; V.vp = e->d_vp.p; V.yp = e->d_yp.p;
     V.sc_pt = e->d_sc_pt.p;
     CU_TRY(cudaStreamSynchronize(s));   // host staging vectors go out of scope
     e->traj.clear();
@@ -503,9 +506,10 @@ void do_set_problem(ba_engine* e, const ba_problem* P) {
     // algorithmic bytes per launch of each kernel in THIS formulation, for roofline.achieved
     const double no = No, np = Np, nc = Nc, jb = e->fi ? 208.0 : 144.0;
     e->stats[KID_K0].bytes = (48 + 160) * nc;
-    e->stats[KID_K1].bytes = no * (24 + jb + 16) + np * (24 + 72) + 160 * nc;
+    const double jca = e->fi ? 192.0 : 128.0;   // by-observation record for K2c
+    e->stats[KID_K1].bytes = no * (24 + jb + 16 + jca) + np * (24 + 72) + 160 * nc;
     e->stats[KID_K1C].bytes = no * 24 + np * 24 + 160 * nc;
-    e->stats[KID_K2C].bytes = no * (96 + (e->fi ? 64 : 0) + 16 + 4) + (288 + 48) * nc;
+    e->stats[KID_K2C].bytes = no * (jca + 4) + (288 + 48) * nc;
     e->stats[KID_K3P].bytes = np * (48 + 24 + 24 + 48 + 24);
     e->stats[KID_K3C].bytes = nc * (288 + 48 + 48 + 288);
     e->stats[KID_K4].bytes = no * (jb + 16 + 8 + 5) + np * 24 + 48 * nc;
@@ -546,10 +550,10 @@ void evaluate_full(ba_engine* e) {
       KL(e), bak::k0_camera_precompute<<<cdiv(e->Nc, 128), 128, 0, s>>>(e->Nc, e->d_pose.p, e->d_camrec.p, e->opt.taylor_rule); }
     if (e->nTiles > 0) {
         LaunchTimer t(e, KID_K1);
-        KL(e), bak::k1_residual_jacobian<<<e->nTiles, bak::TILE_OBS, 0, s>>>(e->V, e->d_camrec.p, e->d_intr.p, e->d_pt.p, rp, e->d_part0.p, &sc->bad_eval);
+        KL(e), bak::k1_residual_jacobian<<<e->k1_grid, bak::TILE_OBS, 0, s>>>(e->V, e->d_camrec.p, e->d_intr.p, e->d_pt.p, rp, e->d_part0.p, &sc->bad_eval);
     }
     { LaunchTimer t(e, KID_MISC);
-      KL(e), bak::k_reduce_partials<<<1, 1024, 0, s>>>(e->d_part0.p, e->nTiles, &sc->cost); }
+      KL(e), bak::k_reduce_partials<<<1, 1024, 0, s>>>(e->d_part0.p, e->nTiles > 0 ? e->k1_grid : 0, &sc->cost); }
     if (e->fi) CU_TRY(cudaMemsetAsync(e->Hii(), 0, size_t(20) * e->Ng * sizeof(double), s));
     if (e->Nc > 0) {
         LaunchTimer t(e, KID_K2C);

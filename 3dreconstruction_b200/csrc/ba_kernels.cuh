@@ -41,6 +41,8 @@ struct View {
     const int* cam_off;          // [Nc+1]
     double2* J2;                 // [9 or 13][ldo]
     double2* r2;                 // [ldo] robustified residual
+    double2* JcA;                // [No][8 or 12] by-observation records (jc0..jc5, r, [ji0..ji3], pad) for the by-camera gather of K2c
+    int jca_stride;              // double2 per record: 8 (128 B), 12 with free intrinsics (192 B) — whole 32-byte sectors
     double* Hpp;                 // [Np][6] upper triangle xx xy xz yy yz zz of sum Jp^T Jp
     double* gp;                  // [Np][3] sum Jp^T r
     double* Hinv;                // [Np][6] (Hpp + Dp^2)^-1
@@ -55,6 +57,16 @@ __device__ __forceinline__ void red_add(double* addr, double v) {
     // fire-and-forget L2 reduction (RED.E.ADD.F64), no return value
     asm volatile("red.global.add.f64 [%0], %1;" ::"l"(addr), "d"(v) : "memory");
 }
+
+// per-thread asynchronous global->shared copies (LDGSTS); a thread that only reads back its OWN slots needs no barrier, just wait_all
+__device__ __forceinline__ void cp_async4(void* smem_dst, const void* gsrc) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(static_cast<uint32_t>(__cvta_generic_to_shared(smem_dst))), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(static_cast<uint32_t>(__cvta_generic_to_shared(smem_dst))), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
 __device__ __forceinline__ double warp_sum(double v) {
 #pragma unroll
@@ -146,6 +158,15 @@ __global__ void k0_camera_precompute(int Nc, const double* __restrict__ pose, do
 
 
 // ---------------------------------------------------------------------------------------------------------
+// A camera record into registers with 16-byte loads (the record is 160 bytes, 16-byte aligned): the per-observation gathers are
+// divergent (one record per lane), so the number of load instructions, not the bytes, is what the L1 tag stage pays for.
+template <int NDOUBLE2>
+__device__ __forceinline__ void load_camrec(const double* __restrict__ camrec, int c, double* __restrict__ dst) {
+    const double2* src = reinterpret_cast<const double2*>(camrec + size_t(c) * CAMREC);
+#pragma unroll
+    for (int k = 0; k < NDOUBLE2; ++k) { const double2 v = __ldg(src + k); dst[2 * k] = v.x; dst[2 * k + 1] = v.y; }
+}
+
 // Projection shared by K1 and K1': ReprojectCost::operator() (BundleAdjuster.h:38-68), trig-free thanks to K0.
 struct Proj { double X[3]; double P[3]; double iz, xn, yn, r0, r1; };
 
@@ -166,18 +187,49 @@ __device__ __forceinline__ void project_obs(const double* __restrict__ cr, const
 // One CTA per tile, one thread per observation; then one thread per point of the tile sums its observations'
 // Jp^T Jp and Jp^T r from shared memory (observations are sorted by point, so a point's are contiguous).
 // Algorithmic bytes: reads 24 No (uv, cam, pt ids) + 24 Np + 160 Nc; writes (144 [+64] + 16) No + 72 Np.
+// Persistent: CTA b walks tiles b, b+G, ...; the NEXT tile's index data (tile offsets two tiles ahead; camera id, point id and
+// pixel of this thread's observation one tile ahead) is loaded while the current tile is computed, so a tile's critical path
+// starts at the camera-record / point gathers instead of three dependent DRAM latencies earlier.  One cost partial per CTA.
 #ifndef K1_CTAS_PER_SM
-#define K1_CTAS_PER_SM 1
+#define K1_CTAS_PER_SM 2
 #endif
 __global__ void __launch_bounds__(TILE_OBS, K1_CTAS_PER_SM)
 k1_residual_jacobian(View V, const double* __restrict__ camrec, const double* __restrict__ intr, const double* __restrict__ pt,
                      RobustParams rp, double* __restrict__ cost_partial, int* __restrict__ bad_flag) {
     __shared__ double sJp[TILE_OBS][9];   // per observation: Jp (2x3) , r (2)  [+1 pad: stride 9 is conflict-free]
     __shared__ double sred[32];
-    const int t = blockIdx.x;
-    const int o0 = V.tile_off[t], o1 = V.tile_off[t + 1];
+    const int G = gridDim.x, nT = V.nTiles;
+    int t = blockIdx.x;
     double cost = 0.0;
     int bad = 0;
+    if (t >= nT) { if (threadIdx.x == 0) cost_partial[blockIdx.x] = 0.0; return; }
+    int o0 = V.tile_off[t], o1 = V.tile_off[t + 1];
+    // landing slots of the prefetch, double-buffered by tile parity: camera id, point id, pixel of this thread's observation
+    __shared__ int sPc[2][TILE_OBS];
+    __shared__ int sPp[2][TILE_OBS];
+    __shared__ __align__(16) double2 sPuv[2][TILE_OBS];
+    auto prefetch = [&](int buf, int a0, int a1) {
+        if (a0 + int(threadIdx.x) < a1) {
+            cp_async4(&sPc[buf][threadIdx.x], V.obs_cam + a0 + threadIdx.x);
+            cp_async4(&sPp[buf][threadIdx.x], V.obs_pt + a0 + threadIdx.x);
+            cp_async16(&sPuv[buf][threadIdx.x], V.obs_uv + a0 + threadIdx.x);
+        }
+        cp_async_commit();
+    };
+    int buf = 0;
+    prefetch(0, o0, o1);
+    int no0 = 0, no1 = 0;
+    if (t + G < nT) { no0 = V.tile_off[t + G]; no1 = V.tile_off[t + G + 1]; }
+    cp_async_wait_all();
+    __syncthreads();
+  for (;;) {
+    // ---- this tile's index data is in sP*[buf] (visible to all: barrier at the end of the previous trip); start the copies for
+    //      tile t+G into the other buffer and load the tile offsets of t+2G ----
+    int nno0 = 0, nno1 = 0;
+    if (t + G < nT) prefetch(buf ^ 1, no0, no1);
+    if (t + 2 * G < nT) { nno0 = V.tile_off[t + 2 * G]; nno1 = V.tile_off[t + 2 * G + 1]; }
+    const int pre_c = sPc[buf][threadIdx.x], pre_p = sPp[buf][threadIdx.x], pre_pf = sPp[buf][0];
+    const double2 pre_uv = sPuv[buf][threadIdx.x];
     // Tiles normally hold <= TILE_OBS observations; a single point with more observations than that forms its own
     // tile and is walked in chunks (its Hpp/g_p are then accumulated across chunks by thread 0's running sums).
     double Hl[6] = {0, 0, 0, 0, 0, 0}, gl[3] = {0, 0, 0};   // long-point accumulators (thread 0 only)
@@ -185,19 +237,22 @@ k1_residual_jacobian(View V, const double* __restrict__ camrec, const double* __
     for (int base = o0; base < o1; base += TILE_OBS) {
         const int o = base + threadIdx.x;
         const bool act = o < o1;
+        const bool first = base == o0;
         // by-point half, issued first so these dependent loads overlap the observation math: thread j takes the j-th point of the chunk
         const int lim = min(o1, base + TILE_OBS);
-        const int pfirst = V.obs_pt[base];
+        const int pfirst = first ? pre_pf : V.obs_pt[base];
         const int plast = V.obs_pt[lim - 1];
         const int pj = pfirst + threadIdx.x;
         int pa = 0, pb = 0;
         if (pj <= plast) { pa = max(V.pt_off[pj], base); pb = min(V.pt_off[pj + 1], lim); }
         if (act) {
-            const int c = V.obs_cam[o], p = V.obs_pt[o], g = V.Ng == 1 ? 0 : V.cam_group[c];   // one shared Camera: no dependent group load
-            const double* cr = camrec + size_t(c) * CAMREC;
+            const int c = first ? pre_c : V.obs_cam[o], p = first ? pre_p : V.obs_pt[o];
+            const int g = V.Ng == 1 ? 0 : V.cam_group[c];   // one shared Camera: no dependent group load
+            double cr[CAMREC];
+            load_camrec<CAMREC / 2>(camrec, c, cr);
             const double* in = intr + 4 * g;
             Proj q;
-            project_obs(cr, pt + 3 * size_t(p), in, ldg2(V.obs_uv + o), q);
+            project_obs(cr, pt + 3 * size_t(p), in, first ? pre_uv : ldg2(V.obs_uv + o), q);
             const double s = q.r0 * q.r0 + q.r1 * q.r1;
             double w;
             const double rho = robust(rp, s, w);
@@ -257,6 +312,17 @@ k1_residual_jacobian(View V, const double* __restrict__ camrec, const double* __
             }
             const double rr0 = w * q.r0, rr1 = w * q.r1;
             V.r2[o] = make_double2(rr0, rr1);
+            {   // by-observation record for K2c: whole sectors, so the by-camera gather fetches no byte it does not use
+                double2* A = V.JcA + size_t(o) * V.jca_stride;
+                A[0] = make_double2(wc * Ja0[0], wc * Ja1[0]); A[1] = make_double2(wc * Ja0[1], wc * Ja1[1]); A[2] = make_double2(wc * Ja0[2], wc * Ja1[2]);
+                A[3] = make_double2(wc * A0[0], wc * A1[0]); A[4] = make_double2(wc * A0[1], wc * A1[1]); A[5] = make_double2(wc * A0[2], wc * A1[2]);
+                A[6] = make_double2(rr0, rr1);
+                if (V.fi) {
+                    const double wi = V.grp_free[g] ? w : 0.0;
+                    A[7] = make_double2(wi * q.xn, 0.0); A[8] = make_double2(0.0, wi * q.yn); A[9] = make_double2(wi, 0.0); A[10] = make_double2(0.0, wi);
+                    A[11] = make_double2(0.0, 0.0);
+                } else A[7] = make_double2(0.0, 0.0);
+            }
             double chk = rr0 + rr1 + rho;
 #pragma unroll
             for (int k = 0; k < 3; ++k) chk += Ja0[k] + Ja1[k] + p0[k] + p1[k] + A0[k] + A1[k];
@@ -300,9 +366,16 @@ k1_residual_jacobian(View V, const double* __restrict__ camrec, const double* __
 #pragma unroll
         for (int k = 0; k < 3; ++k) V.gp[3 * size_t(p) + k] = gl[k];
     }
+    t += G;
+    if (t >= nT) break;
+    o0 = no0; o1 = no1; no0 = nno0; no1 = nno1;
+    buf ^= 1;
+    cp_async_wait_all();
+    __syncthreads();   // every thread's copies for the new tile have landed and are visible (sPp[buf][0] is read by all)
+  }
     if (bad) atomicOr(bad_flag, 1);
     const double cs = block_sum(cost, sred);
-    if (threadIdx.x == 0) cost_partial[t] = cs;
+    if (threadIdx.x == 0) cost_partial[blockIdx.x] = cs;
 }
 
 // K1' — candidate cost: residual + rho only.  Reads 24 No + 24 Np + 160 Nc, writes one partial per tile.
@@ -317,7 +390,9 @@ k1c_candidate_cost(View V, const double* __restrict__ camrec, const double* __re
     for (int o = o0 + threadIdx.x; o < o1; o += TILE_OBS) {
         const int c = V.obs_cam[o], p = V.obs_pt[o];
         Proj q;
-        project_obs(camrec + size_t(c) * CAMREC, pt + 3 * size_t(p), intr + (V.Ng == 1 ? 0 : 4 * V.cam_group[c]), ldg2(V.obs_uv + o), q);
+        double cr[12];   // R, t
+        load_camrec<6>(camrec, c, cr);
+        project_obs(cr, pt + 3 * size_t(p), intr + (V.Ng == 1 ? 0 : 4 * V.cam_group[c]), ldg2(V.obs_uv + o), q);
         const double s = q.r0 * q.r0 + q.r1 * q.r1;
         double w;
         const double rho = robust(rp, s, w);
@@ -543,8 +618,8 @@ k_schur_sweep(View V, const double* __restrict__ xin, double* __restrict__ yout,
 // K2c — by-camera half of K2: Hcc[c] = sum Jc^T Jc (6x6, stored full), gc[c] = sum Jc^T r, over the camera-sorted
 // observation list (one CTA per camera, fixed summation order => deterministic).  With free intrinsics also the
 // per-group 4x4 block and gradient (RED into Hii/gi, one per CTA and component).
-// v1 formulation: gathers Jc through perm_by_cam — 6 x 16 B + 16 B per observation, each in its own 32-byte sector,
-// i.e. DRAM traffic ~2x the 112 No algorithmic bytes.  
+// Gathers the by-observation records K1 wrote (JcA: Jc, r [, Ji] in 128 / 192 contiguous bytes = whole sectors) through
+// perm_by_cam.  (v1 gathered the SoA columns: 7 separate 16-byte pieces per observation, 3.1x DRAM over-fetch.)  
 template <bool FI>
 __global__ void __launch_bounds__(128)
 k2c_camera_blocks(View V, double* __restrict__ Hcc, double* __restrict__ gc, double* __restrict__ Hii, double* __restrict__ gi) {
@@ -552,21 +627,20 @@ k2c_camera_blocks(View V, double* __restrict__ Hcc, double* __restrict__ gc, dou
     __shared__ double sm[4][NV];
     const int c = blockIdx.x;
     const int a0 = V.cam_off[c], a1 = V.cam_off[c + 1];
-    const size_t ld = V.ldo;
     double acc[NV];
 #pragma unroll
     for (int k = 0; k < NV; ++k) acc[k] = 0.0;
     for (int i = a0 + threadIdx.x; i < a1; i += blockDim.x) {
         const int o = V.perm_by_cam[i];
-        const double2* J = V.J2 + o;
+        const double2* A = V.JcA + size_t(o) * V.jca_stride;   // one 128-byte (192-byte) record: whole sectors
         double2 j[FI ? 10 : 6];
 #pragma unroll
-        for (int k = 0; k < 6; ++k) j[k] = ldg2(J + k * ld);
+        for (int k = 0; k < 6; ++k) j[k] = ldg2(A + k);
+        const double2 r = ldg2(A + 6);
         if (FI) {
 #pragma unroll
-            for (int k = 0; k < 4; ++k) j[6 + k] = ldg2(J + (9 + k) * ld);
+            for (int k = 0; k < 4; ++k) j[6 + k] = ldg2(A + 7 + k);
         }
-        const double2 r = V.r2[o];
         int n = 0;
 #pragma unroll
         for (int a = 0; a < 6; ++a)
@@ -658,7 +732,9 @@ __device__ __forceinline__ double damping(double Hjj, double s, const LmParams l
 __global__ void k3_point_blocks(View V, LmParams lm, int* __restrict__ bad_flag) {
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= V.Np) return;
-    const double* H = V.Hpp + 6 * size_t(p);
+    const double2* Hv = reinterpret_cast<const double2*>(V.Hpp + 6 * size_t(p));   // 48-byte rows: three 16-byte loads
+    const double2 ha = Hv[0], hb = Hv[1], hc = Hv[2];
+    const double H[6] = {ha.x, ha.y, hb.x, hb.y, hc.x, hc.y};
     const double* s = V.sc_pt + 3 * size_t(p);
     double A[9];
     A[0] = H[0] + damping(H[0], s[0], lm); A[1] = H[1]; A[2] = H[2];
@@ -666,8 +742,8 @@ __global__ void k3_point_blocks(View V, LmParams lm, int* __restrict__ bad_flag)
     A[6] = H[2]; A[7] = H[4]; A[8] = H[5] + damping(H[5], s[2], lm);
     double I[9];
     if (!spd_inverse<3>(A, I)) { atomicOr(bad_flag, 2); for (int k = 0; k < 9; ++k) I[k] = 0.0; }
-    double* o = V.Hinv + 6 * size_t(p);
-    o[0] = I[0]; o[1] = I[1]; o[2] = I[2]; o[3] = I[4]; o[4] = I[5]; o[5] = I[8];
+    double2* o = reinterpret_cast<double2*>(V.Hinv + 6 * size_t(p));
+    o[0] = make_double2(I[0], I[1]); o[1] = make_double2(I[2], I[4]); o[2] = make_double2(I[5], I[8]);
     const double* g = V.gp + 3 * size_t(p);
     V.vp[3 * size_t(p)] = I[0] * g[0] + I[1] * g[1] + I[2] * g[2];
     V.vp[3 * size_t(p) + 1] = I[3] * g[0] + I[4] * g[1] + I[5] * g[2];
