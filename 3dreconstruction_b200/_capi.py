@@ -49,7 +49,8 @@ class BAOptions(C.Structure):
         ("stream", C.c_void_p),
         ("scatter_mode", C.c_int32),
         ("p2p_allreduce", C.c_int32),
-        ("reserved", C.c_int32 * 6),
+        ("lm_policy", C.c_int32),
+        ("reserved", C.c_int32 * 5),
     ]
 
 

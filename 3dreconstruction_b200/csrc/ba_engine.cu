@@ -492,7 +492,7 @@ void do_set_problem(ba_engine* e, const ba_problem* P) {
     setup_p2p(e);
 
     bak::View& V = e->V;
-    V.Nc = Nc; V.Ng = Ng; V.Np = Np; V.No = No; V.ldo = e->ldo; V.nTiles = e->nTiles; V.fi = e->fi;
+    V.Nc = Nc; V.Ng = Ng; V.Np = Np; V.No = No; V.ldo = e->ldo; V.nTiles = e->nTiles; V.fi = e->fi; V.left_twist = e->opt.lm_policy == BA_POLICY_G2O ? 1 : 0;
     V.tile_off = e->d_tile_off.p; V.obs_cam = e->d_obs_cam.p; V.obs_pt = e->d_obs_pt.p; V.obs_uv = e->d_obs_uv.p;
     V.pt_off = e->d_pt_off.p; V.cam_group = e->d_cam_group.p; V.cam_free = e->d_cam_free.p; V.grp_free = e->d_grp_free.p;
     V.perm_by_cam = e->d_perm.p; V.cam_off = e->d_cam_off.p;
@@ -579,13 +579,15 @@ void gradient_max(ba_engine* e) {
 }
 
 // x+ = x - y and the norms of K8; yf = PCG solution (pose | intrinsics part), yp in V.yp.
-void make_candidate(ba_engine* e, const double* yf) {
+void make_candidate(ba_engine* e, const double* yf, double lambda = 0.0) {
     cudaStream_t s = e->stream;
     bak::Scalars* sc = e->d_scal.p;
     LaunchTimer t(e, KID_K8);
-    KL(e), bak::k8_candidate_points<<<kNormBlocks, 256, 0, s>>>(e->V, e->d_pt.p, e->d_cpt.p, e->d_part0.p, e->d_part1.p);
+    double* scale_part = e->d_part1.p + 1024;   // third partial array (d_part1 holds >= 2048 doubles)
+    KL(e), bak::k8_candidate_points<<<kNormBlocks, 256, 0, s>>>(e->V, e->d_pt.p, e->d_cpt.p, e->d_part0.p, e->d_part1.p, scale_part, lambda);
     KL(e), bak::k8_candidate_cameras<<<1, 1024, 0, s>>>(e->Nc, e->Ng, e->fi, e->d_cam_free.p, e->d_grp_free.p, e->d_pose.p, e->d_intr.p, yf,
-                                                 e->d_cpose.p, e->d_cintr.p, e->d_part0.p, e->d_part1.p, kNormBlocks, sc);
+                                                 e->d_cpose.p, e->d_cintr.p, e->d_part0.p, e->d_part1.p, kNormBlocks, sc, scale_part, e->gc(), lambda,
+                                                 e->V.left_twist);
 }
 
 void candidate_cost(ba_engine* e) {
@@ -663,10 +665,10 @@ void launch_scatter(ba_engine* e, int kid, const double* xin, double* yout, cons
 
 // One linear solve of the LM step at trust-region radius `radius` (K3, K4, PCG with K5, K7).  Leaves the step in
 // d_x (pose|intrinsics part) and V.yp (points), the model cost change in scal.mcc.  Returns PCG iterations, or -1.
-int solve_linear(ba_engine* e, double radius, double* rel_out) {
+int solve_linear(ba_engine* e, double radius, double* rel_out, double lambda = 0.0) {
     cudaStream_t s = e->stream;
     bak::Scalars* sc = e->d_scal.p;
-    const bak::LmParams lm{radius, e->opt.min_lm_diagonal, e->opt.max_lm_diagonal};
+    const bak::LmParams lm{radius, e->opt.min_lm_diagonal, e->opt.max_lm_diagonal, e->opt.lm_policy == BA_POLICY_G2O ? 1 : 0, lambda};
     const bool priv = e->scatter_mode == 2 || e->scatter_mode == 3;
     const int vblocks = std::max(1, std::min(cdiv(e->nf, bak::PCG_BLOCK), 2 * e->num_sms));
     const int cblocks = std::max(1, cdiv((e->Nc + e->Ng) * 8, bak::PCG_BLOCK));
@@ -863,6 +865,96 @@ void lm_solve(ba_engine* e) {
     }
 }
 
+// ---- g2o policy: OptimizationAlgorithmLevenberg::solve + VertexSE3Expmap (same rules as oracle/ba_oracle.cpp::lm_solve_g2o) ----
+void lm_solve_g2o(ba_engine* e) {
+    const ba_options& O = e->opt;
+    cudaStream_t s = e->stream;
+    bak::Scalars* sc = e->d_scal.p;
+    bak::Scalars* H = e->h_scal;
+    ba_summary& S = e->summary;
+    std::memset(&S, 0, sizeof S);
+    S.num_residuals = 2 * e->NoG;
+    e->traj.clear();
+    e->kernel_launches = 0;
+    CU_TRY(cudaEventRecord(e->ev_t0, s));
+    auto finish = [&](int term, const char* msg, double cost) {
+        S.termination = term; S.usable = (term != BA_TERM_FAILURE); S.final_cost = cost; S.num_iterations = int(e->traj.size());
+        std::snprintf(S.message, sizeof S.message, "%s", msg);
+        CU_TRY(cudaEventRecord(e->ev_t1, s));
+        CU_TRY(cudaEventSynchronize(e->ev_t1));
+        float ms = 0.f;
+        CU_TRY(cudaEventElapsedTime(&ms, e->ev_t0, e->ev_t1));
+        S.solve_seconds = ms * 1e-3;
+        S.kernel_launches = e->kernel_launches;
+        resolve_timers(e);
+    };
+    e->d_yp.zero(s); e->d_x.zero(s);
+    evaluate_full(e);
+    {   // no Jacobi scaling in g2o: unit scales; lambda0 = 1e-5 * max diag(H)
+        LaunchTimer t(e, KID_MISC);
+        if (e->Np > 0) KL(e), bak::k_scales_points<<<cdiv(3 * e->Np, 256), 256, 0, s>>>(e->V, 0);
+        KL(e), bak::k_scales_cameras<<<cdiv(e->nf, 256), 256, 0, s>>>(e->Nc, e->Ng, e->fi, e->Hcc(), e->Hii(), e->d_sc_f.p, 0);
+        KL(e), bak::k_maxdiag_points<<<kNormBlocks, 256, 0, s>>>(e->V, e->d_part1.p);
+        KL(e), bak::k_maxdiag_final<<<1, 1024, 0, s>>>(e->Nc, e->Hcc(), e->d_part1.p, kNormBlocks, sc);
+        allreduce_max(e, &sc->maxdiag_pt, 1);
+    }
+    read_scalars(e);
+    double cost = H->cost;
+    S.initial_cost = cost;
+    if (H->bad_eval || !std::isfinite(cost)) { finish(BA_TERM_FAILURE, "initial residual/Jacobian evaluation failed (non-finite)", cost); return; }
+    double lambda = 1e-5 * std::max(H->maxdiag_pt, H->maxdiag_f), nu = 2.0;
+    { ba_iter_record R{}; R.step_is_valid = 1; R.step_is_successful = 1; R.cost = cost; e->traj.push_back(R); S.num_successful_steps = 1; }
+    int record = 0;
+    for (int iteration = 0; iteration < O.max_num_iterations; ++iteration) {
+        if (O.target_chi2 > 0.0 && 2.0 * cost <= O.target_chi2) { finish(BA_TERM_TARGET_REACHED, "target chi2 reached", cost); return; }
+        double rho = 0.0;
+        int qmax = 0;
+        do {
+            ba_iter_record R{}; R.iteration = ++record; R.radius_used = 1.0 / lambda; R.cost = cost;
+            double rel = 0.0;
+            const int its = solve_linear(e, 1.0 / lambda, &rel, lambda);
+            R.pcg_iterations = std::max(its, 0); R.pcg_rel_residual = rel; S.total_pcg_iterations += std::max(its, 0);
+            double tempChi = std::numeric_limits<double>::max(), scale = 0.0;
+            if (its >= 0) {
+                make_candidate(e, e->d_x.p, lambda);
+                candidate_cost(e);
+                if (O.world_size > 1) {
+                    NCCL_TRY(g_nccl.GroupStart());
+                    allreduce_sum(e, &sc->ccost, 1);
+                    allreduce_sum(e, &sc->scale_pt, 1);
+                    allreduce_flags(e, &sc->bad_cand, 1);
+                    NCCL_TRY(g_nccl.GroupEnd());
+                }
+                read_scalars(e);
+                if (!H->bad_cand && std::isfinite(H->ccost)) tempChi = 2.0 * H->ccost;
+                scale = H->scale_pt + H->scale_f;
+            }
+            R.step_is_valid = its >= 0;
+            R.candidate_cost = tempChi >= std::numeric_limits<double>::max() ? tempChi : 0.5 * tempChi;
+            R.model_cost_change = 0.5 * scale;
+            rho = (2.0 * cost - tempChi) / (scale + 1e-3);
+            R.relative_decrease = rho;
+            if (rho > 0.0 && std::isfinite(tempChi)) {
+                lambda *= std::max(1.0 / 3.0, std::min(1.0 - std::pow(2.0 * rho - 1.0, 3), 2.0 / 3.0)); nu = 2.0;
+                swap_params(e);
+                evaluate_full(e);
+                read_scalars(e);
+                cost = H->cost;
+                if (H->bad_eval || !std::isfinite(cost)) { finish(BA_TERM_FAILURE, "residual/Jacobian evaluation failed after an accepted step", cost); return; }
+                R.step_is_successful = 1; R.cost = cost; ++S.num_successful_steps;
+            } else {
+                lambda *= nu; nu *= 2.0; ++S.num_unsuccessful_steps;
+            }
+            R.radius = 1.0 / lambda;
+            e->traj.push_back(R);
+            if (!std::isfinite(lambda)) break;
+            ++qmax;
+        } while (rho < 0.0 && qmax < 10);
+        if (qmax == 10 || rho == 0.0 || !std::isfinite(lambda)) { finish(BA_TERM_CONVERGENCE, "g2o: no further improvement (trial limit, zero gain or lambda overflow)", cost); return; }
+    }
+    finish(BA_TERM_NO_CONVERGENCE, "maximum number of iterations reached", cost);
+}
+
 template <class F>
 int guarded(ba_engine* e, F&& f) {
     try { f(); return BA_OK; }
@@ -892,7 +984,7 @@ int ba_options_default(ba_options* o) {
     o->preconditioner = BA_PRECOND_JACOBI;                         // :171
     o->pcg_max_iterations = 2000; o->pcg_rel_tolerance = 1e-12; o->pcg_forcing = 0; o->eta = 0.1;
     o->target_chi2 = 0.0; o->device = 0; o->num_threads = 1;
-    o->rank = 0; o->world_size = 1; o->nccl_unique_id = nullptr; o->stream = nullptr; o->scatter_mode = 0; o->p2p_allreduce = 0;
+    o->rank = 0; o->world_size = 1; o->nccl_unique_id = nullptr; o->stream = nullptr; o->scatter_mode = 0; o->p2p_allreduce = 0; o->lm_policy = BA_POLICY_CERES;
     return BA_OK;
 }
 
@@ -901,6 +993,7 @@ int ba_create(const ba_options* opt, ba_engine** out) {
     if (opt->abi_version != BA_ABI_VERSION) return fail(nullptr, BA_ERR_INVALID_ARGUMENT, "abi_version mismatch");
     if (opt->linear_solver != BA_LINEAR_PCG) return fail(nullptr, BA_ERR_UNSUPPORTED, "the CUDA engine solves the reduced system by PCG only (linear_solver = BA_LINEAR_PCG)");
     if (opt->model != BA_MODEL_PINHOLE) return fail(nullptr, BA_ERR_UNSUPPORTED, "model not implemented by the CUDA engine yet");
+    if (opt->lm_policy == BA_POLICY_G2O && opt->intrinsics_free) return fail(nullptr, BA_ERR_UNSUPPORTED, "g2o policy: EdgeSE3ProjectXYZ has constant pinhole intrinsics (set intrinsics_free = 0)");
     if (opt->preconditioner != BA_PRECOND_JACOBI) return fail(nullptr, BA_ERR_UNSUPPORTED, "preconditioner not implemented by the CUDA engine yet");
     if (opt->world_size < 1 || opt->rank < 0 || opt->rank >= opt->world_size) return fail(nullptr, BA_ERR_INVALID_ARGUMENT, "bad rank/world_size");
     if (opt->world_size > 1 && !opt->nccl_unique_id) return fail(nullptr, BA_ERR_INVALID_ARGUMENT, "world_size > 1 needs nccl_unique_id");
@@ -968,7 +1061,7 @@ int ba_reset_state(ba_engine* e) {
 int ba_solve(ba_engine* e, ba_summary* out) {
     if (!e) return BA_ERR_INVALID_ARGUMENT;
     if (!e->has_problem) return fail(e, BA_ERR_NO_PROBLEM, "no problem set");
-    const int rc = guarded(e, [&] { CU_TRY(cudaSetDevice(e->device)); lm_solve(e); });
+    const int rc = guarded(e, [&] { CU_TRY(cudaSetDevice(e->device)); if (e->opt.lm_policy == BA_POLICY_G2O) lm_solve_g2o(e); else lm_solve(e); });
     if (out) *out = e->summary;
     return rc;
 }

@@ -28,6 +28,7 @@ struct View {
     int ldo;                     // leading dimension (observations) of J2 / r2
     int nTiles;
     int fi;                      // 1: intrinsics blocks are free (J2 has 13 column pairs)
+    int left_twist;              // 1: pose columns are d/d(omega, upsilon) of T <- exp(omega, upsilon) T (g2o policy); 0: d/d(angle-axis, t)
     const int* tile_off;         // [nTiles+1] first observation of each tile
     const int* obs_cam;          // [No]
     const int* obs_pt;           // [No] local point id, non-decreasing
@@ -276,6 +277,11 @@ k1_residual_jacobian(View V, const double* __restrict__ camrec, const double* __
             const double ca = cr[CR_A], cb = cr[CR_B], c1 = cr[CR_C1], c2 = cr[CR_C2], c3 = cr[CR_C3];
             const double hx = c1 * X0 + c2 * qx + c3 * d * ax, hy = c1 * X1 + c2 * qy + c3 * d * ay, hz = c1 * X2 + c2 * qz + c3 * d * az;
             double Ja0[3], Ja1[3];
+            if (V.left_twist) {   // g2o VertexSE3Expmap: dP/d(omega) = -[P]x  =>  row = P x A_i   (EdgeSE3ProjectXYZ::linearizeOplus)
+                const double P0 = q.P[0], P1 = q.P[1], P2 = q.P[2];
+                Ja0[0] = P1 * A0[2] - P2 * A0[1]; Ja0[1] = P2 * A0[0] - P0 * A0[2]; Ja0[2] = P0 * A0[1] - P1 * A0[0];
+                Ja1[0] = P1 * A1[2] - P2 * A1[1]; Ja1[1] = P2 * A1[0] - P0 * A1[2]; Ja1[2] = P0 * A1[1] - P1 * A1[0];
+            } else {
             {
                 const double Ah = A0[0] * hx + A0[2] * hz, Aa = A0[0] * ax + A0[2] * az;
                 const double cx0 = A0[1] * X2 - A0[2] * X1, cx1 = A0[2] * X0 - A0[0] * X2, cx2 = A0[0] * X1 - A0[1] * X0;  // A0 x X
@@ -289,6 +295,7 @@ k1_residual_jacobian(View V, const double* __restrict__ camrec, const double* __
                 Ja1[0] = Ah * ax - ca * cx0 + cb * (d * A1[0] + Aa * X0);
                 Ja1[1] = Ah * ay - ca * cx1 + cb * (d * A1[1] + Aa * X1);
                 Ja1[2] = Ah * az - ca * cx2 + cb * (d * A1[2] + Aa * X2);
+            }
             }
             const double wc = V.cam_free[c] ? w : 0.0;   // constant pose: its Jacobian columns vanish (SetParameterBlockConstant, :105)
             double2* J = V.J2 + o;
@@ -718,12 +725,13 @@ __device__ __forceinline__ bool spd_inverse(const double* A, double* Ainv) {
     return true;
 }
 
-struct LmParams { double radius, min_diag, max_diag; };
+struct LmParams { double radius, min_diag, max_diag; int policy; double lambda; };   // policy 1 (g2o): uniform damping lambda
 
 // Damping in unscaled coordinates: Ceres solves in Jacobi-scaled space with D^2 = clamp(diag(Js^T Js))/radius;
 // substituting Js = J diag(s) gives the identical step from (J^T J + D'^2) y = J^T r with
 //   D'^2_j = clamp(s_j^2 H_jj, min, max) / (s_j^2 radius).
 __device__ __forceinline__ double damping(double Hjj, double s, const LmParams lm) {
+    if (lm.policy == 1) return lm.lambda;
     const double s2 = s * s;
     return fmin(fmax(s2 * Hjj, lm.min_diag), lm.max_diag) / (s2 * lm.radius);
 }
@@ -803,6 +811,7 @@ struct Scalars {   // everything the host reads back, one D2H copy
     double cost, ccost, mcc, step2_pt, xn2_pt, step2_f, xn2_f, gmax_pt, gmax_f;
     PcgState2 pcg;
     int bad_eval, bad_cand, bad_lin, pad;
+    double maxdiag_pt, maxdiag_f, scale_pt, scale_f;   // g2o policy: max diagonal of H (lambda init), dx.(lambda dx + b)
 };
 
 __device__ __forceinline__ double apply_minv(int j, int Nc, const double* __restrict__ Minv, const double* __restrict__ r) {
@@ -823,33 +832,95 @@ __device__ __forceinline__ double apply_minv(int j, int Nc, const double* __rest
 //   step2 = sum (x - x+)^2 formed from the rounded difference exactly as Ceres does, xn2 = sum (x+)^2, free scalars only.
 __global__ void __launch_bounds__(256)
 k8_candidate_points(View V, const double* __restrict__ pt, double* __restrict__ cpt, double* __restrict__ step2_partial,
-                    double* __restrict__ xn2_partial) {
+                    double* __restrict__ xn2_partial, double* __restrict__ scale_partial, double lambda) {
     __shared__ double sred[32];
-    double s2 = 0.0, x2 = 0.0;
+    double s2 = 0.0, x2 = 0.0, sc = 0.0;
     for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < V.Np; p += gridDim.x * blockDim.x) {   // one point per thread and trip
         const bool fr = V.pt_off[p + 1] > V.pt_off[p];
         const size_t i = 3 * size_t(p);
 #pragma unroll
         for (int a = 0; a < 3; ++a) {
-            const double xo = pt[i + a];
-            const double xc = xo - V.yp[i + a];
+            const double xo = pt[i + a], y = V.yp[i + a];
+            const double xc = xo - y;
             cpt[i + a] = xc;
-            if (fr) { const double d = xo - xc; s2 += d * d; x2 += xc * xc; }
+            if (fr) { const double d = xo - xc; s2 += d * d; x2 += xc * xc; sc += y * (lambda * y + V.gp[i + a]); }
         }
     }
     s2 = block_sum(s2, sred);
     if (threadIdx.x == 0) step2_partial[blockIdx.x] = s2;
     x2 = block_sum(x2, sred);
     if (threadIdx.x == 0) xn2_partial[blockIdx.x] = x2;
+    sc = block_sum(sc, sred);
+    if (threadIdx.x == 0) scale_partial[blockIdx.x] = sc;
+}
+
+// SO(3) exponential / logarithm and the left SE(3) update of g2o's VertexSE3Expmap::oplus: T <- exp(omega, upsilon) T
+__device__ __forceinline__ void so3_exp_dev(const double w[3], double R[9]) {
+    const double th2 = w[0] * w[0] + w[1] * w[1] + w[2] * w[2], th = sqrt(th2);
+    double a, b;
+    if (th < 1e-5) { a = 1.0 - th2 / 6.0; b = 0.5 - th2 / 24.0; } else { a = sin(th) / th; b = (1.0 - cos(th)) / th2; }
+    R[0] = 1.0 - b * (w[1] * w[1] + w[2] * w[2]); R[1] = -a * w[2] + b * w[0] * w[1]; R[2] = a * w[1] + b * w[0] * w[2];
+    R[3] = a * w[2] + b * w[0] * w[1]; R[4] = 1.0 - b * (w[0] * w[0] + w[2] * w[2]); R[5] = -a * w[0] + b * w[1] * w[2];
+    R[6] = -a * w[1] + b * w[0] * w[2]; R[7] = a * w[0] + b * w[1] * w[2]; R[8] = 1.0 - b * (w[0] * w[0] + w[1] * w[1]);
+}
+__device__ __forceinline__ void so3_log_dev(const double R[9], double w[3]) {
+    double q[4];
+    const double tr = R[0] + R[4] + R[8];
+    if (tr > 0.0) { double t = sqrt(tr + 1.0); q[0] = 0.5 * t; t = 0.5 / t; q[1] = (R[7] - R[5]) * t; q[2] = (R[2] - R[6]) * t; q[3] = (R[3] - R[1]) * t; }
+    else {
+        int i = 0; if (R[4] > R[0]) i = 1; if (R[8] > R[4 * i]) i = 2;
+        const int j = (i + 1) % 3, k = (j + 1) % 3;
+        double t = sqrt(R[4 * i] - R[4 * j] - R[4 * k] + 1.0);
+        q[1 + i] = 0.5 * t; t = 0.5 / t;
+        q[0] = (R[3 * k + j] - R[3 * j + k]) * t; q[1 + j] = (R[3 * j + i] + R[3 * i + j]) * t; q[1 + k] = (R[3 * k + i] + R[3 * i + k]) * t;
+    }
+    if (q[0] < 0.0) { q[0] = -q[0]; q[1] = -q[1]; q[2] = -q[2]; q[3] = -q[3]; }
+    const double n = sqrt(q[1] * q[1] + q[2] * q[2] + q[3] * q[3]);
+    if (n == 0.0) { w[0] = w[1] = w[2] = 0.0; return; }
+    const double ang = 2.0 * atan2(n, q[0]);
+    w[0] = ang * q[1] / n; w[1] = ang * q[2] / n; w[2] = ang * q[3] / n;
+}
+__device__ __forceinline__ void se3_left_update_dev(const double* pose, const double w[3], const double u[3], double* out) {
+    double Rd[9], R[9], Rn[9];
+    const double aa[3] = {pose[0], pose[1], pose[2]};
+    so3_exp_dev(w, Rd); so3_exp_dev(aa, R);
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+        for (int j = 0; j < 3; ++j) Rn[i * 3 + j] = Rd[i * 3] * R[j] + Rd[i * 3 + 1] * R[3 + j] + Rd[i * 3 + 2] * R[6 + j];
+    const double th2 = w[0] * w[0] + w[1] * w[1] + w[2] * w[2], th = sqrt(th2);
+    double b, c;
+    if (th < 1e-5) { b = 0.5 - th2 / 24.0; c = 1.0 / 6.0 - th2 / 120.0; } else { b = (1.0 - cos(th)) / th2; c = (th - sin(th)) / (th2 * th); }
+    const double wu[3] = {w[1] * u[2] - w[2] * u[1], w[2] * u[0] - w[0] * u[2], w[0] * u[1] - w[1] * u[0]};
+    const double wwu[3] = {w[1] * wu[2] - w[2] * wu[1], w[2] * wu[0] - w[0] * wu[2], w[0] * wu[1] - w[1] * wu[0]};
+    double lg[3];
+    so3_log_dev(Rn, lg);
+    out[0] = lg[0]; out[1] = lg[1]; out[2] = lg[2];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) out[3 + i] = Rd[i * 3] * pose[3] + Rd[i * 3 + 1] * pose[4] + Rd[i * 3 + 2] * pose[5] + u[i] + b * wu[i] + c * wwu[i];
 }
 
 __global__ void __launch_bounds__(1024)
 k8_candidate_cameras(int Nc, int Ng, int fi, const unsigned char* __restrict__ cam_free, const unsigned char* __restrict__ grp_free,
                      const double* __restrict__ pose, const double* __restrict__ intr, const double* __restrict__ yf,
                      double* __restrict__ cpose, double* __restrict__ cintr, const double* __restrict__ step2_partial,
-                     const double* __restrict__ xn2_partial, int npartial, Scalars* __restrict__ sc) {
+                     const double* __restrict__ xn2_partial, int npartial, Scalars* __restrict__ sc,
+                     const double* __restrict__ scale_partial, const double* __restrict__ gc, double lambda, int left_twist) {
     __shared__ double sred[32];
-    double s2 = 0.0, x2 = 0.0, ps = 0.0, px = 0.0;
+    double s2 = 0.0, x2 = 0.0, ps = 0.0, px = 0.0, sf = 0.0, sp = 0.0;
+    if (left_twist) {   // g2o policy: T <- exp(-y_omega, -y_upsilon) T per free pose; dx.(lambda dx + b) with dx = -y, b = -g
+        for (int c = threadIdx.x; c < Nc; c += blockDim.x) {
+            if (cam_free[c]) {
+                const double w[3] = {-yf[6 * c], -yf[6 * c + 1], -yf[6 * c + 2]}, u[3] = {-yf[6 * c + 3], -yf[6 * c + 4], -yf[6 * c + 5]};
+                se3_left_update_dev(pose + 6 * c, w, u, cpose + 6 * c);
+#pragma unroll
+                for (int k = 0; k < 6; ++k) { const double y = yf[6 * c + k]; sf += y * (lambda * y + gc[6 * c + k]); const double d = pose[6 * c + k] - cpose[6 * c + k]; s2 += d * d; x2 += cpose[6 * c + k] * cpose[6 * c + k]; }
+            } else {
+#pragma unroll
+                for (int k = 0; k < 6; ++k) cpose[6 * c + k] = pose[6 * c + k];
+            }
+        }
+    } else
     for (int j = threadIdx.x; j < 6 * Nc; j += blockDim.x) {
         const double xo = pose[j];
         if (cam_free[j / 6]) { const double xc = xo - yf[j]; cpose[j] = xc; const double d = xo - xc; s2 += d * d; x2 += xc * xc; }
@@ -860,7 +931,7 @@ k8_candidate_cameras(int Nc, int Ng, int fi, const unsigned char* __restrict__ c
         if (fi && grp_free[j / 4]) { const double xc = xo - yf[6 * Nc + j]; cintr[j] = xc; const double d = xo - xc; s2 += d * d; x2 += xc * xc; }
         else cintr[j] = xo;
     }
-    for (int j = threadIdx.x; j < npartial; j += blockDim.x) { ps += step2_partial[j]; px += xn2_partial[j]; }   // point-side partials (fixed order)
+    for (int j = threadIdx.x; j < npartial; j += blockDim.x) { ps += step2_partial[j]; px += xn2_partial[j]; sp += scale_partial[j]; }   // point-side partials (fixed order)
     s2 = block_sum(s2, sred);
     if (threadIdx.x == 0) sc->step2_f = s2;
     x2 = block_sum(x2, sred);
@@ -869,6 +940,42 @@ k8_candidate_cameras(int Nc, int Ng, int fi, const unsigned char* __restrict__ c
     if (threadIdx.x == 0) sc->step2_pt = ps;
     px = block_sum(px, sred);
     if (threadIdx.x == 0) sc->xn2_pt = px;
+    sf = block_sum(sf, sred);
+    if (threadIdx.x == 0) sc->scale_f = sf;
+    sp = block_sum(sp, sred);
+    if (threadIdx.x == 0) sc->scale_pt = sp;
+}
+
+// g2o computeLambdaInit: max diagonal entry of H over point blocks (per-block partial) and pose blocks (final kernel).
+__global__ void __launch_bounds__(256)
+k_maxdiag_points(View V, double* __restrict__ max_partial) {
+    __shared__ double smax[32];
+    double m = 0.0;
+    for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < V.Np; p += gridDim.x * blockDim.x) {
+        const double* H = V.Hpp + 6 * size_t(p);
+        m = fmax(m, fmax(fabs(H[0]), fmax(fabs(H[3]), fabs(H[5]))));
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if ((threadIdx.x & 31) == 0) smax[threadIdx.x >> 5] = m;
+    __syncthreads();
+    if (threadIdx.x == 0) { double r = 0.0; for (int w = 0; w < (blockDim.x >> 5); ++w) r = fmax(r, smax[w]); max_partial[blockIdx.x] = r; }
+}
+__global__ void __launch_bounds__(1024)
+k_maxdiag_final(int Nc, const double* __restrict__ Hcc, const double* __restrict__ max_partial, int npartial, Scalars* __restrict__ sc) {
+    __shared__ double smax[32];
+    double m = 0.0, mp = 0.0;
+    for (int j = threadIdx.x; j < 6 * Nc; j += blockDim.x) m = fmax(m, fabs(Hcc[36 * size_t(j / 6) + 7 * (j % 6)]));
+    for (int j = threadIdx.x; j < npartial; j += blockDim.x) mp = fmax(mp, max_partial[j]);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) { m = fmax(m, __shfl_xor_sync(0xffffffffu, m, o)); mp = fmax(mp, __shfl_xor_sync(0xffffffffu, mp, o)); }
+    if ((threadIdx.x & 31) == 0) smax[threadIdx.x >> 5] = m;
+    __syncthreads();
+    if (threadIdx.x == 0) { double r = 0.0; for (int w = 0; w < 32; ++w) r = fmax(r, smax[w]); sc->maxdiag_f = r; }
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) smax[threadIdx.x >> 5] = mp;
+    __syncthreads();
+    if (threadIdx.x == 0) { double r = 0.0; for (int w = 0; w < 32; ++w) r = fmax(r, smax[w]); sc->maxdiag_pt = r; }
 }
 
 // max |x - (x + (-g))| over free scalars — the minimizer's gradient_max_norm (Plus(x, -g) lifted back, SURVEY a-LM).

@@ -65,6 +65,15 @@ typedef enum ba_preconditioner { BA_PRECOND_JACOBI = 0 /* blockdiag(Hcc + Dc^2) 
 /* Which rule selects the first-order branch of AngleAxisRotatePoint. */
 typedef enum ba_taylor_rule { BA_TAYLOR_THETA2_LE_EPS = 0 /* theta^2 <= DBL_EPSILON */, BA_TAYLOR_THETA_IS_ZERO = 1 /* hypot()==0 */ } ba_taylor_rule;
 
+/* Which minimizer policy drives the outer loop.
+ * CERES: trust-region LM exactly as the reference configures it (BundleAdjuster.h:167-174) — the parity target.
+ * G2O:   g2o's OptimizationAlgorithmLevenberg + VertexSE3Expmap/EdgeSE3ProjectXYZ semantics, for the north star's literal wording
+ *        (the reference finds g2o with CMake but never calls it): lambda0 = 1e-5 max diag(H), uniform damping H + lambda I, no
+ *        Jacobi scaling, gain ratio (chi2 - chi2+) / (dx.(lambda dx + b) + 1e-3), accept iff > 0, lambda *= clamp(1-(2rho-1)^3, 1/3, 2/3)
+ *        on success and *= nu (nu doubles) on failure, <= 10 trials per iteration, stop after max_num_iterations iterations;
+ *        poses move by the SE3 exponential map on the left, T <- exp(omega, upsilon) T; intrinsics are constant. */
+typedef enum ba_lm_policy { BA_POLICY_CERES = 0, BA_POLICY_G2O = 1 } ba_lm_policy;
+
 typedef enum ba_termination {
     BA_TERM_CONVERGENCE = 0,    /* function / parameter / gradient tolerance or minimum radius reached */
     BA_TERM_NO_CONVERGENCE = 1, /* iteration cap */
@@ -114,7 +123,8 @@ typedef struct ba_options {
     int32_t scatter_mode;                /* engine camera-side scatter: 0 = default (4), 1 = red.global.add.f64, 2 = private accumulators, 3 = 2 + bulk-copy pipeline, 4 = partial rows, 5 = 4 as a persistent cp.async pipeline (measured slower) */
     int32_t p2p_allreduce;               /* multi-GPU all-reduce of the PCG matvec: 0 = auto (one-shot NVLink peer-memory all-reduce fused into the
                                             K5b gather when every peer buffer can be mapped with CUDA IPC, else NCCL), 1 = NCCL only, 2 = peer memory required */
-    int32_t reserved[6];
+    int32_t lm_policy;                   /* ba_lm_policy; default CERES */
+    int32_t reserved[5];
 } ba_options;
 
 /* Problem in canonical indexing: observations sorted by point id (non-decreasing obs_pt),

@@ -179,6 +179,13 @@ bool evaluate_model(ba_engine* e, const double* pose, const double* intr, const 
             for (int k = 0; k < 3; ++k) jx[k] = J13(pt[3 * p + k], 10 + k);
             f(ji, je, jx, jr);
             for (int q = 0; q < 2; ++q) { res[q] = jr[q].a; for (int k = 0; k < 13; ++k) jac[q][k] = jr[q].v[k]; }
+            if (e->opt.lm_policy == BA_POLICY_G2O) {   // left twist (omega, upsilon): dP/d(omega) = -[P]x, dP/d(upsilon) = I  =>  row_omega = P x row_t
+                double P[3];
+                oracle::angle_axis_rotate_point(&pose[6 * c], &pt[3 * p], P, e->opt.taylor_rule);
+                P[0] += pose[6 * c + 3]; P[1] += pose[6 * c + 4]; P[2] += pose[6 * c + 5];
+                for (int q = 0; q < 2; ++q) { const double* a = &jac[q][7];
+                    jac[q][4] = P[1] * a[2] - P[2] * a[1]; jac[q][5] = P[2] * a[0] - P[0] * a[2]; jac[q][6] = P[0] * a[1] - P[1] * a[0]; }
+            }
             if (!finite_all(&jac[0][0], 26)) bad[tid] = 1;
         } else {
             f(&intr[4 * g], &pose[6 * c], &pt[3 * p], res);
@@ -474,6 +481,122 @@ void column_sqnorms(const ba_engine* e, vector<double>& n_cam, vector<double>& n
     }
 }
 
+// ---- g2o policy: OptimizationAlgorithmLevenberg + VertexSE3Expmap, restated from g2o's published algorithm ----
+void so3_exp(const double w[3], double R[9]) {
+    const double th2 = w[0] * w[0] + w[1] * w[1] + w[2] * w[2], th = std::sqrt(th2);
+    double a, b;   // R = I + a [w]x + b [w]x^2
+    if (th < 1e-5) { a = 1.0 - th2 / 6.0; b = 0.5 - th2 / 24.0; } else { a = std::sin(th) / th; b = (1.0 - std::cos(th)) / th2; }
+    const double K[9] = {0, -w[2], w[1], w[2], 0, -w[0], -w[1], w[0], 0};
+    for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) {
+        double k2 = 0; for (int m = 0; m < 3; ++m) k2 += K[i * 3 + m] * K[m * 3 + j];
+        R[i * 3 + j] = (i == j ? 1.0 : 0.0) + a * K[i * 3 + j] + b * k2;
+    }
+}
+void so3_log(const double R[9], double w[3]) {   // through the unit quaternion, angle in [0, pi]
+    double q[4]; const double tr = R[0] + R[4] + R[8];
+    if (tr > 0.0) { double t = std::sqrt(tr + 1.0); q[0] = 0.5 * t; t = 0.5 / t; q[1] = (R[7] - R[5]) * t; q[2] = (R[2] - R[6]) * t; q[3] = (R[3] - R[1]) * t; }
+    else { int i = 0; if (R[4] > R[0]) i = 1; if (R[8] > R[4 * i]) i = 2; const int j = (i + 1) % 3, k = (j + 1) % 3;
+           double t = std::sqrt(R[4 * i] - R[4 * j] - R[4 * k] + 1.0); q[1 + i] = 0.5 * t; t = 0.5 / t;
+           q[0] = (R[3 * k + j] - R[3 * j + k]) * t; q[1 + j] = (R[3 * j + i] + R[3 * i + j]) * t; q[1 + k] = (R[3 * k + i] + R[3 * i + k]) * t; }
+    if (q[0] < 0.0) for (double& v : q) v = -v;
+    const double n = std::sqrt(q[1] * q[1] + q[2] * q[2] + q[3] * q[3]);
+    if (n == 0.0) { w[0] = w[1] = w[2] = 0.0; return; }
+    const double ang = 2.0 * std::atan2(n, q[0]);
+    for (int i = 0; i < 3; ++i) w[i] = ang * q[1 + i] / n;
+}
+// pose <- exp(omega, upsilon) * pose  (VertexSE3Expmap::oplus): R' = exp(w) R, t' = exp(w) t + V(w) u
+void se3_left_update(const double pose[6], const double w[3], const double u[3], double out[6]) {
+    double Rd[9], R[9], Rn[9];
+    so3_exp(w, Rd); so3_exp(pose, R);
+    for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) { double v = 0; for (int m = 0; m < 3; ++m) v += Rd[i * 3 + m] * R[m * 3 + j]; Rn[i * 3 + j] = v; }
+    const double th2 = w[0] * w[0] + w[1] * w[1] + w[2] * w[2], th = std::sqrt(th2);
+    double b, c;   // V = I + b [w]x + c [w]x^2
+    if (th < 1e-5) { b = 0.5 - th2 / 24.0; c = 1.0 / 6.0 - th2 / 120.0; } else { b = (1.0 - std::cos(th)) / th2; c = (th - std::sin(th)) / (th2 * th); }
+    const double wu[3] = {w[1] * u[2] - w[2] * u[1], w[2] * u[0] - w[0] * u[2], w[0] * u[1] - w[1] * u[0]};
+    const double wwu[3] = {w[1] * wu[2] - w[2] * wu[1], w[2] * wu[0] - w[0] * wu[2], w[0] * wu[1] - w[1] * wu[0]};
+    so3_log(Rn, out);
+    for (int i = 0; i < 3; ++i) out[3 + i] = Rd[i * 3] * pose[3] + Rd[i * 3 + 1] * pose[4] + Rd[i * 3 + 2] * pose[5] + u[i] + b * wu[i] + c * wwu[i];
+}
+
+int lm_solve_g2o(ba_engine* e) {
+    const ba_options& O = e->opt;
+    const int Nc = e->Nc, Ng = e->Ng, Np = e->Np, No = e->No, ni = e->ni;
+    const auto t0 = std::chrono::steady_clock::now();
+    ba_summary& S = e->summary; std::memset(&S, 0, sizeof S);
+    S.num_residuals = 2 * No;
+    e->traj.clear();
+    e->r.assign(size_t(2) * No, 0.0); e->Jc.assign(size_t(12) * No, 0.0); e->Jp.assign(size_t(6) * No, 0.0); e->Ji.assign(size_t(2) * ni * No, 0.0);
+    e->sc_cam.assign(size_t(6) * Nc, 1.0); e->sc_intr.assign(size_t(ni) * Ng, 1.0); e->sc_pt.assign(size_t(3) * Np, 1.0);
+    vector<double>&pose = e->pose, &pt = e->pt;
+    vector<double> cpose(pose), cpt(pt), g_cam(6 * Nc), g_intr(ni * Ng), g_pt(3 * Np), y_cam(6 * Nc), y_intr(ni * Ng), y_pt(3 * Np);
+    auto finish = [&](int term, const char* msg, double cost) {
+        S.termination = term; S.usable = (term != BA_TERM_FAILURE); S.final_cost = cost; S.num_iterations = int(e->traj.size());
+        std::snprintf(S.message, sizeof S.message, "%s", msg);
+        S.solve_seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+        return BA_OK;
+    };
+    double cost = 0.0;
+    if (!evaluate(e, pose.data(), e->intr.data(), pt.data(), true, &cost, e->r.data(), e->Jc.data(), e->Jp.data(), e->Ji.data(), false)) {
+        S.initial_cost = cost;
+        return finish(BA_TERM_FAILURE, "initial residual/Jacobian evaluation failed (non-finite)", cost);
+    }
+    S.initial_cost = cost;
+    { ba_iter_record R{}; R.step_is_valid = 1; R.step_is_successful = 1; R.cost = cost; e->traj.push_back(R); S.num_successful_steps = 1; }
+    double lambda = 0.0, ni_fac = 2.0;
+    const vector<double> ones_c(6 * Nc, 1.0), ones_i(ni * Ng, 1.0), ones_p(3 * Np, 1.0);
+    int record = 0;
+    for (int iteration = 0; iteration < O.max_num_iterations; ++iteration) {
+        if (O.target_chi2 > 0.0 && 2.0 * cost <= O.target_chi2) return finish(BA_TERM_TARGET_REACHED, "target chi2 reached", cost);
+        gradient(e, e->r.data(), e->Jc.data(), e->Jp.data(), e->Ji.data(), g_cam.data(), g_intr.data(), g_pt.data());
+        if (iteration == 0) {   // computeLambdaInit: tau * max diagonal of H
+            vector<double> n_cam, n_intr, n_pt; column_sqnorms(e, n_cam, n_intr, n_pt);
+            double mx = 0.0;
+            for (double v : n_cam) mx = std::max(mx, v);
+            for (double v : n_pt) mx = std::max(mx, v);
+            lambda = 1e-5 * mx; ni_fac = 2.0;
+        }
+        double rho = 0.0; int qmax = 0;
+        do {
+            ba_iter_record R{}; R.iteration = ++record; R.radius_used = 1.0 / lambda; R.cost = cost;
+            StepOut so = solve_step(e, 1.0 / lambda, ones_c, ones_i, ones_p, y_cam, y_intr, y_pt);
+            R.pcg_iterations = so.pcg_iters; R.pcg_rel_residual = so.pcg_res; S.total_pcg_iterations += so.pcg_iters;
+            double tempChi = std::numeric_limits<double>::max(), scale = 0.0;
+            if (so.ok) {
+                for (int c = 0; c < Nc; ++c) {
+                    if (!e->cam_free[c]) { for (int k = 0; k < 6; ++k) cpose[6 * c + k] = pose[6 * c + k]; continue; }
+                    const double w[3] = {-y_cam[6 * c], -y_cam[6 * c + 1], -y_cam[6 * c + 2]}, u[3] = {-y_cam[6 * c + 3], -y_cam[6 * c + 4], -y_cam[6 * c + 5]};
+                    se3_left_update(&pose[6 * c], w, u, &cpose[6 * c]);
+                }
+                for (int j = 0; j < 3 * Np; ++j) cpt[j] = pt[j] - y_pt[j];
+                double ccost = 0.0;
+                if (evaluate(e, cpose.data(), e->intr.data(), cpt.data(), false, &ccost, nullptr, nullptr, nullptr, nullptr, false)) tempChi = 2.0 * ccost;
+                for (int j = 0; j < 6 * Nc; ++j) scale += y_cam[j] * (lambda * y_cam[j] + g_cam[j]);   // dx.(lambda dx + b), dx = -y, b = -g
+                for (int j = 0; j < 3 * Np; ++j) scale += y_pt[j] * (lambda * y_pt[j] + g_pt[j]);
+            }
+            R.step_is_valid = so.ok; R.candidate_cost = tempChi >= std::numeric_limits<double>::max() ? tempChi : 0.5 * tempChi;
+            R.model_cost_change = 0.5 * scale;
+            rho = (2.0 * cost - tempChi) / (scale + 1e-3);
+            R.relative_decrease = rho;
+            if (rho > 0.0 && std::isfinite(tempChi)) {
+                const double alpha = std::min(1.0 - std::pow(2.0 * rho - 1.0, 3), 2.0 / 3.0);
+                lambda *= std::max(1.0 / 3.0, alpha); ni_fac = 2.0;
+                pose = cpose; pt = cpt;
+                if (!evaluate(e, pose.data(), e->intr.data(), pt.data(), true, &cost, e->r.data(), e->Jc.data(), e->Jp.data(), e->Ji.data(), false))
+                    return finish(BA_TERM_FAILURE, "residual/Jacobian evaluation failed after an accepted step", cost);
+                R.step_is_successful = 1; R.cost = cost; ++S.num_successful_steps;
+            } else {
+                lambda *= ni_fac; ni_fac *= 2.0; ++S.num_unsuccessful_steps;
+            }
+            R.radius = 1.0 / lambda;
+            e->traj.push_back(R);
+            if (!std::isfinite(lambda)) break;
+            ++qmax;
+        } while (rho < 0.0 && qmax < 10);
+        if (qmax == 10 || rho == 0.0 || !std::isfinite(lambda)) return finish(BA_TERM_CONVERGENCE, "g2o: no further improvement (trial limit, zero gain or lambda overflow)", cost);
+    }
+    return finish(BA_TERM_NO_CONVERGENCE, "maximum number of iterations reached", cost);
+}
+
 int lm_solve(ba_engine* e) {
     const ba_options& O = e->opt;
     const int Nc = e->Nc, Ng = e->Ng, Np = e->Np, No = e->No, ni = e->ni;
@@ -618,7 +741,7 @@ int ba_options_default(ba_options* o) {
     o->preconditioner = BA_PRECOND_JACOBI;                         // :171
     o->pcg_max_iterations = 2000; o->pcg_rel_tolerance = 1e-12; o->pcg_forcing = 0; o->eta = 0.1;
     o->target_chi2 = 0.0; o->device = 0; o->num_threads = 1;       // :170
-    o->rank = 0; o->world_size = 1; o->nccl_unique_id = nullptr; o->stream = nullptr; o->scatter_mode = 0;
+    o->rank = 0; o->world_size = 1; o->nccl_unique_id = nullptr; o->stream = nullptr; o->scatter_mode = 0; o->p2p_allreduce = 0; o->lm_policy = BA_POLICY_CERES;
     return BA_OK;
 }
 
@@ -626,6 +749,7 @@ int ba_create(const ba_options* opt, ba_engine** out) {
     if (!opt || !out) return fail(nullptr, BA_ERR_INVALID_ARGUMENT, "null argument");
     if (opt->abi_version != BA_ABI_VERSION) return fail(nullptr, BA_ERR_INVALID_ARGUMENT, "abi_version mismatch");
     if (opt->world_size != 1) return fail(nullptr, BA_ERR_UNSUPPORTED, "the CPU oracle is single-process");
+    if (opt->lm_policy == BA_POLICY_G2O && (opt->intrinsics_free || opt->model != BA_MODEL_PINHOLE)) return fail(nullptr, BA_ERR_UNSUPPORTED, "g2o policy: EdgeSE3ProjectXYZ has constant pinhole intrinsics (set intrinsics_free = 0)");
     ba_engine* e = new (std::nothrow) ba_engine();
     if (!e) return fail(nullptr, BA_ERR_INTERNAL, "out of memory");
     e->opt = *opt;
@@ -669,7 +793,7 @@ int ba_reset_state(ba_engine* e) {
 int ba_solve(ba_engine* e, ba_summary* out) {
     if (!e) return BA_ERR_INVALID_ARGUMENT;
     if (!e->has_problem) return fail(e, BA_ERR_NO_PROBLEM, "no problem set");
-    const int rc = lm_solve(e);
+    const int rc = e->opt.lm_policy == BA_POLICY_G2O ? lm_solve_g2o(e) : lm_solve(e);
     if (out) *out = e->summary;
     return rc;
 }

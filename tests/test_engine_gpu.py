@@ -187,3 +187,16 @@ def test_multi_gpu_matches_single_gpu():
                         "--master-port", "29517", os.path.join(root, "tools", "multi_gpu_check.py"), "ladybug"], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     assert "MISMATCH" not in r.stdout and "OK" in r.stdout
+
+
+@pytest.mark.parametrize("name", ["tiny", "ladybug", "trafalgar"])
+def test_g2o_policy_trajectory_parity(ba, oracle, name):
+    """g2o policy (Levenberg lambda schedule, uniform damping, SE3 exp-map pose update): engine against the oracle in the same policy."""
+    P = ba.synth(name)
+    (se, te, xe), (so, to, xo) = solve_both(ba, oracle, P, intrinsics_free=0, lm_policy=1, max_num_iterations=10)
+    assert se.usable and so.usable and len(te) == len(to) and se.termination == so.termination
+    assert_trajectory_parity(te, to)
+    for a, b in zip(te, to):
+        assert a.relative_decrease == pytest.approx(b.relative_decrease, rel=1e-3, abs=1e-7)   # (chi2 - chi2+) cancels near convergence
+    assert rel_err(xe[0], xo[0]) <= STATE_RTOL and rel_err(xe[2], xo[2]) <= STATE_RTOL
+    assert np.array_equal(xe[1], P.intr)

@@ -211,3 +211,96 @@ def test_termination_usable_flags(ba, oracle):
         h.set_problem(P)
         s = h.solve()
     assert s.termination == 0 and s.usable and s.num_residuals == 2 * P.obs_cam.size
+
+
+# ---- g2o policy: Levenberg rules and the SE3 exponential-map pose update, against SciPy ---------------------
+def twist_update(pose, w, u):
+    """exp((w, u)^) * T with scipy.linalg.expm on the 4x4 twist (independent of the oracle's closed forms); returns (R', t')."""
+    import cv2
+    from scipy.linalg import expm
+    X = np.zeros((4, 4))
+    X[:3, :3] = [[0, -w[2], w[1]], [w[2], 0, -w[0]], [-w[1], w[0], 0]]
+    X[:3, 3] = u
+    E = expm(X)
+    R = cv2.Rodrigues(np.asarray(pose[:3], np.float64).reshape(3, 1))[0]
+    return E[:3, :3] @ R, E[:3, :3] @ np.asarray(pose[3:]) + E[:3, 3]
+
+
+def test_g2o_left_twist_jacobian_vs_finite_differences(ba, oracle):
+    import cv2
+    rng = np.random.default_rng(8)
+    intr = (FX, FY, CX, CY)
+    for _ in range(10):
+        pose = np.concatenate([rng.normal(0, 0.4, 3), rng.normal(0, 1, 3)])
+        X = rng.normal(0, 1, 3) + [0, 0, 7]
+        e = evaluate(oracle, one_obs(ba, pose, X, [10, 20]), robust_kind=0, intrinsics_free=0, lm_policy=1)
+
+        def proj(d):
+            R, t = twist_update(pose, d[:3], d[3:])
+            return rm.project_np(intr, np.r_[cv2.Rodrigues(R)[0].ravel(), t], X)
+        h = 1e-6
+        J = np.stack([(proj(h * np.eye(6)[k]) - proj(-h * np.eye(6)[k])) / (2 * h) for k in range(6)], axis=1)
+        assert np.abs(e["Jc"][0] - J).max() <= 1e-6 * np.abs(J).max()
+
+
+def test_g2o_first_iteration_vs_scipy(ba, oracle):
+    """lambda0 = 1e-5 max diag(H), uniform damping, dense solve of the FULL normal equations, exp-map pose update."""
+    import cv2
+    P = ba.synth("tiny", seed=4)
+    opts = dict(intrinsics_free=0, lm_policy=1, robust_kind=1, robust_a=4.0)
+    e = evaluate(oracle, P, **opts)
+    Nc, _, Np, No = P.sizes
+    J = np.zeros((2 * No, 6 * Nc + 3 * Np))
+    for o in range(No):
+        c, p = int(P.obs_cam[o]), int(P.obs_pt[o])
+        J[2 * o:2 * o + 2, 6 * c:6 * c + 6] = e["Jc"][o]
+        J[2 * o:2 * o + 2, 6 * Nc + 3 * p:6 * Nc + 3 * p + 3] = e["Jp"][o]
+    H = J.T @ J
+    lam = 1e-5 * np.diag(H).max()
+    act = np.diag(H) > 0
+    y = np.zeros(H.shape[0])
+    y[act] = np.linalg.solve((H + lam * np.eye(H.shape[0]))[np.ix_(act, act)], (J.T @ e["r"].ravel())[act])
+    with oracle.create(oracle.default_options(max_num_iterations=1, **opts)) as h:
+        h.set_problem(P)
+        h.solve()
+        t = h.trajectory()
+        pose, intr, pt = h.get_state()
+    assert t[1].step_is_successful and t[1].radius_used == pytest.approx(1.0 / lam, rel=1e-12)
+    assert np.abs(pt - (P.pt - y[6 * Nc:].reshape(Np, 3))).max() <= 1e-9 * np.abs(y).max()
+    for c in range(Nc):
+        R, tt = twist_update(P.pose[c], -y[6 * c:6 * c + 3], -y[6 * c + 3:6 * c + 6])
+        assert np.abs(cv2.Rodrigues(pose[c, :3].reshape(3, 1))[0] - R).max() <= 1e-10
+        assert np.abs(pose[c, 3:] - tt).max() <= 1e-9 * max(1.0, np.abs(tt).max())
+    # gain ratio and lambda update of that trial
+    _, cost1 = rm.residuals(P, 1, 4.0, pose=pose, pt=pt)
+    scale = float(y @ (lam * y + J.T @ e["r"].ravel()))
+    rho = (2 * t[0].cost - 2 * cost1) / (scale + 1e-3)
+    assert t[1].relative_decrease == pytest.approx(rho, rel=1e-7)
+    assert t[1].radius == pytest.approx(1.0 / (lam * max(1 / 3, min(1 - (2 * rho - 1) ** 3, 2 / 3))), rel=1e-7)
+
+
+def test_g2o_lambda_schedule_and_minimum(ba, oracle):
+    P = ba.synth("tiny", seed=5, sigma_aa=1.0, sigma_pt_rel=1.0)
+    with oracle.create(oracle.default_options(intrinsics_free=0, lm_policy=1, max_num_iterations=40)) as h:
+        h.set_problem(P)
+        s = h.solve()
+        t = h.trajectory()
+    assert any(not r.step_is_successful for r in t[1:])
+    nu = 2.0
+    for r in t[1:]:
+        lam = 1.0 / r.radius_used
+        if r.step_is_successful:
+            assert r.relative_decrease > 0
+            want = lam * max(1 / 3, min(1 - (2 * r.relative_decrease - 1) ** 3, 2 / 3)); nu = 2.0
+        else:
+            want = lam * nu; nu *= 2.0
+        assert 1.0 / r.radius == pytest.approx(want, rel=1e-12)
+    with oracle.create(oracle.default_options(intrinsics_free=0, lm_policy=0, max_num_iterations=50)) as h:
+        h.set_problem(ba.synth("tiny", seed=5))
+        sc = h.solve()
+    with oracle.create(oracle.default_options(intrinsics_free=0, lm_policy=1, max_num_iterations=50)) as h:
+        h.set_problem(ba.synth("tiny", seed=5))
+        sg = h.solve()
+    assert sg.final_cost == pytest.approx(sc.final_cost, rel=1e-5)        # both policies reach the same minimum
+    with pytest.raises(ba.BAError):
+        oracle.create(oracle.default_options(intrinsics_free=1, lm_policy=1))
