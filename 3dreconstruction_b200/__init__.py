@@ -268,6 +268,49 @@ def synth_spec(name=None, **kw):
     return s
 
 
+def _problem_from_c(p):
+    Nc, Ng, Np, No = p.num_cameras, p.num_groups, p.num_points, p.num_observations
+
+    def arr(ptr, n, dt):
+        return np.ctypeslib.as_array(ptr, shape=(max(n, 1),))[:n].astype(dt, copy=True)
+
+    return Problem(pose=arr(p.pose, Nc * 6, np.float64), intr=arr(p.intr, Ng * 4, np.float64), cam_group=arr(p.cam_group, Nc, np.int32),
+                   cam_fixed=arr(p.cam_fixed, Nc, np.uint8), pt=arr(p.pt, Np * 3, np.float64), obs_cam=arr(p.obs_cam, No, np.int32),
+                   obs_pt=arr(p.obs_pt, No, np.int32), obs_uv=arr(p.obs_uv, No * 2, np.float64),
+                   pose_true=arr(p.pose_true, Nc * 6, np.float64).reshape(Nc, 6), pt_true=arr(p.pt_true, Np * 3, np.float64).reshape(Np, 3),
+                   extent=p.extent)
+
+
+def read_bal(path):
+    """Read a 'Bundle Adjustment in the Large' text file (Snavely model: solve with model=MODEL_SNAVELY)."""
+    lib = _synth_lib()
+    pp = C.POINTER(SynthProblem)()
+    rc = lib.ba_bal_read(os.fsencode(path), C.byref(pp))
+    if rc != 0:
+        raise BAError(f"ba_bal_read({path!r}) failed ({rc})")
+    try:
+        return _problem_from_c(pp.contents)
+    finally:
+        lib.ba_synth_free(pp)
+
+
+def write_bal(path, P):
+    Nc, _, Np, No = P.sizes
+    d, i = _capi.c_double_p, _capi.c_int32_p
+    rc = _synth_lib().ba_bal_write(os.fsencode(path), Nc, Np, No, P.pose.ctypes.data_as(d), P.intr.ctypes.data_as(d), P.cam_group.ctypes.data_as(i),
+                                   P.pt.ctypes.data_as(d), P.obs_cam.ctypes.data_as(i), P.obs_pt.ctypes.data_as(i), P.obs_uv.ctypes.data_as(d))
+    if rc != 0:
+        raise BAError(f"ba_bal_write failed ({rc})")
+
+
+def write_ply(path, pt, pose):
+    """ASCII PLY of points and camera centres (the reference's writeToPLYFile / exportToPly)."""
+    pt, pose = _as(pt, np.float64).reshape(-1, 3), _as(pose, np.float64).reshape(-1, 6)
+    rc = _synth_lib().ba_write_ply(os.fsencode(path), pt.shape[0], pt.ctypes.data_as(_capi.c_double_p), pose.shape[0], pose.ctypes.data_as(_capi.c_double_p))
+    if rc != 0:
+        raise BAError(f"ba_write_ply failed ({rc})")
+
+
 def synth(name=None, **kw):
     """Generate a deterministic synthetic problem: synth('ladybug'), synth('tiny', seed=7), synth(num_cameras=..)."""
     lib = _synth_lib()

@@ -179,6 +179,9 @@ SYNTH_SYMBOLS = [
     ("ba_synth_named", C.c_int, [C.c_char_p, C.POINTER(SynthSpec)]),
     ("ba_synth_generate", C.c_int, [C.POINTER(SynthSpec), C.POINTER(C.POINTER(SynthProblem))]),
     ("ba_synth_free", None, [C.POINTER(SynthProblem)]),
+    ("ba_bal_read", C.c_int, [C.c_char_p, C.POINTER(C.POINTER(SynthProblem))]),
+    ("ba_bal_write", C.c_int, [C.c_char_p, C.c_int32, C.c_int32, C.c_int32, c_double_p, c_double_p, c_int32_p, c_double_p, c_int32_p, c_int32_p, c_double_p]),
+    ("ba_write_ply", C.c_int, [C.c_char_p, C.c_int32, c_double_p, C.c_int32, c_double_p]),
 ]
 
 

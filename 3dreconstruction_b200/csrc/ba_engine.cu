@@ -550,7 +550,8 @@ void evaluate_full(ba_engine* e) {
       KL(e), bak::k0_camera_precompute<<<cdiv(e->Nc, 128), 128, 0, s>>>(e->Nc, e->d_pose.p, e->d_camrec.p, e->opt.taylor_rule); }
     if (e->nTiles > 0) {
         LaunchTimer t(e, KID_K1);
-        KL(e), bak::k1_residual_jacobian<<<e->k1_grid, bak::TILE_OBS, 0, s>>>(e->V, e->d_camrec.p, e->d_intr.p, e->d_pt.p, rp, e->d_part0.p, &sc->bad_eval);
+        if (e->opt.model == BA_MODEL_SNAVELY) KL(e), bak::k1_residual_jacobian<1><<<e->k1_grid, bak::TILE_OBS, 0, s>>>(e->V, e->d_camrec.p, e->d_intr.p, e->d_pt.p, rp, e->d_part0.p, &sc->bad_eval);
+        else KL(e), bak::k1_residual_jacobian<0><<<e->k1_grid, bak::TILE_OBS, 0, s>>>(e->V, e->d_camrec.p, e->d_intr.p, e->d_pt.p, rp, e->d_part0.p, &sc->bad_eval);
     }
     { LaunchTimer t(e, KID_MISC);
       KL(e), bak::k_reduce_partials<<<1, 1024, 0, s>>>(e->d_part0.p, e->nTiles > 0 ? e->k1_grid : 0, &sc->cost); }
@@ -599,7 +600,8 @@ void candidate_cost(ba_engine* e) {
       KL(e), bak::k0_camera_precompute<<<cdiv(e->Nc, 128), 128, 0, s>>>(e->Nc, e->d_cpose.p, e->d_ccamrec.p, e->opt.taylor_rule); }
     if (e->nTiles > 0) {
         LaunchTimer t(e, KID_K1C);
-        KL(e), bak::k1c_candidate_cost<<<e->nTiles, bak::TILE_OBS, 0, s>>>(e->V, e->d_ccamrec.p, e->d_cintr.p, e->d_cpt.p, rp, e->d_part0.p, &sc->bad_cand);
+        if (e->opt.model == BA_MODEL_SNAVELY) KL(e), bak::k1c_candidate_cost<1><<<e->nTiles, bak::TILE_OBS, 0, s>>>(e->V, e->d_ccamrec.p, e->d_cintr.p, e->d_cpt.p, rp, e->d_part0.p, &sc->bad_cand);
+        else KL(e), bak::k1c_candidate_cost<0><<<e->nTiles, bak::TILE_OBS, 0, s>>>(e->V, e->d_ccamrec.p, e->d_cintr.p, e->d_cpt.p, rp, e->d_part0.p, &sc->bad_cand);
     }
     { LaunchTimer t(e, KID_MISC);
       KL(e), bak::k_reduce_partials<<<1, 1024, 0, s>>>(e->d_part0.p, e->nTiles, &sc->ccost); }
@@ -992,7 +994,8 @@ int ba_create(const ba_options* opt, ba_engine** out) {
     if (!opt || !out) return fail(nullptr, BA_ERR_INVALID_ARGUMENT, "null argument");
     if (opt->abi_version != BA_ABI_VERSION) return fail(nullptr, BA_ERR_INVALID_ARGUMENT, "abi_version mismatch");
     if (opt->linear_solver != BA_LINEAR_PCG) return fail(nullptr, BA_ERR_UNSUPPORTED, "the CUDA engine solves the reduced system by PCG only (linear_solver = BA_LINEAR_PCG)");
-    if (opt->model != BA_MODEL_PINHOLE) return fail(nullptr, BA_ERR_UNSUPPORTED, "model not implemented by the CUDA engine yet");
+    if (opt->model != BA_MODEL_PINHOLE && opt->model != BA_MODEL_SNAVELY) return fail(nullptr, BA_ERR_INVALID_ARGUMENT, "unknown residual model");
+    if (opt->lm_policy == BA_POLICY_G2O && opt->model != BA_MODEL_PINHOLE) return fail(nullptr, BA_ERR_UNSUPPORTED, "g2o policy: EdgeSE3ProjectXYZ is the pinhole model");
     if (opt->lm_policy == BA_POLICY_G2O && opt->intrinsics_free) return fail(nullptr, BA_ERR_UNSUPPORTED, "g2o policy: EdgeSE3ProjectXYZ has constant pinhole intrinsics (set intrinsics_free = 0)");
     if (opt->preconditioner != BA_PRECOND_JACOBI) return fail(nullptr, BA_ERR_UNSUPPORTED, "preconditioner not implemented by the CUDA engine yet");
     if (opt->world_size < 1 || opt->rank < 0 || opt->rank >= opt->world_size) return fail(nullptr, BA_ERR_INVALID_ARGUMENT, "bad rank/world_size");

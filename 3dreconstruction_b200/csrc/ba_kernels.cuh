@@ -171,6 +171,9 @@ __device__ __forceinline__ void load_camrec(const double* __restrict__ camrec, i
 // Projection shared by K1 and K1': ReprojectCost::operator() (BundleAdjuster.h:38-68), trig-free thanks to K0.
 struct Proj { double X[3]; double P[3]; double iz, xn, yn, r0, r1; };
 
+// MODEL 0: ReprojectCost (BundleAdjuster.h:38-68), intrinsics (fx, fy, cx, cy), +z forward.
+// MODEL 1: SnavelyReprojectionError (SnavelyReprojectionError.h:16-48), intrinsics (f, l1, l2), -z forward, radial distortion.
+template <int MODEL>
 __device__ __forceinline__ void project_obs(const double* __restrict__ cr, const double* __restrict__ X, const double* __restrict__ in,
                                             double2 uv, Proj& q) {
     q.X[0] = X[0]; q.X[1] = X[1]; q.X[2] = X[2];
@@ -178,10 +181,40 @@ __device__ __forceinline__ void project_obs(const double* __restrict__ cr, const
     q.P[1] = cr[CR_R + 3] * X[0] + cr[CR_R + 4] * X[1] + cr[CR_R + 5] * X[2] + cr[CR_T + 1];
     q.P[2] = cr[CR_R + 6] * X[0] + cr[CR_R + 7] * X[1] + cr[CR_R + 8] * X[2] + cr[CR_T + 2];
     q.iz = 1.0 / q.P[2];
-    q.xn = q.P[0] / q.P[2];
-    q.yn = q.P[1] / q.P[2];
-    q.r0 = in[0] * q.xn + in[2] - uv.x;   // u - observation.x   (:61,:64)
-    q.r1 = in[1] * q.yn + in[3] - uv.y;   // v - observation.y   (:62,:65)
+    if (MODEL == 0) {
+        q.xn = q.P[0] / q.P[2];
+        q.yn = q.P[1] / q.P[2];
+        q.r0 = in[0] * q.xn + in[2] - uv.x;   // u - observation.x   (:61,:64)
+        q.r1 = in[1] * q.yn + in[3] - uv.y;   // v - observation.y   (:62,:65)
+    } else {
+        q.xn = -q.P[0] / q.P[2];              // xp, yp  (SnavelyReprojectionError.h:30-31)
+        q.yn = -q.P[1] / q.P[2];
+        const double r2 = q.xn * q.xn + q.yn * q.yn;
+        const double dist = 1.0 + r2 * (in[1] + in[2] * r2);                 // :34-37
+        q.r0 = in[0] * dist * q.xn - uv.x;                                   // :40-47
+        q.r1 = in[0] * dist * q.yn - uv.y;
+    }
+}
+
+// A = d(residual)/dP (2x3) and the intrinsics columns d(residual)/d(intrinsics) as (row0, row1) pairs (4 pairs; unused ones zero).
+template <int MODEL>
+__device__ __forceinline__ void model_jacobian(const Proj& q, const double* __restrict__ in, double A0[3], double A1[3], double2 Ji[4]) {
+    if (MODEL == 0) {
+        const double fx = in[0], fy = in[1];
+        A0[0] = fx * q.iz; A0[1] = 0.0; A0[2] = -fx * q.xn * q.iz;
+        A1[0] = 0.0; A1[1] = fy * q.iz; A1[2] = -fy * q.yn * q.iz;
+        Ji[0] = make_double2(q.xn, 0.0); Ji[1] = make_double2(0.0, q.yn); Ji[2] = make_double2(1.0, 0.0); Ji[3] = make_double2(0.0, 1.0);
+    } else {
+        const double f = in[0], l1 = in[1], l2 = in[2];
+        const double xp = q.xn, yp = q.yn, r2 = xp * xp + yp * yp;
+        const double dist = 1.0 + r2 * (l1 + l2 * r2), dd = 2.0 * l1 + 4.0 * l2 * r2;
+        // B = d(pred)/d(xp,yp) = f (dist I + dd (xp,yp)^T (xp,yp));  C = d(xp,yp)/dP = -[iz 0 -Px iz^2; 0 iz -Py iz^2] = [-iz 0 -xp iz; 0 -iz -yp iz]
+        const double B00 = f * (dist + dd * xp * xp), B01 = f * dd * xp * yp, B11 = f * (dist + dd * yp * yp);
+        A0[0] = -B00 * q.iz; A0[1] = -B01 * q.iz; A0[2] = -(B00 * xp + B01 * yp) * q.iz;
+        A1[0] = -B01 * q.iz; A1[1] = -B11 * q.iz; A1[2] = -(B01 * xp + B11 * yp) * q.iz;
+        Ji[0] = make_double2(dist * xp, dist * yp); Ji[1] = make_double2(f * r2 * xp, f * r2 * yp);
+        Ji[2] = make_double2(f * r2 * r2 * xp, f * r2 * r2 * yp); Ji[3] = make_double2(0.0, 0.0);
+    }
 }
 
 // K1 — residual + analytic Jacobian + robust weight + cost, fused with the by-point half of K2 (Hpp, g_p).
@@ -194,6 +227,7 @@ __device__ __forceinline__ void project_obs(const double* __restrict__ cr, const
 #ifndef K1_CTAS_PER_SM
 #define K1_CTAS_PER_SM 2
 #endif
+template <int MODEL>
 __global__ void __launch_bounds__(TILE_OBS, K1_CTAS_PER_SM)
 k1_residual_jacobian(View V, const double* __restrict__ camrec, const double* __restrict__ intr, const double* __restrict__ pt,
                      RobustParams rp, double* __restrict__ cost_partial, int* __restrict__ bad_flag) {
@@ -253,21 +287,21 @@ k1_residual_jacobian(View V, const double* __restrict__ camrec, const double* __
             load_camrec<CAMREC / 2>(camrec, c, cr);
             const double* in = intr + 4 * g;
             Proj q;
-            project_obs(cr, pt + 3 * size_t(p), in, first ? pre_uv : ldg2(V.obs_uv + o), q);
+            project_obs<MODEL>(cr, pt + 3 * size_t(p), in, first ? pre_uv : ldg2(V.obs_uv + o), q);
             const double s = q.r0 * q.r0 + q.r1 * q.r1;
             double w;
             const double rho = robust(rp, s, w);
             cost += 0.5 * rho;
-            // A = d(u,v)/dP
-            const double fx = in[0], fy = in[1];
-            const double A0[3] = {fx * q.iz, 0.0, -fx * q.xn * q.iz};
-            const double A1[3] = {0.0, fy * q.iz, -fy * q.yn * q.iz};
+            // A = d(residual)/dP; the pinhole model's structural zeros (A0[1], A1[0]) are literal constants and fold away
+            double A0[3], A1[3];
+            double2 Jin[4];
+            model_jacobian<MODEL>(q, in, A0, A1, Jin);
             // J_X = A R
             double JX0[3], JX1[3];
 #pragma unroll
             for (int k = 0; k < 3; ++k) {
-                JX0[k] = A0[0] * cr[CR_R + k] + A0[2] * cr[CR_R + 6 + k];
-                JX1[k] = A1[1] * cr[CR_R + 3 + k] + A1[2] * cr[CR_R + 6 + k];
+                JX0[k] = A0[0] * cr[CR_R + k] + A0[1] * cr[CR_R + 3 + k] + A0[2] * cr[CR_R + 6 + k];
+                JX1[k] = A1[0] * cr[CR_R + k] + A1[1] * cr[CR_R + 3 + k] + A1[2] * cr[CR_R + 6 + k];
             }
             // J_aa = A G, row i: (A_i.h) aa - a (A_i x X) + b (d A_i + (A_i.aa) X)
             const double ax = cr[CR_AA], ay = cr[CR_AA + 1], az = cr[CR_AA + 2];
@@ -283,14 +317,14 @@ k1_residual_jacobian(View V, const double* __restrict__ camrec, const double* __
                 Ja1[0] = P1 * A1[2] - P2 * A1[1]; Ja1[1] = P2 * A1[0] - P0 * A1[2]; Ja1[2] = P0 * A1[1] - P1 * A1[0];
             } else {
             {
-                const double Ah = A0[0] * hx + A0[2] * hz, Aa = A0[0] * ax + A0[2] * az;
+                const double Ah = A0[0] * hx + A0[1] * hy + A0[2] * hz, Aa = A0[0] * ax + A0[1] * ay + A0[2] * az;
                 const double cx0 = A0[1] * X2 - A0[2] * X1, cx1 = A0[2] * X0 - A0[0] * X2, cx2 = A0[0] * X1 - A0[1] * X0;  // A0 x X
                 Ja0[0] = Ah * ax - ca * cx0 + cb * (d * A0[0] + Aa * X0);
                 Ja0[1] = Ah * ay - ca * cx1 + cb * (d * A0[1] + Aa * X1);
                 Ja0[2] = Ah * az - ca * cx2 + cb * (d * A0[2] + Aa * X2);
             }
             {
-                const double Ah = A1[1] * hy + A1[2] * hz, Aa = A1[1] * ay + A1[2] * az;
+                const double Ah = A1[0] * hx + A1[1] * hy + A1[2] * hz, Aa = A1[0] * ax + A1[1] * ay + A1[2] * az;
                 const double cx0 = A1[1] * X2 - A1[2] * X1, cx1 = A1[2] * X0 - A1[0] * X2, cx2 = A1[0] * X1 - A1[1] * X0;
                 Ja1[0] = Ah * ax - ca * cx0 + cb * (d * A1[0] + Aa * X0);
                 Ja1[1] = Ah * ay - ca * cx1 + cb * (d * A1[1] + Aa * X1);
@@ -312,10 +346,8 @@ k1_residual_jacobian(View V, const double* __restrict__ camrec, const double* __
             J[8 * ld] = make_double2(p0[2], p1[2]);
             if (V.fi) {   // d(u,v)/d(fx,fy,cx,cy) = [x 0 1 0; 0 y 0 1]
                 const double wi = V.grp_free[g] ? w : 0.0;
-                J[9 * ld] = make_double2(wi * q.xn, 0.0);
-                J[10 * ld] = make_double2(0.0, wi * q.yn);
-                J[11 * ld] = make_double2(wi, 0.0);
-                J[12 * ld] = make_double2(0.0, wi);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) J[(9 + k) * ld] = make_double2(wi * Jin[k].x, wi * Jin[k].y);
             }
             const double rr0 = w * q.r0, rr1 = w * q.r1;
             V.r2[o] = make_double2(rr0, rr1);
@@ -326,7 +358,8 @@ k1_residual_jacobian(View V, const double* __restrict__ camrec, const double* __
                 A[6] = make_double2(rr0, rr1);
                 if (V.fi) {
                     const double wi = V.grp_free[g] ? w : 0.0;
-                    A[7] = make_double2(wi * q.xn, 0.0); A[8] = make_double2(0.0, wi * q.yn); A[9] = make_double2(wi, 0.0); A[10] = make_double2(0.0, wi);
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) A[7 + k] = make_double2(wi * Jin[k].x, wi * Jin[k].y);
                     A[11] = make_double2(0.0, 0.0);
                 } else A[7] = make_double2(0.0, 0.0);
             }
@@ -386,6 +419,7 @@ k1_residual_jacobian(View V, const double* __restrict__ camrec, const double* __
 }
 
 // K1' — candidate cost: residual + rho only.  Reads 24 No + 24 Np + 160 Nc, writes one partial per tile.
+template <int MODEL>
 __global__ void __launch_bounds__(TILE_OBS)
 k1c_candidate_cost(View V, const double* __restrict__ camrec, const double* __restrict__ intr, const double* __restrict__ pt,
                    RobustParams rp, double* __restrict__ cost_partial, int* __restrict__ bad_flag) {
@@ -399,7 +433,7 @@ k1c_candidate_cost(View V, const double* __restrict__ camrec, const double* __re
         Proj q;
         double cr[12];   // R, t
         load_camrec<6>(camrec, c, cr);
-        project_obs(cr, pt + 3 * size_t(p), intr + (V.Ng == 1 ? 0 : 4 * V.cam_group[c]), ldg2(V.obs_uv + o), q);
+        project_obs<MODEL>(cr, pt + 3 * size_t(p), intr + (V.Ng == 1 ? 0 : 4 * V.cam_group[c]), ldg2(V.obs_uv + o), q);
         const double s = q.r0 * q.r0 + q.r1 * q.r1;
         double w;
         const double rho = robust(rp, s, w);

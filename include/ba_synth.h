@@ -58,6 +58,17 @@ int  ba_synth_named(const char* name, ba_synth_spec* s);
 int  ba_synth_generate(const ba_synth_spec* s, ba_synth_problem** out);
 void ba_synth_free(ba_synth_problem* p);
 
+/* "Bundle Adjustment in the Large" text files (the format of the reference's SnavelyReprojectionError model,
+ * src/adjuster/SnavelyReprojectionError.h:16-55): 9 parameters per camera (angle-axis, t, f, k1, k2), 3 per point.
+ * ba_bal_read returns a problem with one intrinsics group per camera (f, k1, k2, 0), observations stably sorted by point,
+ * nothing fixed; free it with ba_synth_free.  Solve with ba_options.model = BA_MODEL_SNAVELY. */
+int  ba_bal_read(const char* path, ba_synth_problem** out);
+int  ba_bal_write(const char* path, int32_t num_cameras, int32_t num_points, int32_t num_observations, const double* pose, const double* intr,
+                  const int32_t* cam_group, const double* pt, const int32_t* obs_cam, const int32_t* obs_pt, const double* obs_uv);
+/* ASCII PLY of points (white) and camera centres (green), the reference's exportToPly / writeToPLYFile
+ * (src/helpers/SfMPlyHelper.hpp:62-116, src/world/WorldStructure.h:83-98). */
+int  ba_write_ply(const char* path, int32_t num_points, const double* pt, int32_t num_cameras, const double* pose);
+
 #ifdef __cplusplus
 }
 #endif
