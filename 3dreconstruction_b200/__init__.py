@@ -209,6 +209,12 @@ class Handle:
             self._check(rc, "ba_evaluate")
         return dict(rc=rc, cost=cost.value, r=r, Jc=Jc, Jp=Jp, Ji=Ji, g=g)
 
+    def linear_solver_in_use(self):
+        """0 (EXACT: dense Schur complement + Cholesky) or 1 (PCG): what linear_solver = AUTO resolved to for the current problem."""
+        v = C.c_int32(0)
+        self._check(self.lib.ba_linear_solver_in_use(self.h, C.byref(v)), "ba_linear_solver_in_use")
+        return v.value
+
     def set_profiling(self, mask):
         """mask: False/0 off, True/1 every kernel, else a bit mask over kernel_stats() order."""
         self._check(self.lib.ba_set_profiling(self.h, int(mask)), "ba_set_profiling")

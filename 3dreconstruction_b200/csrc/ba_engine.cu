@@ -29,6 +29,7 @@
 #include "ba_rows.cuh"
 #include "ba_rows_pipe.cuh"
 #include "ba_p2p.cuh"
+#include "ba_dense.cuh"
 
 namespace {
 using std::vector;
@@ -110,10 +111,11 @@ struct DevBuf {
 };
 
 constexpr int kRedSlices = 8;      // stage-1 slices of the private-copy reduction (ba_pipe.cuh)
-enum KernelId { KID_K0 = 0, KID_K1, KID_K1C, KID_K2C, KID_K3P, KID_K3C, KID_K4, KID_K5, KID_K7, KID_K8, KID_PCGV, KID_MISC, KID_COUNT };
+enum KernelId { KID_K0 = 0, KID_K1, KID_K1C, KID_K2C, KID_K3P, KID_K3C, KID_K4, KID_K5, KID_K7, KID_K8, KID_PCGV, KID_MISC, KID_DFORM, KID_DCHOL, KID_COUNT };
 const char* const kKernelNames[KID_COUNT] = {"K0_camera_precompute", "K1_residual_jacobian", "K1c_candidate_cost", "K2c_camera_blocks",
                                              "K3p_point_blocks",      "K3c_camera_blocks",    "K4_reduced_rhs",     "K5_schur_matvec",
-                                             "K7_backsub_model",      "K8_candidate",         "PCG_vector_update",  "misc_reductions"};
+                                             "K7_backsub_model",      "K8_candidate",         "PCG_vector_update",  "misc_reductions",
+                                             "D1_dense_schur_form",   "D2_dense_cholesky_solve"};
 
 }  // namespace
 
@@ -152,6 +154,15 @@ struct ba_engine {
     DevBuf<int> d_spack;
     DevBuf<double> d_scratch;
     bak::ScatterSched Sch{};
+    // direct solve of the reduced camera system (ba_dense.cuh); dense == true selects it for this problem
+    DevBuf<double> d_ipart;            // [Nc][14] per-camera shares of the group blocks (free intrinsics)
+    DevBuf<int> d_grp_off, d_grp_cams;  // cameras of every group, CSR
+    bool dense = false;
+    DevBuf<double> d_S, d_WU, d_GH, d_corner;
+    DevBuf<int> d_blk_off;
+    DevBuf<int2> d_blk_key, d_pairs;
+    bak::DenseView DV{};
+    int chol_grid = 1;
     DevBuf<double> d_redpart;          // [kRedSlices][ldf] stage-1 output of the copy reduction
     // mode 4: per-(tile, camera) partial rows + by-camera gather (ba_rows.cuh)
     DevBuf<int4> d_tmeta, d_tile_info;
@@ -327,6 +338,81 @@ void shard_points(const vector<int32_t>& gpt_off, int NpG, int NoG, int W, vecto
     }
 }
 
+constexpr int kDenseAutoMaxDim = 2048;                  // BA_LINEAR_AUTO: direct solve up to this many reduced unknowns (341 poses)
+constexpr int kDenseMaxDim = 8192;                      // BA_LINEAR_EXACT refuses beyond (S would exceed 512 MB)
+constexpr int64_t kDenseMaxPairs = int64_t(1) << 27;    // co-observation pair records (8 B each)
+
+// Direct-solve schedule (ba_dense.cuh): every ordered pair (i, j) of observations of one point with cam(i) >= cam(j), grouped by
+// (cam(i), cam(j)) with two stable counting sorts, so that block (ci, cj) of S is the sum over its list in point order.
+void build_dense(ba_engine* e, const ba_problem* P, const vector<int32_t>& pt_off) {
+    e->dense = false;
+    const int mode = e->opt.linear_solver;
+    if (mode == BA_LINEAR_PCG) return;
+    const bool force = mode == BA_LINEAR_EXACT;
+    const int Nc = e->Nc, Np = e->Np, No = e->No;
+    const char* why = nullptr;
+    if (e->opt.world_size > 1) why = "the direct solve runs on one GPU (world_size = 1)";
+    else if (e->nf > (force ? kDenseMaxDim : kDenseAutoMaxDim)) why = "too many reduced unknowns for a dense Schur complement";
+    else if (e->fi && e->Ng != 1) why = "free intrinsics with more than one Camera group";
+    int64_t bound = 0;
+    if (!why) {
+        for (int p = 0; p < Np; ++p) { const int64_t k = pt_off[p + 1] - pt_off[p]; bound += k * k; }
+        if (bound > kDenseMaxPairs) why = "too many co-observation pairs";
+    }
+    if (why) {
+        if (force) throw BaFail{BA_ERR_UNSUPPORTED, std::string("linear_solver = BA_LINEAR_EXACT: ") + why + " (use BA_LINEAR_PCG or BA_LINEAR_AUTO)"};
+        return;
+    }
+    cudaStream_t s = e->stream;
+    const int32_t* cam = P->obs_cam + e->ob;
+    vector<int2> A, B;
+    A.reserve(size_t(bound / 2 + No));
+    for (int p = 0; p < Np; ++p)
+        for (int i = pt_off[p]; i < pt_off[p + 1]; ++i)
+            for (int j = pt_off[p]; j < pt_off[p + 1]; ++j)
+                if (cam[i] >= cam[j]) A.push_back(make_int2(i, j));
+    const size_t np = A.size();
+    B.resize(np);
+    vector<int32_t> cnt(size_t(Nc) + 1);
+    std::fill(cnt.begin(), cnt.end(), 0);
+    for (size_t q = 0; q < np; ++q) ++cnt[cam[A[q].y] + 1];
+    for (int c = 0; c < Nc; ++c) cnt[c + 1] += cnt[c];
+    for (size_t q = 0; q < np; ++q) B[cnt[cam[A[q].y]]++] = A[q];
+    std::fill(cnt.begin(), cnt.end(), 0);
+    for (size_t q = 0; q < np; ++q) ++cnt[cam[B[q].x] + 1];
+    for (int c = 0; c < Nc; ++c) cnt[c + 1] += cnt[c];
+    for (size_t q = 0; q < np; ++q) A[cnt[cam[B[q].x]]++] = B[q];
+    vector<int32_t> blk_off;
+    vector<int2> blk_key;
+    for (size_t q = 0; q < np; ++q) {
+        const int ci = cam[A[q].x], cj = cam[A[q].y];
+        if (blk_key.empty() || blk_key.back().x != ci || blk_key.back().y != cj) { blk_key.push_back(make_int2(ci, cj)); blk_off.push_back(int32_t(q)); }
+    }
+    blk_off.push_back(int32_t(np));
+    bak::DenseView& D = e->DV;
+    D.n = e->nf; D.T = (e->nf + bak::DT - 1) / bak::DT; D.ld = bak::DT * D.T;
+    D.nblk = int(blk_key.size());
+    D.corner_blocks = e->fi ? std::max(1, (Np + 127) / 128) : 0;
+    e->d_S.alloc(size_t(bak::DT) * (D.T + 1) * D.ld);
+    e->d_WU.alloc(size_t(36) * std::max(No, 1));
+    if (e->fi) { e->d_GH.alloc(size_t(24) * std::max(Np, 1)); e->d_corner.alloc(size_t(16) * D.corner_blocks); }
+    e->d_blk_off.upload(blk_off.data(), blk_off.size(), s);
+    e->d_blk_key.upload(blk_key.data(), blk_key.size(), s);
+    e->d_pairs.upload(A.data(), np, s);
+    CU_TRY(cudaStreamSynchronize(s));
+    D.S = e->d_S.p; D.WU = e->d_WU.p; D.GH = e->d_GH.p; D.corner_part = e->d_corner.p;
+    D.blk_off = e->d_blk_off.p; D.blk_key = e->d_blk_key.p; D.pairs = e->d_pairs.p;
+    int occ = 1;
+    CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, bak::k_dense_chol, 256, 0));
+    e->chol_grid = std::max(1, std::min(std::max(occ, 1) * e->num_sms, D.T * (D.T + 1) / 2));
+    e->dense = true;
+    // algorithmic bytes: formation reads the Jacobian columns it needs once and every pair's two 144-byte records,
+    // writes the records and S; the factorisation reads and writes the lower triangle once per elimination step on average T/3 times
+    const double jb = e->fi ? 208.0 : 144.0;
+    e->stats[KID_DFORM].bytes = double(No) * (jb + 288 + 4) + double(np) * (8 + 288) + 8.0 * double(D.ld) * D.ld;
+    e->stats[KID_DCHOL].bytes = 8.0 * double(D.ld) * D.ld * (D.T + 2) / 6.0;
+}
+
 void do_set_problem(ba_engine* e, const ba_problem* P) {
     const int Nc = P->num_cameras, Ng = P->num_groups, NpG = P->num_points, NoG = P->num_observations;
     const int W = e->opt.world_size, R = e->opt.rank;
@@ -466,6 +552,15 @@ void do_set_problem(ba_engine* e, const ba_problem* P) {
     e->d_cam_off.upload(cam_off.data(), cam_off.size(), s);
     e->d_cam_free.upload(e->h_cam_free.data(), Nc, s);
     e->d_grp_free.upload(grp_free.data(), std::max(Ng, 1), s);
+    {   // cameras of every intrinsics group, in camera order (k_group_blocks)
+        vector<int32_t> goff(size_t(std::max(Ng, 1)) + 1, 0), gcams(std::max(Nc, 1));
+        for (int c = 0; c < Nc; ++c) ++goff[P->cam_group[c] + 1];
+        for (int g = 0; g < Ng; ++g) goff[g + 1] += goff[g];
+        vector<int32_t> cur(goff.begin(), goff.end() - 1);
+        for (int c = 0; c < Nc; ++c) gcams[cur[P->cam_group[c]]++] = c;
+        e->d_grp_off.upload(goff.data(), goff.size(), s); e->d_grp_cams.upload(gcams.data(), gcams.size(), s);
+        e->d_ipart.alloc(size_t(14) * std::max(Nc, 1));
+    }
     e->d_pose0.upload(P->pose, size_t(6) * Nc, s);
     e->d_intr0.upload(P->intr, size_t(4) * Ng, s);
     e->d_pt0.upload(P->pt + size_t(3) * e->pb, size_t(3) * Np, s);
@@ -502,6 +597,8 @@ void do_set_problem(ba_engine* e, const ba_problem* P) {
     e->traj.clear();
     e->scales_set = false;
     e->has_problem = true;
+
+    build_dense(e, P, pt_off);
 
     // algorithmic bytes per launch of each kernel in THIS formulation, for roofline.achieved
     const double no = No, np = Np, nc = Nc, jb = e->fi ? 208.0 : 144.0;
@@ -555,11 +652,12 @@ void evaluate_full(ba_engine* e) {
     }
     { LaunchTimer t(e, KID_MISC);
       KL(e), bak::k_reduce_partials<<<1, 1024, 0, s>>>(e->d_part0.p, e->nTiles > 0 ? e->k1_grid : 0, &sc->cost); }
-    if (e->fi) CU_TRY(cudaMemsetAsync(e->Hii(), 0, size_t(20) * e->Ng * sizeof(double), s));
     if (e->Nc > 0) {
         LaunchTimer t(e, KID_K2C);
-        if (e->fi) KL(e), bak::k2c_camera_blocks<true><<<e->Nc, 128, 0, s>>>(e->V, e->Hcc(), e->gc(), e->Hii(), e->gi());
-        else KL(e), bak::k2c_camera_blocks<false><<<e->Nc, 128, 0, s>>>(e->V, e->Hcc(), e->gc(), e->Hii(), e->gi());
+        if (e->fi) {
+            KL(e), bak::k2c_camera_blocks<true><<<e->Nc, 128, 0, s>>>(e->V, e->Hcc(), e->gc(), e->d_ipart.p);
+            KL(e), bak::k_group_blocks<<<cdiv(e->Ng * 32, 128), 128, 0, s>>>(e->Ng, e->d_grp_off.p, e->d_grp_cams.p, e->d_ipart.p, e->Hii(), e->gi());
+        } else KL(e), bak::k2c_camera_blocks<false><<<e->Nc, 128, 0, s>>>(e->V, e->Hcc(), e->gc(), nullptr);
     }
     if (e->opt.world_size > 1) {
         NCCL_TRY(g_nccl.GroupStart());
@@ -700,6 +798,31 @@ int solve_linear(ba_engine* e, double radius, double* rel_out, double lambda = 0
         double* src; int nsrc; reduce_src(G, nullptr, src, nsrc);
         KL(e), bak::k_pcg_q<<<vblocks, bak::PCG_BLOCK, 0, s>>>(e->nf, nsrc, e->Sch.ldf, src, nullptr, nullptr, e->d_b.p, nullptr, nullptr, 1, 0); }
     allreduce_sum(e, e->d_b.p, e->nf);
+    if (e->dense) {   // direct solve (ba_dense.cuh): S formed densely, Cholesky with the right-hand side as an extra row, no host round trip
+        const bak::DenseView& D = e->DV;
+        {
+            LaunchTimer t(e, KID_DFORM);
+            CU_TRY(cudaMemsetAsync(D.S, 0, size_t(bak::DT) * (D.T + 1) * D.ld * sizeof(double), s));
+            if (e->No > 0) KL(e), bak::k_dense_wu<<<cdiv(e->No, 128), 128, 0, s>>>(e->V, D);
+            if (e->fi) KL(e), bak::k_dense_point_g<<<D.corner_blocks, 128, 0, s>>>(e->V, D);
+            KL(e), bak::k_dense_init<<<cdiv(36 * e->Nc + D.ld + 16, 256), 256, 0, s>>>(e->Nc, e->fi, D, e->Hcc(), e->Hii(), e->d_Df2.p, e->d_b.p);
+            if (D.nblk > 0) KL(e), bak::k_dense_pairs<<<std::min(cdiv(D.nblk, 4), 16 * e->num_sms), 128, 0, s>>>(D);
+            if (e->fi && e->No > 0) KL(e), bak::k_dense_border<<<cdiv(e->Nc * 32, 128), 128, 0, s>>>(e->V, D);
+        }
+        {
+            LaunchTimer t(e, KID_DCHOL);
+            bak::DenseView dv = D;
+            double* xp = e->d_x.p; bak::PcgState2* pcg = &sc->pcg; int* bad = &sc->bad_lin;
+            void* args[] = {&dv, &xp, &pcg, &bad};
+            KL(e);
+            CU_TRY(cudaLaunchCooperativeKernel(reinterpret_cast<const void*>(bak::k_dense_chol), dim3(e->chol_grid), dim3(256), args, 0, s));
+        }
+        launch_sweep<bak::SWEEP_BACKSUB>(e, KID_K7, e->d_x.p, nullptr, nullptr, e->d_part0.p);
+        { LaunchTimer t(e, KID_MISC);
+          KL(e), bak::k_reduce_partials<<<1, 1024, 0, s>>>(e->d_part0.p, e->nTiles, &sc->mcc); }
+        *rel_out = 0.0;
+        return 0;   // failure (bad_lin) is seen by the caller's next read-back
+    }
     const bak::PcgParams pp{e->opt.pcg_max_iterations, e->opt.pcg_forcing, e->opt.pcg_rel_tolerance, e->opt.eta};
     { LaunchTimer t(e, KID_PCGV);
       KL(e), bak::k_pcg_init2<<<1, 1024, 0, s>>>(e->nf, e->Nc, e->d_Minv.p, e->d_b.p, e->d_x.p, e->d_r.p, e->d_z.p, e->d_p.p, &sc->pcg); }
@@ -830,7 +953,7 @@ void lm_solve(ba_engine* e) {
             }
             read_scalars(e);
             R.model_cost_change = -H->mcc;
-            valid = std::isfinite(R.model_cost_change) && R.model_cost_change > 0.0;
+            valid = !H->bad_lin && std::isfinite(R.model_cost_change) && R.model_cost_change > 0.0;
         }
         R.step_is_valid = valid;
         if (!valid) {   // HandleInvalidStep
@@ -928,10 +1051,10 @@ void lm_solve_g2o(ba_engine* e) {
                     NCCL_TRY(g_nccl.GroupEnd());
                 }
                 read_scalars(e);
-                if (!H->bad_cand && std::isfinite(H->ccost)) tempChi = 2.0 * H->ccost;
+                if (!H->bad_cand && !H->bad_lin && std::isfinite(H->ccost)) tempChi = 2.0 * H->ccost;
                 scale = H->scale_pt + H->scale_f;
             }
-            R.step_is_valid = its >= 0;
+            R.step_is_valid = its >= 0 && !H->bad_lin;
             R.candidate_cost = tempChi >= std::numeric_limits<double>::max() ? tempChi : 0.5 * tempChi;
             R.model_cost_change = 0.5 * scale;
             rho = (2.0 * cost - tempChi) / (scale + 1e-3);
@@ -982,7 +1105,7 @@ int ba_options_default(ba_options* o) {
     o->max_num_iterations = 50; o->initial_trust_region_radius = 1e4; o->max_trust_region_radius = 1e16; o->min_trust_region_radius = 1e-32;
     o->min_relative_decrease = 1e-3; o->min_lm_diagonal = 1e-6; o->max_lm_diagonal = 1e32; o->max_num_consecutive_invalid_steps = 5;
     o->function_tolerance = 1e-6; o->gradient_tolerance = 1e-10; o->parameter_tolerance = 1e-8; o->jacobi_scaling = 1;
-    o->linear_solver = BA_LINEAR_PCG;                              // the engine's solver; EXACT exists only in the oracle
+    o->linear_solver = BA_LINEAR_AUTO;                             // direct solve for small camera counts, PCG beyond
     o->preconditioner = BA_PRECOND_JACOBI;                         // :171
     o->pcg_max_iterations = 2000; o->pcg_rel_tolerance = 1e-12; o->pcg_forcing = 0; o->eta = 0.1;
     o->target_chi2 = 0.0; o->device = 0; o->num_threads = 1;
@@ -993,7 +1116,7 @@ int ba_options_default(ba_options* o) {
 int ba_create(const ba_options* opt, ba_engine** out) {
     if (!opt || !out) return fail(nullptr, BA_ERR_INVALID_ARGUMENT, "null argument");
     if (opt->abi_version != BA_ABI_VERSION) return fail(nullptr, BA_ERR_INVALID_ARGUMENT, "abi_version mismatch");
-    if (opt->linear_solver != BA_LINEAR_PCG) return fail(nullptr, BA_ERR_UNSUPPORTED, "the CUDA engine solves the reduced system by PCG only (linear_solver = BA_LINEAR_PCG)");
+    if (opt->linear_solver < BA_LINEAR_EXACT || opt->linear_solver > BA_LINEAR_AUTO) return fail(nullptr, BA_ERR_INVALID_ARGUMENT, "unknown linear_solver");
     if (opt->model != BA_MODEL_PINHOLE && opt->model != BA_MODEL_SNAVELY) return fail(nullptr, BA_ERR_INVALID_ARGUMENT, "unknown residual model");
     if (opt->lm_policy == BA_POLICY_G2O && opt->model != BA_MODEL_PINHOLE) return fail(nullptr, BA_ERR_UNSUPPORTED, "g2o policy: EdgeSE3ProjectXYZ is the pinhole model");
     if (opt->lm_policy == BA_POLICY_G2O && opt->intrinsics_free) return fail(nullptr, BA_ERR_UNSUPPORTED, "g2o policy: EdgeSE3ProjectXYZ has constant pinhole intrinsics (set intrinsics_free = 0)");
@@ -1174,6 +1297,13 @@ int ba_set_profiling(ba_engine* e, int32_t enabled) {
     e->profiling = enabled < 0 ? 0xffffffffu : unsigned(enabled);   // bit mask of kernel ids (ba_kernel_stat order); 1 keeps meaning "all" for convenience
     if (enabled == 1) e->profiling = 0xffffffffu;
     for (auto& st : e->stats) { st.launches = 0; st.ms = 0.0; }
+    return BA_OK;
+}
+
+int ba_linear_solver_in_use(ba_engine* e, int32_t* solver) {
+    if (!e || !solver) return BA_ERR_INVALID_ARGUMENT;
+    if (!e->has_problem) return fail(e, BA_ERR_INVALID_ARGUMENT, "no problem set");
+    *solver = e->dense ? BA_LINEAR_EXACT : BA_LINEAR_PCG;
     return BA_OK;
 }
 

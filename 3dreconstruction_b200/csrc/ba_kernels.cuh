@@ -658,12 +658,12 @@ k_schur_sweep(View V, const double* __restrict__ xin, double* __restrict__ yout,
 // ---------------------------------------------------------------------------------------------------------
 // K2c — by-camera half of K2: Hcc[c] = sum Jc^T Jc (6x6, stored full), gc[c] = sum Jc^T r, over the camera-sorted
 // observation list (one CTA per camera, fixed summation order => deterministic).  With free intrinsics also the
-// per-group 4x4 block and gradient (RED into Hii/gi, one per CTA and component).
+// camera's share of its group's 4x4 block and gradient (ipart; k_group_blocks adds the shares in camera order).
 // Gathers the by-observation records K1 wrote (JcA: Jc, r [, Ji] in 128 / 192 contiguous bytes = whole sectors) through
 // perm_by_cam.  (v1 gathered the SoA columns: 7 separate 16-byte pieces per observation, 3.1x DRAM over-fetch.)  
 template <bool FI>
 __global__ void __launch_bounds__(128)
-k2c_camera_blocks(View V, double* __restrict__ Hcc, double* __restrict__ gc, double* __restrict__ Hii, double* __restrict__ gi) {
+k2c_camera_blocks(View V, double* __restrict__ Hcc, double* __restrict__ gc, double* __restrict__ ipart) {
     constexpr int NV = FI ? (21 + 6 + 10 + 4) : (21 + 6);   // Hcc upper, gc, [Hii upper, gi]
     __shared__ double sm[4][NV];
     const int c = blockIdx.x;
@@ -714,17 +714,36 @@ k2c_camera_blocks(View V, double* __restrict__ Hcc, double* __restrict__ gc, dou
         } else if (k < 27) {
             gc[6 * size_t(c) + (k - 21)] = s;
         } else if (FI) {
-            const int g = V.cam_group[c];
-            if (k < 37) {
-                int a = 0, rem = k - 27;
-                while (rem >= 4 - a) { rem -= 4 - a; ++a; }
-                const int b = a + rem;
-                red_add(Hii + 16 * size_t(g) + 4 * a + b, s);
-                if (a != b) red_add(Hii + 16 * size_t(g) + 4 * b + a, s);
-            } else {
-                red_add(gi + 4 * size_t(g) + (k - 37), s);
-            }
+            ipart[14 * size_t(c) + (k - 27)] = s;   // this camera's share of its group's 4x4 block (upper, 10) and gradient (4): k_group_blocks sums them
         }
+    }
+}
+
+// Free intrinsics: Hii / gi of every Camera group = sum of its cameras' shares, in camera order (one warp per group, fixed tree).
+__global__ void __launch_bounds__(128)
+k_group_blocks(int Ng, const int* __restrict__ grp_off, const int* __restrict__ grp_cams, const double* __restrict__ ipart,
+               double* __restrict__ Hii, double* __restrict__ gi) {
+    const int lane = threadIdx.x & 31;
+    const int g = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (g >= Ng) return;
+    double acc[14];
+#pragma unroll
+    for (int k = 0; k < 14; ++k) acc[k] = 0.0;
+    for (int i = grp_off[g] + lane; i < grp_off[g + 1]; i += 32) {
+        const double* p = ipart + 14 * size_t(grp_cams[i]);
+#pragma unroll
+        for (int k = 0; k < 14; ++k) acc[k] += p[k];
+    }
+#pragma unroll
+    for (int k = 0; k < 14; ++k) acc[k] = warp_sum(acc[k]);
+    if (lane == 0) {
+        int n = 0;
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+#pragma unroll
+            for (int b = a; b < 4; ++b) { Hii[16 * size_t(g) + 4 * a + b] = acc[n]; Hii[16 * size_t(g) + 4 * b + a] = acc[n]; ++n; }
+#pragma unroll
+        for (int a = 0; a < 4; ++a) gi[4 * size_t(g) + a] = acc[10 + a];
     }
 }
 

@@ -56,10 +56,14 @@ typedef enum ba_model { BA_MODEL_PINHOLE = 0, BA_MODEL_SNAVELY = 1 } ba_model;
 
 /* How the reduced camera system is solved.
  * EXACT is what the reference configures (SPARSE_SCHUR + EIGEN_SPARSE, BundleAdjuster.h:172-173): a direct
- * factorisation of S — implemented by the oracle only.  PCG is the engine's block-preconditioned conjugate
- * gradients on the implicit Schur complement (what Ceres calls ITERATIVE_SCHUR; the reference even sets
- * preconditioner_type = JACOBI at :171, which only ITERATIVE_SCHUR would read). */
-typedef enum ba_linear_solver { BA_LINEAR_EXACT = 0, BA_LINEAR_PCG = 1 } ba_linear_solver;
+ * factorisation of S.  The engine forms S densely and runs a blocked Cholesky on the GPU; that needs one GPU,
+ * at most 8192 reduced unknowns and, with free intrinsics, one shared Camera group — ba_set_problem fails with
+ * BA_ERR_UNSUPPORTED otherwise.  PCG is block-preconditioned conjugate gradients on the implicit Schur complement
+ * (what Ceres calls ITERATIVE_SCHUR; the reference even sets preconditioner_type = JACOBI at :171, which only
+ * ITERATIVE_SCHUR would read).  AUTO (engine default) takes EXACT when it applies and the reduced system has
+ * at most 2048 unknowns (341 poses: the reference's own SequentialActuator regime), PCG otherwise; the oracle
+ * reads AUTO as EXACT. */
+typedef enum ba_linear_solver { BA_LINEAR_EXACT = 0, BA_LINEAR_PCG = 1, BA_LINEAR_AUTO = 2 } ba_linear_solver;
 typedef enum ba_preconditioner { BA_PRECOND_JACOBI = 0 /* blockdiag(Hcc + Dc^2) */, BA_PRECOND_SCHUR_JACOBI = 1 /* blockdiag(S) */ } ba_preconditioner;
 
 /* Which rule selects the first-order branch of AngleAxisRotatePoint. */
@@ -105,7 +109,7 @@ typedef struct ba_options {
     double  parameter_tolerance;         /* 1e-8 */
     int32_t jacobi_scaling;              /* 1 */
     /* --- reduced-system solve --- */
-    int32_t linear_solver;               /* ba_linear_solver; engine: PCG only */
+    int32_t linear_solver;               /* ba_linear_solver; engine default AUTO, oracle default EXACT */
     int32_t preconditioner;              /* ba_preconditioner */
     int32_t pcg_max_iterations;          /* parity mode 2000 */
     double  pcg_rel_tolerance;           /* stop when sqrt(r'M^-1 r / b'M^-1 b) <= tol; parity mode 1e-12 */
@@ -202,6 +206,7 @@ int  ba_get_structure(ba_engine* e, int32_t* perm_by_cam, int32_t* cam_off, int3
 int  ba_evaluate(ba_engine* e, double* cost, double* r, double* Jc, double* Jp, double* Ji, double* g);
 int  ba_set_profiling(ba_engine* e, int32_t mask);             /* per-kernel CUDA-event timing: 0 off (default), 1 or -1 all kernels, else bit k = kernel k of ba_get_kernel_stats */
 int  ba_get_kernel_stats(ba_engine* e, ba_kernel_stat* out, int32_t cap, int32_t* n);
+int  ba_linear_solver_in_use(ba_engine* e, int32_t* solver);  /* after ba_set_problem: BA_LINEAR_EXACT or BA_LINEAR_PCG, what AUTO resolved to for this problem */
 int  ba_get_io_bytes(int64_t* h2d, int64_t* d2h);              /* cumulative host->device / device->host bytes moved by this library in this process */
 /* Host-only (no device needed): the point ranges of the multi-GPU sharding. Rank r owns points
  * [shard_pt[r], shard_pt[r+1]) and all their observations; ranges are contiguous, cut at point boundaries and

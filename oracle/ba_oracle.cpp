@@ -294,7 +294,7 @@ StepOut solve_step(ba_engine* e, double radius, const vector<double>& dg_cam, co
     }
 
     vector<double> yf(nf, 0.0);
-    if (e->opt.linear_solver == BA_LINEAR_EXACT) {
+    if (e->opt.linear_solver != BA_LINEAR_PCG) {   // EXACT, and AUTO read as EXACT
         // 2a. explicit S = F^T F + Df^2 - sum_p (F^T E_p) Hpp^-1 (E_p^T F), dense; camera rows in parallel
         vector<double> S(size_t(nf) * nf, 0.0);
 #pragma omp parallel for schedule(dynamic, 4) num_threads(nt)
@@ -864,6 +864,7 @@ int ba_evaluate(ba_engine* e, double* cost, double* r, double* Jc, double* Jp, d
 
 int ba_set_profiling(ba_engine* e, int32_t) { return e ? BA_OK : BA_ERR_INVALID_ARGUMENT; }
 int ba_get_kernel_stats(ba_engine* e, ba_kernel_stat*, int32_t, int32_t* n) { if (!e || !n) return BA_ERR_INVALID_ARGUMENT; *n = 0; return BA_OK; }
+int ba_linear_solver_in_use(ba_engine* e, int32_t* solver) { if (!e || !solver) return BA_ERR_INVALID_ARGUMENT; *solver = e->opt.linear_solver == BA_LINEAR_PCG ? BA_LINEAR_PCG : BA_LINEAR_EXACT; return BA_OK; }
 int ba_shard_points(int32_t, int32_t, const int32_t*, int32_t, int32_t*) { return BA_ERR_UNSUPPORTED; }   // engine-side host logic; the oracle is single-process
 int ba_nccl_unique_id(void*) { return BA_ERR_UNSUPPORTED; }
 int ba_get_io_bytes(int64_t* h2d, int64_t* d2h) { if (h2d) *h2d = 0; if (d2h) *d2h = 0; return BA_OK; }

@@ -62,7 +62,7 @@ def test_option_defaults_are_the_reference_configuration(ba, oracle):
         if name in ("linear_solver", "reserved", "nccl_unique_id", "stream"):
             continue
         assert getattr(e, name) == getattr(o, name), name
-    assert (e.linear_solver, o.linear_solver) == (1, 0)
+    assert (e.linear_solver, o.linear_solver) == (2, 0)      # engine AUTO, oracle EXACT
     assert (o.robust_kind, o.robust_a, o.intrinsics_free, o.num_threads) == (1, 4.0, 1, 1)
     assert (o.max_num_iterations, o.initial_trust_region_radius, o.min_relative_decrease) == (50, 1e4, 1e-3)
     assert (o.function_tolerance, o.gradient_tolerance, o.parameter_tolerance) == (1e-6, 1e-10, 1e-8)
@@ -80,7 +80,7 @@ def test_engine_has_no_cpu_fallback(ba):
 
 def test_engine_rejects_unsupported_options_before_touching_a_device(ba):
     lib = ba.engine_library()
-    for bad in (dict(linear_solver=0), dict(abi_version=99), dict(world_size=2), dict(rank=3)):
+    for bad in (dict(linear_solver=7), dict(abi_version=99), dict(world_size=2), dict(rank=3)):
         with pytest.raises(ba.BAError):
             lib.create(lib.default_options(**bad))
 

@@ -16,7 +16,11 @@ def solve_both(ba, oracle, P, **opts):
     oopts = dict(opts)
     threads = oopts.pop("oracle_threads", 4)
     oopts.pop("scatter_mode", None)
+    oopts.pop("engine_solver", None)
     opts.pop("oracle_threads", None)
+    solver = opts.pop("engine_solver", None)      # engine only: 0 dense Schur + Cholesky, 1 PCG, None = AUTO; the oracle stays EXACT
+    if solver is not None:
+        opts["linear_solver"] = solver
     with ba.Engine(**opts) as eng:
         eng.set_problem(P)
         se = eng.solve()
@@ -65,10 +69,12 @@ def test_evaluate_parity(ba, oracle, name):
         assert np.abs(a["g"] - b["g"]).max() <= 1e-10 * np.abs(b["g"]).max()
 
 
-@pytest.mark.parametrize("name,fi", [("tiny", 0), ("tiny", 1), ("ladybug", 0), ("ladybug", 1), ("trafalgar", 0)])
-def test_trajectory_parity(ba, oracle, name, fi):
+@pytest.mark.parametrize("solver", [0, 1])
+@pytest.mark.parametrize("name,fi", [("tiny", 0), ("tiny", 1), ("ladybug", 0), ("ladybug", 1), ("trafalgar", 0), ("trafalgar", 1)])
+def test_trajectory_parity(ba, oracle, name, fi, solver):
+    """Both engine solvers of the reduced system (0: dense Schur complement + Cholesky, 1: PCG) against the oracle's exact solve."""
     P = ba.synth(name)
-    (se, te, xe), (so, to, xo) = solve_both(ba, oracle, P, intrinsics_free=fi, max_num_iterations=12)
+    (se, te, xe), (so, to, xo) = solve_both(ba, oracle, P, intrinsics_free=fi, max_num_iterations=12, engine_solver=solver)
     assert se.usable and so.usable
     assert len(te) == len(to)
     assert_trajectory_parity(te, to)
@@ -83,16 +89,17 @@ def test_trajectory_parity(ba, oracle, name, fi):
 def test_scatter_modes(ba, oracle, mode, fi):
     """All three camera-side scatter implementations (L2 atomics, private accumulators, bulk-copy pipeline) agree with the oracle."""
     P = ba.synth("ladybug", seed=123)
-    (se, te, xe), (so, to, xo) = solve_both(ba, oracle, P, intrinsics_free=fi, max_num_iterations=6, scatter_mode=mode)
+    (se, te, xe), (so, to, xo) = solve_both(ba, oracle, P, intrinsics_free=fi, max_num_iterations=6, scatter_mode=mode, engine_solver=1)
     assert_trajectory_parity(te, to)
 
 
-def test_private_scatter_is_bit_reproducible(ba):
-    """Modes 2 and 3 use a fixed summation order: two solves give bit-identical states."""
+@pytest.mark.parametrize("solver,fi", [(0, 0), (0, 1), (1, 0)])
+def test_solve_is_bit_reproducible(ba, solver, fi):
+    """Every sum has a fixed order (partial rows / by-block pair lists): two solves give bit-identical states."""
     P = ba.synth("ladybug", seed=9)
     states = []
     for _ in range(2):
-        with ba.Engine(intrinsics_free=0, max_num_iterations=5) as eng:
+        with ba.Engine(intrinsics_free=fi, max_num_iterations=5, linear_solver=solver) as eng:
             eng.set_problem(P)
             eng.solve()
             states.append(eng.get_state())
@@ -127,7 +134,8 @@ def test_reset_state_reproduces(ba):
     assert s1.num_iterations == s2.num_iterations
 
 
-def test_long_track_and_ragged(ba, oracle):
+@pytest.mark.parametrize("solver", [0, 1])
+def test_long_track_and_ragged(ba, oracle, solver):
     """A point seen by more cameras than one tile holds (long-point path), empty points and an unobserved camera."""
     P = ba.synth(num_cameras=300, num_points=60, num_observations=60 * 2 + 298 + 100, seed=5, max_track=300)
     # make point 0 visible from every camera: rebuild the observation list by hand
@@ -154,7 +162,7 @@ def test_long_track_and_ragged(ba, oracle):
         uv[i] = [P.intr[0, 0] * Pc[0] / Pc[2] + P.intr[0, 2], P.intr[0, 1] * Pc[1] / Pc[2] + P.intr[0, 3]]
     uv += rng.normal(0, 0.5, uv.shape)
     Q = ba.Problem(pose=P.pose, intr=P.intr, cam_group=P.cam_group, cam_fixed=P.cam_fixed, pt=P.pt, obs_cam=obs_cam, obs_pt=obs_pt, obs_uv=uv)
-    (se, te, xe), (so, to, xo) = solve_both(ba, oracle, Q, intrinsics_free=1, max_num_iterations=6)
+    (se, te, xe), (so, to, xo) = solve_both(ba, oracle, Q, intrinsics_free=1, max_num_iterations=6, engine_solver=solver)
     assert_trajectory_parity(te, to)
     # untouched parameters stay bit-identical
     assert np.array_equal(xe[2][7], Q.pt[7]) and np.array_equal(xe[2][8], Q.pt[8])
@@ -200,3 +208,54 @@ def test_g2o_policy_trajectory_parity(ba, oracle, name):
         assert a.relative_decrease == pytest.approx(b.relative_decrease, rel=1e-3, abs=1e-7)   # (chi2 - chi2+) cancels near convergence
     assert rel_err(xe[0], xo[0]) <= STATE_RTOL and rel_err(xe[2], xo[2]) <= STATE_RTOL
     assert np.array_equal(xe[1], P.intr)
+
+
+def test_linear_solver_resolution(ba):
+    """AUTO takes the direct solve where it applies (SURVEY 8 f-2 regime), PCG elsewhere; EXACT refuses what it cannot do."""
+    P = ba.synth("ladybug")
+    for fi in (0, 1):
+        with ba.Engine(intrinsics_free=fi) as eng:
+            eng.set_problem(P)
+            assert eng.linear_solver_in_use() == 0
+    with ba.Engine(intrinsics_free=0, linear_solver=1) as eng:
+        eng.set_problem(P)
+        assert eng.linear_solver_in_use() == 1
+    big = ba.synth(num_cameras=400, num_points=3000, num_observations=12000, seed=1)      # 2400 reduced unknowns > 2048
+    with ba.Engine(intrinsics_free=0) as eng:
+        eng.set_problem(big)
+        assert eng.linear_solver_in_use() == 1
+    with ba.Engine(intrinsics_free=0, linear_solver=0) as eng:                              # forced: allowed up to 8192
+        eng.set_problem(big)
+        assert eng.linear_solver_in_use() == 0
+    Nc = P.sizes[0]
+    per_cam = ba.Problem(pose=P.pose, intr=np.repeat(P.intr, Nc, axis=0), cam_group=np.arange(Nc, dtype=np.int32), cam_fixed=P.cam_fixed, pt=P.pt,
+                         obs_cam=P.obs_cam, obs_pt=P.obs_pt, obs_uv=P.obs_uv)
+    with ba.Engine(intrinsics_free=1) as eng:
+        eng.set_problem(per_cam)
+        assert eng.linear_solver_in_use() == 1                                              # free intrinsics, one group per camera
+    with ba.Engine(intrinsics_free=1, linear_solver=0) as eng:
+        with pytest.raises(ba.BAError, match="BA_LINEAR_EXACT"):
+            eng.set_problem(per_cam)
+
+
+@pytest.mark.parametrize("fi", [0, 1])
+def test_direct_solve_matches_oracle_tightly(ba, oracle, fi):
+    """The dense path is the oracle's algorithm (exact Schur complement): agreement is at rounding level, not PCG-tolerance level."""
+    P = ba.synth("ladybug", seed=4)
+    (se, te, xe), (so, to, xo) = solve_both(ba, oracle, P, intrinsics_free=fi, max_num_iterations=8, engine_solver=0)
+    assert len(te) == len(to)
+    for a, b in zip(te, to):
+        assert a.step_is_successful == b.step_is_successful and abs(a.cost - b.cost) <= 1e-9 * abs(b.cost)
+        assert a.pcg_iterations == 0
+    assert rel_err(xe[2], xo[2]) <= 1e-8
+
+
+def test_direct_solve_survives_a_singular_system(ba):
+    """No damping on a problem whose scale gauge is free: S is singular to rounding.  Whatever the factorisation meets (a non-positive
+    pivot: invalid step, radius shrinks; or a tiny pivot: a wild step that is rejected) the solve ends cleanly with finite costs."""
+    P = ba.synth("tiny")
+    with ba.Engine(intrinsics_free=0, linear_solver=0, min_lm_diagonal=0.0, max_lm_diagonal=0.0, max_num_iterations=3) as eng:
+        eng.set_problem(P)
+        s = eng.solve()
+        t = eng.trajectory()
+    assert s.num_iterations >= 1 and all(np.isfinite(r.cost) for r in t)
