@@ -38,7 +38,15 @@ struct DenseView {
     const int* blk_off;    // [nblk + 1] into pairs
     const int2* blk_key;   // [nblk] (ci, cj), ci >= cj
     const int2* pairs;     // (observation i, observation j): block (cam i, cam j) -= U_i W_j^T
+    // work items: a block's pair list cut into chunks of <= PAIR_CHUNK pairs, one warp per item
+    int nitems;
+    const int4* items;     // (block, first pair, end pair, first item of the block)
+    const int* blk_item_off;   // [nblk + 1]
+    double* item_part;     // [nitems][36] partial sums of multi-item blocks
+    int* blk_ticket;       // [nblk] arrival counters, zero between launches (the last warp to arrive sums the partials in item order and resets)
+    double* Zinv;          // [T][32][32] transposed inverses of the diagonal factor blocks: Zinv[k][c][m] = (L_kk^-1)[m][c]... see k_dense_chol
 };
+constexpr int PAIR_CHUNK = 64;
 
 __global__ void __launch_bounds__(128) k_dense_wu(View V, DenseView D) {
     const int o = blockIdx.x * blockDim.x + threadIdx.x;
@@ -126,17 +134,18 @@ __global__ void __launch_bounds__(256) k_dense_init(int Nc, int fi, DenseView D,
     }
 }
 
-// One warp per (ci, cj) block: lanes stride over the block's pair list, 36 accumulators each, butterfly reduction, then the block
-// (owned by this warp alone) is updated in place.
+// One warp per work item (a chunk of <= PAIR_CHUNK pairs of one (ci, cj) block): 36 accumulators per lane, butterfly reduction.  A
+// block with one item is updated in place by its warp; otherwise the partial goes to item_part and the LAST warp of the block to
+// arrive (ticket counter) adds the partials in item order — the sum does not depend on which warp that was.
 __global__ void __launch_bounds__(128) k_dense_pairs(DenseView D) {
     const int lane = threadIdx.x & 31;
     const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
-    for (int blk = warp; blk < D.nblk; blk += nwarps) {
-        const int beg = D.blk_off[blk], end = D.blk_off[blk + 1];
+    for (int item = warp; item < D.nitems; item += nwarps) {
+        const int4 it = D.items[item];
         double acc[36];
 #pragma unroll
         for (int k = 0; k < 36; ++k) acc[k] = 0.0;
-        for (int q = beg + lane; q < end; q += 32) {
+        for (int q = it.y + lane; q < it.z; q += 32) {
             const int2 pr = D.pairs[q];
             const double2* U2 = reinterpret_cast<const double2*>(D.WU + 36 * size_t(pr.x));
             const double2* W2 = reinterpret_cast<const double2*>(D.WU + 36 * size_t(pr.y) + 18);
@@ -152,24 +161,51 @@ __global__ void __launch_bounds__(128) k_dense_pairs(DenseView D) {
         for (int k = 0; k < 36; ++k)
 #pragma unroll
             for (int d = 16; d > 0; d >>= 1) acc[k] += __shfl_xor_sync(0xffffffffu, acc[k], d);
+        const int blk = it.x;
+        const int nit = D.blk_item_off[blk + 1] - D.blk_item_off[blk];
         const int2 key = D.blk_key[blk];
         double* Sb = D.S + size_t(6 * key.x) * D.ld + 6 * key.y;
+        if (nit == 1) {
+#pragma unroll
+            for (int k = 0; k < 36; ++k)
+                if (lane == (k & 31)) Sb[size_t(k / 6) * D.ld + (k % 6)] -= acc[k];
+            continue;
+        }
+        double* mine = D.item_part + 36 * size_t(item);
 #pragma unroll
         for (int k = 0; k < 36; ++k)
-            if (lane == (k & 31)) Sb[size_t(k / 6) * D.ld + (k % 6)] -= acc[k];
+            if (lane == (k & 31)) __stcg(mine + k, acc[k]);
+        __threadfence();
+        __syncwarp();
+        int last = 0;
+        if (lane == 0) {
+            last = atomicAdd(D.blk_ticket + blk, 1) == nit - 1;
+            if (last) D.blk_ticket[blk] = 0;
+        }
+        last = __shfl_sync(0xffffffffu, last, 0);
+        if (!last) continue;
+        __threadfence();
+        const double* part = D.item_part + 36 * size_t(it.w);
+        double s0 = 0.0, s1 = 0.0;
+        for (int i = 0; i < nit; ++i) {
+            s0 += __ldcg(part + 36 * size_t(i) + lane);
+            if (lane < 4) s1 += __ldcg(part + 36 * size_t(i) + 32 + lane);
+        }
+        Sb[size_t(lane / 6) * D.ld + (lane % 6)] -= s0;
+        if (lane < 4) Sb[size_t((32 + lane) / 6) * D.ld + ((32 + lane) % 6)] -= s1;
     }
 }
 
 // Free intrinsics (one shared Camera): rows 6 Nc .. 6 Nc + 3 against camera c:  sum over the camera's observations of
-// Ji^T Jc - (G_p Hinv_p) W_o^T.  One warp per camera, by-camera observation list, fixed order.
+// Ji^T Jc - (G_p Hinv_p) W_o^T.  One CTA per camera over its by-camera observation list, fixed order.
 __global__ void __launch_bounds__(128) k_dense_border(View V, DenseView D) {
-    const int lane = threadIdx.x & 31;
-    const int c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    if (c >= V.Nc) return;
+    __shared__ double sm[4][24];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int c = blockIdx.x;
     double acc[24];
 #pragma unroll
     for (int k = 0; k < 24; ++k) acc[k] = 0.0;
-    for (int idx = V.cam_off[c] + lane; idx < V.cam_off[c + 1]; idx += 32) {
+    for (int idx = V.cam_off[c] + threadIdx.x; idx < V.cam_off[c + 1]; idx += blockDim.x) {
         const int o = V.perm_by_cam[idx];
         const double* gh = D.GH + 24 * size_t(V.obs_pt[o]) + 12;
         const double* w = D.WU + 36 * size_t(o) + 18;
@@ -185,47 +221,66 @@ __global__ void __launch_bounds__(128) k_dense_border(View V, DenseView D) {
         }
     }
 #pragma unroll
-    for (int k = 0; k < 24; ++k)
-#pragma unroll
-        for (int d = 16; d > 0; d >>= 1) acc[k] += __shfl_xor_sync(0xffffffffu, acc[k], d);
-#pragma unroll
-    for (int k = 0; k < 24; ++k)
-        if (lane == k) D.S[size_t(6 * V.Nc + k / 6) * D.ld + 6 * c + (k % 6)] = acc[k];
+    for (int k = 0; k < 24; ++k) { const double v = warp_sum(acc[k]); if (lane == 0) sm[wid][k] = v; }
+    __syncthreads();
+    if (threadIdx.x < 24) {
+        const int k = threadIdx.x;
+        D.S[size_t(6 * V.Nc + k / 6) * D.ld + 6 * c + (k % 6)] = (sm[0][k] + sm[1][k]) + (sm[2][k] + sm[3][k]);
+    }
 }
 
 // ---- blocked Cholesky of the augmented matrix, forward substitution folded in, then back substitution -----------------------------
 namespace cg = cooperative_groups;
 
-// In-place Cholesky of the lower triangle of a 32x32 shared-memory tile (row stride DTP) by one warp, lane = row.
-__device__ __forceinline__ bool potrf32(double* L, int lane) {
+// Cholesky of the lower triangle of the 32x32 shared-memory tile L (row stride DTP) AND the transposed inverse of the factor, by one
+// warp with its row in registers (lane = row; every loop is unrolled, so a[] never leaves the register file):
+//   column j:  r = rsqrt(a_jj) from lane j, the column is scaled by r (so L_jj = a_jj r), published through `col` (one STS, broadcast
+//   LDS.128 reads), and every lane folds it into the rest of its row.  One rsqrt, no division, no shared-memory dependency chain.
+// Then lane c solves L z = e_c for column c of L^-1 with z in registers and L read back through broadcast loads (Lb, row stride DT + 2
+// so that rows are 16-byte aligned); 1 / L_jj is the rsqrt already computed.  Writes L back to `L` and Zt[m][c] = (L^-1)[c][m].
+constexpr int DTB = DT + 2;
+__device__ __forceinline__ bool potrf_trinv32(double* L, double* Zt, double* Lb, double* col, double* rinv, int lane) {
+    double a[DT];
+#pragma unroll
+    for (int c = 0; c < DT; ++c) a[c] = L[lane * DTP + c];
     bool ok = true;
+#pragma unroll
     for (int j = 0; j < DT; ++j) {
-        const double d = L[j * DTP + j];
+        const double d = __shfl_sync(0xffffffffu, a[j], j);
         if (!(d > 0.0)) ok = false;   // also catches NaN
-        const double dj = sqrt(d);
-        double l = 0.0;
-        if (lane > j) { l = L[lane * DTP + j] / dj; L[lane * DTP + j] = l; }
-        else if (lane == j) L[j * DTP + j] = dj;
-        __syncwarp();
-#pragma unroll 4
-        for (int c = j + 1; c <= lane; ++c) L[lane * DTP + c] -= l * L[c * DTP + j];
-        __syncwarp();
+        const double r = rsqrt(d);
+        a[j] *= r;                    // lane j: L_jj = d r; lanes below: L_rj
+        if (lane == j) rinv[j] = r;
+        if (j + 1 < DT) {
+            col[lane] = a[j];
+            __syncwarp();
+#pragma unroll
+            for (int c = j + 1; c < DT; ++c) a[c] -= a[j] * col[c];   // lanes >= c hold real entries; the rest is never read
+            __syncwarp();
+        }
     }
+#pragma unroll
+    for (int c = 0; c < DT; ++c) {
+        const double v = c <= lane ? a[c] : 0.0;
+        L[lane * DTP + c] = v;
+        Lb[lane * DTB + c] = v;
+    }
+    __syncwarp();
+    double z[DT];   // z[r] = (L^-1)[r][lane]
+#pragma unroll
+    for (int r = 0; r < DT; ++r) {
+        double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+#pragma unroll
+        for (int m = 0; m < r; ++m) {
+            const double t = Lb[r * DTB + m] * z[m];
+            if ((m & 3) == 0) s0 += t; else if ((m & 3) == 1) s1 += t; else if ((m & 3) == 2) s2 += t; else s3 += t;
+        }
+        const double ri = rinv[r];
+        z[r] = r < lane ? 0.0 : (r == lane ? ri : -((s0 + s1) + (s2 + s3)) * ri);
+    }
+#pragma unroll
+    for (int r = 0; r < DT; ++r) Zt[lane * DTP + r] = z[r];
     return ok;
-}
-
-// Zt[m][c] = (L^-1)[c][m] for the lower-triangular tile L, one warp, lane = column m of the inverse (zero above the diagonal).
-__device__ __forceinline__ void trinv32_t(const double* L, double* Zt, int lane) {
-    double* z = Zt + lane * DTP;   // z[r] = (L^-1)[r][lane]
-    for (int r = 0; r < lane; ++r) z[r] = 0.0;
-    z[lane] = 1.0 / L[lane * DTP + lane];
-    for (int r = lane + 1; r < DT; ++r) {
-        double s0 = 0.0, s1 = 0.0;
-        int m = lane;
-        for (; m + 1 < r; m += 2) { s0 += L[r * DTP + m] * z[m]; s1 += L[r * DTP + m + 1] * z[m + 1]; }
-        if (m < r) s0 += L[r * DTP + m] * z[m];
-        z[r] = -(s0 + s1) / L[r * DTP + r];
-    }
 }
 
 // 256 threads move one 32x32 tile: thread t owns row t>>3, columns 4 (t&7) .. +3.
@@ -253,7 +308,9 @@ __device__ __forceinline__ void tile_mma(const double* A, const double* Bt, int 
 
 __global__ void __launch_bounds__(256) k_dense_chol(DenseView D, double* __restrict__ x, PcgState2* __restrict__ pcg, int* __restrict__ bad_flag) {
     __shared__ double sL[DT * DTP], sZt[DT * DTP], sA[DT * DTP], sBt[DT * DTP];
-    __shared__ double sx[DT];
+    __shared__ __align__(16) double sLb[DT * DTB];
+    __shared__ __align__(16) double scol[DT];
+    __shared__ double sx[DT], srinv[DT];
     __shared__ int s_ok;
     cg::grid_group grid = cg::this_grid();
     const int tid = threadIdx.x, lane = tid & 31, T = D.T, ld = D.ld;
@@ -264,17 +321,16 @@ __global__ void __launch_bounds__(256) k_dense_chol(DenseView D, double* __restr
             tile_load(S + size_t(DT) * k * ld + DT * k, ld, sL, tid);
             __syncthreads();
             if (tid < 32) {
-                const bool ok = potrf32(sL, lane);
-                trinv32_t(sL, sZt, lane);
+                const bool ok = potrf_trinv32(sL, sZt, sLb, scol, srinv, lane);
                 if (lane == 0) s_ok = ok;
             }
             __syncthreads();
-            if (blockIdx.x == 0) {
+            if (blockIdx.x == 0) {   // keep L_kk^-1 (transposed) for the back substitution; L_kk itself is not needed again
                 if (tid == 0 && !s_ok) atomicOr(bad_flag, 16);
                 const int r = tid >> 3, c = (tid & 7) * 4;
-                double* g = S + size_t(DT * k + r) * ld + DT * k + c;
+                double* g = D.Zinv + size_t(DT * DT) * k + DT * r + c;
 #pragma unroll
-                for (int q = 0; q < 4; ++q) if (c + q <= r) g[q] = sL[r * DTP + c + q];
+                for (int q = 0; q < 4; ++q) g[q] = sZt[r * DTP + c + q];
             }
             for (int i = k + 1 + blockIdx.x; i <= T; i += gridDim.x) {
                 double* g = S + size_t(DT) * i * ld + DT * k;
@@ -314,22 +370,22 @@ __global__ void __launch_bounds__(256) k_dense_chol(DenseView D, double* __restr
     }
     grid.sync();
     if (blockIdx.x != 0) return;
-    // ---- L^T x = y, y^T = row 32 T; one CTA, block rows from the bottom, lazy update of the part of y above
+    // ---- L^T x = y, y^T = row 32 T; one CTA, block rows from the bottom: x_k = L_kk^-T y_k with the stored inverse (no sequential
+    // substitution), then the part of y above is updated with block row k of L
     double* y = S + size_t(DT) * T * ld;
     for (int kb = T - 1; kb >= 0; --kb) {
         __syncthreads();
-        tile_load(S + size_t(DT) * kb * ld + DT * kb, ld, sL, tid);
+        tile_load(D.Zinv + size_t(DT * DT) * kb, DT, sZt, tid);   // sZt[c][m] = (L_kk^-1)[m][c]
+        if (tid < DT) sx[tid] = y[DT * kb + tid];
         __syncthreads();
-        if (tid < 32) {
-            double yv = y[DT * kb + lane];
-            const double rinv = 1.0 / sL[lane * DTP + lane];
-            for (int c = DT - 1; c >= 0; --c) {
-                const double xc = __shfl_sync(0xffffffffu, yv * rinv, c);
-                if (lane == c) yv = xc;
-                else if (lane < c) yv -= sL[c * DTP + lane] * xc;
-            }
-            sx[lane] = yv;
-            if (DT * kb + lane < D.n) x[DT * kb + lane] = yv;
+        if (tid < DT) {
+            double a0 = 0.0, a1 = 0.0;
+#pragma unroll
+            for (int m = 0; m < DT; m += 2) { a0 += sZt[tid * DTP + m] * sx[m]; a1 += sZt[tid * DTP + m + 1] * sx[m + 1]; }
+            const double xv = a0 + a1;
+            __syncwarp();
+            sx[tid] = xv;
+            if (DT * kb + tid < D.n) x[DT * kb + tid] = xv;
         }
         __syncthreads();
         const double* Lrow = S + size_t(DT) * kb * ld;

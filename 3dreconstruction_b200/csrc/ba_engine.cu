@@ -161,6 +161,9 @@ struct ba_engine {
     DevBuf<double> d_S, d_WU, d_GH, d_corner;
     DevBuf<int> d_blk_off;
     DevBuf<int2> d_blk_key, d_pairs;
+    DevBuf<int4> d_items;
+    DevBuf<int> d_blk_item_off, d_blk_ticket;
+    DevBuf<double> d_item_part, d_Zinv;
     bak::DenseView DV{};
     int chol_grid = 1;
     DevBuf<double> d_redpart;          // [kRedSlices][ldf] stage-1 output of the copy reduction
@@ -389,6 +392,13 @@ void build_dense(ba_engine* e, const ba_problem* P, const vector<int32_t>& pt_of
         if (blk_key.empty() || blk_key.back().x != ci || blk_key.back().y != cj) { blk_key.push_back(make_int2(ci, cj)); blk_off.push_back(int32_t(q)); }
     }
     blk_off.push_back(int32_t(np));
+    vector<int4> items;
+    vector<int32_t> blk_item_off(blk_key.size() + 1, 0);
+    for (size_t b = 0; b < blk_key.size(); ++b) {
+        const int first = int(items.size());
+        for (int q = blk_off[b]; q < blk_off[b + 1]; q += bak::PAIR_CHUNK) items.push_back(make_int4(int(b), q, std::min(q + bak::PAIR_CHUNK, blk_off[b + 1]), first));
+        blk_item_off[b + 1] = int32_t(items.size());
+    }
     bak::DenseView& D = e->DV;
     D.n = e->nf; D.T = (e->nf + bak::DT - 1) / bak::DT; D.ld = bak::DT * D.T;
     D.nblk = int(blk_key.size());
@@ -399,7 +409,14 @@ void build_dense(ba_engine* e, const ba_problem* P, const vector<int32_t>& pt_of
     e->d_blk_off.upload(blk_off.data(), blk_off.size(), s);
     e->d_blk_key.upload(blk_key.data(), blk_key.size(), s);
     e->d_pairs.upload(A.data(), np, s);
+    e->d_items.upload(items.data(), items.size(), s);
+    e->d_blk_item_off.upload(blk_item_off.data(), blk_item_off.size(), s);
+    e->d_item_part.alloc(size_t(36) * std::max<size_t>(items.size(), 1));
+    e->d_blk_ticket.alloc(std::max<size_t>(blk_key.size(), 1)); e->d_blk_ticket.zero(s);
+    e->d_Zinv.alloc(size_t(bak::DT) * bak::DT * D.T);
     CU_TRY(cudaStreamSynchronize(s));
+    D.nitems = int(items.size()); D.items = e->d_items.p; D.blk_item_off = e->d_blk_item_off.p; D.item_part = e->d_item_part.p;
+    D.blk_ticket = e->d_blk_ticket.p; D.Zinv = e->d_Zinv.p;
     D.S = e->d_S.p; D.WU = e->d_WU.p; D.GH = e->d_GH.p; D.corner_part = e->d_corner.p;
     D.blk_off = e->d_blk_off.p; D.blk_key = e->d_blk_key.p; D.pairs = e->d_pairs.p;
     int occ = 1;
@@ -775,7 +792,7 @@ int solve_linear(ba_engine* e, double radius, double* rel_out, double lambda = 0
     CU_TRY(cudaMemsetAsync(&sc->bad_lin, 0, sizeof(int), s));
     if (e->Np > 0) { LaunchTimer t(e, KID_K3P); KL(e), bak::k3_point_blocks<<<cdiv(e->Np, 256), 256, 0, s>>>(e->V, lm, &sc->bad_lin); }
     { LaunchTimer t(e, KID_K3C);
-      KL(e), bak::k3_camera_blocks<<<cdiv(e->Nc + e->Ng, 128), 128, 0, s>>>(e->Nc, e->Ng, e->fi, e->Hcc(), e->Hii(), e->d_sc_f.p, lm, e->d_Df2.p, e->d_Minv.p, &sc->bad_lin); }
+      KL(e), bak::k3_camera_blocks<<<cdiv(e->Nc + e->Ng, 128), 128, 0, s>>>(e->Nc, e->Ng, e->fi, e->Hcc(), e->Hii(), e->d_sc_f.p, lm, e->d_Df2.p, e->dense ? nullptr : e->d_Minv.p, &sc->bad_lin); }
     // Source of k_pcg_q's reduction: mode 2 sums the G private copies directly (and re-zeroes them); mode 3 first folds
     // them into kRedSlices slices with a wide grid (k_reduce_copies), the pipe kernel clears its own copy on entry.
     auto reduce_src = [&](int G, const int* done, double*& src, int& nsrc) {
@@ -806,8 +823,8 @@ int solve_linear(ba_engine* e, double radius, double* rel_out, double lambda = 0
             if (e->No > 0) KL(e), bak::k_dense_wu<<<cdiv(e->No, 128), 128, 0, s>>>(e->V, D);
             if (e->fi) KL(e), bak::k_dense_point_g<<<D.corner_blocks, 128, 0, s>>>(e->V, D);
             KL(e), bak::k_dense_init<<<cdiv(36 * e->Nc + D.ld + 16, 256), 256, 0, s>>>(e->Nc, e->fi, D, e->Hcc(), e->Hii(), e->d_Df2.p, e->d_b.p);
-            if (D.nblk > 0) KL(e), bak::k_dense_pairs<<<std::min(cdiv(D.nblk, 4), 16 * e->num_sms), 128, 0, s>>>(D);
-            if (e->fi && e->No > 0) KL(e), bak::k_dense_border<<<cdiv(e->Nc * 32, 128), 128, 0, s>>>(e->V, D);
+            if (D.nitems > 0) KL(e), bak::k_dense_pairs<<<std::min(cdiv(D.nitems, 4), 16 * e->num_sms), 128, 0, s>>>(D);
+            if (e->fi && e->Nc > 0) KL(e), bak::k_dense_border<<<e->Nc, 128, 0, s>>>(e->V, D);
         }
         {
             LaunchTimer t(e, KID_DCHOL);

@@ -821,6 +821,7 @@ __global__ void k3_camera_blocks(int Nc, int Ng, int fi, const double* __restric
         double A[36], I[36];
         for (int k = 0; k < 36; ++k) A[k] = Hcc[36 * size_t(b) + k];
         for (int k = 0; k < 6; ++k) { const double d = damping(A[7 * k], sc_f[6 * b + k], lm); Df2[6 * b + k] = d; A[7 * k] += d; }
+        if (!Minv) return;   // direct solve: only the damping is needed
         if (!spd_inverse<6>(A, I)) { atomicOr(bad_flag, 4); for (int k = 0; k < 36; ++k) I[k] = 0.0; }
         for (int k = 0; k < 36; ++k) Minv[36 * size_t(b) + k] = I[k];
     } else if (fi && b < Nc + Ng) {
@@ -828,6 +829,7 @@ __global__ void k3_camera_blocks(int Nc, int Ng, int fi, const double* __restric
         double A[16], I[16];
         for (int k = 0; k < 16; ++k) A[k] = Hii[16 * size_t(g) + k];
         for (int k = 0; k < 4; ++k) { const double d = damping(A[5 * k], sc_f[6 * Nc + 4 * g + k], lm); Df2[6 * Nc + 4 * g + k] = d; A[5 * k] += d; }
+        if (!Minv) return;
         if (!spd_inverse<4>(A, I)) { atomicOr(bad_flag, 4); for (int k = 0; k < 16; ++k) I[k] = 0.0; }
         for (int k = 0; k < 16; ++k) Minv[36 * size_t(Nc) + 16 * size_t(g) + k] = I[k];
     }
