@@ -163,6 +163,42 @@ class Handle:
         self._check(self.lib.ba_set_problem(self.h, C.byref(cs)), "ba_set_problem")
         self.sizes = problem.sizes
 
+    def append(self, pose=None, cam_group=None, cam_fixed=None, intr=None, pt=None, obs_cam=None, obs_pt=None, obs_uv=None):
+        """ba_append: grow the problem held by the handle (new poses / groups / points after the existing ones, observations in any
+        order); the state already in the handle is kept."""
+        pose = _as(np.zeros((0, 6)) if pose is None else pose, np.float64).reshape(-1, 6)
+        nc = pose.shape[0]
+        cam_group = _as(np.zeros(nc) if cam_group is None else cam_group, np.int32).reshape(-1)
+        cam_fixed = _as(np.zeros(nc) if cam_fixed is None else cam_fixed, np.uint8).reshape(-1)
+        intr = _as(np.zeros((0, 4)) if intr is None else intr, np.float64).reshape(-1, 4)
+        pt = _as(np.zeros((0, 3)) if pt is None else pt, np.float64).reshape(-1, 3)
+        obs_cam = _as(np.zeros(0) if obs_cam is None else obs_cam, np.int32).reshape(-1)
+        obs_pt = _as(np.zeros(0) if obs_pt is None else obs_pt, np.int32).reshape(-1)
+        obs_uv = _as(np.zeros((0, 2)) if obs_uv is None else obs_uv, np.float64).reshape(-1, 2)
+        if not (cam_group.size == cam_fixed.size == nc and obs_cam.size == obs_pt.size == obs_uv.shape[0]):
+            raise ValueError("inconsistent delta sizes")
+        d, i, u = _capi.c_double_p, _capi.c_int32_p, _capi.c_uint8_p
+        D = _capi.BADelta(nc, pose.ctypes.data_as(d), cam_group.ctypes.data_as(i), cam_fixed.ctypes.data_as(u), intr.shape[0], intr.ctypes.data_as(d),
+                          pt.shape[0], pt.ctypes.data_as(d), obs_cam.size, obs_cam.ctypes.data_as(i), obs_pt.ctypes.data_as(i), obs_uv.ctypes.data_as(d))
+        self._check(self.lib.ba_append(self.h, C.byref(D)), "ba_append")
+        self.sizes = (self.sizes[0] + nc, self.sizes[1] + intr.shape[0], self.sizes[2] + pt.shape[0], self.sizes[3] + obs_cam.size)
+
+    def update_parameters(self, kind, first, values):
+        """ba_update_parameters: kind 0 poses (n x 6), 1 intrinsics (n x 4), 2 points (n x 3), ids [first, first + n)."""
+        w = (6, 4, 3)[kind]
+        v = _as(values, np.float64).reshape(-1, w)
+        self._check(self.lib.ba_update_parameters(self.h, kind, first, v.shape[0], v.ctypes.data_as(_capi.c_double_p)), "ba_update_parameters")
+
+    def observations(self):
+        """(obs_cam, obs_pt, obs_uv) in the handle's order."""
+        No = self.sizes[3]
+        oc, op, uv = np.empty(No, np.int32), np.empty(No, np.int32), np.empty((No, 2))
+        n = C.c_int32(0)
+        self._check(self.lib.ba_get_observations(self.h, oc.ctypes.data_as(_capi.c_int32_p), op.ctypes.data_as(_capi.c_int32_p),
+                                                 uv.ctypes.data_as(_capi.c_double_p), No, C.byref(n)), "ba_get_observations")
+        assert n.value == No
+        return oc, op, uv
+
     def reset_state(self):
         self._check(self.lib.ba_reset_state(self.h), "ba_reset_state")
 

@@ -50,7 +50,8 @@ class BAOptions(C.Structure):
         ("scatter_mode", C.c_int32),
         ("p2p_allreduce", C.c_int32),
         ("lm_policy", C.c_int32),
-        ("reserved", C.c_int32 * 5),
+        ("warm_start_radius", C.c_int32),
+        ("reserved", C.c_int32 * 4),
     ]
 
 
@@ -68,6 +69,15 @@ class BAProblem(C.Structure):
         ("obs_cam", c_int32_p),
         ("obs_pt", c_int32_p),
         ("obs_uv", c_double_p),
+    ]
+
+
+class BADelta(C.Structure):
+    _fields_ = [
+        ("num_new_cameras", C.c_int32), ("pose", c_double_p), ("cam_group", c_int32_p), ("cam_fixed", c_uint8_p),
+        ("num_new_groups", C.c_int32), ("intr", c_double_p),
+        ("num_new_points", C.c_int32), ("pt", c_double_p),
+        ("num_new_observations", C.c_int32), ("obs_cam", c_int32_p), ("obs_pt", c_int32_p), ("obs_uv", c_double_p),
     ]
 
 
@@ -159,6 +169,9 @@ ENGINE_SYMBOLS = [
     ("ba_create", C.c_int, [C.POINTER(BAOptions), C.POINTER(C.c_void_p)]),
     ("ba_set_problem", C.c_int, [C.c_void_p, C.POINTER(BAProblem)]),
     ("ba_reset_state", C.c_int, [C.c_void_p]),
+    ("ba_append", C.c_int, [C.c_void_p, C.POINTER(BADelta)]),
+    ("ba_update_parameters", C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, c_double_p]),
+    ("ba_get_observations", C.c_int, [C.c_void_p, c_int32_p, c_int32_p, c_double_p, C.c_int32, c_int32_p]),
     ("ba_solve", C.c_int, [C.c_void_p, C.POINTER(BASummary)]),
     ("ba_get_state", C.c_int, [C.c_void_p, c_double_p, c_double_p, c_double_p]),
     ("ba_get_trajectory", C.c_int, [C.c_void_p, C.POINTER(BAIterRecord), C.c_int32, c_int32_p]),

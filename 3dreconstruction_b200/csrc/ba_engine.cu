@@ -9,6 +9,7 @@
 // and all PCG vectors are replicated; per-rank partial sums of camera-side quantities are combined with NCCL
 // all-reduces on the compute stream.  NCCL is loaded with dlopen only when world_size > 1.
 #include "../../include/ba_engine.h"
+#include "../../include/ba_merge.hpp"
 
 #include <cuda_runtime.h>
 #include <dlfcn.h>
@@ -133,6 +134,9 @@ struct ba_engine {
     int Np = 0, No = 0, ldo = 0, nTiles = 0, nf = 0, fi = 0;
     // host copies kept for ba_get_structure and ba_reset_state
     vector<int32_t> h_obs_cam, h_obs_pt;
+    vector<int32_t> h_cam_group;
+    vector<double> h_obs_uv;           // host mirror of the observation pixels (ba_append merges into it)
+    double last_radius = 0.0;          // final trust-region radius of the previous solve (warm_start_radius)
     vector<uint8_t> h_cam_fixed, h_cam_free;
     vector<int32_t> h_shard_pt;   // [world+1] point range boundaries of every rank
     // device: static problem data
@@ -430,7 +434,9 @@ void build_dense(ba_engine* e, const ba_problem* P, const vector<int32_t>& pt_of
     e->stats[KID_DCHOL].bytes = 8.0 * double(D.ld) * D.ld * (D.T + 2) / 6.0;
 }
 
-void do_set_problem(ba_engine* e, const ba_problem* P) {
+struct DevState { const double* pose; const double* intr; const double* pt; };   // device-resident parameters of the whole (merged) problem
+
+void do_set_problem(ba_engine* e, const ba_problem* P, const DevState* dev = nullptr) {
     const int Nc = P->num_cameras, Ng = P->num_groups, NpG = P->num_points, NoG = P->num_observations;
     const int W = e->opt.world_size, R = e->opt.rank;
     CU_TRY(cudaSetDevice(e->device));
@@ -441,6 +447,8 @@ void do_set_problem(ba_engine* e, const ba_problem* P) {
     e->h_obs_cam.assign(P->obs_cam, P->obs_cam + NoG);
     e->h_obs_pt.assign(P->obs_pt, P->obs_pt + NoG);
     e->h_cam_fixed.assign(P->cam_fixed, P->cam_fixed + Nc);
+    e->h_cam_group.assign(P->cam_group, P->cam_group + Nc);
+    e->h_obs_uv.assign(P->obs_uv, P->obs_uv + size_t(2) * NoG);
 
     // global CSR by point, global free masks
     vector<int32_t> gpt_off(size_t(NpG) + 1, 0);
@@ -578,9 +586,16 @@ void do_set_problem(ba_engine* e, const ba_problem* P) {
         e->d_grp_off.upload(goff.data(), goff.size(), s); e->d_grp_cams.upload(gcams.data(), gcams.size(), s);
         e->d_ipart.alloc(size_t(14) * std::max(Nc, 1));
     }
-    e->d_pose0.upload(P->pose, size_t(6) * Nc, s);
-    e->d_intr0.upload(P->intr, size_t(4) * Ng, s);
-    e->d_pt0.upload(P->pt + size_t(3) * e->pb, size_t(3) * Np, s);
+    if (dev) {   // ba_append: the parameters are already on the device
+        e->d_pose0.alloc(size_t(6) * Nc); e->d_intr0.alloc(size_t(4) * Ng); e->d_pt0.alloc(size_t(3) * Np);
+        CU_TRY(cudaMemcpyAsync(e->d_pose0.p, dev->pose, size_t(6) * Nc * sizeof(double), cudaMemcpyDeviceToDevice, s));
+        CU_TRY(cudaMemcpyAsync(e->d_intr0.p, dev->intr, size_t(4) * Ng * sizeof(double), cudaMemcpyDeviceToDevice, s));
+        CU_TRY(cudaMemcpyAsync(e->d_pt0.p, dev->pt, size_t(3) * Np * sizeof(double), cudaMemcpyDeviceToDevice, s));
+    } else {
+        e->d_pose0.upload(P->pose, size_t(6) * Nc, s);
+        e->d_intr0.upload(P->intr, size_t(4) * Ng, s);
+        e->d_pt0.upload(P->pt + size_t(3) * e->pb, size_t(3) * Np, s);
+    }
     for (auto* b : {&e->d_pose, &e->d_cpose}) b->alloc(size_t(6) * Nc);
     for (auto* b : {&e->d_intr, &e->d_cintr}) b->alloc(size_t(4) * Ng);
     for (auto* b : {&e->d_pt, &e->d_cpt}) b->alloc(size_t(3) * Np);
@@ -912,6 +927,7 @@ void lm_solve(ba_engine* e) {
     CU_TRY(cudaEventRecord(e->ev_t0, s));
     auto finish = [&](int term, const char* msg, double cost) {
         S.termination = term; S.usable = (term != BA_TERM_FAILURE); S.final_cost = cost; S.num_iterations = int(e->traj.size());
+        if (!e->traj.empty() && e->traj.back().radius > 0.0) e->last_radius = e->traj.back().radius;
         std::snprintf(S.message, sizeof S.message, "%s", msg);
         CU_TRY(cudaEventRecord(e->ev_t1, s));
         CU_TRY(cudaEventSynchronize(e->ev_t1));
@@ -939,7 +955,7 @@ void lm_solve(ba_engine* e) {
     if (H->bad_eval || !std::isfinite(cost)) { finish(BA_TERM_FAILURE, "initial residual/Jacobian evaluation failed (non-finite)", cost); return; }
     double gmax = std::max(H->gmax_pt, H->gmax_f);
     double x_norm = std::sqrt(H->xn2_pt + H->xn2_f);
-    double radius = O.initial_trust_region_radius, decrease_factor = 2.0;
+    double radius = (O.warm_start_radius && e->last_radius > 0.0) ? e->last_radius : O.initial_trust_region_radius, decrease_factor = 2.0;
     int num_invalid = 0;
     {
         ba_iter_record R{}; R.step_is_valid = 1; R.step_is_successful = 1; R.cost = cost; R.radius = radius; R.radius_used = radius; R.gradient_max_norm = gmax;
@@ -1186,6 +1202,69 @@ int ba_set_problem(ba_engine* e, const ba_problem* p) {
     }
     e->has_problem = false;
     return guarded(e, [&] { do_set_problem(e, p); });
+}
+
+int ba_append(ba_engine* e, const ba_delta* d) {
+    if (!e || !d) return fail(e, BA_ERR_INVALID_ARGUMENT, "null argument");
+    if (!e->has_problem) return fail(e, BA_ERR_NO_PROBLEM, "no problem set");
+    if (e->opt.world_size > 1) return fail(e, BA_ERR_UNSUPPORTED, "ba_append runs on one GPU (world_size = 1)");
+    ba_merge::Merged M;
+    const std::string why = ba_merge::merge(e->Nc, e->Ng, e->NpG, e->NoG, e->h_cam_group.data(), e->h_cam_fixed.data(), e->h_obs_cam.data(), e->h_obs_pt.data(),
+                                            e->h_obs_uv.data(), *d, M);
+    if (!why.empty()) return fail(e, BA_ERR_INVALID_ARGUMENT, "ba_append: " + why);
+    return guarded(e, [&] {
+        CU_TRY(cudaSetDevice(e->device));
+        cudaStream_t s = e->stream;
+        // merged parameters, assembled on the device: [current state | new entries]; only the new entries cross PCIe
+        DevBuf<double> t_pose, t_intr, t_pt;
+        t_pose.alloc(size_t(6) * M.Nc); t_intr.alloc(size_t(4) * M.Ng); t_pt.alloc(size_t(3) * M.Np);
+        auto join = [&](DevBuf<double>& t, const double* cur, size_t n_old, const double* add, size_t n_new) {
+            if (n_old) CU_TRY(cudaMemcpyAsync(t.p, cur, n_old * sizeof(double), cudaMemcpyDeviceToDevice, s));
+            if (n_new) { CU_TRY(cudaMemcpyAsync(t.p + n_old, add, n_new * sizeof(double), cudaMemcpyHostToDevice, s)); g_h2d_bytes += int64_t(n_new * sizeof(double)); }
+        };
+        join(t_pose, e->d_pose.p, size_t(6) * e->Nc, d->pose, size_t(6) * d->num_new_cameras);
+        join(t_intr, e->d_intr.p, size_t(4) * e->Ng, d->intr, size_t(4) * d->num_new_groups);
+        join(t_pt, e->d_pt.p, size_t(3) * e->Np, d->pt, size_t(3) * d->num_new_points);
+        ba_problem P{};
+        P.num_cameras = M.Nc; P.num_groups = M.Ng; P.num_points = M.Np; P.num_observations = M.No;
+        P.cam_group = M.cam_group.data(); P.cam_fixed = M.cam_fixed.data();
+        P.obs_cam = M.obs_cam.data(); P.obs_pt = M.obs_pt.data(); P.obs_uv = M.obs_uv.data();
+        const DevState dev{t_pose.p, t_intr.p, t_pt.p};
+        e->has_problem = false;
+        do_set_problem(e, &P, &dev);
+        CU_TRY(cudaStreamSynchronize(s));   // the temporaries go out of scope
+    });
+}
+
+int ba_update_parameters(ba_engine* e, int32_t kind, int32_t first, int32_t count, const double* values) {
+    if (!e) return BA_ERR_INVALID_ARGUMENT;
+    if (!e->has_problem) return fail(e, BA_ERR_NO_PROBLEM, "no problem set");
+    if (e->opt.world_size > 1) return fail(e, BA_ERR_UNSUPPORTED, "ba_update_parameters runs on one GPU (world_size = 1)");
+    if (kind < 0 || kind > 2) return fail(e, BA_ERR_INVALID_ARGUMENT, "ba_update_parameters: kind must be 0 (poses), 1 (intrinsics) or 2 (points)");
+    const int w = kind == 0 ? 6 : (kind == 1 ? 4 : 3), n = kind == 0 ? e->Nc : (kind == 1 ? e->Ng : e->Np);
+    if (first < 0 || count < 0 || int64_t(first) + count > n || (count && !values)) return fail(e, BA_ERR_INVALID_ARGUMENT, "ba_update_parameters: range out of bounds");
+    if (!count) return BA_OK;
+    return guarded(e, [&] {
+        CU_TRY(cudaSetDevice(e->device));
+        double* cur = kind == 0 ? e->d_pose.p : (kind == 1 ? e->d_intr.p : e->d_pt.p);
+        double* ini = kind == 0 ? e->d_pose0.p : (kind == 1 ? e->d_intr0.p : e->d_pt0.p);
+        const size_t bytes = size_t(w) * count * sizeof(double), off = size_t(w) * first;
+        CU_TRY(cudaMemcpyAsync(cur + off, values, bytes, cudaMemcpyHostToDevice, e->stream));
+        CU_TRY(cudaMemcpyAsync(ini + off, cur + off, bytes, cudaMemcpyDeviceToDevice, e->stream));
+        CU_TRY(cudaStreamSynchronize(e->stream));   // `values` may be pageable and reused by the caller
+        g_h2d_bytes += int64_t(bytes);
+    });
+}
+
+int ba_get_observations(ba_engine* e, int32_t* obs_cam, int32_t* obs_pt, double* obs_uv, int32_t cap, int32_t* n) {
+    if (!e) return BA_ERR_INVALID_ARGUMENT;
+    if (!e->has_problem) return fail(e, BA_ERR_NO_PROBLEM, "no problem set");
+    if (n) *n = e->NoG;
+    const int m = std::max(0, std::min<int>(cap, e->NoG));
+    if (obs_cam) std::copy(e->h_obs_cam.begin(), e->h_obs_cam.begin() + m, obs_cam);
+    if (obs_pt) std::copy(e->h_obs_pt.begin(), e->h_obs_pt.begin() + m, obs_pt);
+    if (obs_uv) std::copy(e->h_obs_uv.begin(), e->h_obs_uv.begin() + size_t(2) * m, obs_uv);
+    return BA_OK;
 }
 
 int ba_reset_state(ba_engine* e) {

@@ -21,6 +21,7 @@ private:
     std::unordered_map<WorldPoint::Idx, WorldPoint::Ptr> world_points_{};
 
     friend class BundleAdjuster;
+    friend class IncrementalBundleAdjuster;   // the one line a maintainer adds for the persistent adjuster
 
 public:
     WorldStructure() = default;

@@ -128,7 +128,8 @@ typedef struct ba_options {
     int32_t p2p_allreduce;               /* multi-GPU all-reduce of the PCG matvec: 0 = auto (one-shot NVLink peer-memory all-reduce fused into the
                                             K5b gather when every peer buffer can be mapped with CUDA IPC, else NCCL), 1 = NCCL only, 2 = peer memory required */
     int32_t lm_policy;                   /* ba_lm_policy; default CERES */
-    int32_t reserved[5];
+    int32_t warm_start_radius;           /* 1: ba_solve starts from the final trust-region radius of the previous solve on this handle (incremental use); 0 (default): always initial_trust_region_radius, as the reference (a fresh ceres::Solver per call) */
+    int32_t reserved[4];
 } ba_options;
 
 /* Problem in canonical indexing: observations sorted by point id (non-decreasing obs_pt),
@@ -192,6 +193,26 @@ int  ba_options_default(ba_options* opt);
 int  ba_create(const ba_options* opt, ba_engine** out);
 int  ba_set_problem(ba_engine* e, const ba_problem* p);       /* copies (engine: host->device) and builds index structure */
 int  ba_reset_state(ba_engine* e);                            /* restore the parameters given to ba_set_problem (engine: device-to-device) */
+
+/* Incremental use.  The reference runs a full bundle adjustment after every image it adds to a growing map and
+ * rebuilds the whole ceres::Problem from the map each time (actuator/SequentialActuator.h:138-229 -> BundleAdjuster.h:158-164,
+ * 176-186).  ba_append grows the problem held by the handle instead: the state already on the device (the result of the last
+ * ba_solve) is kept, new poses / Camera groups / points are appended after the existing ones (ids continue), new observations
+ * may reference old and new ids in any order and are merged into point order (within a point: existing observations first, then
+ * the new ones in the order given).  The merged state becomes the one ba_reset_state restores.  Single GPU only. */
+typedef struct ba_delta {
+    int32_t num_new_cameras;      const double* pose;  const int32_t* cam_group;  const uint8_t* cam_fixed;
+    int32_t num_new_groups;       const double* intr;
+    int32_t num_new_points;       const double* pt;
+    int32_t num_new_observations; const int32_t* obs_cam;  const int32_t* obs_pt;  const double* obs_uv;
+} ba_delta;
+int  ba_append(ba_engine* e, const ba_delta* d);
+/* Overwrite parameters held by the handle, both the current state and the one ba_reset_state restores: kind 0 = poses (6 doubles
+ * each), 1 = intrinsics groups (4), 2 = points (3); ids [first, first + count).  For callers that keep a handle alive while the
+ * map is edited outside bundle adjustment (a re-triangulated point, a pose re-estimated by PnP).  Single GPU only. */
+int  ba_update_parameters(ba_engine* e, int32_t kind, int32_t first, int32_t count, const double* values);
+/* The observation list in the handle's order (what per-observation outputs of ba_evaluate are indexed by); any pointer may be NULL. */
+int  ba_get_observations(ba_engine* e, int32_t* obs_cam, int32_t* obs_pt, double* obs_uv, int32_t cap, int32_t* n);
 int  ba_solve(ba_engine* e, ba_summary* out);                 /* blocking; whole LM loop */
 int  ba_get_state(ba_engine* e, double* pose, double* intr, double* pt); /* any may be NULL */
 int  ba_get_trajectory(ba_engine* e, ba_iter_record* out, int32_t cap, int32_t* n);

@@ -17,6 +17,7 @@
 //   residual + autodiff Jacobian                                     BundleAdjuster.h:38-68,113 -> residuals.h + jet.h
 //   solver options                                                   BundleAdjuster.h:167-174 -> ba_options_default()
 #include "../include/ba_engine.h"
+#include "../include/ba_merge.hpp"
 
 #include <algorithm>
 #include <cfloat>
@@ -780,6 +781,47 @@ int ba_set_problem(ba_engine* e, const ba_problem* p) {
     e->pose = e->pose0; e->intr = e->intr0; e->pt = e->pt0;
     build_structure(e);
     e->traj.clear(); e->has_problem = true;
+    return BA_OK;
+}
+
+int ba_append(ba_engine* e, const ba_delta* d) {
+    if (!e || !d) return fail(e, BA_ERR_INVALID_ARGUMENT, "null argument");
+    if (!e->has_problem) return fail(e, BA_ERR_NO_PROBLEM, "no problem set");
+    ba_merge::Merged M;
+    const std::string why = ba_merge::merge(e->Nc, e->Ng, e->Np, e->No, e->cam_group.data(), e->cam_fixed.data(), e->obs_cam.data(), e->obs_pt.data(), e->obs_uv.data(), *d, M);
+    if (!why.empty()) return fail(e, BA_ERR_INVALID_ARGUMENT, "ba_append: " + why);
+    vector<double> pose = e->pose, intr = e->intr, pt = e->pt;          // the current (optimised) state is kept
+    pose.insert(pose.end(), d->pose, d->pose + size_t(6) * d->num_new_cameras);
+    intr.insert(intr.end(), d->intr, d->intr + size_t(4) * d->num_new_groups);
+    pt.insert(pt.end(), d->pt, d->pt + size_t(3) * d->num_new_points);
+    ba_problem P{};
+    P.num_cameras = M.Nc; P.num_groups = M.Ng; P.num_points = M.Np; P.num_observations = M.No;
+    P.pose = pose.data(); P.intr = intr.data(); P.cam_group = M.cam_group.data(); P.cam_fixed = M.cam_fixed.data(); P.pt = pt.data();
+    P.obs_cam = M.obs_cam.data(); P.obs_pt = M.obs_pt.data(); P.obs_uv = M.obs_uv.data();
+    return ba_set_problem(e, &P);
+}
+
+int ba_update_parameters(ba_engine* e, int32_t kind, int32_t first, int32_t count, const double* values) {
+    if (!e) return BA_ERR_INVALID_ARGUMENT;
+    if (!e->has_problem) return fail(e, BA_ERR_NO_PROBLEM, "no problem set");
+    if (kind < 0 || kind > 2) return fail(e, BA_ERR_INVALID_ARGUMENT, "ba_update_parameters: kind must be 0 (poses), 1 (intrinsics) or 2 (points)");
+    const int w = kind == 0 ? 6 : (kind == 1 ? 4 : 3), n = kind == 0 ? e->Nc : (kind == 1 ? e->Ng : e->Np);
+    if (first < 0 || count < 0 || int64_t(first) + count > n || (count && !values)) return fail(e, BA_ERR_INVALID_ARGUMENT, "ba_update_parameters: range out of bounds");
+    vector<double>& cur = kind == 0 ? e->pose : (kind == 1 ? e->intr : e->pt);
+    vector<double>& ini = kind == 0 ? e->pose0 : (kind == 1 ? e->intr0 : e->pt0);
+    std::copy(values, values + size_t(w) * count, cur.begin() + size_t(w) * first);
+    std::copy(values, values + size_t(w) * count, ini.begin() + size_t(w) * first);
+    return BA_OK;
+}
+
+int ba_get_observations(ba_engine* e, int32_t* obs_cam, int32_t* obs_pt, double* obs_uv, int32_t cap, int32_t* n) {
+    if (!e) return BA_ERR_INVALID_ARGUMENT;
+    if (!e->has_problem) return fail(e, BA_ERR_NO_PROBLEM, "no problem set");
+    if (n) *n = e->No;
+    const int m = std::min<int>(cap, e->No);
+    if (obs_cam) std::copy(e->obs_cam.begin(), e->obs_cam.begin() + m, obs_cam);
+    if (obs_pt) std::copy(e->obs_pt.begin(), e->obs_pt.begin() + m, obs_pt);
+    if (obs_uv) std::copy(e->obs_uv.begin(), e->obs_uv.begin() + size_t(2) * m, obs_uv);
     return BA_OK;
 }
 

@@ -114,3 +114,48 @@ def test_adapter_matches_direct_solve_gpu(ba, tmp_path, fi):
     exe = build_driver(tmp_path, os.path.join(ROOT, "3dreconstruction_b200", "csrc"), "ba_engine")
     check_against_direct_solve(ba, lambda **kw: ba.Engine(**kw), exe, tmp_path, fi)
     check_writeback(ba, exe, tmp_path)
+
+
+# ---- IncrementalBundleAdjuster: one adjuster kept alive over a growing map == a fresh BundleAdjuster per call -------------------
+INC_SRC = os.path.join(ROOT, "tests", "cpp", "incremental_main.cpp")
+
+
+def build_incremental(tmp_path, libdir, libname):
+    exe = str(tmp_path / f"incremental_{libname}")
+    host = os.path.join(ROOT, "3dreconstruction_b200", "host")
+    subprocess.check_call(["g++", "-std=c++20", "-O1", "-Wall", INC_SRC, "-o", exe, f"-L{libdir}", f"-l{libname}", f"-L{host}", "-lba_synth",
+                           f"-Wl,-rpath,{libdir}", f"-Wl,-rpath,{host}", "-Wl,-rpath,/usr/local/cuda/lib64"])
+    return exe
+
+
+def run_incremental(exe, tmp_path, mode, scenario, cuts=(8, 14, 20, 26, 30), max_it=6):
+    out = str(tmp_path / f"inc_{mode}_{scenario}.txt")
+    subprocess.run([exe, "sequential30", out, mode, str(scenario), str(max_it)] + [str(c) for c in cuts], check=True, capture_output=True, text=True)
+    d = dict(stage=[], pose=[], pt=[])
+    for line in open(out):
+        k, *v = line.split()
+        if k in ("calls", "intr"):
+            d[k] = [float(x) for x in v]
+        else:
+            d[k].append([float(x) for x in v])
+    return {k: np.array(v) for k, v in d.items()}
+
+
+def check_incremental(exe, tmp_path):
+    for scenario, (appended, rebuilt) in {0: (4, 1), 1: (4, 1), 2: (3, 2)}.items():
+        a = run_incremental(exe, tmp_path, "fresh", scenario)
+        b = run_incremental(exe, tmp_path, "incremental", scenario)
+        assert list(b["calls"]) == [appended, rebuilt], scenario        # growth (and an edited point) ride ba_append; a lost observation forces a rebuild
+        assert a["stage"][:, 1].all() and np.array_equal(a["stage"], b["stage"]), scenario      # usable, same iterations, bit-identical costs
+        for k in ("pose", "pt", "intr"):
+            assert np.array_equal(a[k], b[k]), (scenario, k)
+        assert (a["stage"][1:, 3] > a["stage"][:-1, 4]).all()           # every stage really added residuals to a converged map
+
+
+def test_incremental_adjuster_matches_fresh_adjuster_cpu(tmp_path):
+    check_incremental(build_incremental(tmp_path, os.path.join(ROOT, "oracle"), "ba_oracle"), tmp_path)
+
+
+@pytest.mark.gpu
+def test_incremental_adjuster_matches_fresh_adjuster_gpu(tmp_path):
+    check_incremental(build_incremental(tmp_path, os.path.join(ROOT, "3dreconstruction_b200", "csrc"), "ba_engine"), tmp_path)
