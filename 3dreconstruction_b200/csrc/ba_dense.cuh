@@ -48,6 +48,15 @@ struct DenseView {
 };
 constexpr int PAIR_CHUNK = 64;
 
+// Dataflow Cholesky (k_dense_chol_df): tiles in column-major order, one flag per tile
+struct CholFlow {
+    int ntasks;
+    const int2* tasks;     // (i, j), j <= i <= T, column by column; CTA b runs tasks b, b + gridDim, ... in this order
+    int* ready;            // [(T + 1)][(T + 1)]: == epoch once L_ij (or, on the diagonal, the inverse of L_jj in Zinv) is in memory
+    int* abort;            // set by a wait that timed out: every later wait returns at once
+    int epoch;             // solve counter, so the flags never need clearing
+};
+
 __global__ void __launch_bounds__(128) k_dense_wu(View V, DenseView D) {
     const int o = blockIdx.x * blockDim.x + threadIdx.x;
     if (o >= V.No) return;
@@ -118,7 +127,7 @@ __global__ void __launch_bounds__(128) k_dense_point_g(View V, DenseView D) {
 __global__ void __launch_bounds__(256) k_dense_init(int Nc, int fi, DenseView D, const double* __restrict__ Hcc, const double* __restrict__ Hii,
                                                     const double* __restrict__ Df2, const double* __restrict__ b) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    const int nd = 36 * Nc;
+    const int nd = 36 * Nc, cbase = (nd + D.ld + 31) / 32 * 32;
     if (i < nd) {
         const int c = i / 36, e = i - 36 * c, r = e / 6, q = e - 6 * r;
         D.S[size_t(6 * c + r) * D.ld + 6 * c + q] = Hcc[i] + (r == q ? Df2[6 * c + r] : 0.0);
@@ -126,11 +135,12 @@ __global__ void __launch_bounds__(256) k_dense_init(int Nc, int fi, DenseView D,
         const int j = i - nd;
         if (j >= D.n) D.S[size_t(j) * D.ld + j] = 1.0;
         else D.S[size_t(DT) * D.T * D.ld + j] = b[j];
-    } else if (fi && i < nd + D.ld + 16) {
-        const int e = i - nd - D.ld, q = e / 4, r = e - 4 * q;
+    } else if (fi && i >= cbase && i < cbase + 16 * 32) {   // one warp per corner entry: lanes stride over the per-CTA partials, fixed tree
+        const int e = (i - cbase) >> 5, lane = (i - cbase) & 31, q = e / 4, r = e - 4 * q;
         double acc = 0.0;
-        for (int k = 0; k < D.corner_blocks; ++k) acc += D.corner_part[16 * size_t(k) + e];
-        D.S[size_t(6 * Nc + q) * D.ld + 6 * Nc + r] = Hii[e] + (q == r ? Df2[6 * Nc + q] : 0.0) - acc;
+        for (int k = lane; k < D.corner_blocks; k += 32) acc += D.corner_part[16 * size_t(k) + e];
+        acc = warp_sum(acc);
+        if (lane == 0) D.S[size_t(6 * Nc + q) * D.ld + 6 * Nc + r] = Hii[e] + (q == r ? Df2[6 * Nc + q] : 0.0) - acc;
     }
 }
 
@@ -394,6 +404,223 @@ __global__ void __launch_bounds__(256) k_dense_chol(DenseView D, double* __restr
 #pragma unroll 8
             for (int r = 0; r < DT; ++r) acc += Lrow[size_t(r) * ld + j] * sx[r];
             y[j] -= acc;
+        }
+    }
+    if (tid == 0) { pcg->k = 0; pcg->done = 1; pcg->rel = 0.0; }
+}
+
+// ---- the same factorisation as a dataflow over tiles: no grid-wide barrier inside the factorisation -------------------------------
+// Task (i, j) is LEFT-looking: acc = sum_{k<j} L_ik L_jk^T is built in registers as the operand tiles become ready (one flag per
+// tile, st.release.gpu / ld.acquire.gpu), then  diagonal: factorise + invert A_jj - acc, publish the inverse;  below the diagonal:
+// L_ij = (A_ij - acc) L_jj^-T, publish.  Tasks are dealt to the CTAs round-robin in column-major order and every CTA works through
+// its list in order; that order is a topological order of the dependency graph and all CTAs are co-resident (cooperative launch), so
+// the earliest unfinished task can always run: no deadlock.  The critical path per column is factorise+invert, one panel tile, one
+// rank-32 update (vs two grid barriers plus the same work before).  A wait that exceeds ~2 s sets `abort` and the solve fails cleanly.
+__device__ __forceinline__ int ld_acquire_gpu(const int* p) { int v; asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory"); return v; }
+__device__ __forceinline__ void st_release_gpu(int* p, int v) { asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
+
+__device__ __forceinline__ bool flow_wait(const int* flag, int epoch, int* abort) {
+    if (ld_acquire_gpu(flag) == epoch) return true;
+    const long long t0 = clock64();
+    for (;;) {
+        if (ld_acquire_gpu(flag) == epoch) return true;
+        if (*reinterpret_cast<volatile int*>(abort)) return false;
+        if (clock64() - t0 > 4000000000ll) { atomicExch(abort, 1); return false; }
+    }
+}
+
+__device__ __forceinline__ void tile_load_cg(const double* __restrict__ g, int ld, double* s, int tid) {   // L2 loads: operands written by other SMs
+    const int r = tid >> 3, c = (tid & 7) * 4;
+    const double2 a = __ldcg(reinterpret_cast<const double2*>(g + size_t(r) * ld + c)), b = __ldcg(reinterpret_cast<const double2*>(g + size_t(r) * ld + c + 2));
+    s[r * DTP + c] = a.x; s[r * DTP + c + 1] = a.y; s[r * DTP + c + 2] = b.x; s[r * DTP + c + 3] = b.y;
+}
+__device__ __forceinline__ void tile_load_t_cg(const double* __restrict__ g, int ld, double* s, int tid) {   // s[m][r] = g[r][m]
+    const int r = tid >> 3, c = (tid & 7) * 4;
+    const double2 a = __ldcg(reinterpret_cast<const double2*>(g + size_t(r) * ld + c)), b = __ldcg(reinterpret_cast<const double2*>(g + size_t(r) * ld + c + 2));
+    s[c * DTP + r] = a.x; s[(c + 1) * DTP + r] = a.y; s[(c + 2) * DTP + r] = b.x; s[(c + 3) * DTP + r] = b.y;
+}
+
+// Finalised tiles are stored TRANSPOSED in global memory (tile (i, j) holds L_ij^T, element (m, r) at [m * ld + r]) so that both
+// operands of L_ik L_jk^T arrive in the [m][row] layout the product wants with straight 16-byte cp.async copies (L2 -> shared, no L1).
+// Product: warp w takes m in [8 (w>>1), +8) and columns [16 (w&1), +16); lane (tr, tc) = (lane>>2, lane&3) owns rows 4tr..+3 and
+// columns +4tc..+3: 4 LDS.128 per 16 DFMA (the first version, one row x four columns per thread over all m, issued one LDS per DFMA
+// and was shared-memory-bandwidth-bound: 2.3 us per 32x32x32 product, tools/probe/chol_probe.cu).  The four m-groups keep their
+// partial sums in registers over the whole task and are added through shared memory once, at the end.
+constexpr int DTQ = DT + 2;             // operand row stride: rows 16-byte aligned
+constexpr int TQ = DT * DTQ;
+
+__device__ __forceinline__ void tile_cp_async(const double* __restrict__ g, int ld, double* s, int tid) {   // s[m][r] <- g[m * ld + r], 256 threads
+    const int m = tid >> 3, r4 = (tid & 7) * 4;
+    cp_async16(s + m * DTQ + r4, g + size_t(m) * ld + r4);
+    cp_async16(s + m * DTQ + r4 + 2, g + size_t(m) * ld + r4 + 2);
+}
+__device__ __forceinline__ void cp_async_wait_1() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
+
+// acc[4][4] += sum over this warp's 8 m of At[m][rows] * Bt[m][cols]
+__device__ __forceinline__ void tile_fma(const double* At, const double* Bt, int warp, int lane, double acc[16]) {
+    const int m0 = 8 * (warp >> 1), r0 = 4 * (lane >> 2), c0 = 16 * (warp & 1) + 4 * (lane & 3);
+#pragma unroll
+    for (int mm = 0; mm < 8; ++mm) {
+        const double2 a01 = *reinterpret_cast<const double2*>(At + (m0 + mm) * DTQ + r0), a23 = *reinterpret_cast<const double2*>(At + (m0 + mm) * DTQ + r0 + 2);
+        const double2 b01 = *reinterpret_cast<const double2*>(Bt + (m0 + mm) * DTQ + c0), b23 = *reinterpret_cast<const double2*>(Bt + (m0 + mm) * DTQ + c0 + 2);
+        const double a[4] = {a01.x, a01.y, a23.x, a23.y}, b[4] = {b01.x, b01.y, b23.x, b23.y};
+#pragma unroll
+        for (int p = 0; p < 4; ++p)
+#pragma unroll
+            for (int q = 0; q < 4; ++q) acc[4 * p + q] += a[p] * b[q];
+    }
+}
+// partial sums of the 4 m-groups -> red[g][row][col] (row stride DTQ)
+__device__ __forceinline__ void tile_spill(double* red, int warp, int lane, const double acc[16]) {
+    const int r0 = 4 * (lane >> 2), c0 = 16 * (warp & 1) + 4 * (lane & 3);
+    double* base = red + (warp >> 1) * TQ;
+#pragma unroll
+    for (int p = 0; p < 4; ++p) {
+        *reinterpret_cast<double2*>(base + (r0 + p) * DTQ + c0) = make_double2(acc[4 * p], acc[4 * p + 1]);
+        *reinterpret_cast<double2*>(base + (r0 + p) * DTQ + c0 + 2) = make_double2(acc[4 * p + 2], acc[4 * p + 3]);
+    }
+}
+
+__global__ void __launch_bounds__(256) k_dense_chol_df(DenseView D, CholFlow F, double* __restrict__ x, PcgState2* __restrict__ pcg, int* __restrict__ bad_flag) {
+    // shared memory (46.6 KB static): 4 operand buffers [32][34] (A0 B0 A1 B1; as one block also the 4 x [32][34] reduction scratch,
+    // and on the diagonal path the tile being factorised, its broadcast copy and the transposed inverse), plus Zt [32][34]
+    __shared__ __align__(16) double sm[5 * TQ];
+    __shared__ __align__(16) double scol[DT];
+    __shared__ double sx[DT], srinv[DT];
+    __shared__ int s_go;
+    double* const sZ = sm + 4 * TQ;
+    cg::grid_group grid = cg::this_grid();
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, T = D.T, ld = D.ld, W = T + 1;
+    const int r = tid >> 3, c = (tid & 7) * 4;
+    double* S = D.S;
+    bool alive = true;
+    for (int t = blockIdx.x; t < F.ntasks && alive; t += gridDim.x) {
+        const int2 ij = F.tasks[t];
+        const int i = ij.x, j = ij.y;
+        const bool diag = i == j;
+        double acc[16];
+#pragma unroll
+        for (int q = 0; q < 16; ++q) acc[q] = 0.0;
+        // ---- acc = sum_{k<j} L_ik L_jk^T: operands double-buffered with cp.async, the copy of step k+1 overlaps the product of step k
+        if (j > 0) {
+            if (tid == 0) s_go = flow_wait(F.ready + i * W, F.epoch, F.abort) && (diag || flow_wait(F.ready + j * W, F.epoch, F.abort));
+            __syncthreads();
+            if (!s_go) { alive = false; break; }
+            tile_cp_async(S + size_t(DT) * i * ld, ld, sm, tid);
+            if (!diag) tile_cp_async(S + size_t(DT) * j * ld, ld, sm + TQ, tid);
+            cp_async_commit();
+        }
+        for (int k = 0; k < j; ++k) {
+            const bool more = k + 1 < j;
+            if (more && tid == 0) s_go = flow_wait(F.ready + i * W + k + 1, F.epoch, F.abort) && (diag || flow_wait(F.ready + j * W + k + 1, F.epoch, F.abort));
+            __syncthreads();                       // flags of step k+1 seen; everyone is done with the buffers of step k-1
+            if (more && !s_go) { alive = false; break; }
+            if (more) {
+                double* nb = sm + 2 * ((k + 1) & 1) * TQ;
+                tile_cp_async(S + size_t(DT) * i * ld + DT * (k + 1), ld, nb, tid);
+                if (!diag) tile_cp_async(S + size_t(DT) * j * ld + DT * (k + 1), ld, nb + TQ, tid);
+                cp_async_commit();
+                cp_async_wait_1();
+            } else {
+                cp_async_wait_all();
+            }
+            __syncthreads();                       // step k's tiles are complete
+            const double* At = sm + 2 * (k & 1) * TQ;
+            tile_fma(At, diag ? At : At + TQ, warp, lane, acc);
+        }
+        if (!alive) { cp_async_wait_all(); break; }
+        // ---- v = own tile (still row-major, as the formation kernels wrote it) - acc
+        __syncthreads();
+        tile_spill(sm, warp, lane, acc);
+        double* g = S + size_t(DT * i + r) * ld + DT * j + c;
+        const double2 a0 = *reinterpret_cast<const double2*>(g), a1 = *reinterpret_cast<const double2*>(g + 2);
+        __syncthreads();
+        double v[4];
+        {
+            const double* p0 = sm + r * DTQ + c;
+            const double2 s00 = *reinterpret_cast<const double2*>(p0), s01 = *reinterpret_cast<const double2*>(p0 + 2);
+            const double2 s10 = *reinterpret_cast<const double2*>(p0 + TQ), s11 = *reinterpret_cast<const double2*>(p0 + TQ + 2);
+            const double2 s20 = *reinterpret_cast<const double2*>(p0 + 2 * TQ), s21 = *reinterpret_cast<const double2*>(p0 + 2 * TQ + 2);
+            const double2 s30 = *reinterpret_cast<const double2*>(p0 + 3 * TQ), s31 = *reinterpret_cast<const double2*>(p0 + 3 * TQ + 2);
+            v[0] = a0.x - ((s00.x + s10.x) + (s20.x + s30.x)); v[1] = a0.y - ((s00.y + s10.y) + (s20.y + s30.y));
+            v[2] = a1.x - ((s01.x + s11.x) + (s21.x + s31.x)); v[3] = a1.y - ((s01.y + s11.y) + (s21.y + s31.y));
+        }
+        __syncthreads();
+        if (diag) {
+            double* sL = sm;                 // [32][33]
+            double* sLb = sm + TQ;           // [32][34]
+            double* sZt = sm + 2 * TQ;       // [32][33]: sZt[m][c] = (L^-1)[c][m]
+            sL[r * DTP + c] = v[0]; sL[r * DTP + c + 1] = v[1]; sL[r * DTP + c + 2] = v[2]; sL[r * DTP + c + 3] = v[3];
+            __syncthreads();
+            if (tid < 32) {
+                const bool ok = potrf_trinv32(sL, sZt, sLb, scol, srinv, lane);
+                if (lane == 0 && !ok) atomicOr(bad_flag, 16);
+            }
+            __syncthreads();
+            double* z = D.Zinv + size_t(DT * DT) * j + DT * r + c;
+            *reinterpret_cast<double2*>(z) = make_double2(sZt[r * DTP + c], sZt[r * DTP + c + 1]);
+            *reinterpret_cast<double2*>(z + 2) = make_double2(sZt[r * DTP + c + 2], sZt[r * DTP + c + 3]);
+        } else {
+            // L_ij = v L_jj^-T: A operand = v^T ([m][row]), B operand = Zt ([m][c]) straight from Zinv
+            double* At = sm;
+            At[c * DTQ + r] = v[0]; At[(c + 1) * DTQ + r] = v[1]; At[(c + 2) * DTQ + r] = v[2]; At[(c + 3) * DTQ + r] = v[3];
+            if (tid == 0) s_go = flow_wait(F.ready + j * W + j, F.epoch, F.abort);
+            __syncthreads();
+            if (!s_go) { alive = false; break; }
+            tile_cp_async(D.Zinv + size_t(DT * DT) * j, DT, sZ, tid);
+            cp_async_commit();
+            cp_async_wait_all();
+            __syncthreads();
+#pragma unroll
+            for (int q = 0; q < 16; ++q) acc[q] = 0.0;
+            tile_fma(At, sZ, warp, lane, acc);
+            __syncthreads();
+            tile_spill(sm, warp, lane, acc);
+            __syncthreads();
+            // transposed write-back: thread (m = r, rows c..c+3) sums the four partials of L_ij[c..c+3][m] and stores them contiguously
+            double o[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const double* p0 = sm + (c + q) * DTQ + r;
+                o[q] = (p0[0] + p0[TQ]) + (p0[2 * TQ] + p0[3 * TQ]);
+            }
+            double* gt = S + size_t(DT * i + r) * ld + DT * j + c;      // element (m = r, row c + q) of the transposed tile
+            *reinterpret_cast<double2*>(gt) = make_double2(o[0], o[1]);
+            *reinterpret_cast<double2*>(gt + 2) = make_double2(o[2], o[3]);
+        }
+        __syncthreads();
+        if (tid == 0) { __threadfence(); st_release_gpu(F.ready + i * W + j, F.epoch); }   // barrier, then fence + flag by one thread (cumulative)
+    }
+    grid.sync();
+    if (blockIdx.x != 0) return;
+    if (*reinterpret_cast<volatile int*>(F.abort)) { if (tid == 0) atomicOr(bad_flag, 16); return; }
+    // ---- L^T x = y by CTA 0.  y_j[c] is row 0 of the (transposed) right-hand-side tile (T, j): S[(32 T + c) ld + 32 j].
+    for (int kb = T - 1; kb >= 0; --kb) {
+        __syncthreads();
+        tile_cp_async(D.Zinv + size_t(DT * DT) * kb, DT, sZ, tid);   // sZ[c][m] = (L_kk^-1)[m][c]
+        cp_async_commit();
+        if (tid < DT) sx[tid] = __ldcg(S + size_t(DT * T + tid) * ld + DT * kb);
+        cp_async_wait_all();
+        __syncthreads();
+        if (tid < DT) {
+            double a0 = 0.0, a1 = 0.0;
+#pragma unroll
+            for (int m = 0; m < DT; m += 2) { a0 += sZ[tid * DTQ + m] * sx[m]; a1 += sZ[tid * DTQ + m + 1] * sx[m + 1]; }
+            const double xv = a0 + a1;
+            __syncwarp();
+            sx[tid] = xv;
+            if (DT * kb + tid < D.n) x[DT * kb + tid] = xv;
+        }
+        __syncthreads();
+        // y_jt[cc] -= sum_rr L_(kb, jt)[rr][cc] x[rr]; the tile is transposed: element (rr, cc) at [(32 kb + cc) ld + 32 jt + rr]
+        for (int jj = tid; jj < DT * kb; jj += blockDim.x) {
+            const int jt = jj >> 5, cc = jj & 31;
+            const double2* row = reinterpret_cast<const double2*>(S + size_t(DT * kb + cc) * ld + DT * jt);
+            double a = 0.0, b = 0.0;
+#pragma unroll
+            for (int q = 0; q < DT / 2; ++q) { const double2 l = __ldcg(row + q); a += l.x * sx[2 * q]; b += l.y * sx[2 * q + 1]; }
+            double* yp = S + size_t(DT * T + cc) * ld + DT * jt;
+            *yp = __ldcg(yp) - (a + b);
         }
     }
     if (tid == 0) { pcg->k = 0; pcg->done = 1; pcg->rel = 0.0; }

@@ -21,7 +21,10 @@
 #include <cstdlib>
 #include <cstring>
 #include <limits>
+#include <exception>
+#include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "ba_kernels.cuh"
@@ -168,6 +171,10 @@ struct ba_engine {
     DevBuf<int4> d_items;
     DevBuf<int> d_blk_item_off, d_blk_ticket;
     DevBuf<double> d_item_part, d_Zinv;
+    DevBuf<int2> d_chol_tasks;
+    DevBuf<int> d_chol_ready;           // tile flags + abort word (last)
+    bak::CholFlow CF{};
+    int chol_mode = 1;                  // 1: dataflow (k_dense_chol_df), 0: barrier per phase (k_dense_chol); BA_CHOL_MODE overrides
     bak::DenseView DV{};
     int chol_grid = 1;
     DevBuf<double> d_redpart;          // [kRedSlices][ldf] stage-1 output of the copy reduction
@@ -254,6 +261,24 @@ void allreduce_flags(ba_engine* e, int* buf, size_t n) {
 
 // Cut the point-sorted observation list [0,No) into tiles of whole points with <= TILE_OBS observations; a point with
 // more observations than that becomes a tile of its own (the kernels walk it in chunks).
+// Host threads over [0, n) in contiguous ranges (the per-tile schedule construction of ba_set_problem; ranges write disjoint slices).
+template <class F>
+void parallel_ranges(int n, F&& f) {
+    int nt = int(std::thread::hardware_concurrency());
+    if (const char* v = std::getenv("BA_HOST_THREADS")) nt = std::atoi(v);
+    nt = std::max(1, std::min(nt, 16));
+    if (n < 2048 || nt == 1) { f(0, n); return; }
+    std::vector<std::thread> th;
+    std::exception_ptr err;
+    std::mutex mu;
+    for (int k = 0; k < nt; ++k) {
+        const int a = int(int64_t(n) * k / nt), b = int(int64_t(n) * (k + 1) / nt);
+        th.emplace_back([&, a, b] { try { f(a, b); } catch (...) { std::lock_guard<std::mutex> g(mu); err = std::current_exception(); } });
+    }
+    for (auto& t : th) t.join();
+    if (err) std::rethrow_exception(err);
+}
+
 void build_tiles(const vector<int32_t>& pt_off, int Np, vector<int32_t>& tile_off) {
     tile_off.clear();
     tile_off.push_back(0);
@@ -423,8 +448,20 @@ void build_dense(ba_engine* e, const ba_problem* P, const vector<int32_t>& pt_of
     D.blk_ticket = e->d_blk_ticket.p; D.Zinv = e->d_Zinv.p;
     D.S = e->d_S.p; D.WU = e->d_WU.p; D.GH = e->d_GH.p; D.corner_part = e->d_corner.p;
     D.blk_off = e->d_blk_off.p; D.blk_key = e->d_blk_key.p; D.pairs = e->d_pairs.p;
+    {   // dataflow task list: tiles column by column, diagonal first
+        vector<int2> tasks;
+        for (int j = 0; j < D.T; ++j) for (int i = j; i <= D.T; ++i) tasks.push_back(make_int2(i, j));
+        e->d_chol_tasks.upload(tasks.data(), tasks.size(), s);
+        const size_t nflags = size_t(D.T + 1) * (D.T + 1) + 1;
+        e->d_chol_ready.alloc(nflags);
+        CU_TRY(cudaMemsetAsync(e->d_chol_ready.p, 0, nflags * sizeof(int), s));
+        CU_TRY(cudaStreamSynchronize(s));
+        e->CF.ntasks = int(tasks.size()); e->CF.tasks = e->d_chol_tasks.p; e->CF.ready = e->d_chol_ready.p; e->CF.abort = e->d_chol_ready.p + (nflags - 1); e->CF.epoch = 0;
+        if (const char* m = std::getenv("BA_CHOL_MODE")) e->chol_mode = std::atoi(m);
+    }
     int occ = 1;
-    CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, bak::k_dense_chol, 256, 0));
+    if (e->chol_mode == 1) CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, bak::k_dense_chol_df, 256, 0));
+    else CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, bak::k_dense_chol, 256, 0));
     e->chol_grid = std::max(1, std::min(std::max(occ, 1) * e->num_sms, D.T * (D.T + 1) / 2));
     e->dense = true;
     // algorithmic bytes: formation reads the Jacobian columns it needs once and every pair's two 144-byte records,
@@ -485,47 +522,47 @@ void do_set_problem(ba_engine* e, const ba_problem* P, const DevState* dev = nul
     // sorted position the camera + segment length at segment heads (ba_scatter.cuh)
     vector<unsigned char> slot(No, 0);
     vector<int32_t> spack(No, -1);
-    {
-        vector<int32_t> idx(bak::TILE_OBS);
-        for (int t = 0; t < e->nTiles; ++t) {
-            const int o0 = tile_off[t], n = tile_off[t + 1] - o0;
-            if (n > bak::TILE_OBS) continue;   // long-point tile: handled with atomics, no schedule
-            for (int i = 0; i < n; ++i) idx[i] = i;
-            std::stable_sort(idx.begin(), idx.begin() + n, [&](int a, int b) { return P->obs_cam[e->ob + o0 + a] < P->obs_cam[e->ob + o0 + b]; });
-            for (int j = 0; j < n;) {
-                const int cam = P->obs_cam[e->ob + o0 + idx[j]];
-                int k = j;
-                while (k < n && P->obs_cam[e->ob + o0 + idx[k]] == cam) { slot[o0 + idx[k]] = static_cast<unsigned char>(k); ++k; }
-                spack[o0 + j] = cam | ((k - j) << 22);
-                j = k;
-            }
-        }
-    }
     if (Nc >= (1 << 22)) throw BaFail{BA_ERR_UNSUPPORTED, "more than 4M cameras"};
-    // mode-4 schedule: level-1 chunk counts, head ranks, compact row numbering and the by-camera row lists
+    const int32_t* ocam = P->obs_cam + e->ob;
+    // mode-4 schedule: level-1 chunk counts, head ranks, compact row numbering and the by-camera row lists.  Tiles are independent:
+    // pass A (host threads over tile ranges) sorts each tile by camera and counts its rows, a prefix sum numbers the rows, pass B fills.
     {
         vector<unsigned char> lvl1(No, 0), hrank(No, 0);
         vector<int32_t> hbase(size_t(e->nTiles) + 1, 0), row_cam;
-        row_cam.reserve(No / 2 + 16);
-        for (int t = 0; t < e->nTiles; ++t) {
-            const int o0 = tile_off[t], n = tile_off[t + 1] - o0;
-            hbase[t] = int(row_cam.size());
-            if (n > bak::TILE_OBS) { for (int i = 0; i < n; ++i) row_cam.push_back(P->obs_cam[e->ob + o0 + i]); continue; }
-            int rank = 0;
-            for (int j = 0; j < n;) {
-                const int pk = spack[o0 + j];            // head at sorted position j
-                const int cam = pk & 0x3fffff, len = pk >> 22, end = j + len;
-                hrank[o0 + j] = static_cast<unsigned char>(rank++);
-                row_cam.push_back(cam);
-                for (int q = j; q < end;) {               // chunk leaders: the head, then every multiple of L1_CHUNK inside the segment
-                    const int nxt = std::min((q / bak::L1_CHUNK + 1) * bak::L1_CHUNK, end);
-                    lvl1[o0 + q] = static_cast<unsigned char>(nxt - q);
-                    q = nxt;
+        parallel_ranges(e->nTiles, [&](int t0, int t1) {
+            uint32_t key[bak::TILE_OBS];
+            for (int t = t0; t < t1; ++t) {
+                const int o0 = tile_off[t], n = tile_off[t + 1] - o0;
+                if (n > bak::TILE_OBS) { hbase[t + 1] = n; continue; }   // long-point tile: one row per observation, no schedule
+                for (int i = 0; i < n; ++i) key[i] = uint32_t(ocam[o0 + i]) << 9 | uint32_t(i);   // unique keys: std::sort == stable sort by camera
+                std::sort(key, key + n);
+                int rank = 0;
+                for (int j = 0; j < n;) {
+                    const int cam = int(key[j] >> 9);
+                    int k = j;
+                    while (k < n && int(key[k] >> 9) == cam) { slot[o0 + (key[k] & 511u)] = static_cast<unsigned char>(k); ++k; }
+                    spack[o0 + j] = cam | ((k - j) << 22);
+                    hrank[o0 + j] = static_cast<unsigned char>(rank++);
+                    for (int q = j; q < k;) {             // chunk leaders: the head, then every multiple of L1_CHUNK inside the segment
+                        const int nxt = std::min((q / bak::L1_CHUNK + 1) * bak::L1_CHUNK, k);
+                        lvl1[o0 + q] = static_cast<unsigned char>(nxt - q);
+                        q = nxt;
+                    }
+                    j = k;
                 }
-                j = end;
+                hbase[t + 1] = rank;
             }
-        }
-        hbase[e->nTiles] = int(row_cam.size());
+        });
+        for (int t = 0; t < e->nTiles; ++t) hbase[t + 1] += hbase[t];
+        row_cam.resize(hbase[e->nTiles]);
+        parallel_ranges(e->nTiles, [&](int t0, int t1) {
+            for (int t = t0; t < t1; ++t) {
+                const int o0 = tile_off[t], n = tile_off[t + 1] - o0;
+                int32_t* rc = row_cam.data() + hbase[t];
+                if (n > bak::TILE_OBS) { for (int i = 0; i < n; ++i) rc[i] = ocam[o0 + i]; continue; }
+                for (int j = 0; j < n;) { const int pk = spack[o0 + j]; *rc++ = pk & 0x3fffff; j += pk >> 22; }
+            }
+        });
         const int nRows = int(row_cam.size());
         vector<int32_t> cro(size_t(Nc) + 1, 0), crows(nRows);
         for (int r = 0; r < nRows; ++r) ++cro[row_cam[r] + 1];
@@ -533,7 +570,8 @@ void do_set_problem(ba_engine* e, const ba_problem* P, const DevState* dev = nul
         { vector<int32_t> cur(cro.begin(), cro.end() - 1); for (int r = 0; r < nRows; ++r) crows[cur[row_cam[r]]++] = r; }
         // pack the per-position records (RowSched::tmeta) and per-tile records (RowSched::tile_info)
         vector<int4> tmeta(No), tinfo(std::max(e->nTiles, 1));
-        for (int t = 0; t < e->nTiles; ++t) {
+        parallel_ranges(e->nTiles, [&](int t0, int t1) {
+          for (int t = t0; t < t1; ++t) {
             const int o0 = tile_off[t], n = tile_off[t + 1] - o0;
             const int pfirst = obs_pt[o0];
             tinfo[t] = make_int4(o0, n, hbase[t], pfirst);
@@ -546,7 +584,8 @@ void do_set_problem(ba_engine* e, const ba_problem* P, const DevState* dev = nul
                 if (pfirst + i <= plast) { const int a = pt_off[pfirst + i] - o0, cnt = pt_off[pfirst + i + 1] - pt_off[pfirst + i]; pw = cnt > 0 ? (a | cnt << 16) : 0; }
                 tmeta[o0 + i] = make_int4(P->obs_cam[e->ob + o0 + i], int(packA), spack[o0 + i], pw);
             }
-        }
+          }
+        });
         e->d_tmeta.upload(tmeta.data(), No, s); e->d_tile_info.upload(tinfo.data(), tinfo.size(), s);
         e->d_cam_row_off.upload(cro.data(), cro.size(), s); e->d_cam_rows.upload(crows.data(), nRows, s);
         e->d_rows.alloc(size_t(nRows) * bak::ROW_DOUBLES); e->d_rows.zero(s);
@@ -837,7 +876,7 @@ int solve_linear(ba_engine* e, double radius, double* rel_out, double lambda = 0
             CU_TRY(cudaMemsetAsync(D.S, 0, size_t(bak::DT) * (D.T + 1) * D.ld * sizeof(double), s));
             if (e->No > 0) KL(e), bak::k_dense_wu<<<cdiv(e->No, 128), 128, 0, s>>>(e->V, D);
             if (e->fi) KL(e), bak::k_dense_point_g<<<D.corner_blocks, 128, 0, s>>>(e->V, D);
-            KL(e), bak::k_dense_init<<<cdiv(36 * e->Nc + D.ld + 16, 256), 256, 0, s>>>(e->Nc, e->fi, D, e->Hcc(), e->Hii(), e->d_Df2.p, e->d_b.p);
+            KL(e), bak::k_dense_init<<<cdiv(36 * e->Nc + D.ld + 32 + 16 * 32, 256), 256, 0, s>>>(e->Nc, e->fi, D, e->Hcc(), e->Hii(), e->d_Df2.p, e->d_b.p);
             if (D.nitems > 0) KL(e), bak::k_dense_pairs<<<std::min(cdiv(D.nitems, 4), 16 * e->num_sms), 128, 0, s>>>(D);
             if (e->fi && e->Nc > 0) KL(e), bak::k_dense_border<<<e->Nc, 128, 0, s>>>(e->V, D);
         }
@@ -845,9 +884,16 @@ int solve_linear(ba_engine* e, double radius, double* rel_out, double lambda = 0
             LaunchTimer t(e, KID_DCHOL);
             bak::DenseView dv = D;
             double* xp = e->d_x.p; bak::PcgState2* pcg = &sc->pcg; int* bad = &sc->bad_lin;
-            void* args[] = {&dv, &xp, &pcg, &bad};
             KL(e);
-            CU_TRY(cudaLaunchCooperativeKernel(reinterpret_cast<const void*>(bak::k_dense_chol), dim3(e->chol_grid), dim3(256), args, 0, s));
+            if (e->chol_mode == 1) {
+                bak::CholFlow cf = e->CF;
+                cf.epoch = ++e->CF.epoch;
+                void* args[] = {&dv, &cf, &xp, &pcg, &bad};
+                CU_TRY(cudaLaunchCooperativeKernel(reinterpret_cast<const void*>(bak::k_dense_chol_df), dim3(e->chol_grid), dim3(256), args, 0, s));
+            } else {
+                void* args[] = {&dv, &xp, &pcg, &bad};
+                CU_TRY(cudaLaunchCooperativeKernel(reinterpret_cast<const void*>(bak::k_dense_chol), dim3(e->chol_grid), dim3(256), args, 0, s));
+            }
         }
         launch_sweep<bak::SWEEP_BACKSUB>(e, KID_K7, e->d_x.p, nullptr, nullptr, e->d_part0.p);
         { LaunchTimer t(e, KID_MISC);

@@ -11,7 +11,7 @@ for name in shapes:
             t0 = time.perf_counter(); e.set_problem(P); t1 = time.perf_counter(); s = e.solve(); t2 = time.perf_counter()
         tr = e.trajectory()
         e.set_profiling(True); e.set_problem(P); e.solve()
-        ks = {k['name']: (k['launches'], round(1e3 * k['total_ms'] / max(k['launches'], 1), 1)) for k in e.kernel_stats() if k['launches']}
+        ks = {k['name']: (k['launches'], round(1e3 * k['total_ms'] / max(k['launches'], 1), 1)) for k in e.kernel_stats() if k['launches'] and (k['name'][0] == 'D' or os.environ.get('ALLK'))}
         pcg = s.total_pcg_iterations
         print(json.dumps(dict(shape=name, sizes=P.sizes, set_problem_ms=round((t1 - t0) * 1e3, 3), solve_wall_ms=round((t2 - t1) * 1e3, 3),
                               solve_dev_ms=round(s.solve_seconds * 1e3, 3), launches=s.kernel_launches, lm=len(tr) - 1, pcg=pcg,
