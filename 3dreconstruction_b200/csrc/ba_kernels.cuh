@@ -13,7 +13,10 @@
 
 namespace bak {
 
-constexpr int TILE_OBS = 256;     // observations per tile == threads per CTA of the observation sweeps
+#ifndef BA_TILE_OBS
+#define BA_TILE_OBS 128   // 256 measured 3% slower on the Venice shape (K5a 222 vs 208 us: shorter barrier chains; K5b 54 vs 58 us: more rows), 64 slower again (K5b 66 us)
+#endif
+constexpr int TILE_OBS = BA_TILE_OBS;     // observations per tile == threads per CTA of the observation sweeps
 constexpr int CAMREC = 20;        // doubles per camera record
 constexpr int NJC = 6, NJP = 3, NJI = 4;
 
@@ -225,7 +228,7 @@ __device__ __forceinline__ void model_jacobian(const Proj& q, const double* __re
 // pixel of this thread's observation one tile ahead) is loaded while the current tile is computed, so a tile's critical path
 // starts at the camera-record / point gathers instead of three dependent DRAM latencies earlier.  One cost partial per CTA.
 #ifndef K1_CTAS_PER_SM
-#define K1_CTAS_PER_SM 2
+#define K1_CTAS_PER_SM 4
 #endif
 template <int MODEL>
 __global__ void __launch_bounds__(TILE_OBS, K1_CTAS_PER_SM)
