@@ -2,12 +2,15 @@
 // peer-memory all-reduce over NVLink/NVSwitch, fused into the K5b gather and the PCG dot-product kernel ("B200-native step
 // beyond NCCL").  NCCL's all-reduce of this payload is latency-bound (tens of microseconds, comparable to the local matvec at 8 GPUs).
 //
-//   k_camera_gather_push : K5b on every rank — sums camera c's partial rows (fixed order) and stores the 6-vector straight into slot
-//                          [parity][my rank] of EVERY rank's receive buffer (peer pointers mapped with CUDA IPC; plain 16-byte st.global
-//                          over NVLink).  The last CTA to finish (ticket) publishes flag[my rank] = seq on every rank (st.release.sys).
-//   k_pcg_q_p2p          : waits (ld.acquire.sys on LOCAL memory) until all W flags show seq, then y = sum over ranks IN RANK ORDER of the
-//                          W slots — the same order on every rank, so all ranks hold bit-identical y and take identical decisions —
-//                          and continues with q = y + Df2 p, p.q, alpha as k_pcg_q.
+//   k_camera_gather_push : K5b on every rank — sums camera c's partial rows (fixed order) into slot [parity] of the rank's OWN exchange
+//                          buffer (local stores).  The last CTA to finish (ticket) fences once at system scope and publishes
+//                          flag[my rank] = seq on every rank (st.release.sys over NVLink).
+//   k_pcg_q_p2p          : waits (ld.acquire.sys on LOCAL memory) until all W flags show seq, then y = sum over ranks IN RANK ORDER of
+//                          the W ranks' slots, read straight from the peers' memory (ld.relaxed.sys over NVLink; peer pointers mapped
+//                          with CUDA IPC) — the same order on every rank, so all ranks hold bit-identical y and take identical
+//                          decisions — and continues with q = y + Df2 p, p.q, alpha as k_pcg_q.
+// (The first version PUSHED every camera's 6-vector into every peer's buffer; that needs a system-scope fence after the remote stores
+// in each of the 1779 CTAs, which cost ~35 us per PCG iteration at 2 GPUs.  Pulling needs one.)
 // Slots are double-buffered by the parity of seq: a rank can be at most one all-reduce ahead of the slowest rank (it needs that rank's
 // slot of the current sequence number to finish), so parity p is never overwritten while someone still reads it.
 // One rank per GPU only: the wait spins on flags another GPU writes (never emulate several ranks on one GPU with this path).
@@ -19,7 +22,7 @@ namespace bak {
 constexpr int P2P_MAX_RANKS = 8;
 
 struct PeerView {
-    double* data[P2P_MAX_RANKS];        // rank r's receive buffer: [2][W][ldf] doubles (data[rank] is the local one)
+    double* data[P2P_MAX_RANKS];        // rank r's exchange buffer: slot [parity] at data[r] + parity * ldf (data[rank] is the local one)
     unsigned int* flags[P2P_MAX_RANKS]; // rank r's flag array [W]: flags[r][s] = last sequence number rank s has fully delivered to r
     int W, rank, ldf;
     int* timeout_flag;                  // local Scalars::bad_lin: bit 8 set if a wait gave up (the host turns it into BA_ERR_NCCL)
@@ -32,6 +35,12 @@ __device__ __forceinline__ unsigned int ld_acquire_sys(const unsigned int* p) {
     return v;
 }
 
+__device__ __forceinline__ double ld_relaxed_sys_f64(const double* p) {   // home-memory read (local HBM/L2 or a peer's, over NVLink); never a stale cached copy
+    double v;
+    asm volatile("ld.relaxed.sys.global.f64 %0, [%1];" : "=d"(v) : "l"(p) : "memory");
+    return v;
+}
+
 __global__ void __launch_bounds__(GATHER_WARPS * 32)
 k_camera_gather_push(int Nc, int Ng, int fi, int nTiles, RowSched S, const double* __restrict__ ylocal_rw, PeerView P, unsigned int seq,
                      PcgState2* __restrict__ st, int check_done) {
@@ -40,11 +49,29 @@ k_camera_gather_push(int Nc, int Ng, int fi, int nTiles, RowSched S, const doubl
     if (check_done && st->done) return;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int ioff = 6 * Nc;
-    const size_t slot = (size_t(seq & 1u) * P.W + P.rank) * P.ldf;
+    double* const mine = P.data[P.rank] + size_t(seq & 1u) * P.ldf;
     const int c = blockIdx.x;
     if (c < Nc) {
         double s0 = 0, s1 = 0, s2 = 0, s3 = 0, s4 = 0, s5 = 0;
-        for (int i = S.cam_row_off[c] + threadIdx.x, e = S.cam_row_off[c + 1]; i < e; i += GATHER_WARPS * 32) {
+        // four independent rows per thread and trip, as k_camera_gather (same summation order)
+        constexpr int NT = GATHER_WARPS * 32;
+        const int e = S.cam_row_off[c + 1];
+        int i = S.cam_row_off[c] + threadIdx.x;
+        for (; i + 3 * NT < e; i += 4 * NT) {
+            const int i0 = S.cam_rows[i], i1 = S.cam_rows[i + NT], i2 = S.cam_rows[i + 2 * NT], i3 = S.cam_rows[i + 3 * NT];
+            const double2* r0 = reinterpret_cast<const double2*>(S.rows + size_t(ROW_DOUBLES) * i0);
+            const double2* r1 = reinterpret_cast<const double2*>(S.rows + size_t(ROW_DOUBLES) * i1);
+            const double2* r2 = reinterpret_cast<const double2*>(S.rows + size_t(ROW_DOUBLES) * i2);
+            const double2* r3 = reinterpret_cast<const double2*>(S.rows + size_t(ROW_DOUBLES) * i3);
+            const double2 a0 = __ldcg(r0), b0 = __ldcg(r0 + 1), c0 = __ldcg(r0 + 2);
+            const double2 a1 = __ldcg(r1), b1 = __ldcg(r1 + 1), c1 = __ldcg(r1 + 2);
+            const double2 a2 = __ldcg(r2), b2 = __ldcg(r2 + 1), c2 = __ldcg(r2 + 2);
+            const double2 a3 = __ldcg(r3), b3 = __ldcg(r3 + 1), c3 = __ldcg(r3 + 2);
+            s0 += (a0.x + a1.x) + (a2.x + a3.x); s1 += (a0.y + a1.y) + (a2.y + a3.y);
+            s2 += (b0.x + b1.x) + (b2.x + b3.x); s3 += (b0.y + b1.y) + (b2.y + b3.y);
+            s4 += (c0.x + c1.x) + (c2.x + c3.x); s5 += (c0.y + c1.y) + (c2.y + c3.y);
+        }
+        for (; i < e; i += NT) {
             const double2* row = reinterpret_cast<const double2*>(S.rows + size_t(ROW_DOUBLES) * S.cam_rows[i]);
             const double2 a = __ldcg(row), bq = __ldcg(row + 1), cq = __ldcg(row + 2);
             s0 += a.x; s1 += a.y; s2 += bq.x; s3 += bq.y; s4 += cq.x; s5 += cq.y;
@@ -52,13 +79,12 @@ k_camera_gather_push(int Nc, int Ng, int fi, int nTiles, RowSched S, const doubl
         s0 = warp_sum(s0); s1 = warp_sum(s1); s2 = warp_sum(s2); s3 = warp_sum(s3); s4 = warp_sum(s4); s5 = warp_sum(s5);
         if (lane == 0) { sw[wid][0] = s0; sw[wid][1] = s1; sw[wid][2] = s2; sw[wid][3] = s3; sw[wid][4] = s4; sw[wid][5] = s5; }
         __syncthreads();
-        // thread (r, h): half-row h (16 bytes) of this camera's 6-vector to rank r
-        if (threadIdx.x < 3 * P.W) {
-            const int r = threadIdx.x / 3, h = threadIdx.x - 3 * r;
+        if (threadIdx.x < 3) {   // thread h: 16 bytes of this camera's 6-vector
+            const int h = threadIdx.x;
             double2 v = make_double2(0.0, 0.0);
 #pragma unroll
             for (int w = 0; w < GATHER_WARPS; ++w) { v.x += sw[w][2 * h]; v.y += sw[w][2 * h + 1]; }
-            *reinterpret_cast<double2*>(P.data[r] + slot + 6 * size_t(c) + 2 * h) = v;
+            __stcg(reinterpret_cast<double2*>(mine + 6 * size_t(c) + 2 * h), v);
         }
     } else if (fi) {
         // intrinsics entries: single group -> ordered sum of the per-tile partials; several groups -> RED-accumulated in ylocal_rw already
@@ -69,13 +95,14 @@ k_camera_gather_push(int Nc, int Ng, int fi, int nTiles, RowSched S, const doubl
                 for (int t = lane; t < nTiles; t += 32) s += __ldcg(S.tile_intr + 4 * size_t(t) + k);
                 v = warp_sum(s);
             } else v = ylocal_rw[ioff + k];
-            if (lane < P.W) P.data[lane][slot + ioff + k] = v;
+            if (lane == 0) __stcg(mine + ioff + k, v);
         }
     }
-    // publish: every CTA fences its remote stores at system scope before taking a ticket; the last one raises the flags
+    // publish: every CTA fences its (local) stores at GPU scope before taking a ticket; the last one fences once at system scope and
+    // raises the flags on every rank
     __syncthreads();
     if (threadIdx.x == 0) {
-        __threadfence_system();
+        __threadfence();
         const unsigned int tk = atomicAdd(&st->ticket_q, 1u);
         last = (tk == gridDim.x - 1);
     }
@@ -101,11 +128,15 @@ k_pcg_q_p2p(int nf, PeerView P, unsigned int seq, const double* __restrict__ Df2
         }
     }
     __syncthreads();
-    const double* base = P.data[P.rank] + size_t(seq & 1u) * P.W * P.ldf;
+    const size_t off = size_t(seq & 1u) * P.ldf;
     double acc = 0.0;
     for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < nf; j += gridDim.x * blockDim.x) {
+        double v[P2P_MAX_RANKS];
+#pragma unroll
+        for (int r = 0; r < P2P_MAX_RANKS; ++r) v[r] = r < P.W ? ld_relaxed_sys_f64(P.data[r] + off + j) : 0.0;   // all loads in flight, then
         double s = 0.0;
-        for (int r = 0; r < P.W; ++r) s += __ldcg(base + size_t(r) * P.ldf + j);
+#pragma unroll
+        for (int r = 0; r < P2P_MAX_RANKS; ++r) if (r < P.W) s += v[r];                                              // the sum in rank order
         if (do_dot) { const double pj = p[j]; s += Df2[j] * pj; acc += pj * s; }
         y[j] = s;
     }
