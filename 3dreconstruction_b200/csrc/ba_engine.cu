@@ -34,6 +34,7 @@
 #include "ba_rows_pipe.cuh"
 #include "ba_p2p.cuh"
 #include "ba_dense.cuh"
+#include "ba_pcg_cluster.cuh"
 
 namespace {
 using std::vector;
@@ -906,36 +907,41 @@ int solve_linear(ba_engine* e, double radius, double* rel_out, double lambda = 0
       KL(e), bak::k_pcg_init2<<<1, 1024, 0, s>>>(e->nf, e->Nc, e->d_Minv.p, e->d_b.p, e->d_x.p, e->d_r.p, e->d_z.p, e->d_p.p, &sc->pcg); }
     if (e->scatter_mode == 1) e->d_y.zero(s);
     const int batch = 8;
+    bak::TailArgs ta{};
+    ta.Nc = e->Nc; ta.Ng = e->Ng; ta.fi = e->fi; ta.Minv = e->d_Minv.p; ta.b = e->d_b.p; ta.Df2 = e->d_Df2.p;
+    ta.y = e->d_y.p; ta.p = e->d_p.p; ta.x = e->d_x.p; ta.r = e->d_r.p; ta.z = e->d_z.p; ta.st = &sc->pcg; ta.pp = pp;
     const bool multi = e->opt.world_size > 1;
     for (;;) {
         for (int i = 0; i < batch; ++i) {
             launch_scatter<bak::SWEEP_MATVEC>(e, KID_K5, e->d_p.p, e->d_y.p, &sc->pcg.done, &G);
             LaunchTimer t(e, KID_PCGV);
             double* src = nullptr; int nsrc = 0;
+            // y (and, on one GPU, q = y + Df2 p and alpha) from the scatter mode's own reduction; tail.mode says what is left to do
+            ta.mode = 0;
             if (rowsm) {
-                if (multi && e->p2p.on) {   // one-shot NVLink all-reduce fused into the gather and the dot-product kernel (ba_p2p.cuh)
-                    const unsigned int seq = ++e->p2p.seq;
-                    KL(e), bak::k_camera_gather_push<<<gblocks, bak::GATHER_WARPS * 32, 0, s>>>(e->Nc, e->Ng, e->fi, e->nTiles, e->RS, e->d_y.p, e->p2p.view, seq, &sc->pcg, 1);
-                    KL(e), bak::k_pcg_q_p2p<<<vblocks, 128, 0, s>>>(e->nf, e->p2p.view, seq, e->d_Df2.p, e->d_p.p, e->d_y.p, e->d_part1.p, &sc->pcg, 1, 1);
+                if (multi && e->p2p.on) {   // one-shot NVLink all-reduce: local gather + flags here, the pull and the sum inside the tail (ba_p2p.cuh)
+                    ta.seq = ++e->p2p.seq; ta.P = e->p2p.view; ta.mode = 2;
+                    KL(e), bak::k_camera_gather_push<<<gblocks, bak::GATHER_WARPS * 32, 0, s>>>(e->Nc, e->Ng, e->fi, e->nTiles, e->RS, e->d_y.p, e->p2p.view, ta.seq, &sc->pcg, 1);
                 } else if (multi) {
-                    KL(e), bak::k_camera_gather<<<gblocks, bak::GATHER_WARPS * 32, 0, s>>>(e->Nc, e->Ng, e->fi, e->nTiles, e->RS, nullptr, nullptr, e->d_y.p, nullptr, nullptr, 0);
+                    KL(e), bak::k_camera_gather<<<gblocks, bak::GATHER_WARPS * 32, 0, s>>>(e->Nc, e->Ng, e->fi, e->nTiles, e->RS, nullptr, nullptr, e->d_y.p, nullptr, &sc->pcg, 0);
                     allreduce_sum(e, e->d_y.p, e->nf);
-                    KL(e), bak::k_pcg_q<<<vblocks, bak::PCG_BLOCK, 0, s>>>(e->nf, 0, e->Sch.ldf, nullptr, e->d_Df2.p, e->d_p.p, e->d_y.p, e->d_part1.p, &sc->pcg, 0, 1);
-                } else {
-                    KL(e), bak::k_camera_gather<<<gblocks, bak::GATHER_WARPS * 32, 0, s>>>(e->Nc, e->Ng, e->fi, e->nTiles, e->RS, e->d_Df2.p, e->d_p.p, e->d_y.p, e->d_part1.p, &sc->pcg, 1);
+                    ta.mode = 1;
+                } else {   // one GPU: plain gather (no ticket); q, p.q and alpha are the tail's
+                    KL(e), bak::k_camera_gather<<<gblocks, bak::GATHER_WARPS * 32, 0, s>>>(e->Nc, e->Ng, e->fi, e->nTiles, e->RS, nullptr, nullptr, e->d_y.p, nullptr, &sc->pcg, 0);
+                    ta.mode = 1;
                 }
             } else {
-            if (priv) reduce_src(G, &sc->pcg.done, src, nsrc);
-            if (multi) {   // reduce the private copies, all-reduce across ranks, then the dot product
-                if (priv) KL(e), bak::k_pcg_q<<<vblocks, bak::PCG_BLOCK, 0, s>>>(e->nf, nsrc, e->Sch.ldf, src, nullptr, nullptr, e->d_y.p, nullptr, nullptr, 1, 0);
-                allreduce_sum(e, e->d_y.p, e->nf);
-                KL(e), bak::k_pcg_q<<<vblocks, bak::PCG_BLOCK, 0, s>>>(e->nf, 0, e->Sch.ldf, nullptr, e->d_Df2.p, e->d_p.p, e->d_y.p, e->d_part1.p, &sc->pcg, 0, 1);
-            } else {
-                KL(e), bak::k_pcg_q<<<vblocks, bak::PCG_BLOCK, 0, s>>>(e->nf, nsrc, e->Sch.ldf, src, e->d_Df2.p, e->d_p.p, e->d_y.p, e->d_part1.p, &sc->pcg, priv ? 1 : 0, 1);
+                if (priv) reduce_src(G, &sc->pcg.done, src, nsrc);
+                if (multi) {   // reduce the private copies, all-reduce across ranks; the dot product is the tail's
+                    if (priv) KL(e), bak::k_pcg_q<<<vblocks, bak::PCG_BLOCK, 0, s>>>(e->nf, nsrc, e->Sch.ldf, src, nullptr, nullptr, e->d_y.p, nullptr, nullptr, 1, 0);
+                    allreduce_sum(e, e->d_y.p, e->nf);
+                    ta.mode = 1;
+                } else {
+                    KL(e), bak::k_pcg_q<<<vblocks, bak::PCG_BLOCK, 0, s>>>(e->nf, nsrc, e->Sch.ldf, src, e->d_Df2.p, e->d_p.p, e->d_y.p, e->d_part1.p, &sc->pcg, priv ? 1 : 0, 1);
+                }
             }
-            }
-            KL(e), bak::k_pcg_xr<<<cblocks, bak::PCG_BLOCK, 0, s>>>(e->Nc, e->Ng, e->fi, e->d_Minv.p, e->d_b.p, e->d_y.p, e->d_p.p, e->d_x.p, e->d_r.p, e->d_z.p, e->d_part1.p, &sc->pcg, pp);
-            KL(e), bak::k_pcg_p<<<vblocks, bak::PCG_BLOCK, 0, s>>>(e->nf, e->d_z.p, e->d_p.p, &sc->pcg);
+            // x, r, z, rho, beta, stop test and the new search direction: one thread-block cluster (ba_pcg_cluster.cuh)
+            KL(e), bak::k_pcg_tail<<<bak::TAIL_CL, bak::TAIL_THREADS, 0, s>>>(ta);
             if (e->scatter_mode == 1) e->d_y.zero(s);
         }
         read_scalars(e);

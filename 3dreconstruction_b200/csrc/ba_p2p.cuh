@@ -3,9 +3,10 @@
 // beyond NCCL").  NCCL's all-reduce of this payload is latency-bound (tens of microseconds, comparable to the local matvec at 8 GPUs).
 //
 //   k_camera_gather_push : K5b on every rank — sums camera c's partial rows (fixed order) into slot [parity] of the rank's OWN exchange
-//                          buffer (local stores).  The last CTA to finish (ticket) fences once at system scope and publishes
-//                          flag[my rank] = seq on every rank (st.release.sys over NVLink).
-//   k_pcg_q_p2p          : waits (ld.acquire.sys on LOCAL memory) until all W flags show seq, then y = sum over ranks IN RANK ORDER of
+//                          buffer (local stores, no ticket, no flag).
+//   k_pcg_tail (mode 2)  : (ba_pcg_cluster.cuh) first fences once at system scope and publishes flag[my rank] = seq on every rank
+//                          (st.release.sys over NVLink; the kernel boundary already ordered the gather's stores), then
+//                          waits (ld.acquire.sys on LOCAL memory) until all W flags show seq, then y = sum over ranks IN RANK ORDER of
 //                          the W ranks' slots, read straight from the peers' memory (ld.relaxed.sys over NVLink; peer pointers mapped
 //                          with CUDA IPC) — the same order on every rank, so all ranks hold bit-identical y and take identical
 //                          decisions — and continues with q = y + Df2 p, p.q, alpha as k_pcg_q.
@@ -45,7 +46,6 @@ __global__ void __launch_bounds__(GATHER_WARPS * 32)
 k_camera_gather_push(int Nc, int Ng, int fi, int nTiles, RowSched S, const double* __restrict__ ylocal_rw, PeerView P, unsigned int seq,
                      PcgState2* __restrict__ st, int check_done) {
     __shared__ double sw[GATHER_WARPS][6];
-    __shared__ bool last;
     if (check_done && st->done) return;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int ioff = 6 * Nc;
@@ -98,19 +98,7 @@ k_camera_gather_push(int Nc, int Ng, int fi, int nTiles, RowSched S, const doubl
             if (lane == 0) __stcg(mine + ioff + k, v);
         }
     }
-    // publish: every CTA fences its (local) stores at GPU scope before taking a ticket; the last one fences once at system scope and
-    // raises the flags on every rank
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        __threadfence();
-        const unsigned int tk = atomicAdd(&st->ticket_q, 1u);
-        last = (tk == gridDim.x - 1);
-    }
-    __syncthreads();
-    if (last) {
-        if (threadIdx.x == 0) st->ticket_q = 0;
-        if (threadIdx.x < P.W) { __threadfence_system(); st_release_sys(P.flags[threadIdx.x] + P.rank, seq); }
-    }
+    // no ticket, no flag: the kernel boundary orders these stores before the tail kernel, which publishes the flags (ba_pcg_cluster.cuh)
 }
 
 // y = sum_r slot[r] in rank order (after all W ranks delivered sequence number seq); with do_dot: q = y + Df2 p in y, p.q, alpha.

@@ -233,7 +233,7 @@ k_camera_gather(int Nc, int Ng, int fi, int nTiles, RowSched S, const double* __
                 double* __restrict__ y, double* __restrict__ partial, PcgState2* __restrict__ st, int do_dot) {
     __shared__ double sw[GATHER_WARPS][6];
     __shared__ bool last;
-    if (do_dot && st->done) return;
+    if (st && st->done) return;   // PCG already stopped inside this batch of launches
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int ioff = 6 * Nc;
     double dot = 0.0;
