@@ -61,10 +61,8 @@ __global__ void __launch_bounds__(128) k_dense_wu(View V, DenseView D) {
     const int o = blockIdx.x * blockDim.x + threadIdx.x;
     if (o >= V.No) return;
     double2 jc[6], jp[3];
-#pragma unroll
-    for (int k = 0; k < 6; ++k) jc[k] = V.J2[size_t(k) * V.ldo + o];
-#pragma unroll
-    for (int a = 0; a < 3; ++a) jp[a] = V.J2[size_t(6 + a) * V.ldo + o];
+    load_jc(V, V.J2 + o, jc);
+    load_jp(V, V.J2 + o, jp);
     const double* h = V.Hinv + 6 * size_t(V.obs_pt[o]);
     const double H[3][3] = {{h[0], h[1], h[2]}, {h[1], h[3], h[4]}, {h[2], h[4], h[5]}};
     double2* out = reinterpret_cast<double2*>(D.WU + 36 * size_t(o));
@@ -91,12 +89,12 @@ __global__ void __launch_bounds__(128) k_dense_point_g(View V, DenseView D) {
     double G[4][3] = {}, GHm[4][3] = {};
     if (p < V.Np) {
         for (int o = V.pt_off[p]; o < V.pt_off[p + 1]; ++o) {
-            double2 jp[3];
-#pragma unroll
-            for (int a = 0; a < 3; ++a) jp[a] = V.J2[size_t(6 + a) * V.ldo + o];
+            double2 jp[3], jiq[4];
+            load_jp(V, V.J2 + o, jp);
+            load_ji(V, V.J2 + o, jiq);
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
-                const double2 ji = V.J2[size_t(9 + q) * V.ldo + o];
+                const double2 ji = jiq[q];
 #pragma unroll
                 for (int a = 0; a < 3; ++a) G[q][a] += ji.x * jp[a].x + ji.y * jp[a].y;
             }
@@ -219,12 +217,12 @@ __global__ void __launch_bounds__(128) k_dense_border(View V, DenseView D) {
         const int o = V.perm_by_cam[idx];
         const double* gh = D.GH + 24 * size_t(V.obs_pt[o]) + 12;
         const double* w = D.WU + 36 * size_t(o) + 18;
-        double2 jc[6];
-#pragma unroll
-        for (int k = 0; k < 6; ++k) jc[k] = V.J2[size_t(k) * V.ldo + o];
+        double2 jc[6], jiq[4];
+        load_jc(V, V.J2 + o, jc);
+        load_ji(V, V.J2 + o, jiq);
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
-            const double2 ji = V.J2[size_t(9 + q) * V.ldo + o];
+            const double2 ji = jiq[q];
             const double g0 = gh[3 * q], g1 = gh[3 * q + 1], g2 = gh[3 * q + 2];
 #pragma unroll
             for (int k = 0; k < 6; ++k) acc[6 * q + k] += ji.x * jc[k].x + ji.y * jc[k].y - (g0 * w[3 * k] + g1 * w[3 * k + 1] + g2 * w[3 * k + 2]);

@@ -52,6 +52,12 @@ thread_local std::string g_create_error;
 
 struct BaFail { int code; std::string msg; };
 #define KL(eng) (++(eng)->kernel_launches)   // every kernel launch is counted (reported in ba_summary.kernel_launches)
+#ifndef BA_JPACK_DEFAULT
+#define BA_JPACK_DEFAULT 1
+#endif
+#ifndef BA_PDL_DEFAULT
+#define BA_PDL_DEFAULT 1
+#endif
 
 // ---- minimal NCCL binding, resolved at run time (torch bundles its own libnccl.so.2; whichever is already loaded wins) ----
 struct Nccl {
@@ -204,7 +210,10 @@ struct ba_engine {
     // profiling
     int64_t kernel_launches = 0;
     unsigned profiling = 0;           // bit k set: time kernel id k with CUDA events
-    struct Stat { int64_t launches = 0; double ms = 0.0; double bytes = 0.0; } stats[KID_COUNT];
+    struct Stat { int64_t launches = 0; int64_t timed = 0; double ms = 0.0; double bytes = 0.0; } stats[KID_COUNT];
+    int k5_sample_stride = 1;         // time every n-th K5 launch only (events between two launches serialise them; BA_K5_SAMPLE)
+    int pdl = 0;                      // programmatic dependent launch along the PCG chain (BA_PDL)
+    int jpack = 0;                    // packed translation columns of J (pinhole model)
     struct Pending { int kid; cudaEvent_t a, b; };
     vector<Pending> pending;
     vector<cudaEvent_t> ev_pool;
@@ -228,9 +237,10 @@ int fail(ba_engine* e, int code, const std::string& msg) { if (e) e->err = msg; 
 // Profiling hook around one launch: CUDA events on the engine's stream, resolved after the solve's final sync.
 struct LaunchTimer {
     ba_engine* e; int kid; cudaEvent_t a = nullptr, b = nullptr;
-    LaunchTimer(ba_engine* e_, int kid_) : e(e_), kid(kid_) {
+    LaunchTimer(ba_engine* e_, int kid_, bool sample = true) : e(e_), kid(kid_) {
         ++e->stats[kid].launches;
-        if (!((e->profiling >> kid) & 1u)) return;
+        if (!((e->profiling >> kid) & 1u) || !sample) return;
+        ++e->stats[kid].timed;
         auto get = [&]() { cudaEvent_t ev; if (!e->ev_pool.empty()) { ev = e->ev_pool.back(); e->ev_pool.pop_back(); } else cudaEventCreate(&ev); return ev; };
         a = get(); b = get();
         cudaEventRecord(a, e->stream);
@@ -467,7 +477,7 @@ void build_dense(ba_engine* e, const ba_problem* P, const vector<int32_t>& pt_of
     e->dense = true;
     // algorithmic bytes: formation reads the Jacobian columns it needs once and every pair's two 144-byte records,
     // writes the records and S; the factorisation reads and writes the lower triangle once per elimination step on average T/3 times
-    const double jb = e->fi ? 208.0 : 144.0;
+    const double jb = (e->fi ? 208.0 : 144.0) - 16.0 * e->jpack;
     e->stats[KID_DFORM].bytes = double(No) * (jb + 288 + 4) + double(np) * (8 + 288) + 8.0 * double(D.ld) * D.ld;
     e->stats[KID_DCHOL].bytes = 8.0 * double(D.ld) * D.ld * (D.T + 2) / 6.0;
 }
@@ -524,11 +534,12 @@ void do_set_problem(ba_engine* e, const ba_problem* P, const DevState* dev = nul
     vector<unsigned char> slot(No, 0);
     vector<int32_t> spack(No, -1);
     if (Nc >= (1 << 22)) throw BaFail{BA_ERR_UNSUPPORTED, "more than 4M cameras"};
+    static_assert(bak::TILE_OBS <= 256, "tile positions are packed into 8 bits");
     const int32_t* ocam = P->obs_cam + e->ob;
     // mode-4 schedule: level-1 chunk counts, head ranks, compact row numbering and the by-camera row lists.  Tiles are independent:
     // pass A (host threads over tile ranges) sorts each tile by camera and counts its rows, a prefix sum numbers the rows, pass B fills.
     {
-        vector<unsigned char> lvl1(No, 0), hrank(No, 0);
+        vector<unsigned char> lvl1(No, 0), hrank(No, 0), hpos(No, 0);
         vector<int32_t> hbase(size_t(e->nTiles) + 1, 0), row_cam;
         parallel_ranges(e->nTiles, [&](int t0, int t1) {
             uint32_t key[bak::TILE_OBS];
@@ -541,7 +552,7 @@ void do_set_problem(ba_engine* e, const ba_problem* P, const DevState* dev = nul
                 for (int j = 0; j < n;) {
                     const int cam = int(key[j] >> 9);
                     int k = j;
-                    while (k < n && int(key[k] >> 9) == cam) { slot[o0 + (key[k] & 511u)] = static_cast<unsigned char>(k); ++k; }
+                    while (k < n && int(key[k] >> 9) == cam) { slot[o0 + (key[k] & 511u)] = static_cast<unsigned char>(k); hpos[o0 + (key[k] & 511u)] = static_cast<unsigned char>(j); ++k; }
                     spack[o0 + j] = cam | ((k - j) << 22);
                     hrank[o0 + j] = static_cast<unsigned char>(rank++);
                     for (int q = j; q < k;) {             // chunk leaders: the head, then every multiple of L1_CHUNK inside the segment
@@ -583,7 +594,7 @@ void do_set_problem(ba_engine* e, const ba_problem* P, const DevState* dev = nul
                 const unsigned packA = unsigned(slot[o0 + i]) | unsigned(lvl1[o0 + i]) << 8 | unsigned(hrank[o0 + i]) << 16 | unsigned(lpt) << 24;
                 int pw = 0;
                 if (pfirst + i <= plast) { const int a = pt_off[pfirst + i] - o0, cnt = pt_off[pfirst + i + 1] - pt_off[pfirst + i]; pw = cnt > 0 ? (a | cnt << 16) : 0; }
-                tmeta[o0 + i] = make_int4(P->obs_cam[e->ob + o0 + i], int(packA), spack[o0 + i], pw);
+                tmeta[o0 + i] = make_int4(int(unsigned(P->obs_cam[e->ob + o0 + i]) | unsigned(hpos[o0 + i]) << 24), int(packA), spack[o0 + i], pw);
             }
           }
         });
@@ -640,7 +651,11 @@ void do_set_problem(ba_engine* e, const ba_problem* P, const DevState* dev = nul
     for (auto* b : {&e->d_intr, &e->d_cintr}) b->alloc(size_t(4) * Ng);
     for (auto* b : {&e->d_pt, &e->d_cpt}) b->alloc(size_t(3) * Np);
     e->d_camrec.alloc(size_t(bak::CAMREC) * Nc); e->d_ccamrec.alloc(size_t(bak::CAMREC) * Nc);
-    e->d_J2.alloc(size_t(e->fi ? 13 : 9) * e->ldo); e->d_r2.alloc(e->ldo);
+    // pinhole model: translation columns 3 and 4 share one stored column (ba_kernels.cuh: load_jc); the alternative scatter kernels
+    // (modes 2, 3, 5) read the unpacked layout
+    e->jpack = (e->opt.model == BA_MODEL_PINHOLE && (e->scatter_mode == 4 || e->scatter_mode == 1) && BA_JPACK_DEFAULT) ? 1 : 0;
+    if (const char* v = std::getenv("BA_JPACK")) e->jpack = (std::atoi(v) && e->opt.model == BA_MODEL_PINHOLE && (e->scatter_mode == 4 || e->scatter_mode == 1)) ? 1 : 0;
+    e->d_J2.alloc(size_t((e->fi ? 13 : 9) - e->jpack) * e->ldo); e->d_r2.alloc(e->ldo);
     e->d_JcA.alloc(size_t(e->fi ? 12 : 8) * std::max(No, 1));
     e->k1_grid = std::max(1, std::min(e->nTiles, e->num_sms * K1_CTAS_PER_SM));
     e->d_Hpp.alloc(size_t(6) * Np); e->d_gp.alloc(size_t(3) * Np); e->d_Hinv.alloc(size_t(6) * Np);
@@ -663,6 +678,7 @@ void do_set_problem(ba_engine* e, const ba_problem* P, const DevState* dev = nul
     V.tile_off = e->d_tile_off.p; V.obs_cam = e->d_obs_cam.p; V.obs_pt = e->d_obs_pt.p; V.obs_uv = e->d_obs_uv.p;
     V.pt_off = e->d_pt_off.p; V.cam_group = e->d_cam_group.p; V.cam_free = e->d_cam_free.p; V.grp_free = e->d_grp_free.p;
     V.perm_by_cam = e->d_perm.p; V.cam_off = e->d_cam_off.p;
+    V.jpack = e->jpack;
     V.J2 = e->d_J2.p; V.r2 = e->d_r2.p; V.JcA = e->d_JcA.p; V.jca_stride = e->fi ? 12 : 8; V.Hpp = e->d_Hpp.p; V.gp = e->d_gp.p; V.Hinv = e->d_Hinv.p; V.vp = e->d_vp.p; V.yp = e->d_yp.p;
     V.sc_pt = e->d_sc_pt.p;
     CU_TRY(cudaStreamSynchronize(s));   // host staging vectors go out of scope
@@ -673,7 +689,7 @@ void do_set_problem(ba_engine* e, const ba_problem* P, const DevState* dev = nul
     build_dense(e, P, pt_off);
 
     // algorithmic bytes per launch of each kernel in THIS formulation, for roofline.achieved
-    const double no = No, np = Np, nc = Nc, jb = e->fi ? 208.0 : 144.0;
+    const double no = No, np = Np, nc = Nc, jb = (e->fi ? 208.0 : 144.0) - 16.0 * e->jpack;
     e->stats[KID_K0].bytes = (48 + 160) * nc;
     const double jca = e->fi ? 192.0 : 128.0;   // by-observation record for K2c
     e->stats[KID_K1].bytes = no * (24 + jb + 16 + jca) + np * (24 + 72) + 160 * nc;
@@ -777,12 +793,32 @@ void candidate_cost(ba_engine* e) {
       KL(e), bak::k_reduce_partials<<<1, 1024, 0, s>>>(e->d_part0.p, e->nTiles, &sc->ccost); }
 }
 
+// Launch along the PCG chain (K5a -> K5b -> tail -> K5a ...) with programmatic dependent launch: the next kernel's CTAs are scheduled
+// once every CTA of its predecessor has executed griddepcontrol.launch_dependents (all three do, first thing), run their prologue
+// (K5a: the tile's J columns and schedule record, none of which the predecessor writes) and block in griddepcontrol.wait until the
+// predecessor grid has completed and flushed.  Every kernel of the chain executes the wait before touching anything a predecessor
+// writes, so completion stays transitive.  Without the attribute (e->pdl == 0, or any other launch site) both instructions are no-ops.
+template <class... KArgs, class... Args>
+void launch_chain(ba_engine* e, void (*kern)(KArgs...), dim3 grid, dim3 block, Args&&... args) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = 0; cfg.stream = e->stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = e->pdl ? 1 : 0;
+    KL(e);
+    CU_TRY(cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...));
+}
+
 template <int MODE>
 void launch_sweep(ba_engine* e, int kid, const double* xin, double* yout, const int* done, double* partial) {
     if (e->nTiles == 0) return;
     LaunchTimer t(e, kid);
-    if (e->fi) KL(e), bak::k_schur_sweep<MODE, true><<<e->nTiles, bak::TILE_OBS, 0, e->stream>>>(e->V, xin, yout, done, partial);
-    else KL(e), bak::k_schur_sweep<MODE, false><<<e->nTiles, bak::TILE_OBS, 0, e->stream>>>(e->V, xin, yout, done, partial);
+    KL(e);
+    if (e->fi) { if (e->jpack) bak::k_schur_sweep<MODE, true, 1><<<e->nTiles, bak::TILE_OBS, 0, e->stream>>>(e->V, xin, yout, done, partial);
+                 else bak::k_schur_sweep<MODE, true, 0><<<e->nTiles, bak::TILE_OBS, 0, e->stream>>>(e->V, xin, yout, done, partial); }
+    else { if (e->jpack) bak::k_schur_sweep<MODE, false, 1><<<e->nTiles, bak::TILE_OBS, 0, e->stream>>>(e->V, xin, yout, done, partial);
+           else bak::k_schur_sweep<MODE, false, 0><<<e->nTiles, bak::TILE_OBS, 0, e->stream>>>(e->V, xin, yout, done, partial); }
 }
 
 // Camera-side product F^T(...) by the configured scatter.  Result: in `yout` for mode 1 (L2 atomics), otherwise in the
@@ -812,7 +848,8 @@ void launch_scatter(ba_engine* e, int kid, const double* xin, double* yout, cons
     *G_out = 0;
     if (e->nTiles == 0) return;
     if (e->scatter_mode == 1) { launch_sweep<MODE>(e, kid, xin, yout, done, nullptr); return; }
-    LaunchTimer t(e, kid);
+    const bool sample = kid != KID_K5 || e->stats[KID_K5].launches % e->k5_sample_stride == 0;
+    LaunchTimer t(e, kid, sample);
     if (e->scatter_mode == 5) {
         if (e->fi && e->Ng > 1) CU_TRY(cudaMemsetAsync(yout + 6 * e->Nc, 0, size_t(4) * e->Ng * sizeof(double), e->stream));
         if (e->fi) launch_rows_pipe<MODE, true>(e, xin, yout, done);
@@ -821,8 +858,14 @@ void launch_scatter(ba_engine* e, int kid, const double* xin, double* yout, cons
     }
     if (e->scatter_mode == 4) {
         if (e->fi && e->Ng > 1) CU_TRY(cudaMemsetAsync(yout + 6 * e->Nc, 0, size_t(4) * e->Ng * sizeof(double), e->stream));
-        if (e->fi) KL(e), bak::k_schur_rows<MODE, true><<<e->nTiles, bak::TILE_OBS, 0, e->stream>>>(e->V, e->RS, xin, yout, done);
-        else KL(e), bak::k_schur_rows<MODE, false><<<e->nTiles, bak::TILE_OBS, 0, e->stream>>>(e->V, e->RS, xin, yout, done);
+        // K5a goes down the PDL chain (launch_chain); K4 is an ordinary launch (both instructions are no-ops there)
+        const bool chain = MODE == bak::SWEEP_MATVEC;
+        auto go = [&](auto kern) {
+            if (chain) launch_chain(e, kern, dim3(e->nTiles), dim3(bak::TILE_OBS), e->V, e->RS, xin, yout, done);
+            else { KL(e); kern<<<e->nTiles, bak::TILE_OBS, 0, e->stream>>>(e->V, e->RS, xin, yout, done); }
+        };
+        if (e->fi) { if (e->jpack) go(bak::k_schur_rows<MODE, true, 1>); else go(bak::k_schur_rows<MODE, true, 0>); }
+        else { if (e->jpack) go(bak::k_schur_rows<MODE, false, 1>); else go(bak::k_schur_rows<MODE, false, 0>); }
         return;
     }
     if (e->scatter_mode == 2) {
@@ -913,21 +956,22 @@ int solve_linear(ba_engine* e, double radius, double* rel_out, double lambda = 0
     const bool multi = e->opt.world_size > 1;
     for (;;) {
         for (int i = 0; i < batch; ++i) {
+            const bool sample = e->stats[KID_K5].launches % e->k5_sample_stride == 0;
             launch_scatter<bak::SWEEP_MATVEC>(e, KID_K5, e->d_p.p, e->d_y.p, &sc->pcg.done, &G);
-            LaunchTimer t(e, KID_PCGV);
+            LaunchTimer t(e, KID_PCGV, sample);
             double* src = nullptr; int nsrc = 0;
             // y (and, on one GPU, q = y + Df2 p and alpha) from the scatter mode's own reduction; tail.mode says what is left to do
             ta.mode = 0;
             if (rowsm) {
                 if (multi && e->p2p.on) {   // one-shot NVLink all-reduce: local gather + flags here, the pull and the sum inside the tail (ba_p2p.cuh)
                     ta.seq = ++e->p2p.seq; ta.P = e->p2p.view; ta.mode = 2;
-                    KL(e), bak::k_camera_gather_push<<<gblocks, bak::GATHER_WARPS * 32, 0, s>>>(e->Nc, e->Ng, e->fi, e->nTiles, e->RS, e->d_y.p, e->p2p.view, ta.seq, &sc->pcg, 1);
+                    launch_chain(e, bak::k_camera_gather_push, dim3(gblocks), dim3(bak::GATHER_WARPS * 32), e->Nc, e->Ng, e->fi, e->nTiles, e->RS, e->d_y.p, e->p2p.view, ta.seq, &sc->pcg, 1);
                 } else if (multi) {
                     KL(e), bak::k_camera_gather<<<gblocks, bak::GATHER_WARPS * 32, 0, s>>>(e->Nc, e->Ng, e->fi, e->nTiles, e->RS, nullptr, nullptr, e->d_y.p, nullptr, &sc->pcg, 0);
                     allreduce_sum(e, e->d_y.p, e->nf);
                     ta.mode = 1;
                 } else {   // one GPU: plain gather (no ticket); q, p.q and alpha are the tail's
-                    KL(e), bak::k_camera_gather<<<gblocks, bak::GATHER_WARPS * 32, 0, s>>>(e->Nc, e->Ng, e->fi, e->nTiles, e->RS, nullptr, nullptr, e->d_y.p, nullptr, &sc->pcg, 0);
+                    launch_chain(e, bak::k_camera_gather, dim3(gblocks), dim3(bak::GATHER_WARPS * 32), e->Nc, e->Ng, e->fi, e->nTiles, e->RS, nullptr, nullptr, e->d_y.p, nullptr, &sc->pcg, 0);
                     ta.mode = 1;
                 }
             } else {
@@ -941,7 +985,7 @@ int solve_linear(ba_engine* e, double radius, double* rel_out, double lambda = 0
                 }
             }
             // x, r, z, rho, beta, stop test and the new search direction: one thread-block cluster (ba_pcg_cluster.cuh)
-            KL(e), bak::k_pcg_tail<<<bak::TAIL_CL, bak::TAIL_THREADS, 0, s>>>(ta);
+            launch_chain(e, bak::k_pcg_tail, dim3(bak::TAIL_CL), dim3(bak::TAIL_THREADS), ta);
             if (e->scatter_mode == 1) e->d_y.zero(s);
         }
         read_scalars(e);
@@ -1224,6 +1268,9 @@ int ba_create(const ba_options* opt, ba_engine** out) {
         e->num_sms = prop.multiProcessorCount;
         e->scatter_mode = (opt->scatter_mode >= 1 && opt->scatter_mode <= 5) ? opt->scatter_mode : 4;
         if (const char* g = std::getenv("BA_L2_FETCH")) CU_TRY(cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, size_t(std::atoi(g))));   // experiment knob: 32 / 64 / 128
+        if (const char* v = std::getenv("BA_K5_SAMPLE")) e->k5_sample_stride = std::max(1, std::atoi(v));
+        e->pdl = BA_PDL_DEFAULT;
+        if (const char* v = std::getenv("BA_PDL")) e->pdl = std::atoi(v) ? 1 : 0;
         if (prop.major < 10) throw BaFail{BA_ERR_CUDA, std::string("device ") + prop.name + " is not sm_100-class; this library holds sm_100a code only"};
         if (opt->stream) e->stream = static_cast<cudaStream_t>(opt->stream);
         else { CU_TRY(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking)); e->own_stream = true; }
@@ -1419,15 +1466,20 @@ int ba_evaluate(ba_engine* e, double* cost, double* r, double* Jc, double* Jp, d
         read_scalars(e);
         bad = e->h_scal->bad_eval;
         if (cost) *cost = e->h_scal->cost;
-        const int No = e->No, ld = e->ldo, ncol = e->fi ? 13 : 9;
+        const int No = e->No, ld = e->ldo, pk = e->jpack, ncol = (e->fi ? 13 : 9) - pk;
         vector<double2> hJ(size_t(ncol) * ld), hr(ld);
         CU_TRY(cudaMemcpy(hJ.data(), e->d_J2.p, hJ.size() * sizeof(double2), cudaMemcpyDeviceToHost));
         CU_TRY(cudaMemcpy(hr.data(), e->d_r2.p, hr.size() * sizeof(double2), cudaMemcpyDeviceToHost));
         for (int o = 0; o < No; ++o) {
             if (r) { r[2 * o] = hr[o].x; r[2 * o + 1] = hr[o].y; }
-            if (Jc) for (int k = 0; k < 6; ++k) { Jc[(2 * o) * 6 + k] = hJ[size_t(k) * ld + o].x; Jc[(2 * o + 1) * 6 + k] = hJ[size_t(k) * ld + o].y; }
-            if (Jp) for (int k = 0; k < 3; ++k) { Jp[(2 * o) * 3 + k] = hJ[size_t(6 + k) * ld + o].x; Jp[(2 * o + 1) * 3 + k] = hJ[size_t(6 + k) * ld + o].y; }
-            if (Ji) for (int k = 0; k < 4; ++k) { Ji[(2 * o) * 4 + k] = e->fi ? hJ[size_t(9 + k) * ld + o].x : 0.0; Ji[(2 * o + 1) * 4 + k] = e->fi ? hJ[size_t(9 + k) * ld + o].y : 0.0; }
+            if (Jc) for (int k = 0; k < 6; ++k) {
+                double2 v = hJ[size_t(k - (pk && k > 3 ? 1 : 0)) * ld + o];
+                if (pk && k == 3) v.y = 0.0;      // packed translation columns (load_jc): stored (d r0/d tx, d r1/d ty)
+                if (pk && k == 4) v.x = 0.0;
+                Jc[(2 * o) * 6 + k] = v.x; Jc[(2 * o + 1) * 6 + k] = v.y;
+            }
+            if (Jp) for (int k = 0; k < 3; ++k) { Jp[(2 * o) * 3 + k] = hJ[size_t(6 - pk + k) * ld + o].x; Jp[(2 * o + 1) * 3 + k] = hJ[size_t(6 - pk + k) * ld + o].y; }
+            if (Ji) for (int k = 0; k < 4; ++k) { Ji[(2 * o) * 4 + k] = e->fi ? hJ[size_t(9 - pk + k) * ld + o].x : 0.0; Ji[(2 * o + 1) * 4 + k] = e->fi ? hJ[size_t(9 - pk + k) * ld + o].y : 0.0; }
         }
         if (g) {
             CU_TRY(cudaMemcpy(g, e->gc(), size_t(6) * e->Nc * sizeof(double), cudaMemcpyDeviceToHost));
@@ -1444,7 +1496,7 @@ int ba_set_profiling(ba_engine* e, int32_t enabled) {
     if (!e) return BA_ERR_INVALID_ARGUMENT;
     e->profiling = enabled < 0 ? 0xffffffffu : unsigned(enabled);   // bit mask of kernel ids (ba_kernel_stat order); 1 keeps meaning "all" for convenience
     if (enabled == 1) e->profiling = 0xffffffffu;
-    for (auto& st : e->stats) { st.launches = 0; st.ms = 0.0; }
+    for (auto& st : e->stats) { st.launches = 0; st.timed = 0; st.ms = 0.0; }
     return BA_OK;
 }
 
@@ -1461,7 +1513,9 @@ int ba_get_kernel_stats(ba_engine* e, ba_kernel_stat* out, int32_t cap, int32_t*
     if (out) for (int i = 0; i < std::min<int>(cap, KID_COUNT); ++i) {
         std::memset(&out[i], 0, sizeof out[i]);
         std::snprintf(out[i].name, sizeof out[i].name, "%s", kKernelNames[i]);
-        out[i].launches = e->stats[i].launches; out[i].total_ms = e->stats[i].ms; out[i].bytes_per_launch = e->stats[i].bytes;
+        out[i].launches = e->stats[i].launches; out[i].bytes_per_launch = e->stats[i].bytes;
+        // launches that were not bracketed by events (sampled timing of K5) count at the mean of the timed ones
+        out[i].total_ms = e->stats[i].timed > 0 ? e->stats[i].ms * double(e->stats[i].launches) / double(e->stats[i].timed) : 0.0;
     }
     return BA_OK;
 }

@@ -31,6 +31,7 @@ struct View {
     int ldo;                     // leading dimension (observations) of J2 / r2
     int nTiles;
     int fi;                      // 1: intrinsics blocks are free (J2 has 13 column pairs)
+    int jpack;                   // 1: pinhole model, columns 3 and 4 share one stored column (see load_jc): J2 has 8 (12) column pairs
     int left_twist;              // 1: pose columns are d/d(omega, upsilon) of T <- exp(omega, upsilon) T (g2o policy); 0: d/d(angle-axis, t)
     const int* tile_off;         // [nTiles+1] first observation of each tile
     const int* obs_cam;          // [No]
@@ -43,7 +44,7 @@ struct View {
     // camera-sorted view (for the by-camera segmented reductions)
     const int* perm_by_cam;      // [No] local observation ids, stable by camera
     const int* cam_off;          // [Nc+1]
-    double2* J2;                 // [9 or 13][ldo]
+    double2* J2;                 // [9 or 13][ldo]  ([8 or 12][ldo] with jpack)
     double2* r2;                 // [ldo] robustified residual
     double2* JcA;                // [No][8 or 12] by-observation records (jc0..jc5, r, [ji0..ji3], pad) for the by-camera gather of K2c
     int jca_stride;              // double2 per record: 8 (128 B), 12 with free intrinsics (192 B) — whole 32-byte sectors
@@ -56,6 +57,34 @@ struct View {
 };
 
 __device__ __forceinline__ double2 ldg2(const double2* p) { return __ldg(p); }
+
+// The Jacobian columns of observation o (J = V.J2 + o, column stride V.ldo).  Pinhole model (ReprojectCost, BundleAdjuster.h:55-62):
+// u depends on P only through (Px, Pz) and v through (Py, Pz), so d(r0)/d(ty) = d(r1)/d(tx) = 0 exactly; with V.jpack the translation
+// columns 3 = (a, 0) and 4 = (0, b) are stored as ONE column (a, b) and every later column moves up by one: 128 instead of 144 bytes per
+// observation (192 / 208 with free intrinsics) in every sweep over J.
+// PK: 1 packed, 0 unpacked (compile-time, the streaming kernels), -1 as V.jpack says (run-time, everything else).
+template <int PK = -1>
+__device__ __forceinline__ void load_jc(const View& V, const double2* __restrict__ J, double2 (&jc)[6]) {
+    const size_t ld = V.ldo;
+    const bool pk = PK < 0 ? V.jpack != 0 : PK != 0;
+    jc[0] = ldg2(J); jc[1] = ldg2(J + ld); jc[2] = ldg2(J + 2 * ld);
+    const double2 d = ldg2(J + 3 * ld);
+    if (pk) { jc[3] = make_double2(d.x, 0.0); jc[4] = make_double2(0.0, d.y); jc[5] = ldg2(J + 4 * ld); }
+    else { jc[3] = d; jc[4] = ldg2(J + 4 * ld); jc[5] = ldg2(J + 5 * ld); }
+}
+template <int PK = -1>
+__device__ __forceinline__ void load_jp(const View& V, const double2* __restrict__ J, double2 (&jp)[3]) {
+    const int pk = PK < 0 ? V.jpack : PK;
+    const double2* Jp = J + size_t(6 - pk) * V.ldo;
+    jp[0] = ldg2(Jp); jp[1] = ldg2(Jp + V.ldo); jp[2] = ldg2(Jp + 2 * size_t(V.ldo));
+}
+template <int PK = -1>
+__device__ __forceinline__ void load_ji(const View& V, const double2* __restrict__ J, double2 (&ji)[4]) {
+    const int pk = PK < 0 ? V.jpack : PK;
+    const double2* Ji = J + size_t(9 - pk) * V.ldo;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) ji[k] = ldg2(Ji + size_t(k) * V.ldo);
+}
 
 __device__ __forceinline__ void red_add(double* addr, double v) {
     // fire-and-forget L2 reduction (RED.E.ADD.F64), no return value
@@ -71,6 +100,10 @@ __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
+// Programmatic dependent launch (ba_engine.cu: launch_chain).  No-ops in a kernel launched without the attribute.
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
 __device__ __forceinline__ double warp_sum(double v) {
 #pragma unroll
@@ -227,6 +260,12 @@ __device__ __forceinline__ void model_jacobian(const Proj& q, const double* __re
 // Persistent: CTA b walks tiles b, b+G, ...; the NEXT tile's index data (tile offsets two tiles ahead; camera id, point id and
 // pixel of this thread's observation one tile ahead) is loaded while the current tile is computed, so a tile's critical path
 // starts at the camera-record / point gathers instead of three dependent DRAM latencies earlier.  One cost partial per CTA.
+#ifndef BA_K1_JCA_SMEM
+#define BA_K1_JCA_SMEM 1
+#endif
+#ifndef BA_K1_CAM_SMEM
+#define BA_K1_CAM_SMEM 0   // needs BA_K1_JCA_SMEM (shares its staging area)
+#endif
 #ifndef K1_CTAS_PER_SM
 #define K1_CTAS_PER_SM 4
 #endif
@@ -235,11 +274,15 @@ __global__ void __launch_bounds__(TILE_OBS, K1_CTAS_PER_SM)
 k1_residual_jacobian(View V, const double* __restrict__ camrec, const double* __restrict__ intr, const double* __restrict__ pt,
                      RobustParams rp, double* __restrict__ cost_partial, int* __restrict__ bad_flag) {
     __shared__ double sJp[TILE_OBS][9];   // per observation: Jp (2x3) , r (2)  [+1 pad: stride 9 is conflict-free]
+#if BA_K1_JCA_SMEM
+    __shared__ __align__(16) double2 sA[TILE_OBS * 12];   // staging of the by-observation records (8 or 12 double2 each)
+#endif
     __shared__ double sred[32];
     const int G = gridDim.x, nT = V.nTiles;
     int t = blockIdx.x;
     double cost = 0.0;
     int bad = 0;
+    const int rot12 = (threadIdx.x >> 1) % 12;   // slot rotation of this thread's 12 x 16-byte staging area (sA)
     if (t >= nT) { if (threadIdx.x == 0) cost_partial[blockIdx.x] = 0.0; return; }
     int o0 = V.tile_off[t], o1 = V.tile_off[t + 1];
     // landing slots of the prefetch, double-buffered by tile parity: camera id, point id, pixel of this thread's observation
@@ -283,11 +326,29 @@ k1_residual_jacobian(View V, const double* __restrict__ camrec, const double* __
         const int pj = pfirst + threadIdx.x;
         int pa = 0, pb = 0;
         if (pj <= plast) { pa = max(V.pt_off[pj], base); pb = min(V.pt_off[pj + 1], lim); }
+#if BA_K1_CAM_SMEM
+        {   // the chunk's camera records, fetched by consecutive lanes (10 lanes per 160-byte record: ~7 lines per warp instruction
+            // instead of one line per lane) into the threads' staging areas; thread i then reads record i from its own area
+            const int nq = (lim - base) * (CAMREC / 2);
+            for (int q = threadIdx.x; q < nq; q += TILE_OBS) {
+                const int i = q / (CAMREC / 2), k = q - i * (CAMREC / 2);
+                const int cc = first ? sPc[buf][i] : V.obs_cam[base + i];
+                int sl = k + (i >> 1) % 12; if (sl >= 12) sl -= 12;
+                sA[i * 12 + sl] = __ldg(reinterpret_cast<const double2*>(camrec + size_t(cc) * CAMREC) + k);
+            }
+            __syncthreads();
+        }
+#endif
         if (act) {
             const int c = first ? pre_c : V.obs_cam[o], p = first ? pre_p : V.obs_pt[o];
             const int g = V.Ng == 1 ? 0 : V.cam_group[c];   // one shared Camera: no dependent group load
             double cr[CAMREC];
+#if BA_K1_CAM_SMEM
+#pragma unroll
+            for (int k = 0; k < CAMREC / 2; ++k) { int sl = k + rot12; if (sl >= 12) sl -= 12; const double2 v = sA[threadIdx.x * 12 + sl]; cr[2 * k] = v.x; cr[2 * k + 1] = v.y; }
+#else
             load_camrec<CAMREC / 2>(camrec, c, cr);
+#endif
             const double* in = intr + 4 * g;
             Proj q;
             project_obs<MODEL>(cr, pt + 3 * size_t(p), in, first ? pre_uv : ldg2(V.obs_uv + o), q);
@@ -340,31 +401,41 @@ k1_residual_jacobian(View V, const double* __restrict__ camrec, const double* __
             J[0 * ld] = make_double2(wc * Ja0[0], wc * Ja1[0]);
             J[1 * ld] = make_double2(wc * Ja0[1], wc * Ja1[1]);
             J[2 * ld] = make_double2(wc * Ja0[2], wc * Ja1[2]);
-            J[3 * ld] = make_double2(wc * A0[0], wc * A1[0]);
-            J[4 * ld] = make_double2(wc * A0[1], wc * A1[1]);
-            J[5 * ld] = make_double2(wc * A0[2], wc * A1[2]);
+            const int pk = V.jpack;   // pinhole: A0[1] = A1[0] = 0, columns 3 and 4 share one stored column (load_jc)
+            if (pk) J[3 * ld] = make_double2(wc * A0[0], wc * A1[1]);
+            else { J[3 * ld] = make_double2(wc * A0[0], wc * A1[0]); J[4 * ld] = make_double2(wc * A0[1], wc * A1[1]); }
+            J[(5 - pk) * ld] = make_double2(wc * A0[2], wc * A1[2]);
             const double p0[3] = {w * JX0[0], w * JX0[1], w * JX0[2]}, p1[3] = {w * JX1[0], w * JX1[1], w * JX1[2]};
-            J[6 * ld] = make_double2(p0[0], p1[0]);
-            J[7 * ld] = make_double2(p0[1], p1[1]);
-            J[8 * ld] = make_double2(p0[2], p1[2]);
+            J[(6 - pk) * ld] = make_double2(p0[0], p1[0]);
+            J[(7 - pk) * ld] = make_double2(p0[1], p1[1]);
+            J[(8 - pk) * ld] = make_double2(p0[2], p1[2]);
             if (V.fi) {   // d(u,v)/d(fx,fy,cx,cy) = [x 0 1 0; 0 y 0 1]
                 const double wi = V.grp_free[g] ? w : 0.0;
 #pragma unroll
-                for (int k = 0; k < 4; ++k) J[(9 + k) * ld] = make_double2(wi * Jin[k].x, wi * Jin[k].y);
+                for (int k = 0; k < 4; ++k) J[(9 - pk + k) * ld] = make_double2(wi * Jin[k].x, wi * Jin[k].y);
             }
             const double rr0 = w * q.r0, rr1 = w * q.r1;
             V.r2[o] = make_double2(rr0, rr1);
             {   // by-observation record for K2c: whole sectors, so the by-camera gather fetches no byte it does not use
+#if BA_K1_JCA_SMEM
+                // staged in shared memory (12 slots of 16 bytes per thread, chunk k in slot (k + rot) % 12: conflict-free for the 16-byte
+                // accesses of 8 adjacent lanes) and written out after the barrier by consecutive lanes: whole lines per warp instruction.
+                // Storing the records straight from the registers is 8 STG.128 to 32 different lines each = 256 L1 wavefronts per warp.
+                double2* A = sA + threadIdx.x * 12;
+                auto put = [&](int k, double2 v) { int sl = k + rot12; if (sl >= 12) sl -= 12; A[sl] = v; };
+#else
                 double2* A = V.JcA + size_t(o) * V.jca_stride;
-                A[0] = make_double2(wc * Ja0[0], wc * Ja1[0]); A[1] = make_double2(wc * Ja0[1], wc * Ja1[1]); A[2] = make_double2(wc * Ja0[2], wc * Ja1[2]);
-                A[3] = make_double2(wc * A0[0], wc * A1[0]); A[4] = make_double2(wc * A0[1], wc * A1[1]); A[5] = make_double2(wc * A0[2], wc * A1[2]);
-                A[6] = make_double2(rr0, rr1);
+                auto put = [&](int k, double2 v) { A[k] = v; };
+#endif
+                put(0, make_double2(wc * Ja0[0], wc * Ja1[0])); put(1, make_double2(wc * Ja0[1], wc * Ja1[1])); put(2, make_double2(wc * Ja0[2], wc * Ja1[2]));
+                put(3, make_double2(wc * A0[0], wc * A1[0])); put(4, make_double2(wc * A0[1], wc * A1[1])); put(5, make_double2(wc * A0[2], wc * A1[2]));
+                put(6, make_double2(rr0, rr1));
                 if (V.fi) {
                     const double wi = V.grp_free[g] ? w : 0.0;
 #pragma unroll
-                    for (int k = 0; k < 4; ++k) A[7 + k] = make_double2(wi * Jin[k].x, wi * Jin[k].y);
-                    A[11] = make_double2(0.0, 0.0);
-                } else A[7] = make_double2(0.0, 0.0);
+                    for (int k = 0; k < 4; ++k) put(7 + k, make_double2(wi * Jin[k].x, wi * Jin[k].y));
+                    put(11, make_double2(0.0, 0.0));
+                } else put(7, make_double2(0.0, 0.0));
             }
             double chk = rr0 + rr1 + rho;
 #pragma unroll
@@ -374,6 +445,17 @@ k1_residual_jacobian(View V, const double* __restrict__ camrec, const double* __
             sj[0] = p0[0]; sj[1] = p0[1]; sj[2] = p0[2]; sj[3] = p1[0]; sj[4] = p1[1]; sj[5] = p1[2]; sj[6] = rr0; sj[7] = rr1;
         }
         __syncthreads();
+#if BA_K1_JCA_SMEM
+        {   // write the chunk's records out: consecutive lanes take consecutive 16-byte pieces of the records
+            const int st = V.jca_stride, nq = (lim - base) * st;
+            double2* dst = V.JcA + size_t(base) * st;
+            for (int q = threadIdx.x; q < nq; q += TILE_OBS) {
+                const int i = st == 8 ? (q >> 3) : (q / 12), k = q - i * st;
+                int sl = k + (i >> 1) % 12; if (sl >= 12) sl -= 12;
+                dst[q] = sA[i * 12 + sl];
+            }
+        }
+#endif
         // by-point half of K2
         const int p = pj;
         if (p <= plast) {
@@ -468,7 +550,7 @@ __global__ void k_reduce_partials(const double* __restrict__ partial, int n, dou
 // The damping term Df^2 x of the matvec is added by the PCG vector kernel, not here.
 enum { SWEEP_MATVEC = 0, SWEEP_RHS = 1, SWEEP_BACKSUB = 2 };
 
-template <int MODE, bool FI>
+template <int MODE, bool FI, int PK>
 __global__ void __launch_bounds__(TILE_OBS)
 k_schur_sweep(View V, const double* __restrict__ xin, double* __restrict__ yout, const int* __restrict__ done_flag,
               double* __restrict__ partial) {
@@ -493,14 +575,11 @@ k_schur_sweep(View V, const double* __restrict__ xin, double* __restrict__ yout,
         if (act) {
             c = V.obs_cam[o]; p = V.obs_pt[o];
             const double2* J = V.J2 + o;
-#pragma unroll
-            for (int k = 0; k < 6; ++k) jc[k] = ldg2(J + k * ld);
-#pragma unroll
-            for (int k = 0; k < 3; ++k) jp[k] = ldg2(J + (6 + k) * ld);
+            load_jc<PK>(V, J, jc);
+            load_jp<PK>(V, J, jp);
             if (FI) {
                 g = V.cam_group[c];
-#pragma unroll
-                for (int k = 0; k < 4; ++k) ji[k] = ldg2(J + (9 + k) * ld);
+                load_ji<PK>(V, J, ji);
             }
             if (MODE != SWEEP_RHS) {
                 const double* xc = xin + 6 * c;
@@ -572,15 +651,20 @@ k_schur_sweep(View V, const double* __restrict__ xin, double* __restrict__ yout,
                 const int c = V.obs_cam[o];
                 const double2* J = V.J2 + o;
                 double2 u = make_double2(0.0, 0.0);
+                double2 jc[6], jp[3];
+                load_jc<PK>(V, J, jc);
 #pragma unroll
-                for (int k = 0; k < 6; ++k) { const double2 j = ldg2(J + k * ld); const double xv = __ldg(xin + 6 * c + k); u.x += j.x * xv; u.y += j.y * xv; }
+                for (int k = 0; k < 6; ++k) { const double xv = __ldg(xin + 6 * c + k); u.x += jc[k].x * xv; u.y += jc[k].y * xv; }
                 if (FI) {
                     const int g = V.cam_group[c];
+                    double2 ji[4];
+                    load_ji<PK>(V, J, ji);
 #pragma unroll
-                    for (int k = 0; k < 4; ++k) { const double2 j = ldg2(J + (9 + k) * ld); const double xv = __ldg(xin + ioff + 4 * g + k); u.x += j.x * xv; u.y += j.y * xv; }
+                    for (int k = 0; k < 4; ++k) { const double xv = __ldg(xin + ioff + 4 * g + k); u.x += ji[k].x * xv; u.y += ji[k].y * xv; }
                 }
+                load_jp<PK>(V, J, jp);
 #pragma unroll
-                for (int a = 0; a < 3; ++a) { const double2 j = ldg2(J + (6 + a) * ld); W[a] += j.x * u.x + j.y * u.y; }
+                for (int a = 0; a < 3; ++a) W[a] += jp[a].x * u.x + jp[a].y * u.y;
             }
 #pragma unroll
             for (int a = 0; a < 3; ++a) { const double s = block_sum(W[a], sred); if (threadIdx.x == 0) sV[0][a] = s; }
@@ -604,14 +688,10 @@ k_schur_sweep(View V, const double* __restrict__ xin, double* __restrict__ yout,
             const int c = V.obs_cam[o];
             const int g = FI ? V.cam_group[c] : 0;
             const double2* J = V.J2 + o;
-            double2 jc[6], ji[4];
+            double2 jc[6], ji[4], jp[3];
             double2 u = make_double2(0.0, 0.0);
-#pragma unroll
-            for (int k = 0; k < 6; ++k) jc[k] = ldg2(J + k * ld);
-            if (FI) {
-#pragma unroll
-                for (int k = 0; k < 4; ++k) ji[k] = ldg2(J + (9 + k) * ld);
-            }
+            load_jc<PK>(V, J, jc);
+            if (FI) load_ji<PK>(V, J, ji);
             if (MODE != SWEEP_RHS) {
 #pragma unroll
                 for (int k = 0; k < 6; ++k) { const double xv = __ldg(xin + 6 * c + k); u.x += jc[k].x * xv; u.y += jc[k].y * xv; }
@@ -621,8 +701,9 @@ k_schur_sweep(View V, const double* __restrict__ xin, double* __restrict__ yout,
                 }
             }
             double e0 = 0.0, e1 = 0.0;
+            load_jp<PK>(V, J, jp);
 #pragma unroll
-            for (int a = 0; a < 3; ++a) { const double2 j = ldg2(J + (6 + a) * ld); e0 += j.x * v[a]; e1 += j.y * v[a]; }
+            for (int a = 0; a < 3; ++a) { e0 += jp[a].x * v[a]; e1 += jp[a].y * v[a]; }
             double2 tt;
             if (MODE == SWEEP_MATVEC) { tt.x = u.x - e0; tt.y = u.y - e1; }
             else if (MODE == SWEEP_RHS) { const double2 r = V.r2[o]; tt.x = r.x - e0; tt.y = r.y - e1; }
@@ -664,6 +745,72 @@ k_schur_sweep(View V, const double* __restrict__ xin, double* __restrict__ yout,
 // camera's share of its group's 4x4 block and gradient (ipart; k_group_blocks adds the shares in camera order).
 // Gathers the by-observation records K1 wrote (JcA: Jc, r [, Ji] in 128 / 192 contiguous bytes = whole sectors) through
 // perm_by_cam.  (v1 gathered the SoA columns: 7 separate 16-byte pieces per observation, 3.1x DRAM over-fetch.)  
+#ifndef BA_K2C_COOP
+#define BA_K2C_COOP 1
+#endif
+#if BA_K2C_COOP
+// 8 adjacent lanes (16 with free intrinsics) share one record: lane k loads its k-th 16 bytes, so a warp instruction reads 4 (2)
+// whole records = 4 (3) lines, one L1 wavefront per record; the first version (below, #else) gave every lane a whole record: 7 LDG.128
+// to 32 different lines each = 7 wavefronts per record, and the kernel sat at 0.55 of the HBM roofline waiting on the load/store unit.
+// Lane a < 6 then forms row a of Jc^T Jc and (Jc^T r)[a] from the other lanes' pieces by width-8 shuffles (lanes 7..10: Ji).
+template <bool FI>
+__global__ void __launch_bounds__(128)
+k2c_camera_blocks(View V, double* __restrict__ Hcc, double* __restrict__ gc, double* __restrict__ ipart) {
+    constexpr int LPR = FI ? 16 : 8;        // lanes per record
+    constexpr int NGRP = 128 / LPR;         // records per CTA and load instruction
+    constexpr int UNR = 4;                  // records in flight per group
+    __shared__ double sm[4][LPR][7];
+    const int c = blockIdx.x;
+    const int a0 = V.cam_off[c], a1 = V.cam_off[c + 1];
+    const int sub = threadIdx.x & (LPR - 1), grp = threadIdx.x / LPR;
+    const int sbase = (FI && sub >= 7) ? 7 : 0;
+    const bool loads = sub < V.jca_stride;
+    double acc[7];
+#pragma unroll
+    for (int k = 0; k < 7; ++k) acc[k] = 0.0;
+    for (int ib = a0; ib < a1; ib += UNR * NGRP) {   // the trip count must not depend on grp: the shuffles below are warp-wide
+        const int i = ib + grp;
+        int o[UNR];
+#pragma unroll
+        for (int u = 0; u < UNR; ++u) { const int idx = i + u * NGRP; o[u] = idx < a1 ? __ldg(V.perm_by_cam + idx) : -1; }
+        double2 v[UNR];
+#pragma unroll
+        for (int u = 0; u < UNR; ++u) v[u] = (o[u] >= 0 && loads) ? ldg2(V.JcA + size_t(o[u]) * V.jca_stride + sub) : make_double2(0.0, 0.0);
+#pragma unroll
+        for (int u = 0; u < UNR; ++u) {
+#pragma unroll
+            for (int bq = 0; bq < 6; ++bq) {
+                const double jx = __shfl_sync(0xffffffffu, v[u].x, sbase + bq, LPR), jy = __shfl_sync(0xffffffffu, v[u].y, sbase + bq, LPR);
+                acc[bq] += v[u].x * jx + v[u].y * jy;
+            }
+            const double rx = __shfl_sync(0xffffffffu, v[u].x, 6, LPR), ry = __shfl_sync(0xffffffffu, v[u].y, 6, LPR);
+            acc[6] += v[u].x * rx + v[u].y * ry;
+        }
+    }
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+#pragma unroll
+    for (int k = 0; k < 7; ++k) {
+#pragma unroll
+        for (int off = LPR; off < 32; off <<= 1) acc[k] += __shfl_xor_sync(0xffffffffu, acc[k], off);
+    }
+    if (lane < LPR) {
+#pragma unroll
+        for (int k = 0; k < 7; ++k) sm[wid][lane][k] = acc[k];
+    }
+    __syncthreads();
+    if (threadIdx.x < LPR * 7) {
+        const int a = threadIdx.x / 7, k = threadIdx.x % 7;
+        const double s = (sm[0][a][k] + sm[1][a][k]) + (sm[2][a][k] + sm[3][a][k]);
+        if (a < 6) {
+            if (k < 6) Hcc[36 * size_t(c) + 6 * a + k] = s; else gc[6 * size_t(c) + a] = s;
+        } else if (FI && a >= 7 && a < 11) {   // this camera's share of its group's 4x4 block (upper, 10) and gradient (4): k_group_blocks sums them
+            const int ia = a - 7;
+            if (k == 6) ipart[14 * size_t(c) + 10 + ia] = s;
+            else if (k >= ia && k < 4) ipart[14 * size_t(c) + (ia * 4 - ia * (ia - 1) / 2) + (k - ia)] = s;
+        }
+    }
+}
+#else
 template <bool FI>
 __global__ void __launch_bounds__(128)
 k2c_camera_blocks(View V, double* __restrict__ Hcc, double* __restrict__ gc, double* __restrict__ ipart) {
@@ -721,6 +868,8 @@ k2c_camera_blocks(View V, double* __restrict__ Hcc, double* __restrict__ gc, dou
         }
     }
 }
+
+#endif
 
 // Free intrinsics: Hii / gi of every Camera group = sum of its cameras' shares, in camera order (one warp per group, fixed tree).
 __global__ void __launch_bounds__(128)

@@ -46,44 +46,18 @@ __global__ void __launch_bounds__(GATHER_WARPS * 32)
 k_camera_gather_push(int Nc, int Ng, int fi, int nTiles, RowSched S, const double* __restrict__ ylocal_rw, PeerView P, unsigned int seq,
                      PcgState2* __restrict__ st, int check_done) {
     __shared__ double sw[GATHER_WARPS][6];
+    pdl_trigger();
+    pdl_wait();
     if (check_done && st->done) return;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int ioff = 6 * Nc;
     double* const mine = P.data[P.rank] + size_t(seq & 1u) * P.ldf;
     const int c = blockIdx.x;
     if (c < Nc) {
-        double s0 = 0, s1 = 0, s2 = 0, s3 = 0, s4 = 0, s5 = 0;
-        // four independent rows per thread and trip, as k_camera_gather (same summation order)
-        constexpr int NT = GATHER_WARPS * 32;
-        const int e = S.cam_row_off[c + 1];
-        int i = S.cam_row_off[c] + threadIdx.x;
-        for (; i + 3 * NT < e; i += 4 * NT) {
-            const int i0 = S.cam_rows[i], i1 = S.cam_rows[i + NT], i2 = S.cam_rows[i + 2 * NT], i3 = S.cam_rows[i + 3 * NT];
-            const double2* r0 = reinterpret_cast<const double2*>(S.rows + size_t(ROW_DOUBLES) * i0);
-            const double2* r1 = reinterpret_cast<const double2*>(S.rows + size_t(ROW_DOUBLES) * i1);
-            const double2* r2 = reinterpret_cast<const double2*>(S.rows + size_t(ROW_DOUBLES) * i2);
-            const double2* r3 = reinterpret_cast<const double2*>(S.rows + size_t(ROW_DOUBLES) * i3);
-            const double2 a0 = __ldcg(r0), b0 = __ldcg(r0 + 1), c0 = __ldcg(r0 + 2);
-            const double2 a1 = __ldcg(r1), b1 = __ldcg(r1 + 1), c1 = __ldcg(r1 + 2);
-            const double2 a2 = __ldcg(r2), b2 = __ldcg(r2 + 1), c2 = __ldcg(r2 + 2);
-            const double2 a3 = __ldcg(r3), b3 = __ldcg(r3 + 1), c3 = __ldcg(r3 + 2);
-            s0 += (a0.x + a1.x) + (a2.x + a3.x); s1 += (a0.y + a1.y) + (a2.y + a3.y);
-            s2 += (b0.x + b1.x) + (b2.x + b3.x); s3 += (b0.y + b1.y) + (b2.y + b3.y);
-            s4 += (c0.x + c1.x) + (c2.x + c3.x); s5 += (c0.y + c1.y) + (c2.y + c3.y);
-        }
-        for (; i < e; i += NT) {
-            const double2* row = reinterpret_cast<const double2*>(S.rows + size_t(ROW_DOUBLES) * S.cam_rows[i]);
-            const double2 a = __ldcg(row), bq = __ldcg(row + 1), cq = __ldcg(row + 2);
-            s0 += a.x; s1 += a.y; s2 += bq.x; s3 += bq.y; s4 += cq.x; s5 += cq.y;
-        }
-        s0 = warp_sum(s0); s1 = warp_sum(s1); s2 = warp_sum(s2); s3 = warp_sum(s3); s4 = warp_sum(s4); s5 = warp_sum(s5);
-        if (lane == 0) { sw[wid][0] = s0; sw[wid][1] = s1; sw[wid][2] = s2; sw[wid][3] = s3; sw[wid][4] = s4; sw[wid][5] = s5; }
-        __syncthreads();
+        camera_row_sum(S, c, sw);
         if (threadIdx.x < 3) {   // thread h: 16 bytes of this camera's 6-vector
             const int h = threadIdx.x;
-            double2 v = make_double2(0.0, 0.0);
-#pragma unroll
-            for (int w = 0; w < GATHER_WARPS; ++w) { v.x += sw[w][2 * h]; v.y += sw[w][2 * h + 1]; }
+            const double2 v = make_double2(sw[0][2 * h], sw[0][2 * h + 1]);
             __stcg(reinterpret_cast<double2*>(mine + 6 * size_t(c) + 2 * h), v);
         }
     } else if (fi) {

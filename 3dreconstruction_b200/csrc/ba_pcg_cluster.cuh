@@ -50,6 +50,8 @@ __global__ void __cluster_dims__(TAIL_CL, 1, 1) __launch_bounds__(TAIL_THREADS) 
     __shared__ double cell[3];
     cg::cluster_group cl = cg::this_cluster();
     PcgState2* st = A.st;
+    pdl_trigger();
+    pdl_wait();
     if (st->done) return;                        // uniform over the cluster: nobody reaches a barrier
     const int Nc = A.Nc, nblk = Nc + (A.fi ? A.Ng : 0);
     const int per = ((nblk + TAIL_CL - 1) / TAIL_CL + 3) & ~3;          // diagonal blocks per CTA, whole warps of 8-lane groups
@@ -149,8 +151,14 @@ __global__ void __cluster_dims__(TAIL_CL, 1, 1) __launch_bounds__(TAIL_THREADS) 
         }
         if (act) { A.z[off + sub] = zz; rz += rra * zz; }
     }
-    const double rho_new = cluster_total(cl, rz, &cell[1], sred);
-    const double xb = cluster_total(cl, xq, &cell[2], sred);
+    // r.z and x.(b + r) in ONE cluster barrier
+    rz = block_sum(rz, sred);
+    xq = block_sum(xq, sred);
+    if (threadIdx.x == 0) { cell[1] = rz; cell[2] = xq; }
+    cl.sync();
+    double rho_new = 0.0, xb = 0.0;
+#pragma unroll
+    for (int k = 0; k < TAIL_CL; ++k) { const double* c = cl.map_shared_rank(&cell[0], k); rho_new += c[1]; xb += c[2]; }
 
     // ---- stop rules (identical in every thread; CTA 0 records them), then p = z + beta p -----------------------------------------
     const int k = st->k + 1;

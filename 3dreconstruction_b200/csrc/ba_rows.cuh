@@ -15,10 +15,11 @@ namespace bak {
 
 constexpr int ROW_DOUBLES = 8;    // 6 used; 64-byte rows = two full 32-byte sectors
 constexpr int L1_CHUNK = 8;       // level-1 chunk of the in-tile segmented sum
+constexpr int GATHER_WARPS = 4;   // warps per CTA of the by-camera gather (K5b)
 
 struct RowSched {
     // One 16-byte record per tile position i = o0 + tid, read with a single LDG.128 at kernel entry:
-    //   .x  camera of observation i
+    //   .x  camera of observation i | sorted position of the head of its camera segment << 24
     //   .y  slot | lvl1 << 8 | hrank << 16 | lpt << 24   (observation i: rank in the tile's camera-sorted order; sorted position
     //       tid: rows to fold in level 1, index of this segment head among the tile's heads; observation i: tile-local point)
     //   .z  sorted position tid: camera | segment length << 22 at segment heads, -1 elsewhere
@@ -33,14 +34,23 @@ struct RowSched {
     int nRows;
 };
 
-template <int MODE, bool FI>
-__global__ void __launch_bounds__(TILE_OBS)
+#ifndef BA_K5A_MINB
+#define BA_K5A_MINB 6          // min CTAs/SM for ptxas: 6 = 80 registers, no spills (A/B knob: 7 and 8 cap the registers at 72 / 64)
+#endif
+#ifndef BA_K5A_XSMEM
+#define BA_K5A_XSMEM 0        // 1: the search direction p[c] reaches the observations through shared memory, one fetch per distinct camera of the tile
+#endif
+#ifndef BA_K5A_OBS_HINV
+#define BA_K5A_OBS_HINV 0      // 1: every observation thread sums its point's W and applies Hinv itself (one barrier less)
+#endif
+template <int MODE, bool FI, int PK>
+__global__ void __launch_bounds__(TILE_OBS, BA_K5A_MINB)
 k_schur_rows(View V, RowSched S, const double* __restrict__ xin, double* __restrict__ atomic_out, const int* __restrict__ done_flag) {
     __shared__ double sW[TILE_OBS][3];
     __shared__ double sV[TILE_OBS][3];
     __shared__ __align__(16) double sC[TILE_OBS][6];
     __shared__ double sred[32];
-    if (done_flag && *done_flag) return;
+    pdl_trigger();
     const int t = blockIdx.x;
     const int4 ti = __ldg(S.tile_info + t);
     const int o0 = ti.x, n = ti.y, hbase = ti.z, pfirst = ti.w;
@@ -57,32 +67,45 @@ k_schur_rows(View V, RowSched S, const double* __restrict__ xin, double* __restr
         if (act) {
             tm = __ldg(S.tmeta + o);
             const double2* J = V.J2 + o;
-#pragma unroll
-            for (int k = 0; k < 6; ++k) jc[k] = ldg2(J + k * ld);
-#pragma unroll
-            for (int k = 0; k < 3; ++k) jp[k] = ldg2(J + (6 + k) * ld);
-            if (FI) {
-#pragma unroll
-                for (int k = 0; k < 4; ++k) ji[k] = ldg2(J + (9 + k) * ld);
-            }
+            load_jc<PK>(V, J, jc);
+            load_jp<PK>(V, J, jp);
+            if (FI) load_ji<PK>(V, J, ji);
             if (MODE == SWEEP_RHS) rr = V.r2[o];
         }
         const int npt_obs = tm.w >> 16, pstart = tm.w & 0xffff;   // this thread as a point thread
         double2 h0 = make_double2(0, 0), h1 = h0, h2 = h0;
-        if (MODE == SWEEP_MATVEC && npt_obs > 0) {
+        if (MODE == SWEEP_MATVEC && npt_obs > 0 && !BA_K5A_OBS_HINV) {
             const double2* H = reinterpret_cast<const double2*>(V.Hinv + 6 * size_t(pfirst + threadIdx.x));
             h0 = __ldg(H); h1 = __ldg(H + 1); h2 = __ldg(H + 2);      // (H0,H1) (H2,H3) (H4,H5)
         }
-        const int c = tm.x;
+        // everything above is static during a linear solve; xin and the done flag are the predecessor's (PCG tail) output
+        pdl_wait();
+        if (done_flag && *done_flag) return;
+        const int c = tm.x & 0xffffff, hp = int(unsigned(tm.x) >> 24);
         const int slot = tm.y & 0xff, n1 = (tm.y >> 8) & 0xff, hrank = (tm.y >> 16) & 0xff, lpt = (tm.y >> 24) & 0xff;
         const int pk = tm.z;
         const int g = (FI && act) ? V.cam_group[c] : 0;
         double2 u = make_double2(0.0, 0.0);
         double2 tt = make_double2(0.0, 0.0);
         if (MODE == SWEEP_MATVEC) {
+#if BA_K5A_XSMEM
+            // every distinct camera of the tile is fetched once, by its segment head (sorted position tid), into sC[tid]; the
+            // observations read it back from there: 2.3x fewer divergent 16-byte gathers than one fetch per observation
+            if (pk >= 0) {
+                const double2* xc = reinterpret_cast<const double2*>(xin + 6 * (pk & 0x3fffff));
+                double2* sx = reinterpret_cast<double2*>(sC[threadIdx.x]);
+                sx[0] = __ldg(xc); sx[1] = __ldg(xc + 1); sx[2] = __ldg(xc + 2);
+            }
+            __syncthreads();
+#endif
             if (act) {
+#if BA_K5A_XSMEM
+                const double2* sx = reinterpret_cast<const double2*>(sC[hp]);
+                const double2 x0 = sx[0], x1 = sx[1], x2 = sx[2];
+#else
                 const double2* xc = reinterpret_cast<const double2*>(xin + 6 * c);
                 const double2 x0 = __ldg(xc), x1 = __ldg(xc + 1), x2 = __ldg(xc + 2);
+#endif
                 u.x = jc[0].x * x0.x + jc[1].x * x0.y + jc[2].x * x1.x + jc[3].x * x1.y + jc[4].x * x2.x + jc[5].x * x2.y;
                 u.y = jc[0].y * x0.x + jc[1].y * x0.y + jc[2].y * x1.x + jc[3].y * x1.y + jc[4].y * x2.x + jc[5].y * x2.y;
                 if (FI) {
@@ -92,6 +115,23 @@ k_schur_rows(View V, RowSched S, const double* __restrict__ xin, double* __restr
 #pragma unroll
                 for (int a = 0; a < 3; ++a) sW[threadIdx.x][a] = jp[a].x * u.x + jp[a].y * u.y;
             }
+#if BA_K5A_OBS_HINV
+            reinterpret_cast<int*>(sV)[threadIdx.x] = tm.w;      // point thread's (first observation | count << 16), read back by its observations
+            double2 g0 = make_double2(0, 0), g1 = g0, g2 = g0;
+            if (act) {
+                const double2* H = reinterpret_cast<const double2*>(V.Hinv + 6 * size_t(pfirst + lpt));
+                g0 = __ldg(H); g1 = __ldg(H + 1); g2 = __ldg(H + 2);
+            }
+            __syncthreads();
+            if (act) {
+                const int pw = reinterpret_cast<const int*>(sV)[lpt];
+                double W0 = 0, W1 = 0, W2 = 0;
+                for (int i = pw & 0xffff, e = i + (pw >> 16); i < e; ++i) { W0 += sW[i][0]; W1 += sW[i][1]; W2 += sW[i][2]; }
+                const double v0 = g0.x * W0 + g0.y * W1 + g1.x * W2, v1 = g0.y * W0 + g1.y * W1 + g2.x * W2, v2 = g1.x * W0 + g2.x * W1 + g2.y * W2;
+                tt.x = u.x - (jp[0].x * v0 + jp[1].x * v1 + jp[2].x * v2);
+                tt.y = u.y - (jp[0].y * v0 + jp[1].y * v1 + jp[2].y * v2);
+            }
+#else
             __syncthreads();
             if (npt_obs > 0) {
                 double W0 = 0, W1 = 0, W2 = 0;
@@ -106,6 +146,7 @@ k_schur_rows(View V, RowSched S, const double* __restrict__ xin, double* __restr
                 tt.x = u.x - (jp[0].x * v[0] + jp[1].x * v[1] + jp[2].x * v[2]);
                 tt.y = u.y - (jp[0].y * v[0] + jp[1].y * v[1] + jp[2].y * v[2]);
             }
+#endif
         } else if (act) {   // SWEEP_RHS: t = r - E vp
             const double* v = V.vp + 3 * size_t(pfirst + lpt);
             tt.x = rr.x - (jp[0].x * v[0] + jp[1].x * v[1] + jp[2].x * v[2]);
@@ -153,6 +194,8 @@ k_schur_rows(View V, RowSched S, const double* __restrict__ xin, double* __restr
         }
     } else {
         // ---- one point with more than TILE_OBS observations (rare): two passes, every observation is its own row ----
+        pdl_wait();
+        if (done_flag && *done_flag) return;
         const int o1 = o0 + n;
         const int p = pfirst;
         double v[3];
@@ -162,15 +205,20 @@ k_schur_rows(View V, RowSched S, const double* __restrict__ xin, double* __restr
                 const int c = V.obs_cam[o];
                 const double2* J = V.J2 + o;
                 double2 u = make_double2(0.0, 0.0);
+                double2 jc[6], jp[3];
+                load_jc<PK>(V, J, jc);
 #pragma unroll
-                for (int k = 0; k < 6; ++k) { const double2 j = ldg2(J + k * ld); const double xv = __ldg(xin + 6 * c + k); u.x += j.x * xv; u.y += j.y * xv; }
+                for (int k = 0; k < 6; ++k) { const double xv = __ldg(xin + 6 * c + k); u.x += jc[k].x * xv; u.y += jc[k].y * xv; }
                 if (FI) {
                     const int g = V.cam_group[c];
+                    double2 ji[4];
+                    load_ji<PK>(V, J, ji);
 #pragma unroll
-                    for (int k = 0; k < 4; ++k) { const double2 j = ldg2(J + (9 + k) * ld); const double xv = __ldg(xin + ioff + 4 * g + k); u.x += j.x * xv; u.y += j.y * xv; }
+                    for (int k = 0; k < 4; ++k) { const double xv = __ldg(xin + ioff + 4 * g + k); u.x += ji[k].x * xv; u.y += ji[k].y * xv; }
                 }
+                load_jp<PK>(V, J, jp);
 #pragma unroll
-                for (int a = 0; a < 3; ++a) { const double2 j = ldg2(J + (6 + a) * ld); W[a] += j.x * u.x + j.y * u.y; }
+                for (int a = 0; a < 3; ++a) W[a] += jp[a].x * u.x + jp[a].y * u.y;
             }
 #pragma unroll
             for (int a = 0; a < 3; ++a) { const double s = block_sum(W[a], sred); if (threadIdx.x == 0) sV[0][a] = s; }
@@ -183,14 +231,10 @@ k_schur_rows(View V, RowSched S, const double* __restrict__ xin, double* __restr
             const int c = V.obs_cam[o];
             const int g = FI ? V.cam_group[c] : 0;
             const double2* J = V.J2 + o;
-            double2 jc[6], ji[4];
+            double2 jc[6], ji[4], jp[3];
             double2 u = make_double2(0.0, 0.0);
-#pragma unroll
-            for (int k = 0; k < 6; ++k) jc[k] = ldg2(J + k * ld);
-            if (FI) {
-#pragma unroll
-                for (int k = 0; k < 4; ++k) ji[k] = ldg2(J + (9 + k) * ld);
-            }
+            load_jc<PK>(V, J, jc);
+            if (FI) load_ji<PK>(V, J, ji);
             if (MODE == SWEEP_MATVEC) {
 #pragma unroll
                 for (int k = 0; k < 6; ++k) { const double xv = __ldg(xin + 6 * c + k); u.x += jc[k].x * xv; u.y += jc[k].y * xv; }
@@ -200,8 +244,9 @@ k_schur_rows(View V, RowSched S, const double* __restrict__ xin, double* __restr
                 }
             }
             double e0 = 0.0, e1 = 0.0;
+            load_jp<PK>(V, J, jp);
 #pragma unroll
-            for (int a = 0; a < 3; ++a) { const double2 j = ldg2(J + (6 + a) * ld); e0 += j.x * v[a]; e1 += j.y * v[a]; }
+            for (int a = 0; a < 3; ++a) { e0 += jp[a].x * v[a]; e1 += jp[a].y * v[a]; }
             double2 tt;
             if (MODE == SWEEP_MATVEC) { tt.x = u.x - e0; tt.y = u.y - e1; }
             else { const double2 r = V.r2[o]; tt.x = r.x - e0; tt.y = r.y - e1; }
@@ -224,52 +269,109 @@ k_schur_rows(View V, RowSched S, const double* __restrict__ xin, double* __restr
     }
 }
 
+// Sum of camera c's partial rows (static list, fixed order => bit-reproducible), by the whole CTA.  On return (after a CTA barrier)
+// sw[0][0..5] holds the 6-vector.
+// BA_GATHER_COOP (default): four adjacent lanes share one 64-byte row, lane k loading its k-th 16 bytes, so a warp instruction touches
+// 8 rows = 8 lines.  The first version gave every lane a whole row (3 LDG.128 to 32 different lines per instruction): 3 L1
+// wavefronts per row instead of 1, and ncu showed the kernel throttled by the load/store unit (lg_throttle 15, mio_throttle 12 per issue).
+#ifndef BA_GATHER_COOP
+#define BA_GATHER_COOP 1
+#endif
+__device__ __forceinline__ void camera_row_sum(const RowSched& S, int c, double (*sw)[6]) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int e = S.cam_row_off[c + 1];
+#if BA_GATHER_COOP
+    constexpr int NG = GATHER_WARPS * 8;          // 4-lane groups per CTA
+    const int sub = threadIdx.x & 3;
+    const double2* R2 = reinterpret_cast<const double2*>(S.rows);
+    double2 acc = make_double2(0.0, 0.0);
+    int i = S.cam_row_off[c] + (threadIdx.x >> 2);
+    if (sub < 3) {
+        for (; i + 7 * NG < e; i += 8 * NG) {     // eight rows per group and trip: 8 index loads, then 8 row loads in flight per lane
+            int id[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) id[k] = __ldg(S.cam_rows + i + k * NG);
+            double2 v[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) v[k] = __ldcg(R2 + size_t(ROW_DOUBLES / 2) * id[k] + sub);
+            acc.x += ((v[0].x + v[1].x) + (v[2].x + v[3].x)) + ((v[4].x + v[5].x) + (v[6].x + v[7].x));
+            acc.y += ((v[0].y + v[1].y) + (v[2].y + v[3].y)) + ((v[4].y + v[5].y) + (v[6].y + v[7].y));
+        }
+        for (; i < e; i += NG) {
+            const double2 v = __ldcg(R2 + size_t(ROW_DOUBLES / 2) * __ldg(S.cam_rows + i) + sub);
+            acc.x += v.x; acc.y += v.y;
+        }
+    }
+    // the 8 groups of a warp (lanes with equal sub), fixed tree
+#pragma unroll
+    for (int off = 4; off < 32; off <<= 1) { acc.x += __shfl_xor_sync(0xffffffffu, acc.x, off); acc.y += __shfl_xor_sync(0xffffffffu, acc.y, off); }
+    __shared__ double swp[GATHER_WARPS][6];
+    if (lane < 3) { swp[wid][2 * lane] = acc.x; swp[wid][2 * lane + 1] = acc.y; }
+    __syncthreads();
+    if (threadIdx.x < 6) {
+        double v = 0.0;
+#pragma unroll
+        for (int w = 0; w < GATHER_WARPS; ++w) v += swp[w][threadIdx.x];
+        sw[0][threadIdx.x] = v;
+    }
+    __syncthreads();
+#else
+    double s0 = 0, s1 = 0, s2 = 0, s3 = 0, s4 = 0, s5 = 0;
+    // four independent rows per thread and trip: 4 index loads, then 12 row loads in flight
+    constexpr int NT = GATHER_WARPS * 32;
+    int i = S.cam_row_off[c] + threadIdx.x;
+    for (; i + 3 * NT < e; i += 4 * NT) {
+        const int i0 = S.cam_rows[i], i1 = S.cam_rows[i + NT], i2 = S.cam_rows[i + 2 * NT], i3 = S.cam_rows[i + 3 * NT];
+        const double2* r0 = reinterpret_cast<const double2*>(S.rows + size_t(ROW_DOUBLES) * i0);
+        const double2* r1 = reinterpret_cast<const double2*>(S.rows + size_t(ROW_DOUBLES) * i1);
+        const double2* r2 = reinterpret_cast<const double2*>(S.rows + size_t(ROW_DOUBLES) * i2);
+        const double2* r3 = reinterpret_cast<const double2*>(S.rows + size_t(ROW_DOUBLES) * i3);
+        const double2 a0 = __ldcg(r0), b0 = __ldcg(r0 + 1), c0 = __ldcg(r0 + 2);
+        const double2 a1 = __ldcg(r1), b1 = __ldcg(r1 + 1), c1 = __ldcg(r1 + 2);
+        const double2 a2 = __ldcg(r2), b2 = __ldcg(r2 + 1), c2 = __ldcg(r2 + 2);
+        const double2 a3 = __ldcg(r3), b3 = __ldcg(r3 + 1), c3 = __ldcg(r3 + 2);
+        s0 += (a0.x + a1.x) + (a2.x + a3.x); s1 += (a0.y + a1.y) + (a2.y + a3.y);
+        s2 += (b0.x + b1.x) + (b2.x + b3.x); s3 += (b0.y + b1.y) + (b2.y + b3.y);
+        s4 += (c0.x + c1.x) + (c2.x + c3.x); s5 += (c0.y + c1.y) + (c2.y + c3.y);
+    }
+    for (; i < e; i += NT) {
+        const double2* row = reinterpret_cast<const double2*>(S.rows + size_t(ROW_DOUBLES) * S.cam_rows[i]);
+        const double2 a = __ldcg(row), bq = __ldcg(row + 1), cq = __ldcg(row + 2);
+        s0 += a.x; s1 += a.y; s2 += bq.x; s3 += bq.y; s4 += cq.x; s5 += cq.y;
+    }
+    s0 = warp_sum(s0); s1 = warp_sum(s1); s2 = warp_sum(s2); s3 = warp_sum(s3); s4 = warp_sum(s4); s5 = warp_sum(s5);
+    __shared__ double swp[GATHER_WARPS][6];
+    if (lane == 0) { swp[wid][0] = s0; swp[wid][1] = s1; swp[wid][2] = s2; swp[wid][3] = s3; swp[wid][4] = s4; swp[wid][5] = s5; }
+    __syncthreads();
+    if (threadIdx.x < 6) {
+        double v = 0.0;
+#pragma unroll
+        for (int w = 0; w < GATHER_WARPS; ++w) v += swp[w][threadIdx.x];
+        sw[0][threadIdx.x] = v;
+    }
+    __syncthreads();
+#endif
+}
+
 // K5b — y[c] = sum of camera c's partial rows: one 4-warp CTA per camera, lanes stride the static row list, fixed combine
 // order; with do_dot: q = y + Df2 p stored in y, one p.q partial per CTA, last CTA forms alpha = rho / p.q  (PcgState2).
 // CTA `Nc` (the last) reduces the per-tile intrinsics partials instead (free intrinsics, single group).
-constexpr int GATHER_WARPS = 4;
 __global__ void __launch_bounds__(GATHER_WARPS * 32)
 k_camera_gather(int Nc, int Ng, int fi, int nTiles, RowSched S, const double* __restrict__ Df2, const double* __restrict__ p,
                 double* __restrict__ y, double* __restrict__ partial, PcgState2* __restrict__ st, int do_dot) {
     __shared__ double sw[GATHER_WARPS][6];
     __shared__ bool last;
+    pdl_trigger();
+    pdl_wait();
     if (st && st->done) return;   // PCG already stopped inside this batch of launches
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int ioff = 6 * Nc;
     double dot = 0.0;
     const int c = blockIdx.x;
     if (c < Nc) {
-        double s0 = 0, s1 = 0, s2 = 0, s3 = 0, s4 = 0, s5 = 0;
-        // four independent rows per thread and trip: 4 index loads, then 12 row loads in flight
-        constexpr int NT = GATHER_WARPS * 32;
-        const int e = S.cam_row_off[c + 1];
-        int i = S.cam_row_off[c] + threadIdx.x;
-        for (; i + 3 * NT < e; i += 4 * NT) {
-            const int i0 = S.cam_rows[i], i1 = S.cam_rows[i + NT], i2 = S.cam_rows[i + 2 * NT], i3 = S.cam_rows[i + 3 * NT];
-            const double2* r0 = reinterpret_cast<const double2*>(S.rows + size_t(ROW_DOUBLES) * i0);
-            const double2* r1 = reinterpret_cast<const double2*>(S.rows + size_t(ROW_DOUBLES) * i1);
-            const double2* r2 = reinterpret_cast<const double2*>(S.rows + size_t(ROW_DOUBLES) * i2);
-            const double2* r3 = reinterpret_cast<const double2*>(S.rows + size_t(ROW_DOUBLES) * i3);
-            const double2 a0 = __ldcg(r0), b0 = __ldcg(r0 + 1), c0 = __ldcg(r0 + 2);
-            const double2 a1 = __ldcg(r1), b1 = __ldcg(r1 + 1), c1 = __ldcg(r1 + 2);
-            const double2 a2 = __ldcg(r2), b2 = __ldcg(r2 + 1), c2 = __ldcg(r2 + 2);
-            const double2 a3 = __ldcg(r3), b3 = __ldcg(r3 + 1), c3 = __ldcg(r3 + 2);
-            s0 += (a0.x + a1.x) + (a2.x + a3.x); s1 += (a0.y + a1.y) + (a2.y + a3.y);
-            s2 += (b0.x + b1.x) + (b2.x + b3.x); s3 += (b0.y + b1.y) + (b2.y + b3.y);
-            s4 += (c0.x + c1.x) + (c2.x + c3.x); s5 += (c0.y + c1.y) + (c2.y + c3.y);
-        }
-        for (; i < e; i += NT) {
-            const double2* row = reinterpret_cast<const double2*>(S.rows + size_t(ROW_DOUBLES) * S.cam_rows[i]);
-            const double2 a = __ldcg(row), bq = __ldcg(row + 1), cq = __ldcg(row + 2);
-            s0 += a.x; s1 += a.y; s2 += bq.x; s3 += bq.y; s4 += cq.x; s5 += cq.y;
-        }
-        s0 = warp_sum(s0); s1 = warp_sum(s1); s2 = warp_sum(s2); s3 = warp_sum(s3); s4 = warp_sum(s4); s5 = warp_sum(s5);
-        if (lane == 0) { sw[wid][0] = s0; sw[wid][1] = s1; sw[wid][2] = s2; sw[wid][3] = s3; sw[wid][4] = s4; sw[wid][5] = s5; }
-        __syncthreads();
+        camera_row_sum(S, c, sw);
         if (threadIdx.x < 6) {
-            double v = 0.0;
-#pragma unroll
-            for (int w = 0; w < GATHER_WARPS; ++w) v += sw[w][threadIdx.x];
+            double v = sw[0][threadIdx.x];
             const int j = 6 * c + threadIdx.x;
             if (do_dot) { const double pj = p[j]; v += Df2[j] * pj; dot = pj * v; }
             y[j] = v;

@@ -164,7 +164,7 @@ k_schur_rows_pipe(View V, RowSched S, const double* __restrict__ xin, double* __
                 const double2* H = reinterpret_cast<const double2*>(V.Hinv + 6 * size_t(pfirst + threadIdx.x));
                 h0 = __ldg(H); h1 = __ldg(H + 1); h2 = __ldg(H + 2);
             }
-            const int c = tm.x;
+            const int c = tm.x & 0xffffff;
             const int slot = tm.y & 0xff, n1 = (tm.y >> 8) & 0xff, hrank = (tm.y >> 16) & 0xff, lpt = (tm.y >> 24) & 0xff;
             const int pk = tm.z;
             const int g = (FI && act) ? V.cam_group[c] : 0;
