@@ -52,6 +52,9 @@ thread_local std::string g_create_error;
 
 struct BaFail { int code; std::string msg; };
 #define KL(eng) (++(eng)->kernel_launches)   // every kernel launch is counted (reported in ba_summary.kernel_launches)
+#ifndef BA_FUSE_DEFAULT
+#define BA_FUSE_DEFAULT 0
+#endif
 #ifndef BA_JPACK_DEFAULT
 #define BA_JPACK_DEFAULT 1
 #endif
@@ -187,6 +190,8 @@ struct ba_engine {
     DevBuf<double> d_redpart;          // [kRedSlices][ldf] stage-1 output of the copy reduction
     // mode 4: per-(tile, camera) partial rows + by-camera gather (ba_rows.cuh)
     DevBuf<int4> d_tmeta, d_tile_info;
+    DevBuf<int> d_cam_cnt, d_zero_cams; // fused gather: rows delivered per camera (zero between launches); cameras without rows
+    int fuse_gather = 0;
     DevBuf<int> d_cam_row_off, d_cam_rows;
     DevBuf<double> d_rows, d_tile_intr;
     bak::RowSched RS{};
@@ -606,6 +611,16 @@ void do_set_problem(ba_engine* e, const ba_problem* P, const DevState* dev = nul
         bak::RowSched& RS = e->RS;
         RS.tmeta = e->d_tmeta.p; RS.tile_info = e->d_tile_info.p;
         RS.rows = e->d_rows.p; RS.tile_intr = e->d_tile_intr.p; RS.cam_row_off = e->d_cam_row_off.p; RS.cam_rows = e->d_cam_rows.p; RS.nRows = nRows;
+        // fused by-camera gather (ba_rows.cuh): pose-only reduced systems (intrinsics fixed) with the rows scatter
+        e->fuse_gather = (BA_FUSE_DEFAULT && !e->fi && e->scatter_mode == 4) ? 1 : 0;
+        if (const char* v = std::getenv("BA_FUSE")) e->fuse_gather = (std::atoi(v) && !e->fi && e->scatter_mode == 4) ? 1 : 0;
+        e->d_cam_cnt.alloc(size_t(std::max(Nc, 1))); e->d_cam_cnt.zero(s);
+        CU_TRY(cudaStreamSynchronize(s));
+        vector<int32_t> zc;
+        for (int c = 0; c < Nc; ++c) if (cro[c + 1] == cro[c]) zc.push_back(c);
+        e->d_zero_cams.upload(zc.data(), zc.size(), s);
+        CU_TRY(cudaStreamSynchronize(s));
+        RS.cam_cnt = e->d_cam_cnt.p; RS.zero_cams = e->d_zero_cams.p; RS.n_zero = int(zc.size()); RS.fuse = e->fuse_gather;
     }
     e->d_slot.upload(slot.data(), No, s);
     e->d_spack.upload(spack.data(), No, s);
@@ -708,6 +723,10 @@ void do_set_problem(ba_engine* e, const ba_problem* P, const DevState* dev = nul
         e->stats[KID_K4].bytes = no * (jb + 16 + 16) + np * 24 + 64 * nr + 16.0 * e->nTiles;
         e->stats[KID_K5].bytes = no * (jb + 16) + np * 48 + 48 * nc + 64 * nr + 16.0 * e->nTiles;
         e->stats[KID_PCGV].bytes = 68 * nr + double(e->nf) * 8 * 12 + 288 * nc;
+        if (e->fuse_gather) {   // the by-camera gather (row and row-list reads, y stores) runs inside K4/K5a
+            e->stats[KID_K4].bytes += 68 * nr + 48 * nc; e->stats[KID_K5].bytes += 68 * nr + 48 * nc;
+            e->stats[KID_PCGV].bytes -= 68 * nr;
+        }
     }
 }
 
@@ -846,7 +865,10 @@ void launch_rows_pipe(ba_engine* e, const double* xin, double* yout, const int* 
 template <int MODE>
 void launch_scatter(ba_engine* e, int kid, const double* xin, double* yout, const int* done, int* G_out) {
     *G_out = 0;
-    if (e->nTiles == 0) return;
+    if (e->nTiles == 0) {   // a rank without observations: the fused gather has nobody to store its (zero) result
+        if (e->fuse_gather && e->scatter_mode == 4) CU_TRY(cudaMemsetAsync(yout, 0, size_t(6) * e->Nc * sizeof(double), e->stream));
+        return;
+    }
     if (e->scatter_mode == 1) { launch_sweep<MODE>(e, kid, xin, yout, done, nullptr); return; }
     const bool sample = kid != KID_K5 || e->stats[KID_K5].launches % e->k5_sample_stride == 0;
     LaunchTimer t(e, kid, sample);
@@ -907,7 +929,8 @@ int solve_linear(ba_engine* e, double radius, double* rel_out, double lambda = 0
     launch_scatter<bak::SWEEP_RHS>(e, KID_K4, nullptr, e->d_b.p, nullptr, &G);
     const bool rowsm = e->scatter_mode >= 4;
     const int gblocks = e->Nc + 1;
-    if (rowsm) { LaunchTimer t(e, KID_PCGV);
+    if (rowsm && e->fuse_gather) {   // K4 delivered b itself (fused gather)
+    } else if (rowsm) { LaunchTimer t(e, KID_PCGV);
         KL(e), bak::k_camera_gather<<<gblocks, bak::GATHER_WARPS * 32, 0, s>>>(e->Nc, e->Ng, e->fi, e->nTiles, e->RS, nullptr, nullptr, e->d_b.p, nullptr, nullptr, 0);
     } else if (priv) { LaunchTimer t(e, KID_PCGV);
         double* src; int nsrc; reduce_src(G, nullptr, src, nsrc);
@@ -957,12 +980,20 @@ int solve_linear(ba_engine* e, double radius, double* rel_out, double lambda = 0
     for (;;) {
         for (int i = 0; i < batch; ++i) {
             const bool sample = e->stats[KID_K5].launches % e->k5_sample_stride == 0;
-            launch_scatter<bak::SWEEP_MATVEC>(e, KID_K5, e->d_p.p, e->d_y.p, &sc->pcg.done, &G);
+            double* ydst = e->d_y.p;
+            if (rowsm && e->fuse_gather && multi && e->p2p.on) {   // fused gather writes straight into this rank's exchange slot
+                ta.seq = ++e->p2p.seq; ta.P = e->p2p.view;
+                ydst = e->p2p.view.data[e->p2p.view.rank] + size_t(ta.seq & 1u) * e->p2p.view.ldf;
+            }
+            launch_scatter<bak::SWEEP_MATVEC>(e, KID_K5, e->d_p.p, ydst, &sc->pcg.done, &G);
             LaunchTimer t(e, KID_PCGV, sample);
             double* src = nullptr; int nsrc = 0;
             // y (and, on one GPU, q = y + Df2 p and alpha) from the scatter mode's own reduction; tail.mode says what is left to do
             ta.mode = 0;
-            if (rowsm) {
+            if (rowsm && e->fuse_gather) {
+                if (multi && e->p2p.on) ta.mode = 2;
+                else { if (multi) allreduce_sum(e, e->d_y.p, e->nf); ta.mode = 1; }
+            } else if (rowsm) {
                 if (multi && e->p2p.on) {   // one-shot NVLink all-reduce: local gather + flags here, the pull and the sum inside the tail (ba_p2p.cuh)
                     ta.seq = ++e->p2p.seq; ta.P = e->p2p.view; ta.mode = 2;
                     launch_chain(e, bak::k_camera_gather_push, dim3(gblocks), dim3(bak::GATHER_WARPS * 32), e->Nc, e->Ng, e->fi, e->nTiles, e->RS, e->d_y.p, e->p2p.view, ta.seq, &sc->pcg, 1);

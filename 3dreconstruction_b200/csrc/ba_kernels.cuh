@@ -57,6 +57,29 @@ struct View {
 };
 
 __device__ __forceinline__ double2 ldg2(const double2* p) { return __ldg(p); }
+// Read-once streams (J columns, schedule records): do not allocate in L1, so the 85 KB search direction the same kernel gathers by
+// camera stays L1-resident instead of being evicted by 900 MB of streaming data.  BA_J_NOALLOC=0 restores plain ld.global.nc.
+#ifndef BA_J_NOALLOC
+#define BA_J_NOALLOC 0
+#endif
+__device__ __forceinline__ double2 ldg2s(const double2* p) {
+#if BA_J_NOALLOC
+    double2 v;
+    asm volatile("ld.global.nc.L1::no_allocate.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "l"(p));
+    return v;
+#else
+    return __ldg(p);
+#endif
+}
+__device__ __forceinline__ int4 ldg4s(const int4* p) {
+#if BA_J_NOALLOC
+    int4 v;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.s32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+    return v;
+#else
+    return __ldg(p);
+#endif
+}
 
 // The Jacobian columns of observation o (J = V.J2 + o, column stride V.ldo).  Pinhole model (ReprojectCost, BundleAdjuster.h:55-62):
 // u depends on P only through (Px, Pz) and v through (Py, Pz), so d(r0)/d(ty) = d(r1)/d(tx) = 0 exactly; with V.jpack the translation
@@ -67,23 +90,23 @@ template <int PK = -1>
 __device__ __forceinline__ void load_jc(const View& V, const double2* __restrict__ J, double2 (&jc)[6]) {
     const size_t ld = V.ldo;
     const bool pk = PK < 0 ? V.jpack != 0 : PK != 0;
-    jc[0] = ldg2(J); jc[1] = ldg2(J + ld); jc[2] = ldg2(J + 2 * ld);
-    const double2 d = ldg2(J + 3 * ld);
-    if (pk) { jc[3] = make_double2(d.x, 0.0); jc[4] = make_double2(0.0, d.y); jc[5] = ldg2(J + 4 * ld); }
-    else { jc[3] = d; jc[4] = ldg2(J + 4 * ld); jc[5] = ldg2(J + 5 * ld); }
+    jc[0] = ldg2s(J); jc[1] = ldg2s(J + ld); jc[2] = ldg2s(J + 2 * ld);
+    const double2 d = ldg2s(J + 3 * ld);
+    if (pk) { jc[3] = make_double2(d.x, 0.0); jc[4] = make_double2(0.0, d.y); jc[5] = ldg2s(J + 4 * ld); }
+    else { jc[3] = d; jc[4] = ldg2s(J + 4 * ld); jc[5] = ldg2s(J + 5 * ld); }
 }
 template <int PK = -1>
 __device__ __forceinline__ void load_jp(const View& V, const double2* __restrict__ J, double2 (&jp)[3]) {
     const int pk = PK < 0 ? V.jpack : PK;
     const double2* Jp = J + size_t(6 - pk) * V.ldo;
-    jp[0] = ldg2(Jp); jp[1] = ldg2(Jp + V.ldo); jp[2] = ldg2(Jp + 2 * size_t(V.ldo));
+    jp[0] = ldg2s(Jp); jp[1] = ldg2s(Jp + V.ldo); jp[2] = ldg2s(Jp + 2 * size_t(V.ldo));
 }
 template <int PK = -1>
 __device__ __forceinline__ void load_ji(const View& V, const double2* __restrict__ J, double2 (&ji)[4]) {
     const int pk = PK < 0 ? V.jpack : PK;
     const double2* Ji = J + size_t(9 - pk) * V.ldo;
 #pragma unroll
-    for (int k = 0; k < 4; ++k) ji[k] = ldg2(Ji + size_t(k) * V.ldo);
+    for (int k = 0; k < 4; ++k) ji[k] = ldg2s(Ji + size_t(k) * V.ldo);
 }
 
 __device__ __forceinline__ void red_add(double* addr, double v) {
@@ -746,7 +769,7 @@ k_schur_sweep(View V, const double* __restrict__ xin, double* __restrict__ yout,
 // Gathers the by-observation records K1 wrote (JcA: Jc, r [, Ji] in 128 / 192 contiguous bytes = whole sectors) through
 // perm_by_cam.  (v1 gathered the SoA columns: 7 separate 16-byte pieces per observation, 3.1x DRAM over-fetch.)  
 #ifndef BA_K2C_COOP
-#define BA_K2C_COOP 1
+#define BA_K2C_COOP 0   // measured on the Venice shape: 296 us against 185 us for the one-record-per-lane version below: the 28 shuffles per record cost more than the 6 L1 wavefronts they save
 #endif
 #if BA_K2C_COOP
 // 8 adjacent lanes (16 with free intrinsics) share one record: lane k loads its k-th 16 bytes, so a warp instruction reads 4 (2)

@@ -32,8 +32,100 @@ struct RowSched {
     const int* cam_row_off;       // [Nc+1]
     const int* cam_rows;          // [nRows] compact row ids, ascending
     int nRows;
+    // fused gather (BA_K5A_FUSE): rows delivered so far per camera; the CTA that delivers a camera's last row sums them all
+    int* cam_cnt;                 // [Nc], zero between launches (the summing CTA resets its camera)
+    const int* zero_cams;         // cameras without any row on this rank (nobody delivers them): CTA 0 stores their zeros
+    int n_zero;
+    int fuse;
 };
 
+// Sum of camera c's partial rows (static list, fixed order => bit-reproducible), by the whole CTA.  On return (after a CTA barrier)
+// sw[0][0..5] holds the 6-vector.
+// BA_GATHER_COOP (default): four adjacent lanes share one 64-byte row, lane k loading its k-th 16 bytes, so a warp instruction touches
+// 8 rows = 8 lines.  The first version gave every lane a whole row (3 LDG.128 to 32 different lines per instruction): 3 L1
+// wavefronts per row instead of 1, and ncu showed the kernel throttled by the load/store unit (lg_throttle 15, mio_throttle 12 per issue).
+#ifndef BA_GATHER_COOP
+#define BA_GATHER_COOP 1
+#endif
+__device__ __forceinline__ void camera_row_sum(const RowSched& S, int c, double (*sw)[6]) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int e = S.cam_row_off[c + 1];
+#if BA_GATHER_COOP
+    constexpr int NG = GATHER_WARPS * 8;          // 4-lane groups per CTA
+    const int sub = threadIdx.x & 3;
+    const double2* R2 = reinterpret_cast<const double2*>(S.rows);
+    double2 acc = make_double2(0.0, 0.0);
+    int i = S.cam_row_off[c] + (threadIdx.x >> 2);
+    if (sub < 3) {
+        for (; i + 7 * NG < e; i += 8 * NG) {     // eight rows per group and trip: 8 index loads, then 8 row loads in flight per lane
+            int id[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) id[k] = __ldg(S.cam_rows + i + k * NG);
+            double2 v[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) v[k] = __ldcg(R2 + size_t(ROW_DOUBLES / 2) * id[k] + sub);
+            acc.x += ((v[0].x + v[1].x) + (v[2].x + v[3].x)) + ((v[4].x + v[5].x) + (v[6].x + v[7].x));
+            acc.y += ((v[0].y + v[1].y) + (v[2].y + v[3].y)) + ((v[4].y + v[5].y) + (v[6].y + v[7].y));
+        }
+        for (; i < e; i += NG) {
+            const double2 v = __ldcg(R2 + size_t(ROW_DOUBLES / 2) * __ldg(S.cam_rows + i) + sub);
+            acc.x += v.x; acc.y += v.y;
+        }
+    }
+    // the 8 groups of a warp (lanes with equal sub), fixed tree
+#pragma unroll
+    for (int off = 4; off < 32; off <<= 1) { acc.x += __shfl_xor_sync(0xffffffffu, acc.x, off); acc.y += __shfl_xor_sync(0xffffffffu, acc.y, off); }
+    __shared__ double swp[GATHER_WARPS][6];
+    if (lane < 3) { swp[wid][2 * lane] = acc.x; swp[wid][2 * lane + 1] = acc.y; }
+    __syncthreads();
+    if (threadIdx.x < 6) {
+        double v = 0.0;
+#pragma unroll
+        for (int w = 0; w < GATHER_WARPS; ++w) v += swp[w][threadIdx.x];
+        sw[0][threadIdx.x] = v;
+    }
+    __syncthreads();
+#else
+    double s0 = 0, s1 = 0, s2 = 0, s3 = 0, s4 = 0, s5 = 0;
+    // four independent rows per thread and trip: 4 index loads, then 12 row loads in flight
+    constexpr int NT = GATHER_WARPS * 32;
+    int i = S.cam_row_off[c] + threadIdx.x;
+    for (; i + 3 * NT < e; i += 4 * NT) {
+        const int i0 = S.cam_rows[i], i1 = S.cam_rows[i + NT], i2 = S.cam_rows[i + 2 * NT], i3 = S.cam_rows[i + 3 * NT];
+        const double2* r0 = reinterpret_cast<const double2*>(S.rows + size_t(ROW_DOUBLES) * i0);
+        const double2* r1 = reinterpret_cast<const double2*>(S.rows + size_t(ROW_DOUBLES) * i1);
+        const double2* r2 = reinterpret_cast<const double2*>(S.rows + size_t(ROW_DOUBLES) * i2);
+        const double2* r3 = reinterpret_cast<const double2*>(S.rows + size_t(ROW_DOUBLES) * i3);
+        const double2 a0 = __ldcg(r0), b0 = __ldcg(r0 + 1), c0 = __ldcg(r0 + 2);
+        const double2 a1 = __ldcg(r1), b1 = __ldcg(r1 + 1), c1 = __ldcg(r1 + 2);
+        const double2 a2 = __ldcg(r2), b2 = __ldcg(r2 + 1), c2 = __ldcg(r2 + 2);
+        const double2 a3 = __ldcg(r3), b3 = __ldcg(r3 + 1), c3 = __ldcg(r3 + 2);
+        s0 += (a0.x + a1.x) + (a2.x + a3.x); s1 += (a0.y + a1.y) + (a2.y + a3.y);
+        s2 += (b0.x + b1.x) + (b2.x + b3.x); s3 += (b0.y + b1.y) + (b2.y + b3.y);
+        s4 += (c0.x + c1.x) + (c2.x + c3.x); s5 += (c0.y + c1.y) + (c2.y + c3.y);
+    }
+    for (; i < e; i += NT) {
+        const double2* row = reinterpret_cast<const double2*>(S.rows + size_t(ROW_DOUBLES) * S.cam_rows[i]);
+        const double2 a = __ldcg(row), bq = __ldcg(row + 1), cq = __ldcg(row + 2);
+        s0 += a.x; s1 += a.y; s2 += bq.x; s3 += bq.y; s4 += cq.x; s5 += cq.y;
+    }
+    s0 = warp_sum(s0); s1 = warp_sum(s1); s2 = warp_sum(s2); s3 = warp_sum(s3); s4 = warp_sum(s4); s5 = warp_sum(s5);
+    __shared__ double swp[GATHER_WARPS][6];
+    if (lane == 0) { swp[wid][0] = s0; swp[wid][1] = s1; swp[wid][2] = s2; swp[wid][3] = s3; swp[wid][4] = s4; swp[wid][5] = s5; }
+    __syncthreads();
+    if (threadIdx.x < 6) {
+        double v = 0.0;
+#pragma unroll
+        for (int w = 0; w < GATHER_WARPS; ++w) v += swp[w][threadIdx.x];
+        sw[0][threadIdx.x] = v;
+    }
+    __syncthreads();
+#endif
+}
+
+#ifndef BA_K5A_FUSE
+#define BA_K5A_FUSE 1          // compile the fused by-camera gather into K4/K5a (enabled at run time by RowSched::fuse)
+#endif
 #ifndef BA_K5A_MINB
 #define BA_K5A_MINB 6          // min CTAs/SM for ptxas: 6 = 80 registers, no spills (A/B knob: 7 and 8 cap the registers at 72 / 64)
 #endif
@@ -50,6 +142,36 @@ k_schur_rows(View V, RowSched S, const double* __restrict__ xin, double* __restr
     __shared__ double sV[TILE_OBS][3];
     __shared__ __align__(16) double sC[TILE_OBS][6];
     __shared__ double sred[32];
+#if BA_K5A_FUSE
+    __shared__ int s_ncomp, s_comp[TILE_OBS];
+    __shared__ double s_sw[1][6];
+    if (threadIdx.x == 0) s_ncomp = 0;      // several barriers before its first use
+    // A camera's total is complete when its last row has been delivered; the deliverer's CTA then adds the rows in the static
+    // order of the row list (so the sum does not depend on who does it) and stores the camera's 6-vector: the by-camera gather
+    // (K5b, ~36 us as a kernel of its own on the Venice shape) runs in the shadow of the streaming sweep.
+    auto deliver = [&](int cam) {
+        __threadfence();                                       // this thread's row first
+        const int total = __ldg(S.cam_row_off + cam + 1) - __ldg(S.cam_row_off + cam);
+        if (atomicAdd(S.cam_cnt + cam, 1) == total - 1) s_comp[atomicAdd(&s_ncomp, 1)] = cam;
+    };
+    auto finish = [&]() {                                      // whole CTA; between two CTA barriers
+        __syncthreads();
+        const int ncomp = s_ncomp;
+        for (int k = 0; k < ncomp; ++k) {
+            const int cam = s_comp[k];
+            __threadfence();
+            camera_row_sum(S, cam, s_sw);
+            if (threadIdx.x < 6) __stcg(atomic_out + 6 * size_t(cam) + threadIdx.x, s_sw[0][threadIdx.x]);
+            if (threadIdx.x == 0) S.cam_cnt[cam] = 0;
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) s_ncomp = 0;
+    };
+    auto zero_unseen = [&]() {                                 // after pdl_wait: the previous kernel of the chain wrote q over y
+        if (!FI && S.fuse && blockIdx.x == 0)
+            for (int i = threadIdx.x; i < 6 * S.n_zero; i += TILE_OBS) __stcg(atomic_out + 6 * size_t(S.zero_cams[i / 6]) + i % 6, 0.0);
+    };
+#endif
     pdl_trigger();
     const int t = blockIdx.x;
     const int4 ti = __ldg(S.tile_info + t);
@@ -65,7 +187,7 @@ k_schur_rows(View V, RowSched S, const double* __restrict__ xin, double* __restr
         int4 tm = make_int4(0, 0, -1, 0);
         double2 jc[6], jp[3], ji[4], rr = make_double2(0.0, 0.0);
         if (act) {
-            tm = __ldg(S.tmeta + o);
+            tm = ldg4s(S.tmeta + o);
             const double2* J = V.J2 + o;
             load_jc<PK>(V, J, jc);
             load_jp<PK>(V, J, jp);
@@ -81,6 +203,9 @@ k_schur_rows(View V, RowSched S, const double* __restrict__ xin, double* __restr
         // everything above is static during a linear solve; xin and the done flag are the predecessor's (PCG tail) output
         pdl_wait();
         if (done_flag && *done_flag) return;
+#if BA_K5A_FUSE
+        zero_unseen();
+#endif
         const int c = tm.x & 0xffffff, hp = int(unsigned(tm.x) >> 24);
         const int slot = tm.y & 0xff, n1 = (tm.y >> 8) & 0xff, hrank = (tm.y >> 16) & 0xff, lpt = (tm.y >> 24) & 0xff;
         const int pk = tm.z;
@@ -191,11 +316,20 @@ k_schur_rows(View V, RowSched S, const double* __restrict__ xin, double* __restr
             }
             double2* dst = reinterpret_cast<double2*>(S.rows + size_t(ROW_DOUBLES) * (hbase + hrank));
             __stcg(dst, a); __stcg(dst + 1, bq); __stcg(dst + 2, cq);
+#if BA_K5A_FUSE
+            if (!FI && S.fuse) deliver(pk & 0x3fffff);
+#endif
         }
+#if BA_K5A_FUSE
+        if (!FI && S.fuse) finish();
+#endif
     } else {
         // ---- one point with more than TILE_OBS observations (rare): two passes, every observation is its own row ----
         pdl_wait();
         if (done_flag && *done_flag) return;
+#if BA_K5A_FUSE
+        zero_unseen();
+#endif
         const int o1 = o0 + n;
         const int p = pfirst;
         double v[3];
@@ -227,7 +361,9 @@ k_schur_rows(View V, RowSched S, const double* __restrict__ xin, double* __restr
             const double w0 = sV[0][0], w1 = sV[0][1], w2 = sV[0][2];
             v[0] = H[0] * w0 + H[1] * w1 + H[2] * w2; v[1] = H[1] * w0 + H[3] * w1 + H[4] * w2; v[2] = H[2] * w0 + H[4] * w1 + H[5] * w2;
         } else { v[0] = V.vp[3 * size_t(p)]; v[1] = V.vp[3 * size_t(p) + 1]; v[2] = V.vp[3 * size_t(p) + 2]; }
-        for (int o = o0 + threadIdx.x; o < o1; o += TILE_OBS) {
+        for (int base = o0; base < o1; base += TILE_OBS) {
+          const int o = base + threadIdx.x;
+          if (o < o1) {
             const int c = V.obs_cam[o];
             const int g = FI ? V.cam_group[c] : 0;
             const double2* J = V.J2 + o;
@@ -261,96 +397,19 @@ k_schur_rows(View V, RowSched S, const double* __restrict__ xin, double* __restr
                     if (V.Ng > 1) red_add(atomic_out + ioff + 4 * g + k, contrib); else yi[k] += contrib;
                 }
             }
+#if BA_K5A_FUSE
+            if (!FI && S.fuse) deliver(c);
+#endif
+          }
+#if BA_K5A_FUSE
+          if (!FI && S.fuse) finish();
+#endif
         }
     }
     if (FI && V.Ng == 1) {   // one shared intrinsics group: per-tile partial, summed in tile order by k_camera_gather
 #pragma unroll
         for (int k = 0; k < 4; ++k) { const double s = block_sum(yi[k], sred); if (threadIdx.x == 0) S.tile_intr[4 * size_t(t) + k] = s; }
     }
-}
-
-// Sum of camera c's partial rows (static list, fixed order => bit-reproducible), by the whole CTA.  On return (after a CTA barrier)
-// sw[0][0..5] holds the 6-vector.
-// BA_GATHER_COOP (default): four adjacent lanes share one 64-byte row, lane k loading its k-th 16 bytes, so a warp instruction touches
-// 8 rows = 8 lines.  The first version gave every lane a whole row (3 LDG.128 to 32 different lines per instruction): 3 L1
-// wavefronts per row instead of 1, and ncu showed the kernel throttled by the load/store unit (lg_throttle 15, mio_throttle 12 per issue).
-#ifndef BA_GATHER_COOP
-#define BA_GATHER_COOP 1
-#endif
-__device__ __forceinline__ void camera_row_sum(const RowSched& S, int c, double (*sw)[6]) {
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const int e = S.cam_row_off[c + 1];
-#if BA_GATHER_COOP
-    constexpr int NG = GATHER_WARPS * 8;          // 4-lane groups per CTA
-    const int sub = threadIdx.x & 3;
-    const double2* R2 = reinterpret_cast<const double2*>(S.rows);
-    double2 acc = make_double2(0.0, 0.0);
-    int i = S.cam_row_off[c] + (threadIdx.x >> 2);
-    if (sub < 3) {
-        for (; i + 7 * NG < e; i += 8 * NG) {     // eight rows per group and trip: 8 index loads, then 8 row loads in flight per lane
-            int id[8];
-#pragma unroll
-            for (int k = 0; k < 8; ++k) id[k] = __ldg(S.cam_rows + i + k * NG);
-            double2 v[8];
-#pragma unroll
-            for (int k = 0; k < 8; ++k) v[k] = __ldcg(R2 + size_t(ROW_DOUBLES / 2) * id[k] + sub);
-            acc.x += ((v[0].x + v[1].x) + (v[2].x + v[3].x)) + ((v[4].x + v[5].x) + (v[6].x + v[7].x));
-            acc.y += ((v[0].y + v[1].y) + (v[2].y + v[3].y)) + ((v[4].y + v[5].y) + (v[6].y + v[7].y));
-        }
-        for (; i < e; i += NG) {
-            const double2 v = __ldcg(R2 + size_t(ROW_DOUBLES / 2) * __ldg(S.cam_rows + i) + sub);
-            acc.x += v.x; acc.y += v.y;
-        }
-    }
-    // the 8 groups of a warp (lanes with equal sub), fixed tree
-#pragma unroll
-    for (int off = 4; off < 32; off <<= 1) { acc.x += __shfl_xor_sync(0xffffffffu, acc.x, off); acc.y += __shfl_xor_sync(0xffffffffu, acc.y, off); }
-    __shared__ double swp[GATHER_WARPS][6];
-    if (lane < 3) { swp[wid][2 * lane] = acc.x; swp[wid][2 * lane + 1] = acc.y; }
-    __syncthreads();
-    if (threadIdx.x < 6) {
-        double v = 0.0;
-#pragma unroll
-        for (int w = 0; w < GATHER_WARPS; ++w) v += swp[w][threadIdx.x];
-        sw[0][threadIdx.x] = v;
-    }
-    __syncthreads();
-#else
-    double s0 = 0, s1 = 0, s2 = 0, s3 = 0, s4 = 0, s5 = 0;
-    // four independent rows per thread and trip: 4 index loads, then 12 row loads in flight
-    constexpr int NT = GATHER_WARPS * 32;
-    int i = S.cam_row_off[c] + threadIdx.x;
-    for (; i + 3 * NT < e; i += 4 * NT) {
-        const int i0 = S.cam_rows[i], i1 = S.cam_rows[i + NT], i2 = S.cam_rows[i + 2 * NT], i3 = S.cam_rows[i + 3 * NT];
-        const double2* r0 = reinterpret_cast<const double2*>(S.rows + size_t(ROW_DOUBLES) * i0);
-        const double2* r1 = reinterpret_cast<const double2*>(S.rows + size_t(ROW_DOUBLES) * i1);
-        const double2* r2 = reinterpret_cast<const double2*>(S.rows + size_t(ROW_DOUBLES) * i2);
-        const double2* r3 = reinterpret_cast<const double2*>(S.rows + size_t(ROW_DOUBLES) * i3);
-        const double2 a0 = __ldcg(r0), b0 = __ldcg(r0 + 1), c0 = __ldcg(r0 + 2);
-        const double2 a1 = __ldcg(r1), b1 = __ldcg(r1 + 1), c1 = __ldcg(r1 + 2);
-        const double2 a2 = __ldcg(r2), b2 = __ldcg(r2 + 1), c2 = __ldcg(r2 + 2);
-        const double2 a3 = __ldcg(r3), b3 = __ldcg(r3 + 1), c3 = __ldcg(r3 + 2);
-        s0 += (a0.x + a1.x) + (a2.x + a3.x); s1 += (a0.y + a1.y) + (a2.y + a3.y);
-        s2 += (b0.x + b1.x) + (b2.x + b3.x); s3 += (b0.y + b1.y) + (b2.y + b3.y);
-        s4 += (c0.x + c1.x) + (c2.x + c3.x); s5 += (c0.y + c1.y) + (c2.y + c3.y);
-    }
-    for (; i < e; i += NT) {
-        const double2* row = reinterpret_cast<const double2*>(S.rows + size_t(ROW_DOUBLES) * S.cam_rows[i]);
-        const double2 a = __ldcg(row), bq = __ldcg(row + 1), cq = __ldcg(row + 2);
-        s0 += a.x; s1 += a.y; s2 += bq.x; s3 += bq.y; s4 += cq.x; s5 += cq.y;
-    }
-    s0 = warp_sum(s0); s1 = warp_sum(s1); s2 = warp_sum(s2); s3 = warp_sum(s3); s4 = warp_sum(s4); s5 = warp_sum(s5);
-    __shared__ double swp[GATHER_WARPS][6];
-    if (lane == 0) { swp[wid][0] = s0; swp[wid][1] = s1; swp[wid][2] = s2; swp[wid][3] = s3; swp[wid][4] = s4; swp[wid][5] = s5; }
-    __syncthreads();
-    if (threadIdx.x < 6) {
-        double v = 0.0;
-#pragma unroll
-        for (int w = 0; w < GATHER_WARPS; ++w) v += swp[w][threadIdx.x];
-        sw[0][threadIdx.x] = v;
-    }
-    __syncthreads();
-#endif
 }
 
 // K5b — y[c] = sum of camera c's partial rows: one 4-warp CTA per camera, lanes stride the static row list, fixed combine
