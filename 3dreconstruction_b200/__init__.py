@@ -251,8 +251,10 @@ class Handle:
         self._check(self.lib.ba_linear_solver_in_use(self.h, C.byref(v)), "ba_linear_solver_in_use")
         return v.value
 
-    def set_profiling(self, mask):
-        """mask: False/0 off, True/1 every kernel, else a bit mask over kernel_stats() order."""
+    def set_profiling(self, mask, stride=1):
+        """mask: False/0 off, True/1 every kernel, else a bit mask over kernel_stats() order; stride: time every n-th launch of
+        the PCG-loop kernels only (events between launches serialise the chain's programmatic dependent launches)."""
+        self._check(self.lib.ba_set_profiling_stride(self.h, int(stride)), "ba_set_profiling_stride")
         self._check(self.lib.ba_set_profiling(self.h, int(mask)), "ba_set_profiling")
 
     def kernel_stats(self):

@@ -52,6 +52,9 @@ thread_local std::string g_create_error;
 
 struct BaFail { int code; std::string msg; };
 #define KL(eng) (++(eng)->kernel_launches)   // every kernel launch is counted (reported in ba_summary.kernel_launches)
+#ifndef BA_L2_PERSIST_DEFAULT
+#define BA_L2_PERSIST_DEFAULT 0
+#endif
 #ifndef BA_FUSE_DEFAULT
 #define BA_FUSE_DEFAULT 0
 #endif
@@ -219,6 +222,7 @@ struct ba_engine {
     int k5_sample_stride = 1;         // time every n-th K5 launch only (events between two launches serialise them; BA_K5_SAMPLE)
     int pdl = 0;                      // programmatic dependent launch along the PCG chain (BA_PDL)
     int jpack = 0;                    // packed translation columns of J (pinhole model)
+    bool l2_window = false;           // a persisting-L2 access-policy window for the partial rows is set on the stream
     struct Pending { int kid; cudaEvent_t a, b; };
     vector<Pending> pending;
     vector<cudaEvent_t> ev_pool;
@@ -606,6 +610,31 @@ void do_set_problem(ba_engine* e, const ba_problem* P, const DevState* dev = nul
         e->d_tmeta.upload(tmeta.data(), No, s); e->d_tile_info.upload(tinfo.data(), tinfo.size(), s);
         e->d_cam_row_off.upload(cro.data(), cro.size(), s); e->d_cam_rows.upload(crows.data(), nRows, s);
         e->d_rows.alloc(size_t(nRows) * bak::ROW_DOUBLES); e->d_rows.zero(s);
+        // The rows are written by K5a and read back by the gather a few microseconds later, every PCG iteration: ask L2 to keep them
+        // (persisting access-policy window on the engine's stream) so that they need not travel to HBM and back.  BA_L2_PERSIST=0 disables.
+        {
+            int on = BA_L2_PERSIST_DEFAULT;
+            if (const char* v = std::getenv("BA_L2_PERSIST")) on = std::atoi(v);
+            cudaDeviceProp prop{};
+            CU_TRY(cudaGetDeviceProperties(&prop, e->device));
+            const size_t bytes = size_t(nRows) * bak::ROW_DOUBLES * sizeof(double);
+            cudaStreamAttrValue attr{};
+            if (on && bytes > 0 && prop.persistingL2CacheMaxSize > 0) {
+                const size_t setaside = std::min<size_t>(prop.persistingL2CacheMaxSize, on > 1 ? size_t(on) << 20 : bytes);
+                CU_TRY(cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, setaside));
+                const size_t win = std::min<size_t>(bytes, size_t(prop.accessPolicyMaxWindowSize));
+                attr.accessPolicyWindow.base_ptr = e->d_rows.p;
+                attr.accessPolicyWindow.num_bytes = win;
+                attr.accessPolicyWindow.hitRatio = float(std::min(1.0, double(setaside) / double(win)));
+                attr.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+                attr.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+                e->l2_window = true;
+            } else {
+                attr.accessPolicyWindow.num_bytes = 0;
+                e->l2_window = false;
+            }
+            CU_TRY(cudaStreamSetAttribute(e->stream, cudaStreamAttributeAccessPolicyWindow, &attr));
+        }
         e->d_tile_intr.alloc(size_t(4) * std::max(e->nTiles, 1)); e->d_tile_intr.zero(s);
         CU_TRY(cudaStreamSynchronize(s));
         bak::RowSched& RS = e->RS;
@@ -720,12 +749,13 @@ void do_set_problem(ba_engine* e, const ba_problem* P, const DevState* dev = nul
     e->stats[KID_MISC].bytes = 0;
     if (e->scatter_mode >= 4) {   // partial-row formulation: + 7 B/obs of schedule, 64 B written per (tile, camera) row, read back by the gather
         const double nr = e->RS.nRows;
-        e->stats[KID_K4].bytes = no * (jb + 16 + 16) + np * 24 + 64 * nr + 16.0 * e->nTiles;
-        e->stats[KID_K5].bytes = no * (jb + 16) + np * 48 + 48 * nc + 64 * nr + 16.0 * e->nTiles;
-        e->stats[KID_PCGV].bytes = 68 * nr + double(e->nf) * 8 * 12 + 288 * nc;
+        const double rb = 8.0 * bak::ROW_DOUBLES;   // bytes per partial row as stored
+        e->stats[KID_K4].bytes = no * (jb + 16 + 16) + np * 24 + rb * nr + 16.0 * e->nTiles;
+        e->stats[KID_K5].bytes = no * (jb + 16) + np * 48 + 48 * nc + rb * nr + 16.0 * e->nTiles;
+        e->stats[KID_PCGV].bytes = (rb + 4) * nr + double(e->nf) * 8 * 12 + 288 * nc;
         if (e->fuse_gather) {   // the by-camera gather (row and row-list reads, y stores) runs inside K4/K5a
-            e->stats[KID_K4].bytes += 68 * nr + 48 * nc; e->stats[KID_K5].bytes += 68 * nr + 48 * nc;
-            e->stats[KID_PCGV].bytes -= 68 * nr;
+            e->stats[KID_K4].bytes += (rb + 4) * nr + 48 * nc; e->stats[KID_K5].bytes += (rb + 4) * nr + 48 * nc;
+            e->stats[KID_PCGV].bytes -= (rb + 4) * nr;
         }
     }
 }
@@ -1531,6 +1561,12 @@ int ba_set_profiling(ba_engine* e, int32_t enabled) {
     return BA_OK;
 }
 
+int ba_set_profiling_stride(ba_engine* e, int32_t stride) {
+    if (!e || stride < 1) return BA_ERR_INVALID_ARGUMENT;
+    e->k5_sample_stride = stride;
+    return BA_OK;
+}
+
 int ba_linear_solver_in_use(ba_engine* e, int32_t* solver) {
     if (!e || !solver) return BA_ERR_INVALID_ARGUMENT;
     if (!e->has_problem) return fail(e, BA_ERR_INVALID_ARGUMENT, "no problem set");
@@ -1583,6 +1619,12 @@ void ba_destroy(ba_engine* e) {
     if (!e) return;
     cudaSetDevice(e->device);
     if (e->stream) cudaStreamSynchronize(e->stream);
+    if (e->l2_window && e->stream) {   // a borrowed stream must not keep a window onto memory that is about to be freed
+        cudaStreamAttrValue attr{};
+        attr.accessPolicyWindow.num_bytes = 0;
+        cudaStreamSetAttribute(e->stream, cudaStreamAttributeAccessPolicyWindow, &attr);
+        cudaCtxResetPersistingL2Cache();
+    }
     teardown_p2p(e);
     if (e->comm) g_nccl.CommDestroy(e->comm);
     for (auto& p : e->pending) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }

@@ -42,19 +42,18 @@ __device__ __forceinline__ double ld_relaxed_sys_f64(const double* p) {   // hom
     return v;
 }
 
-__global__ void __launch_bounds__(GATHER_WARPS * 32)
+__global__ void __launch_bounds__(GATHER_WARPS * 32, BA_GATHER_MINB)
 k_camera_gather_push(int Nc, int Ng, int fi, int nTiles, RowSched S, const double* __restrict__ ylocal_rw, PeerView P, unsigned int seq,
                      PcgState2* __restrict__ st, int check_done) {
     __shared__ double sw[GATHER_WARPS][6];
     pdl_trigger();
-    pdl_wait();
-    if (check_done && st->done) return;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int ioff = 6 * Nc;
     double* const mine = P.data[P.rank] + size_t(seq & 1u) * P.ldf;
     const int c = blockIdx.x;
+    if (c >= Nc) { pdl_wait(); if (check_done && st->done) return; }
     if (c < Nc) {
-        camera_row_sum(S, c, sw);
+        if (!camera_row_sum<true>(S, c, sw, check_done ? &st->done : nullptr)) return;
         if (threadIdx.x < 3) {   // thread h: 16 bytes of this camera's 6-vector
             const int h = threadIdx.x;
             const double2 v = make_double2(sw[0][2 * h], sw[0][2 * h + 1]);

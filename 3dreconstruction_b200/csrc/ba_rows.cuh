@@ -13,7 +13,10 @@
 
 namespace bak {
 
-constexpr int ROW_DOUBLES = 8;    // 6 used; 64-byte rows = two full 32-byte sectors
+#ifndef BA_ROW_DOUBLES
+#define BA_ROW_DOUBLES 6
+#endif
+constexpr int ROW_DOUBLES = BA_ROW_DOUBLES;    // 6 used; 8: 64-byte rows = two full 32-byte sectors; 6: packed 48-byte rows (less to write, the gather still fetches two sectors per row)
 constexpr int L1_CHUNK = 8;       // level-1 chunk of the in-tile segmented sum
 constexpr int GATHER_WARPS = 4;   // warps per CTA of the by-camera gather (K5b)
 
@@ -47,25 +50,44 @@ struct RowSched {
 #ifndef BA_GATHER_COOP
 #define BA_GATHER_COOP 1
 #endif
-__device__ __forceinline__ void camera_row_sum(const RowSched& S, int c, double (*sw)[6]) {
+#ifndef BA_GATHER_UNR
+#define BA_GATHER_UNR 8        // rows in flight per lane
+#endif
+#ifndef BA_GATHER_MINB
+#define BA_GATHER_MINB 12      // min CTAs/SM of the gather kernels: 12 = 40 registers (16 with BA_GATHER_UNR=4 keeps all 1779 Venice CTAs resident at once)
+#endif
+// WAIT: the kernel is a link of the PDL chain; the row list (static) is read first, griddepcontrol.wait comes right before the rows.
+// Returns false (whole CTA, before any barrier) when *done says the PCG loop has already stopped.
+template <bool WAIT = false>
+__device__ __forceinline__ bool camera_row_sum(const RowSched& S, int c, double (*sw)[6], const int* done = nullptr) {
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int e = S.cam_row_off[c + 1];
 #if BA_GATHER_COOP
     constexpr int NG = GATHER_WARPS * 8;          // 4-lane groups per CTA
+    constexpr int UNR = BA_GATHER_UNR;
     const int sub = threadIdx.x & 3;
     const double2* R2 = reinterpret_cast<const double2*>(S.rows);
     double2 acc = make_double2(0.0, 0.0);
     int i = S.cam_row_off[c] + (threadIdx.x >> 2);
+    int id[UNR];
+    const bool full0 = i + (UNR - 1) * NG < e;
+    if (full0) {
+#pragma unroll
+        for (int k = 0; k < UNR; ++k) id[k] = __ldg(S.cam_rows + i + k * NG);
+    }
+    if (WAIT) { pdl_wait(); if (done && *done) return false; }
     if (sub < 3) {
-        for (; i + 7 * NG < e; i += 8 * NG) {     // eight rows per group and trip: 8 index loads, then 8 row loads in flight per lane
-            int id[8];
+        for (bool first = true; i + (UNR - 1) * NG < e; i += UNR * NG, first = false) {     // UNR rows per group and trip, all in flight
+            if (!first) {
 #pragma unroll
-            for (int k = 0; k < 8; ++k) id[k] = __ldg(S.cam_rows + i + k * NG);
-            double2 v[8];
+                for (int k = 0; k < UNR; ++k) id[k] = __ldg(S.cam_rows + i + k * NG);
+            }
+            double2 v[UNR];
 #pragma unroll
-            for (int k = 0; k < 8; ++k) v[k] = __ldcg(R2 + size_t(ROW_DOUBLES / 2) * id[k] + sub);
-            acc.x += ((v[0].x + v[1].x) + (v[2].x + v[3].x)) + ((v[4].x + v[5].x) + (v[6].x + v[7].x));
-            acc.y += ((v[0].y + v[1].y) + (v[2].y + v[3].y)) + ((v[4].y + v[5].y) + (v[6].y + v[7].y));
+            for (int k = 0; k < UNR; ++k) v[k] = __ldcg(R2 + size_t(ROW_DOUBLES / 2) * id[k] + sub);
+#pragma unroll
+            for (int k = 1; k < UNR; ++k) { v[0].x += v[k].x; v[0].y += v[k].y; }
+            acc.x += v[0].x; acc.y += v[0].y;
         }
         for (; i < e; i += NG) {
             const double2 v = __ldcg(R2 + size_t(ROW_DOUBLES / 2) * __ldg(S.cam_rows + i) + sub);
@@ -86,6 +108,7 @@ __device__ __forceinline__ void camera_row_sum(const RowSched& S, int c, double 
     }
     __syncthreads();
 #else
+    if (WAIT) { pdl_wait(); if (done && *done) return false; }
     double s0 = 0, s1 = 0, s2 = 0, s3 = 0, s4 = 0, s5 = 0;
     // four independent rows per thread and trip: 4 index loads, then 12 row loads in flight
     constexpr int NT = GATHER_WARPS * 32;
@@ -121,10 +144,12 @@ __device__ __forceinline__ void camera_row_sum(const RowSched& S, int c, double 
     }
     __syncthreads();
 #endif
+    return true;
 }
 
 #ifndef BA_K5A_FUSE
-#define BA_K5A_FUSE 1          // compile the fused by-camera gather into K4/K5a (enabled at run time by RowSched::fuse)
+#define BA_K5A_FUSE 0          // 1 / 2: compile the fused by-camera gather into K4/K5a (enabled at run time by RowSched::fuse). Measured on the
+                               // Venice shape: 1 (fence + counter per row) K5a 205 -> 315 us against the 37 us gather it replaces; 2 = one fence per CTA
 #endif
 #ifndef BA_K5A_MINB
 #define BA_K5A_MINB 6          // min CTAs/SM for ptxas: 6 = 80 registers, no spills (A/B knob: 7 and 8 cap the registers at 72 / 64)
@@ -150,7 +175,9 @@ k_schur_rows(View V, RowSched S, const double* __restrict__ xin, double* __restr
     // order of the row list (so the sum does not depend on who does it) and stores the camera's 6-vector: the by-camera gather
     // (K5b, ~36 us as a kernel of its own on the Venice shape) runs in the shadow of the streaming sweep.
     auto deliver = [&](int cam) {
+#if BA_K5A_FUSE == 1
         __threadfence();                                       // this thread's row first
+#endif
         const int total = __ldg(S.cam_row_off + cam + 1) - __ldg(S.cam_row_off + cam);
         if (atomicAdd(S.cam_cnt + cam, 1) == total - 1) s_comp[atomicAdd(&s_ncomp, 1)] = cam;
     };
@@ -316,10 +343,18 @@ k_schur_rows(View V, RowSched S, const double* __restrict__ xin, double* __restr
             }
             double2* dst = reinterpret_cast<double2*>(S.rows + size_t(ROW_DOUBLES) * (hbase + hrank));
             __stcg(dst, a); __stcg(dst + 1, bq); __stcg(dst + 2, cq);
-#if BA_K5A_FUSE
+#if BA_K5A_FUSE == 1
             if (!FI && S.fuse) deliver(pk & 0x3fffff);
 #endif
         }
+#if BA_K5A_FUSE == 2
+        if (!FI && S.fuse) {   // one fence for the whole CTA's rows (ordered before it by the barrier), then the counters
+            __syncthreads();
+            if (threadIdx.x == 0) __threadfence();
+            __syncthreads();
+            if (pk >= 0) deliver(pk & 0x3fffff);
+        }
+#endif
 #if BA_K5A_FUSE
         if (!FI && S.fuse) finish();
 #endif
@@ -397,10 +432,18 @@ k_schur_rows(View V, RowSched S, const double* __restrict__ xin, double* __restr
                     if (V.Ng > 1) red_add(atomic_out + ioff + 4 * g + k, contrib); else yi[k] += contrib;
                 }
             }
-#if BA_K5A_FUSE
+#if BA_K5A_FUSE == 1
             if (!FI && S.fuse) deliver(c);
 #endif
           }
+#if BA_K5A_FUSE == 2
+          if (!FI && S.fuse) {
+              __syncthreads();
+              if (threadIdx.x == 0) __threadfence();
+              __syncthreads();
+              if (o < o1) deliver(V.obs_cam[o]);
+          }
+#endif
 #if BA_K5A_FUSE
           if (!FI && S.fuse) finish();
 #endif
@@ -415,20 +458,19 @@ k_schur_rows(View V, RowSched S, const double* __restrict__ xin, double* __restr
 // K5b — y[c] = sum of camera c's partial rows: one 4-warp CTA per camera, lanes stride the static row list, fixed combine
 // order; with do_dot: q = y + Df2 p stored in y, one p.q partial per CTA, last CTA forms alpha = rho / p.q  (PcgState2).
 // CTA `Nc` (the last) reduces the per-tile intrinsics partials instead (free intrinsics, single group).
-__global__ void __launch_bounds__(GATHER_WARPS * 32)
+__global__ void __launch_bounds__(GATHER_WARPS * 32, BA_GATHER_MINB)
 k_camera_gather(int Nc, int Ng, int fi, int nTiles, RowSched S, const double* __restrict__ Df2, const double* __restrict__ p,
                 double* __restrict__ y, double* __restrict__ partial, PcgState2* __restrict__ st, int do_dot) {
     __shared__ double sw[GATHER_WARPS][6];
     __shared__ bool last;
     pdl_trigger();
-    pdl_wait();
-    if (st && st->done) return;   // PCG already stopped inside this batch of launches
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int ioff = 6 * Nc;
     double dot = 0.0;
     const int c = blockIdx.x;
+    if (c >= Nc) { pdl_wait(); if (st && st->done) return; }   // PCG already stopped inside this batch of launches
     if (c < Nc) {
-        camera_row_sum(S, c, sw);
+        if (!camera_row_sum<true>(S, c, sw, st ? &st->done : nullptr)) return;
         if (threadIdx.x < 6) {
             double v = sw[0][threadIdx.x];
             const int j = 6 * c + threadIdx.x;

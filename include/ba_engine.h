@@ -226,6 +226,9 @@ int  ba_get_structure(ba_engine* e, int32_t* perm_by_cam, int32_t* cam_off, int3
  * g[6Nc+4Ng+3Np] (pose, intrinsics, point order).  Any output may be NULL. For the K1/K2 parity tests. */
 int  ba_evaluate(ba_engine* e, double* cost, double* r, double* Jc, double* Jp, double* Ji, double* g);
 int  ba_set_profiling(ba_engine* e, int32_t mask);             /* per-kernel CUDA-event timing: 0 off (default), 1 or -1 all kernels, else bit k = kernel k of ba_get_kernel_stats */
+int  ba_set_profiling_stride(ba_engine* e, int32_t stride);    /* time only every stride-th launch of the PCG-loop kernels (K5, PCG vector part): an event
+                                                                 * between two launches serialises them, which would hide the programmatic dependent launch
+                                                                 * of the chain from the very measurement; ba_get_kernel_stats scales total_ms to all launches */
 int  ba_get_kernel_stats(ba_engine* e, ba_kernel_stat* out, int32_t cap, int32_t* n);
 int  ba_linear_solver_in_use(ba_engine* e, int32_t* solver);  /* after ba_set_problem: BA_LINEAR_EXACT or BA_LINEAR_PCG, what AUTO resolved to for this problem */
 int  ba_get_io_bytes(int64_t* h2d, int64_t* d2h);              /* cumulative host->device / device->host bytes moved by this library in this process */

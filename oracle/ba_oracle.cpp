@@ -905,6 +905,7 @@ int ba_evaluate(ba_engine* e, double* cost, double* r, double* Jc, double* Jp, d
 }
 
 int ba_set_profiling(ba_engine* e, int32_t) { return e ? BA_OK : BA_ERR_INVALID_ARGUMENT; }
+int ba_set_profiling_stride(ba_engine* e, int32_t stride) { return (e && stride >= 1) ? BA_OK : BA_ERR_INVALID_ARGUMENT; }
 int ba_get_kernel_stats(ba_engine* e, ba_kernel_stat*, int32_t, int32_t* n) { if (!e || !n) return BA_ERR_INVALID_ARGUMENT; *n = 0; return BA_OK; }
 int ba_linear_solver_in_use(ba_engine* e, int32_t* solver) { if (!e || !solver) return BA_ERR_INVALID_ARGUMENT; *solver = e->opt.linear_solver == BA_LINEAR_PCG ? BA_LINEAR_PCG : BA_LINEAR_EXACT; return BA_OK; }
 int ba_shard_points(int32_t, int32_t, const int32_t*, int32_t, int32_t*) { return BA_ERR_UNSUPPORTED; }   // engine-side host logic; the oracle is single-process
