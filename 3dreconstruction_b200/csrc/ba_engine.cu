@@ -17,6 +17,7 @@
 #include <algorithm>
 #include <cfloat>
 #include <cmath>
+#include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -127,6 +128,27 @@ struct DevBuf {
     ~DevBuf() { release(); }
 };
 
+// Page-locked std::vector storage for the host arrays ba_set_problem builds and uploads: kept in the engine between calls, so a call
+// neither page-faults its way through 150 MB of fresh allocations nor stages its uploads through the driver's bounce buffer.
+template <class T>
+struct PinnedAlloc {
+    using value_type = T;
+    PinnedAlloc() = default;
+    template <class U> PinnedAlloc(const PinnedAlloc<U>&) {}
+    T* allocate(size_t n) { void* p = nullptr; if (cudaMallocHost(&p, std::max<size_t>(n, 1) * sizeof(T)) != cudaSuccess) throw std::bad_alloc(); return static_cast<T*>(p); }
+    void deallocate(T* p, size_t) { cudaFreeHost(p); }
+    template <class U> bool operator==(const PinnedAlloc<U>&) const { return true; }
+    template <class U> bool operator!=(const PinnedAlloc<U>&) const { return false; }
+};
+template <class T> using pvec = std::vector<T, PinnedAlloc<T>>;
+
+struct HostScratch {   // ba_set_problem's work arrays (capacity survives between calls)
+    pvec<int4> tmeta;
+    pvec<int32_t> perm, obs_pt, crows;
+    std::vector<unsigned char> slot, lvl1, hrank, hpos;
+    std::vector<int32_t> spack, row_cam, hbase;
+};
+
 constexpr int kRedSlices = 8;      // stage-1 slices of the private-copy reduction (ba_pipe.cuh)
 enum KernelId { KID_K0 = 0, KID_K1, KID_K1C, KID_K2C, KID_K3P, KID_K3C, KID_K4, KID_K5, KID_K7, KID_K8, KID_PCGV, KID_MISC, KID_DFORM, KID_DCHOL, KID_COUNT };
 const char* const kKernelNames[KID_COUNT] = {"K0_camera_precompute", "K1_residual_jacobian", "K1c_candidate_cost", "K2c_camera_blocks",
@@ -193,6 +215,7 @@ struct ba_engine {
     DevBuf<double> d_redpart;          // [kRedSlices][ldf] stage-1 output of the copy reduction
     // mode 4: per-(tile, camera) partial rows + by-camera gather (ba_rows.cuh)
     DevBuf<int4> d_tmeta, d_tile_info;
+    HostScratch hs;
     DevBuf<int> d_cam_cnt, d_zero_cams; // fused gather: rows delivered per camera (zero between launches); cameras without rows
     int fuse_gather = 0;
     DevBuf<int> d_cam_row_off, d_cam_rows;
@@ -222,6 +245,7 @@ struct ba_engine {
     int k5_sample_stride = 1;         // time every n-th K5 launch only (events between two launches serialise them; BA_K5_SAMPLE)
     int pdl = 0;                      // programmatic dependent launch along the PCG chain (BA_PDL)
     int jpack = 0;                    // packed translation columns of J (pinhole model)
+    bool l2_window_ever = false;
     bool l2_window = false;           // a persisting-L2 access-policy window for the partial rows is set on the stream
     struct Pending { int kid; cudaEvent_t a, b; };
     vector<Pending> pending;
@@ -282,6 +306,26 @@ void allreduce_flags(ba_engine* e, int* buf, size_t n) {
 // Cut the point-sorted observation list [0,No) into tiles of whole points with <= TILE_OBS observations; a point with
 // more observations than that becomes a tile of its own (the kernels walk it in chunks).
 // Host threads over [0, n) in contiguous ranges (the per-tile schedule construction of ba_set_problem; ranges write disjoint slices).
+int host_threads() {
+    int nt = int(std::thread::hardware_concurrency());
+    if (const char* v = std::getenv("BA_HOST_THREADS")) nt = std::atoi(v);
+    return std::max(1, std::min(nt, 16));
+}
+// f(k, a, b) on nt host threads: chunk k of nt covers [a, b) of [0, n)
+template <class F>
+void parallel_chunks(int n, int nt, F&& f) {
+    if (nt <= 1) { f(0, 0, n); return; }
+    std::vector<std::thread> th;
+    std::exception_ptr err;
+    std::mutex mu;
+    for (int k = 0; k < nt; ++k) {
+        const int a = int(int64_t(n) * k / nt), b = int(int64_t(n) * (k + 1) / nt);
+        th.emplace_back([&, k, a, b] { try { f(k, a, b); } catch (...) { std::lock_guard<std::mutex> g(mu); err = std::current_exception(); } });
+    }
+    for (auto& t : th) t.join();
+    if (err) std::rethrow_exception(err);
+}
+
 template <class F>
 void parallel_ranges(int n, F&& f) {
     int nt = int(std::thread::hardware_concurrency());
@@ -493,7 +537,20 @@ void build_dense(ba_engine* e, const ba_problem* P, const vector<int32_t>& pt_of
 
 struct DevState { const double* pose; const double* intr; const double* pt; };   // device-resident parameters of the whole (merged) problem
 
+// BA_TIMING=1: host-side phase times of ba_set_problem on stderr (what separates bench.py's e2e from its HBM-resident value)
+struct PhaseTimer {
+    bool on = std::getenv("BA_TIMING") != nullptr;
+    std::chrono::steady_clock::time_point t = std::chrono::steady_clock::now();
+    void tick(const char* what) {
+        if (!on) return;
+        const auto n = std::chrono::steady_clock::now();
+        std::fprintf(stderr, "[ba_set_problem] %-28s %8.2f ms\n", what, std::chrono::duration<double, std::milli>(n - t).count());
+        t = n;
+    }
+};
+
 void do_set_problem(ba_engine* e, const ba_problem* P, const DevState* dev = nullptr) {
+    PhaseTimer pt_;
     const int Nc = P->num_cameras, Ng = P->num_groups, NpG = P->num_points, NoG = P->num_observations;
     const int W = e->opt.world_size, R = e->opt.rank;
     CU_TRY(cudaSetDevice(e->device));
@@ -501,17 +558,35 @@ void do_set_problem(ba_engine* e, const ba_problem* P, const DevState* dev = nul
     e->Nc = Nc; e->Ng = Ng; e->NpG = NpG; e->NoG = NoG;
     e->fi = e->opt.intrinsics_free ? 1 : 0;
     e->nf = 6 * Nc + (e->fi ? 4 * Ng : 0);
-    e->h_obs_cam.assign(P->obs_cam, P->obs_cam + NoG);
-    e->h_obs_pt.assign(P->obs_pt, P->obs_pt + NoG);
-    e->h_cam_fixed.assign(P->cam_fixed, P->cam_fixed + Nc);
-    e->h_cam_group.assign(P->cam_group, P->cam_group + Nc);
-    e->h_obs_uv.assign(P->obs_uv, P->obs_uv + size_t(2) * NoG);
+    // the engine's own copy of the index structure and pixels (ba_append merges into it): 120 MB on the Venice shape, copied by a
+    // helper thread while this one builds the schedule; joined before returning (the caller's arrays are only borrowed for the call)
+    struct Joiner { std::thread t; ~Joiner() { if (t.joinable()) t.join(); } } copier;
+    copier.t = std::thread([e, P, NoG, Nc] {
+        e->h_obs_cam.assign(P->obs_cam, P->obs_cam + NoG);
+        e->h_obs_pt.assign(P->obs_pt, P->obs_pt + NoG);
+        e->h_cam_fixed.assign(P->cam_fixed, P->cam_fixed + Nc);
+        e->h_cam_group.assign(P->cam_group, P->cam_group + Nc);
+        e->h_obs_uv.assign(P->obs_uv, P->obs_uv + size_t(2) * NoG);
+    });
 
-    // global CSR by point, global free masks
+    pt_.tick("host copies (append)");
+    // global CSR by point, global free masks.  The observations are sorted by point, so the offsets are the positions where the point id
+    // changes; the by-camera permutation is a stable counting sort with one histogram per host thread (chunks of observations in order).
+    const int nth = NoG >= (1 << 16) ? host_threads() : 1;
     vector<int32_t> gpt_off(size_t(NpG) + 1, 0);
     vector<int32_t> cam_cnt(Nc, 0);
-    for (int o = 0; o < NoG; ++o) { ++gpt_off[P->obs_pt[o] + 1]; ++cam_cnt[P->obs_cam[o]]; }
-    for (int p = 0; p < NpG; ++p) gpt_off[p + 1] += gpt_off[p];
+    parallel_chunks(NoG, nth, [&](int, int a, int b) {
+        for (int o = a; o < b; ++o) {
+            const int p0 = o ? P->obs_pt[o - 1] : -1, p1 = P->obs_pt[o];
+            for (int p = p0 + 1; p <= p1; ++p) gpt_off[p] = o;          // first observation of every point in (p0, p1]
+        }
+    });
+    for (int p = (NoG ? P->obs_pt[NoG - 1] : -1) + 1; p <= NpG; ++p) gpt_off[p] = NoG;
+    {
+        vector<int32_t> hist(size_t(nth) * std::max(Nc, 1), 0);
+        parallel_chunks(NoG, nth, [&](int k, int a, int b) { int32_t* h = hist.data() + size_t(k) * Nc; for (int o = a; o < b; ++o) ++h[P->obs_cam[o]]; });
+        for (int k = 0; k < nth; ++k) for (int c = 0; c < Nc; ++c) cam_cnt[c] += hist[size_t(k) * Nc + c];
+    }
     e->h_cam_free.assign(Nc, 0);
     vector<unsigned char> grp_free(std::max(Ng, 1), 0);
     for (int c = 0; c < Nc; ++c) {
@@ -528,32 +603,54 @@ void do_set_problem(ba_engine* e, const ba_problem* P, const DevState* dev = nul
     e->ldo = (No + 31) / 32 * 32 + 32;
 
     // local index arrays
-    vector<int32_t> pt_off(size_t(Np) + 1), obs_pt(No), tile_off, perm(No), cam_off(size_t(Nc) + 1, 0);
+    HostScratch& hs = e->hs;
+    vector<int32_t> pt_off(size_t(Np) + 1), tile_off, cam_off(size_t(Nc) + 1, 0);
+    pvec<int32_t>& obs_pt = hs.obs_pt; obs_pt.resize(std::max(No, 1));
+    pvec<int32_t>& perm = hs.perm; perm.resize(std::max(No, 1));
     for (int p = 0; p <= Np; ++p) pt_off[p] = gpt_off[e->pb + p] - e->ob;
-    for (int o = 0; o < No; ++o) { obs_pt[o] = P->obs_pt[e->ob + o] - e->pb; ++cam_off[P->obs_cam[e->ob + o] + 1]; }
-    for (int c = 0; c < Nc; ++c) cam_off[c + 1] += cam_off[c];
     {
-        vector<int32_t> cur(cam_off.begin(), cam_off.end() - 1);
-        for (int o = 0; o < No; ++o) perm[cur[P->obs_cam[e->ob + o]]++] = o;
+        const int nt2 = No >= (1 << 16) ? nth : 1;
+        vector<int32_t> hist(size_t(nt2) * std::max(Nc, 1), 0);
+        const int32_t* lcam = P->obs_cam + e->ob;
+        const int32_t* lpt = P->obs_pt + e->ob;
+        const int pb = e->pb;
+        parallel_chunks(No, nt2, [&](int k, int a, int b) {
+            int32_t* h = hist.data() + size_t(k) * Nc;
+            for (int o = a; o < b; ++o) { obs_pt[o] = lpt[o] - pb; ++h[lcam[o]]; }
+        });
+        for (int c = 0; c < Nc; ++c) {           // exclusive scan over (camera, chunk): chunk k's first slot of camera c
+            int32_t run = cam_off[c];
+            for (int k = 0; k < nt2; ++k) { const int32_t n = hist[size_t(k) * Nc + c]; hist[size_t(k) * Nc + c] = run; run += n; }
+            cam_off[c + 1] = run;
+        }
+        parallel_chunks(No, nt2, [&](int k, int a, int b) {
+            int32_t* cur = hist.data() + size_t(k) * Nc;
+            for (int o = a; o < b; ++o) perm[cur[lcam[o]]++] = o;
+        });
     }
+    pt_.tick("csr, shard, perm");
     build_tiles(pt_off, Np, tile_off);
     e->nTiles = int(tile_off.size()) - 1;
+    pt_.tick("tiles");
     // static scatter schedule: within each tile, the rank of every observation in camera-sorted (stable) order, and per
     // sorted position the camera + segment length at segment heads (ba_scatter.cuh)
-    vector<unsigned char> slot(No, 0);
-    vector<int32_t> spack(No, -1);
+    std::vector<unsigned char>& slot = hs.slot; slot.resize(std::max(No, 1));      // every entry is (re)written per tile below
+    std::vector<int32_t>& spack = hs.spack; spack.resize(std::max(No, 1));
     if (Nc >= (1 << 22)) throw BaFail{BA_ERR_UNSUPPORTED, "more than 4M cameras"};
     static_assert(bak::TILE_OBS <= 256, "tile positions are packed into 8 bits");
     const int32_t* ocam = P->obs_cam + e->ob;
     // mode-4 schedule: level-1 chunk counts, head ranks, compact row numbering and the by-camera row lists.  Tiles are independent:
     // pass A (host threads over tile ranges) sorts each tile by camera and counts its rows, a prefix sum numbers the rows, pass B fills.
     {
-        vector<unsigned char> lvl1(No, 0), hrank(No, 0), hpos(No, 0);
-        vector<int32_t> hbase(size_t(e->nTiles) + 1, 0), row_cam;
+        std::vector<unsigned char>&lvl1 = hs.lvl1, &hrank = hs.hrank, &hpos = hs.hpos;
+        lvl1.resize(std::max(No, 1)); hrank.resize(std::max(No, 1)); hpos.resize(std::max(No, 1));
+        std::vector<int32_t>&hbase = hs.hbase, &row_cam = hs.row_cam;
+        hbase.assign(size_t(e->nTiles) + 1, 0);
         parallel_ranges(e->nTiles, [&](int t0, int t1) {
             uint32_t key[bak::TILE_OBS];
             for (int t = t0; t < t1; ++t) {
                 const int o0 = tile_off[t], n = tile_off[t + 1] - o0;
+                for (int i = 0; i < n; ++i) { slot[o0 + i] = 0; spack[o0 + i] = -1; lvl1[o0 + i] = 0; hrank[o0 + i] = 0; hpos[o0 + i] = 0; }   // the arrays are reused between calls
                 if (n > bak::TILE_OBS) { hbase[t + 1] = n; continue; }   // long-point tile: one row per observation, no schedule
                 for (int i = 0; i < n; ++i) key[i] = uint32_t(ocam[o0 + i]) << 9 | uint32_t(i);   // unique keys: std::sort == stable sort by camera
                 std::sort(key, key + n);
@@ -585,12 +682,22 @@ void do_set_problem(ba_engine* e, const ba_problem* P, const DevState* dev = nul
             }
         });
         const int nRows = int(row_cam.size());
-        vector<int32_t> cro(size_t(Nc) + 1, 0), crows(nRows);
-        for (int r = 0; r < nRows; ++r) ++cro[row_cam[r] + 1];
-        for (int c = 0; c < Nc; ++c) cro[c + 1] += cro[c];
-        { vector<int32_t> cur(cro.begin(), cro.end() - 1); for (int r = 0; r < nRows; ++r) crows[cur[row_cam[r]]++] = r; }
+        vector<int32_t> cro(size_t(Nc) + 1, 0);
+        pvec<int32_t>& crows = hs.crows; crows.resize(std::max(nRows, 1));
+        {   // rows by camera: stable counting sort, one histogram per host thread
+            const int nt3 = nRows >= (1 << 16) ? nth : 1;
+            vector<int32_t> hist(size_t(nt3) * std::max(Nc, 1), 0);
+            parallel_chunks(nRows, nt3, [&](int k, int a, int b) { int32_t* h = hist.data() + size_t(k) * Nc; for (int r = a; r < b; ++r) ++h[row_cam[r]]; });
+            for (int c = 0; c < Nc; ++c) {
+                int32_t run = cro[c];
+                for (int k = 0; k < nt3; ++k) { const int32_t n = hist[size_t(k) * Nc + c]; hist[size_t(k) * Nc + c] = run; run += n; }
+                cro[c + 1] = run;
+            }
+            parallel_chunks(nRows, nt3, [&](int k, int a, int b) { int32_t* cur = hist.data() + size_t(k) * Nc; for (int r = a; r < b; ++r) crows[cur[row_cam[r]]++] = r; });
+        }
         // pack the per-position records (RowSched::tmeta) and per-tile records (RowSched::tile_info)
-        vector<int4> tmeta(No), tinfo(std::max(e->nTiles, 1));
+        pvec<int4>& tmeta = hs.tmeta; tmeta.resize(std::max(No, 1));
+        vector<int4> tinfo(std::max(e->nTiles, 1));
         parallel_ranges(e->nTiles, [&](int t0, int t1) {
           for (int t = t0; t < t1; ++t) {
             const int o0 = tile_off[t], n = tile_off[t + 1] - o0;
@@ -607,6 +714,7 @@ void do_set_problem(ba_engine* e, const ba_problem* P, const DevState* dev = nul
             }
           }
         });
+        pt_.tick("row schedule (host threads)");
         e->d_tmeta.upload(tmeta.data(), No, s); e->d_tile_info.upload(tinfo.data(), tinfo.size(), s);
         e->d_cam_row_off.upload(cro.data(), cro.size(), s); e->d_cam_rows.upload(crows.data(), nRows, s);
         e->d_rows.alloc(size_t(nRows) * bak::ROW_DOUBLES); e->d_rows.zero(s);
@@ -616,7 +724,7 @@ void do_set_problem(ba_engine* e, const ba_problem* P, const DevState* dev = nul
             int on = BA_L2_PERSIST_DEFAULT;
             if (const char* v = std::getenv("BA_L2_PERSIST")) on = std::atoi(v);
             cudaDeviceProp prop{};
-            CU_TRY(cudaGetDeviceProperties(&prop, e->device));
+            if (on) CU_TRY(cudaGetDeviceProperties(&prop, e->device));
             const size_t bytes = size_t(nRows) * bak::ROW_DOUBLES * sizeof(double);
             cudaStreamAttrValue attr{};
             if (on && bytes > 0 && prop.persistingL2CacheMaxSize > 0) {
@@ -633,7 +741,7 @@ void do_set_problem(ba_engine* e, const ba_problem* P, const DevState* dev = nul
                 attr.accessPolicyWindow.num_bytes = 0;
                 e->l2_window = false;
             }
-            CU_TRY(cudaStreamSetAttribute(e->stream, cudaStreamAttributeAccessPolicyWindow, &attr));
+            if (on || e->l2_window_ever) { CU_TRY(cudaStreamSetAttribute(e->stream, cudaStreamAttributeAccessPolicyWindow, &attr)); e->l2_window_ever = true; }
         }
         e->d_tile_intr.alloc(size_t(4) * std::max(e->nTiles, 1)); e->d_tile_intr.zero(s);
         CU_TRY(cudaStreamSynchronize(s));
@@ -651,8 +759,11 @@ void do_set_problem(ba_engine* e, const ba_problem* P, const DevState* dev = nul
         CU_TRY(cudaStreamSynchronize(s));
         RS.cam_cnt = e->d_cam_cnt.p; RS.zero_cams = e->d_zero_cams.p; RS.n_zero = int(zc.size()); RS.fuse = e->fuse_gather;
     }
-    e->d_slot.upload(slot.data(), No, s);
-    e->d_spack.upload(spack.data(), No, s);
+    pt_.tick("schedule uploads, rows alloc");
+    if (e->scatter_mode == 2 || e->scatter_mode == 3) {   // only the private-accumulator scatters read these
+        e->d_slot.upload(slot.data(), No, s);
+        e->d_spack.upload(spack.data(), No, s);
+    }
     {
         const int G = std::max(1, std::min(e->nTiles, e->num_sms * 2));
         const int ldf = (e->nf + 15) / 16 * 16;
@@ -715,6 +826,7 @@ void do_set_problem(ba_engine* e, const ba_problem* P, const DevState* dev = nul
     CU_TRY(cudaMemcpyAsync(e->d_intr.p, e->d_intr0.p, size_t(4) * Ng * sizeof(double), cudaMemcpyDeviceToDevice, s));
     CU_TRY(cudaMemcpyAsync(e->d_pt.p, e->d_pt0.p, size_t(3) * Np * sizeof(double), cudaMemcpyDeviceToDevice, s));
 
+    pt_.tick("index/parameter uploads, allocs");
     setup_p2p(e);
 
     bak::View& V = e->V;
@@ -730,7 +842,11 @@ void do_set_problem(ba_engine* e, const ba_problem* P, const DevState* dev = nul
     e->scales_set = false;
     e->has_problem = true;
 
+    pt_.tick("p2p, view");
     build_dense(e, P, pt_off);
+    pt_.tick("dense setup");
+    CU_TRY(cudaStreamSynchronize(s));   // the uploads read page-locked arrays this engine reuses in its next call
+    pt_.tick("upload drain");
 
     // algorithmic bytes per launch of each kernel in THIS formulation, for roofline.achieved
     const double no = No, np = Np, nc = Nc, jb = (e->fi ? 208.0 : 144.0) - 16.0 * e->jpack;

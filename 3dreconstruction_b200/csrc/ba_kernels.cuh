@@ -769,9 +769,102 @@ k_schur_sweep(View V, const double* __restrict__ xin, double* __restrict__ yout,
 // Gathers the by-observation records K1 wrote (JcA: Jc, r [, Ji] in 128 / 192 contiguous bytes = whole sectors) through
 // perm_by_cam.  (v1 gathered the SoA columns: 7 separate 16-byte pieces per observation, 3.1x DRAM over-fetch.)  
 #ifndef BA_K2C_COOP
-#define BA_K2C_COOP 0   // measured on the Venice shape: 296 us against 185 us for the one-record-per-lane version below: the 28 shuffles per record cost more than the 6 L1 wavefronts they save
+#define BA_K2C_COOP 2   // 2: records staged through shared memory with cp.async (174 us on the Venice shape); 0: one record per lane (186 us); 1: 8 lanes per record + shuffles (296 us: 28 shuffles per record cost more than the 6 L1 wavefronts they save)
 #endif
-#if BA_K2C_COOP
+#if BA_K2C_COOP == 2
+// Records staged through shared memory with cp.async (no staging registers): consecutive lanes fetch consecutive 16-byte pieces of the
+// records (8 or 12 lanes per record: one L1 wavefront per record instead of 7 for one-record-per-lane) into rotated 16-byte slots
+// (conflict-free for 8 adjacent lanes); every thread then reads ITS record back with 7 (11) LDS.128 and forms the 27 (41) products as the
+// first version does.  Fixed intrinsics: two buffers, the next 128 records are in flight while this batch is multiplied.
+#ifndef BA_K2C_MINB
+#define BA_K2C_MINB 5
+#endif
+template <bool FI>
+__global__ void __launch_bounds__(128, FI ? 4 : BA_K2C_MINB)
+k2c_camera_blocks(View V, double* __restrict__ Hcc, double* __restrict__ gc, double* __restrict__ ipart) {
+    constexpr int NV = FI ? (21 + 6 + 10 + 4) : (21 + 6);   // Hcc upper, gc, [Hii upper, gi]
+    constexpr int ST = FI ? 12 : 8;                          // double2 per record
+    constexpr int NBUF = FI ? 1 : 2;
+    __shared__ double sm[4][NV];
+    __shared__ __align__(16) double2 sR[NBUF][128 * ST];
+    const int c = blockIdx.x;
+    const int a0 = V.cam_off[c], a1 = V.cam_off[c + 1];
+    auto rotof = [](int i) { return FI ? (i >> 1) % 12 : (i & 7); };
+    const int rot = rotof(threadIdx.x);
+    auto stage = [&](int buf, int ib) {
+        const int nrec = min(128, a1 - ib);
+#pragma unroll
+        for (int m = 0; m < ST; ++m) {
+            const int q = threadIdx.x + 128 * m;
+            const int i = q / ST, k = q - i * ST;
+            if (i < nrec) {
+                const int o = __ldg(V.perm_by_cam + ib + i);
+                int sl = k + rotof(i); if (sl >= ST) sl -= ST;
+                cp_async16(&sR[buf][i * ST + sl], V.JcA + size_t(o) * ST + k);
+            }
+        }
+        cp_async_commit();
+    };
+    double acc[NV];
+#pragma unroll
+    for (int k = 0; k < NV; ++k) acc[k] = 0.0;
+    int buf = 0;
+    if (a0 < a1) stage(0, a0);
+    for (int ib = a0; ib < a1; ib += 128) {
+        const int nrec = min(128, a1 - ib);
+        cp_async_wait_all();
+        __syncthreads();                                   // batch ib has landed; everybody is done with the other buffer
+        if (NBUF == 2 && ib + 128 < a1) stage(buf ^ 1, ib + 128);
+        if (threadIdx.x < nrec) {
+            double2 j[FI ? 10 : 6], r;
+            const double2* rec = sR[buf] + threadIdx.x * ST;
+#pragma unroll
+            for (int k = 0; k < 6; ++k) { int sl = k + rot; if (sl >= ST) sl -= ST; j[k] = rec[sl]; }
+            { int sl = 6 + rot; if (sl >= ST) sl -= ST; r = rec[sl]; }
+            if (FI) {
+#pragma unroll
+                for (int k = 0; k < 4; ++k) { int sl = 7 + k + rot; if (sl >= ST) sl -= ST; j[6 + k] = rec[sl]; }
+            }
+            int n = 0;
+#pragma unroll
+            for (int a = 0; a < 6; ++a)
+#pragma unroll
+                for (int b = a; b < 6; ++b) acc[n++] += j[a].x * j[b].x + j[a].y * j[b].y;
+#pragma unroll
+            for (int a = 0; a < 6; ++a) acc[n++] += j[a].x * r.x + j[a].y * r.y;
+            if (FI) {
+#pragma unroll
+                for (int a = 0; a < 4; ++a)
+#pragma unroll
+                    for (int b = a; b < 4; ++b) acc[n++] += j[6 + a].x * j[6 + b].x + j[6 + a].y * j[6 + b].y;
+#pragma unroll
+                for (int a = 0; a < 4; ++a) acc[n++] += j[6 + a].x * r.x + j[6 + a].y * r.y;
+            }
+        }
+        if (NBUF == 2) buf ^= 1;
+        else { __syncthreads(); if (ib + 128 < a1) stage(0, ib + 128); }
+    }
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+#pragma unroll
+    for (int k = 0; k < NV; ++k) { const double s = warp_sum(acc[k]); if (lane == 0) sm[wid][k] = s; }
+    __syncthreads();
+    if (threadIdx.x < NV) {
+        const int k = threadIdx.x;
+        const double s = sm[0][k] + sm[1][k] + sm[2][k] + sm[3][k];
+        if (k < 21) {   // unpack upper-triangle index k -> (a,b)
+            int a = 0, rem = k;
+            while (rem >= 6 - a) { rem -= 6 - a; ++a; }
+            const int b = a + rem;
+            Hcc[36 * size_t(c) + 6 * a + b] = s;
+            Hcc[36 * size_t(c) + 6 * b + a] = s;
+        } else if (k < 27) {
+            gc[6 * size_t(c) + (k - 21)] = s;
+        } else if (FI) {
+            ipart[14 * size_t(c) + (k - 27)] = s;
+        }
+    }
+}
+#elif BA_K2C_COOP
 // 8 adjacent lanes (16 with free intrinsics) share one record: lane k loads its k-th 16 bytes, so a warp instruction reads 4 (2)
 // whole records = 4 (3) lines, one L1 wavefront per record; the first version (below, #else) gave every lane a whole record: 7 LDG.128
 // to 32 different lines each = 7 wavefronts per record, and the kernel sat at 0.55 of the HBM roofline waiting on the load/store unit.

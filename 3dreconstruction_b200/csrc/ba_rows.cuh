@@ -17,6 +17,31 @@ namespace bak {
 #define BA_ROW_DOUBLES 6
 #endif
 constexpr int ROW_DOUBLES = BA_ROW_DOUBLES;    // 6 used; 8: 64-byte rows = two full 32-byte sectors; 6: packed 48-byte rows (less to write, the gather still fetches two sectors per row)
+// Cache operators of the partial rows (A/B knobs): store 0 = st.cg, 1 = st.cs (streaming), 2 = default; load 0 = ld.cg, 1 = ld.cs, 2 = ld.lu (last use)
+#ifndef BA_ROW_ST
+#define BA_ROW_ST 0
+#endif
+#ifndef BA_ROW_LD
+#define BA_ROW_LD 0
+#endif
+__device__ __forceinline__ void row_store(double2* p, double2 v) {
+#if BA_ROW_ST == 1
+    __stcs(p, v);
+#elif BA_ROW_ST == 2
+    *p = v;
+#else
+    __stcg(p, v);
+#endif
+}
+__device__ __forceinline__ double2 row_load(const double2* p) {
+#if BA_ROW_LD == 1
+    return __ldcs(p);
+#elif BA_ROW_LD == 2
+    return __ldlu(p);
+#else
+    return __ldcg(p);
+#endif
+}
 constexpr int L1_CHUNK = 8;       // level-1 chunk of the in-tile segmented sum
 constexpr int GATHER_WARPS = 4;   // warps per CTA of the by-camera gather (K5b)
 
@@ -84,13 +109,13 @@ __device__ __forceinline__ bool camera_row_sum(const RowSched& S, int c, double 
             }
             double2 v[UNR];
 #pragma unroll
-            for (int k = 0; k < UNR; ++k) v[k] = __ldcg(R2 + size_t(ROW_DOUBLES / 2) * id[k] + sub);
+            for (int k = 0; k < UNR; ++k) v[k] = row_load(R2 + size_t(ROW_DOUBLES / 2) * id[k] + sub);
 #pragma unroll
             for (int k = 1; k < UNR; ++k) { v[0].x += v[k].x; v[0].y += v[k].y; }
             acc.x += v[0].x; acc.y += v[0].y;
         }
         for (; i < e; i += NG) {
-            const double2 v = __ldcg(R2 + size_t(ROW_DOUBLES / 2) * __ldg(S.cam_rows + i) + sub);
+            const double2 v = row_load(R2 + size_t(ROW_DOUBLES / 2) * __ldg(S.cam_rows + i) + sub);
             acc.x += v.x; acc.y += v.y;
         }
     }
@@ -342,7 +367,7 @@ k_schur_rows(View V, RowSched S, const double* __restrict__ xin, double* __restr
                 a.x += a2.x; a.y += a2.y; bq.x += b2.x; bq.y += b2.y; cq.x += c2.x; cq.y += c2.y;
             }
             double2* dst = reinterpret_cast<double2*>(S.rows + size_t(ROW_DOUBLES) * (hbase + hrank));
-            __stcg(dst, a); __stcg(dst + 1, bq); __stcg(dst + 2, cq);
+            row_store(dst, a); row_store(dst + 1, bq); row_store(dst + 2, cq);
 #if BA_K5A_FUSE == 1
             if (!FI && S.fuse) deliver(pk & 0x3fffff);
 #endif
