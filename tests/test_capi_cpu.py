@@ -129,3 +129,13 @@ def test_shard_points_partition(ba):
     assert sp[0] == 0 and sp[-1] == 2 and np.all(np.diff(sp) >= 0)
     with pytest.raises(ba.BAError):
         lib.shard_points(np.array([1, 0], np.int32), 2, 2)   # not sorted
+
+
+def test_profiling_entry_points(ba, oracle):
+    """ba_set_profiling / ba_set_profiling_stride / ba_get_kernel_stats exist on both libraries; the stride is validated (>= 1)."""
+    with oracle.create(oracle.default_options()) as h:
+        h.set_profiling(1 << 7, stride=16)          # the call bench.py makes
+        h.set_profiling(0)
+        assert h.kernel_stats() == []               # the CPU oracle has no kernels to report
+        with pytest.raises(ba.BAError):
+            h.set_profiling(1, stride=0)
