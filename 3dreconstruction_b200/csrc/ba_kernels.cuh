@@ -987,6 +987,68 @@ k2c_camera_blocks(View V, double* __restrict__ Hcc, double* __restrict__ gc, dou
 
 #endif
 
+// K3s — the pose blocks' Schur correction for preconditioner = BA_PRECOND_SCHUR_JACOBI (Ceres' SCHUR_JACOBI: the block diagonal of the
+// reduced camera matrix S instead of that of B = F^T F + Dc^2):  corr[c] = sum over the points p camera c sees of W Hinv_p W^T with
+// W = sum over c's observations of p of Jc^T Jp (6x3).  One CTA per camera over the camera-sorted list; that list is the stable sort of
+// a point-sorted one, so repeated observations of a point by the same camera are adjacent and are folded by the first of them.
+// Needs Hinv of THIS damping (runs after K3p); fixed-order reduction as K2c.  Bytes: (96 + 48 + 48 + 12) No + 288 Nc.
+// EXPERIMENTAL: written in round 1 after the GPU budget was spent; compiled, not yet run (ba_create keeps it behind an opt-in).
+__global__ void __launch_bounds__(128)
+k_schur_diag(View V, double* __restrict__ corr) {
+    __shared__ double sm[4][21];
+    const int c = blockIdx.x;
+    const int a0 = V.cam_off[c], a1 = V.cam_off[c + 1];
+    double acc[21];
+#pragma unroll
+    for (int k = 0; k < 21; ++k) acc[k] = 0.0;
+    for (int i = a0 + threadIdx.x; i < a1; i += blockDim.x) {
+        const int o = V.perm_by_cam[i];
+        const int p = V.obs_pt[o];
+        if (i > a0 && V.obs_pt[V.perm_by_cam[i - 1]] == p) continue;      // a repeat: folded into the first observation of (c, p)
+        double W[6][3];
+#pragma unroll
+        for (int a = 0; a < 6; ++a) { W[a][0] = 0.0; W[a][1] = 0.0; W[a][2] = 0.0; }
+        for (int ii = i; ii < a1; ++ii) {
+            const int oo = ii == i ? o : V.perm_by_cam[ii];
+            if (ii != i && V.obs_pt[oo] != p) break;
+            const double2* A = V.JcA + size_t(oo) * V.jca_stride;
+            double2 jc[6], jp[3];
+#pragma unroll
+            for (int k = 0; k < 6; ++k) jc[k] = ldg2(A + k);
+            load_jp(V, V.J2 + oo, jp);
+#pragma unroll
+            for (int a = 0; a < 6; ++a)
+#pragma unroll
+                for (int k = 0; k < 3; ++k) W[a][k] += jc[a].x * jp[k].x + jc[a].y * jp[k].y;
+        }
+        const double* h = V.Hinv + 6 * size_t(p);
+        const double H[3][3] = {{h[0], h[1], h[2]}, {h[1], h[3], h[4]}, {h[2], h[4], h[5]}};
+        double U[6][3];
+#pragma unroll
+        for (int a = 0; a < 6; ++a)
+#pragma unroll
+            for (int k = 0; k < 3; ++k) U[a][k] = W[a][0] * H[0][k] + W[a][1] * H[1][k] + W[a][2] * H[2][k];
+        int n = 0;
+#pragma unroll
+        for (int a = 0; a < 6; ++a)
+#pragma unroll
+            for (int b = a; b < 6; ++b) acc[n++] += U[a][0] * W[b][0] + U[a][1] * W[b][1] + U[a][2] * W[b][2];
+    }
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+#pragma unroll
+    for (int k = 0; k < 21; ++k) { const double s = warp_sum(acc[k]); if (lane == 0) sm[wid][k] = s; }
+    __syncthreads();
+    if (threadIdx.x < 21) {
+        const int k = threadIdx.x;
+        const double s = sm[0][k] + sm[1][k] + sm[2][k] + sm[3][k];
+        int a = 0, rem = k;
+        while (rem >= 6 - a) { rem -= 6 - a; ++a; }
+        const int b = a + rem;
+        corr[36 * size_t(c) + 6 * a + b] = s;
+        corr[36 * size_t(c) + 6 * b + a] = s;
+    }
+}
+
 // Free intrinsics: Hii / gi of every Camera group = sum of its cameras' shares, in camera order (one warp per group, fixed tree).
 __global__ void __launch_bounds__(128)
 k_group_blocks(int Ng, const int* __restrict__ grp_off, const int* __restrict__ grp_cams, const double* __restrict__ ipart,
@@ -1104,6 +1166,18 @@ __global__ void k3_camera_blocks(int Nc, int Ng, int fi, const double* __restric
 }
 
 // Jacobi column scales s_j = 1/(1 + sqrt(H_jj)) from the iteration-0 Hessian diagonals (frozen afterwards).
+// Schur-Jacobi pose blocks: overwrites k3_camera_blocks' Minv[c] by (Hcc[c] + Dc^2 - corr[c])^-1; if rounding made a block indefinite
+// the plain block (already in Minv) stays.  Runs after k3_camera_blocks (Df2) and k_schur_diag (corr).  EXPERIMENTAL, see k_schur_diag.
+__global__ void k3_schur_jacobi_blocks(int Nc, const double* __restrict__ Hcc, const double* __restrict__ Df2, const double* __restrict__ corr,
+                                       double* __restrict__ Minv) {
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= Nc) return;
+    double A[36], I[36];
+    for (int k = 0; k < 36; ++k) A[k] = Hcc[36 * size_t(b) + k] - corr[36 * size_t(b) + k];
+    for (int k = 0; k < 6; ++k) A[7 * k] += Df2[6 * b + k];
+    if (spd_inverse<6>(A, I)) for (int k = 0; k < 36; ++k) Minv[36 * size_t(b) + k] = I[k];
+}
+
 __global__ void k_scales_points(View V, int enabled) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= 3 * V.Np) return;

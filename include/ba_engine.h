@@ -65,6 +65,8 @@ typedef enum ba_model { BA_MODEL_PINHOLE = 0, BA_MODEL_SNAVELY = 1 } ba_model;
  * reads AUTO as EXACT. */
 typedef enum ba_linear_solver { BA_LINEAR_EXACT = 0, BA_LINEAR_PCG = 1, BA_LINEAR_AUTO = 2 } ba_linear_solver;
 typedef enum ba_preconditioner { BA_PRECOND_JACOBI = 0 /* blockdiag(Hcc + Dc^2) */, BA_PRECOND_SCHUR_JACOBI = 1 /* blockdiag(S) */ } ba_preconditioner;
+/* The CUDA engine runs BA_PRECOND_JACOBI; its BA_PRECOND_SCHUR_JACOBI (k_schur_diag) is written but not yet validated on hardware and is
+ * refused unless BA_EXPERIMENTAL_SCHUR_JACOBI=1 is set in the environment.  The CPU oracle implements both. */
 
 /* Which rule selects the first-order branch of AngleAxisRotatePoint. */
 typedef enum ba_taylor_rule { BA_TAYLOR_THETA2_LE_EPS = 0 /* theta^2 <= DBL_EPSILON */, BA_TAYLOR_THETA_IS_ZERO = 1 /* hypot()==0 */ } ba_taylor_rule;

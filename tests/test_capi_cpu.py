@@ -80,7 +80,7 @@ def test_engine_has_no_cpu_fallback(ba):
 
 def test_engine_rejects_unsupported_options_before_touching_a_device(ba):
     lib = ba.engine_library()
-    for bad in (dict(linear_solver=7), dict(abi_version=99), dict(world_size=2), dict(rank=3)):
+    for bad in (dict(linear_solver=7), dict(abi_version=99), dict(world_size=2), dict(rank=3), dict(preconditioner=1), dict(preconditioner=5)):   # SCHUR_JACOBI is an opt-in (BA_EXPERIMENTAL_SCHUR_JACOBI=1)
         with pytest.raises(ba.BAError):
             lib.create(lib.default_options(**bad))
 

@@ -259,3 +259,25 @@ def test_direct_solve_survives_a_singular_system(ba):
         s = eng.solve()
         t = eng.trajectory()
     assert s.num_iterations >= 1 and all(np.isfinite(r.cost) for r in t)
+
+
+@pytest.mark.skipif(__import__("os").environ.get("BA_EXPERIMENTAL_SCHUR_JACOBI") != "1",
+                    reason="Schur-Jacobi preconditioner of the engine is an opt-in that has not run on hardware yet (set BA_EXPERIMENTAL_SCHUR_JACOBI=1)")
+@pytest.mark.parametrize("fi", [0, 1])
+def test_schur_jacobi_preconditioner(ba, oracle, fi):
+    """preconditioner = SCHUR_JACOBI (block diagonal of S): same trajectory as the exact-solve oracle, the same PCG iteration counts as the
+    oracle's own Schur-Jacobi PCG (to within rounding of the stop test), and fewer iterations than block-Jacobi on B."""
+    P = ba.synth("ladybug")
+    common = dict(intrinsics_free=fi, max_num_iterations=6)
+    (se, te, xe), (so, to, xo) = solve_both(ba, oracle, P, engine_solver=1, preconditioner=1, **common)
+    assert_trajectory_parity(te, to)
+    with oracle.create(oracle.default_options(num_threads=4, linear_solver=1, preconditioner=1, **common)) as h:
+        h.set_problem(P)
+        h.solve()
+        tp = h.trajectory()
+    with ba.Engine(linear_solver=1, preconditioner=0, **common) as eng:
+        eng.set_problem(P)
+        sj = eng.solve()
+    for a, b in zip(te[1:], tp[1:]):
+        assert abs(a.pcg_iterations - b.pcg_iterations) <= 2, (a.iteration, a.pcg_iterations, b.pcg_iterations)
+    assert se.total_pcg_iterations < sj.total_pcg_iterations

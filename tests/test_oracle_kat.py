@@ -304,3 +304,21 @@ def test_g2o_lambda_schedule_and_minimum(ba, oracle):
     assert sg.final_cost == pytest.approx(sc.final_cost, rel=1e-5)        # both policies reach the same minimum
     with pytest.raises(ba.BAError):
         oracle.create(oracle.default_options(intrinsics_free=1, lm_policy=1))
+
+
+def test_schur_jacobi_preconditioner_in_the_oracle(ba, oracle):
+    """The oracle's two PCG preconditioners (block diagonal of B = Ceres JACOBI, of S = SCHUR_JACOBI) reach the exact-solve trajectory, and
+    the block diagonal of the system actually being solved needs fewer iterations (what the engine's opt-in Schur-Jacobi is measured against)."""
+    P = ba.synth("ladybug")
+    common = dict(intrinsics_free=0, max_num_iterations=5, num_threads=4)
+    runs = {}
+    for key, extra in (("exact", dict(linear_solver=0)), ("jacobi", dict(linear_solver=1, preconditioner=0)), ("schur", dict(linear_solver=1, preconditioner=1))):
+        with oracle.create(oracle.default_options(**common, **extra)) as h:
+            h.set_problem(P)
+            s = h.solve()
+            runs[key] = (s, h.trajectory())
+    for key in ("jacobi", "schur"):
+        for a, b in zip(runs[key][1], runs["exact"][1]):
+            assert a.step_is_successful == b.step_is_successful
+            assert abs(a.cost - b.cost) <= 1e-9 * abs(b.cost)
+    assert 0 < runs["schur"][0].total_pcg_iterations < runs["jacobi"][0].total_pcg_iterations
