@@ -4,7 +4,10 @@
 // TEST INFRASTRUCTURE ONLY.  Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference
 // legs may load this library; the product path (3dreconstruction_b200/) never links, imports or executes it.
 //
-// PARITY UNPINNED: the reference holds no golden vectors, known-answer tests or fixtures for this path
+// PARITY: PINNED FOR THE RESIDUAL MODELS, UNPINNED FOR THE SOLVER.  The reference's own cost functors (ReprojectCost,
+// SnavelyReprojectionError) are compiled here from /root/reference by oracle/ref_build.sh (oracle/_ref/libref_cost.so) and this
+// oracle's residuals and Jacobians equal theirs to 1e-13 (tests/test_reference_functors.py, vectors in tests/golden/).  Beyond that the
+// reference holds no golden vectors, known-answer tests or fixtures for this path
 //  and cannot be built here (F5: Ceres 2.2, Eigen, OpenCV, Sophus, PCL absent).  The solver the
 // reference delegates to — Ceres Solver 2.2 (CMakeLists.txt:32, un-vendored, patch version unpinned),
 // TrustRegionMinimizer + LevenbergMarquardtStrategy + SPARSE_SCHUR/EIGEN_SPARSE as configured at

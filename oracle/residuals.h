@@ -1,9 +1,9 @@
 // oracle/residuals.h — CPU restatement of the reference's residual models and robust kernels.
-// TEST INFRASTRUCTURE ONLY (see oracle/README.md).  "parity unpinned": the reference has no tests or golden
-// vectors for this path and Ceres itself is not in /root/reference; the third-party pieces below
-// (AngleAxisRotatePoint, HuberLoss, CauchyLoss of Ceres Solver 2.2, un-vendored: CMakeLists.txt:32) are restated
-// from their published algorithms and cross-checked against cv2.Rodrigues / cv2.projectPoints / finite differences
-// in tests/test_oracle_kat.py.
+// TEST INFRASTRUCTURE ONLY.  The two cost functors below are checked against the reference's OWN functors compiled from
+// /root/reference (oracle/ref_build.sh -> oracle/_ref/libref_cost.so; tests/test_reference_functors.py: equal to 1e-13, vectors committed
+// under tests/golden/).  Still unpinned: the third-party pieces (AngleAxisRotatePoint, HuberLoss, CauchyLoss of Ceres Solver 2.2,
+// un-vendored: CMakeLists.txt:32), restated from their published algorithms and cross-checked against cv2.Rodrigues /
+// cv2.projectPoints / finite differences in tests/test_oracle_kat.py.
 #ifndef BA_ORACLE_RESIDUALS_H
 #define BA_ORACLE_RESIDUALS_H
 #include <cfloat>
