@@ -29,10 +29,8 @@
 #include <vector>
 
 #include "ba_kernels.cuh"
-#include "ba_scatter.cuh"
-#include "ba_pipe.cuh"
 #include "ba_rows.cuh"
-#include "ba_rows_pipe.cuh"
+#include "ba_stream.cuh"
 #include "ba_p2p.cuh"
 #include "ba_dense.cuh"
 #include "ba_pcg_cluster.cuh"
@@ -52,12 +50,21 @@ thread_local std::string g_create_error;
     } while (0)
 
 struct BaFail { int code; std::string msg; };
-#define KL(eng) (++(eng)->kernel_launches)   // every kernel launch is counted (reported in ba_summary.kernel_launches)
+// Every kernel launch is counted (ba_summary.kernel_launches) and every launch site first checks that no earlier launch on this host
+// thread failed (a <<<>>> launch reports configuration errors, a missing sm_100a image or a missing attribute only through
+// cudaGetLastError): a failed launch can never be skipped silently.  The last launch of a sequence is checked by read_scalars() / finish().
+inline void launch_check(const char* file, int line) {
+    const cudaError_t x = cudaPeekAtLastError();
+    if (x != cudaSuccess) {
+        cudaGetLastError();
+        char b[256];
+        std::snprintf(b, sizeof b, "a kernel launch before %s:%d failed: %s", file, line, cudaGetErrorString(x));
+        throw BaFail{BA_ERR_CUDA, b};
+    }
+}
+#define KL(eng) (launch_check(__FILE__, __LINE__), ++(eng)->kernel_launches)
 #ifndef BA_L2_PERSIST_DEFAULT
 #define BA_L2_PERSIST_DEFAULT 0
-#endif
-#ifndef BA_FUSE_DEFAULT
-#define BA_FUSE_DEFAULT 0
 #endif
 #ifndef BA_JPACK_DEFAULT
 #define BA_JPACK_DEFAULT 1
@@ -146,15 +153,15 @@ struct HostScratch {   // ba_set_problem's work arrays (capacity survives betwee
     pvec<int4> tmeta;
     pvec<int32_t> perm, obs_pt, crows;
     std::vector<unsigned char> slot, lvl1, hrank, hpos;
-    std::vector<int32_t> spack, row_cam, hbase;
+    std::vector<int32_t> spack, row_cam, hbase, tpts;
 };
 
-constexpr int kRedSlices = 8;      // stage-1 slices of the private-copy reduction (ba_pipe.cuh)
-enum KernelId { KID_K0 = 0, KID_K1, KID_K1C, KID_K2C, KID_K3P, KID_K3C, KID_K4, KID_K5, KID_K7, KID_K8, KID_PCGV, KID_MISC, KID_DFORM, KID_DCHOL, KID_COUNT };
+enum KernelId { KID_K0 = 0, KID_K1, KID_K1C, KID_K2C, KID_K3P, KID_K3C, KID_K4, KID_K5, KID_K7, KID_K8, KID_PCGV, KID_MISC, KID_DFORM, KID_DCHOL, KID_GATHER, KID_TAIL,
+                KID_COUNT };
 const char* const kKernelNames[KID_COUNT] = {"K0_camera_precompute", "K1_residual_jacobian", "K1c_candidate_cost", "K2c_camera_blocks",
                                              "K3p_point_blocks",      "K3c_camera_blocks",    "K4_reduced_rhs",     "K5_schur_matvec",
                                              "K7_backsub_model",      "K8_candidate",         "PCG_vector_update",  "misc_reductions",
-                                             "D1_dense_schur_form",   "D2_dense_cholesky_solve"};
+                                             "D1_dense_schur_form",   "D2_dense_cholesky_solve", "K5b_camera_gather",  "PCG_cluster_tail"};
 
 }  // namespace
 
@@ -192,11 +199,6 @@ struct ba_engine {
     DevBuf<double> d_sc_f, d_Df2, d_Minv, d_b, d_x, d_r, d_z, d_p, d_y;
     DevBuf<double> d_sdiag;           // Schur-Jacobi: per-pose correction blocks (k_schur_diag)
     DevBuf<double> d_part0, d_part1;   // per-tile / per-block partials
-    // static scatter schedule + private accumulators (ba_scatter.cuh)
-    DevBuf<unsigned char> d_slot;
-    DevBuf<int> d_spack;
-    DevBuf<double> d_scratch;
-    bak::ScatterSched Sch{};
     // direct solve of the reduced camera system (ba_dense.cuh); dense == true selects it for this problem
     DevBuf<double> d_ipart;            // [Nc][14] per-camera shares of the group blocks (free intrinsics)
     DevBuf<int> d_grp_off, d_grp_cams;  // cameras of every group, CSR
@@ -213,16 +215,15 @@ struct ba_engine {
     int chol_mode = 1;                  // 1: dataflow (k_dense_chol_df), 0: barrier per phase (k_dense_chol); BA_CHOL_MODE overrides
     bak::DenseView DV{};
     int chol_grid = 1;
-    DevBuf<double> d_redpart;          // [kRedSlices][ldf] stage-1 output of the copy reduction
-    // mode 4: per-(tile, camera) partial rows + by-camera gather (ba_rows.cuh)
+    // per-(tile, camera) partial rows + by-camera gather (ba_rows.cuh, ba_stream.cuh)
     DevBuf<int4> d_tmeta, d_tile_info;
     HostScratch hs;
-    DevBuf<int> d_cam_cnt, d_zero_cams; // fused gather: rows delivered per camera (zero between launches); cameras without rows
-    int fuse_gather = 0;
     DevBuf<int> d_cam_row_off, d_cam_rows;
     DevBuf<double> d_rows, d_tile_intr;
     bak::RowSched RS{};
-    int scatter_mode = 4;              // 1 = red.global atomics, 2 = private accumulators, 3 = 2 + bulk-copy pipeline, 4 = partial rows (default), 5 = 4 as a persistent cp.async pipeline
+    int scatter_mode = 6;              // 1 = red.global atomics, 4 = partial rows, one CTA per tile, 6 = partial rows, persistent streaming kernel (default)
+    int scatter_eff = 4;               // what scatter_mode resolves to for the current problem (auto: 6 for large problems, 4 for small ones)
+    bool stream_attr_set = false;      // max dynamic shared memory of the k_schur_stream instantiations (per engine: per device)
     int num_sms = 148;
     DevBuf<bak::Scalars> d_scal;
     bak::Scalars* h_scal = nullptr;    // pinned
@@ -243,12 +244,14 @@ struct ba_engine {
     int64_t kernel_launches = 0;
     unsigned profiling = 0;           // bit k set: time kernel id k with CUDA events
     struct Stat { int64_t launches = 0; int64_t timed = 0; double ms = 0.0; double bytes = 0.0; } stats[KID_COUNT];
+    int pcg_tag = -1;                 // ordinal of the PCG iteration being launched (LaunchTimer tags; -1 outside the PCG loop)
+    int pcg_pred = 0;                 // PCG iterations of the previous linear solve on this handle (first batch size)
     int k5_sample_stride = 1;         // time every n-th K5 launch only (events between two launches serialise them; BA_K5_SAMPLE)
     int pdl = 0;                      // programmatic dependent launch along the PCG chain (BA_PDL)
     int jpack = 0;                    // packed translation columns of J (pinhole model)
     bool l2_window_ever = false;
     bool l2_window = false;           // a persisting-L2 access-policy window for the partial rows is set on the stream
-    struct Pending { int kid; cudaEvent_t a, b; };
+    struct Pending { int kid; cudaEvent_t a, b; int tag; };   // tag: PCG iteration ordinal within its linear solve (-1: not a PCG-loop launch)
     vector<Pending> pending;
     vector<cudaEvent_t> ev_pool;
     cudaEvent_t ev_t0 = nullptr, ev_t1 = nullptr;
@@ -270,8 +273,8 @@ int fail(ba_engine* e, int code, const std::string& msg) { if (e) e->err = msg; 
 
 // Profiling hook around one launch: CUDA events on the engine's stream, resolved after the solve's final sync.
 struct LaunchTimer {
-    ba_engine* e; int kid; cudaEvent_t a = nullptr, b = nullptr;
-    LaunchTimer(ba_engine* e_, int kid_, bool sample = true) : e(e_), kid(kid_) {
+    ba_engine* e; int kid; cudaEvent_t a = nullptr, b = nullptr; int tag;
+    LaunchTimer(ba_engine* e_, int kid_, bool sample = true, int tag_ = -1) : e(e_), kid(kid_), tag(tag_) {
         ++e->stats[kid].launches;
         if (!((e->profiling >> kid) & 1u) || !sample) return;
         ++e->stats[kid].timed;
@@ -279,13 +282,13 @@ struct LaunchTimer {
         a = get(); b = get();
         cudaEventRecord(a, e->stream);
     }
-    ~LaunchTimer() { if (a) { cudaEventRecord(b, e->stream); e->pending.push_back({kid, a, b}); } }
+    ~LaunchTimer() { if (a) { cudaEventRecord(b, e->stream); e->pending.push_back({kid, a, b, tag}); } }
 };
 
 void resolve_timers(ba_engine* e) {
     for (auto& p : e->pending) {
         float ms = 0.f;
-        if (cudaEventElapsedTime(&ms, p.a, p.b) == cudaSuccess) e->stats[p.kid].ms += ms;
+        if (p.kid >= 0 && cudaEventElapsedTime(&ms, p.a, p.b) == cudaSuccess) e->stats[p.kid].ms += ms;   // kid < 0: a voided no-op launch
         e->ev_pool.push_back(p.a); e->ev_pool.push_back(p.b);
     }
     e->pending.clear();
@@ -344,23 +347,44 @@ void parallel_ranges(int n, F&& f) {
     if (err) std::rethrow_exception(err);
 }
 
+// A tile also holds at most TILE_MAX_PTS points, consecutive ids all of them observed (the streaming kernel copies the Hinv blocks of a
+// tile's points as one piece, and point j of the tile is handled by thread j < observations of the tile).
 void build_tiles(const vector<int32_t>& pt_off, int Np, vector<int32_t>& tile_off) {
     tile_off.clear();
     tile_off.push_back(0);
-    int start = 0;   // first observation of the open tile
+    int start = 0;      // first observation of the open tile
+    int pstart = -1;    // first point of the open tile (-1: the tile is empty)
     for (int p = 0; p < Np; ++p) {
         const int a = pt_off[p], b = pt_off[p + 1];
-        if (b == a) continue;
-        if (b - start > bak::TILE_OBS) {          // point p does not fit into the open tile
-            if (a > start) { tile_off.push_back(a); start = a; }
-            if (b - a > bak::TILE_OBS) { tile_off.push_back(b); start = b; }   // long point: closes its own tile
+        if (b == a) {   // an unobserved point closes the open tile: a tile's points are consecutive ids, one point thread each
+            if (pstart >= 0) { tile_off.push_back(a); start = a; pstart = -1; }
+            continue;
         }
+        if (pstart >= 0 && (b - start > bak::TILE_OBS || p - pstart + 1 > bak::TILE_MAX_PTS)) {   // point p does not fit into the open tile
+            tile_off.push_back(a); start = a; pstart = -1;
+        }
+        if (b - a > bak::TILE_OBS) { tile_off.push_back(b); start = b; pstart = -1; continue; }     // long point: a tile of its own
+        if (pstart < 0) pstart = p;
     }
     if (tile_off.back() != pt_off[Np]) tile_off.push_back(pt_off[Np]);
 }
 
-void teardown_p2p(ba_engine* e) {
+// Two phases (CUDA IPC: freeing an exported allocation while a peer still has it mapped is undefined): every rank first closes the
+// mappings it imported, then all ranks meet in a collective (one-int NCCL all-reduce + stream sync), and only then does each rank free
+// the buffers it exported.  `collective` = every rank is known to be in this call (setup_p2p's reallocation and failure paths,
+// ba_destroy of a healthy handle); a handle that is destroyed after an error skips the rendezvous rather than risk a hang.
+void teardown_p2p(ba_engine* e, bool collective) {
     for (int i = 0; i < e->p2p.nopened; ++i) cudaIpcCloseMemHandle(e->p2p.opened[i]);
+    e->p2p.nopened = 0;
+    if (collective && e->comm && e->p2p.local && e->stream) {
+        int* d = nullptr;
+        if (cudaMalloc(reinterpret_cast<void**>(&d), sizeof(int)) == cudaSuccess) {
+            cudaMemsetAsync(d, 0, sizeof(int), e->stream);
+            g_nccl.AllReduce(d, d, 1, Nccl::kInt32, Nccl::kMax, e->comm, e->stream);
+            cudaStreamSynchronize(e->stream);
+            cudaFree(d);
+        }
+    }
     if (e->p2p.local) cudaFree(e->p2p.local);
     if (e->p2p.lflags) cudaFree(e->p2p.lflags);
     e->p2p = ba_engine::P2P{};
@@ -377,7 +401,7 @@ void setup_p2p(ba_engine* e) {
     const size_t need = size_t(2) * W * ldf;
     cudaStream_t s = e->stream;
     if (e->p2p.on && e->p2p.cap >= need) { e->p2p.view.ldf = ldf; return; }
-    teardown_p2p(e);
+    teardown_p2p(e, true);
     ba_engine::P2P& Q = e->p2p;
     CU_TRY(cudaMalloc(reinterpret_cast<void**>(&Q.local), need * sizeof(double)));
     CU_TRY(cudaMalloc(reinterpret_cast<void**>(&Q.lflags), 64 * sizeof(unsigned int)));
@@ -415,7 +439,7 @@ void setup_p2p(ba_engine* e) {
     CU_TRY(cudaMemcpyAsync(&fail_any, d_fail.p, sizeof(int), cudaMemcpyDeviceToHost, s));
     CU_TRY(cudaStreamSynchronize(s));
     if (fail_any) {
-        teardown_p2p(e);
+        teardown_p2p(e, true);
         if (e->opt.p2p_allreduce == 2) throw BaFail{BA_ERR_NCCL, "peer-memory all-reduce required (p2p_allreduce = 2) but CUDA IPC mapping of a peer buffer failed"};
         return;
     }
@@ -632,6 +656,8 @@ void do_set_problem(ba_engine* e, const ba_problem* P, const DevState* dev = nul
     pt_.tick("csr, shard, perm");
     build_tiles(pt_off, Np, tile_off);
     e->nTiles = int(tile_off.size()) - 1;
+    // auto: the persistent streaming kernel once every SM has a few tiles to stream, one CTA per tile below that (latency-bound regime)
+    e->scatter_eff = e->scatter_mode ? e->scatter_mode : (e->nTiles >= 4 * e->num_sms ? 6 : 4);
     pt_.tick("tiles");
     // static scatter schedule: within each tile, the rank of every observation in camera-sorted (stable) order, and per
     // sorted position the camera + segment length at segment heads (ba_scatter.cuh)
@@ -706,6 +732,7 @@ void do_set_problem(ba_engine* e, const ba_problem* P, const DevState* dev = nul
             tinfo[t] = make_int4(o0, n, hbase[t], pfirst);
             if (n > bak::TILE_OBS) { for (int i = 0; i < n; ++i) tmeta[o0 + i] = make_int4(P->obs_cam[e->ob + o0 + i], 0, -1, 0); continue; }
             const int plast = obs_pt[o0 + n - 1];
+            tinfo[t].y = int(unsigned(n) | unsigned(plast - pfirst + 1) << 24);   // points of the tile's range (<= TILE_MAX_PTS)
             for (int i = 0; i < n; ++i) {
                 const int lpt = obs_pt[o0 + i] - pfirst;
                 const unsigned packA = unsigned(slot[o0 + i]) | unsigned(lvl1[o0 + i]) << 8 | unsigned(hrank[o0 + i]) << 16 | unsigned(lpt) << 24;
@@ -749,31 +776,8 @@ void do_set_problem(ba_engine* e, const ba_problem* P, const DevState* dev = nul
         bak::RowSched& RS = e->RS;
         RS.tmeta = e->d_tmeta.p; RS.tile_info = e->d_tile_info.p;
         RS.rows = e->d_rows.p; RS.tile_intr = e->d_tile_intr.p; RS.cam_row_off = e->d_cam_row_off.p; RS.cam_rows = e->d_cam_rows.p; RS.nRows = nRows;
-        // fused by-camera gather (ba_rows.cuh): pose-only reduced systems (intrinsics fixed) with the rows scatter
-        e->fuse_gather = (BA_FUSE_DEFAULT && !e->fi && e->scatter_mode == 4) ? 1 : 0;
-        if (const char* v = std::getenv("BA_FUSE")) e->fuse_gather = (std::atoi(v) && !e->fi && e->scatter_mode == 4) ? 1 : 0;
-        e->d_cam_cnt.alloc(size_t(std::max(Nc, 1))); e->d_cam_cnt.zero(s);
-        CU_TRY(cudaStreamSynchronize(s));
-        vector<int32_t> zc;
-        for (int c = 0; c < Nc; ++c) if (cro[c + 1] == cro[c]) zc.push_back(c);
-        e->d_zero_cams.upload(zc.data(), zc.size(), s);
-        CU_TRY(cudaStreamSynchronize(s));
-        RS.cam_cnt = e->d_cam_cnt.p; RS.zero_cams = e->d_zero_cams.p; RS.n_zero = int(zc.size()); RS.fuse = e->fuse_gather;
     }
     pt_.tick("schedule uploads, rows alloc");
-    if (e->scatter_mode == 2 || e->scatter_mode == 3) {   // only the private-accumulator scatters read these
-        e->d_slot.upload(slot.data(), No, s);
-        e->d_spack.upload(spack.data(), No, s);
-    }
-    {
-        const int G = std::max(1, std::min(e->nTiles, e->num_sms * 2));
-        const int ldf = (e->nf + 15) / 16 * 16;
-        e->d_scratch.alloc(size_t(G) * ldf);
-        e->d_scratch.zero(s);
-        e->Sch.slot = e->d_slot.p; e->Sch.spack = e->d_spack.p; e->Sch.scratch = e->d_scratch.p; e->Sch.ldf = ldf; e->Sch.G = G;
-        e->d_redpart.alloc(size_t(kRedSlices) * ldf);
-    }
-
     e->d_tile_off.upload(tile_off.data(), tile_off.size(), s);
     e->d_obs_cam.upload(P->obs_cam + e->ob, No, s);
     e->d_obs_pt.upload(obs_pt.data(), No, s);
@@ -807,10 +811,9 @@ void do_set_problem(ba_engine* e, const ba_problem* P, const DevState* dev = nul
     for (auto* b : {&e->d_intr, &e->d_cintr}) b->alloc(size_t(4) * Ng);
     for (auto* b : {&e->d_pt, &e->d_cpt}) b->alloc(size_t(3) * Np);
     e->d_camrec.alloc(size_t(bak::CAMREC) * Nc); e->d_ccamrec.alloc(size_t(bak::CAMREC) * Nc);
-    // pinhole model: translation columns 3 and 4 share one stored column (ba_kernels.cuh: load_jc); the alternative scatter kernels
-    // (modes 2, 3, 5) read the unpacked layout
-    e->jpack = (e->opt.model == BA_MODEL_PINHOLE && (e->scatter_mode == 4 || e->scatter_mode == 1) && BA_JPACK_DEFAULT) ? 1 : 0;
-    if (const char* v = std::getenv("BA_JPACK")) e->jpack = (std::atoi(v) && e->opt.model == BA_MODEL_PINHOLE && (e->scatter_mode == 4 || e->scatter_mode == 1)) ? 1 : 0;
+    // pinhole model: translation columns 3 and 4 share one stored column (ba_kernels.cuh: load_jc)
+    e->jpack = (e->opt.model == BA_MODEL_PINHOLE && BA_JPACK_DEFAULT) ? 1 : 0;
+    if (const char* v = std::getenv("BA_JPACK")) e->jpack = (std::atoi(v) && e->opt.model == BA_MODEL_PINHOLE) ? 1 : 0;
     e->d_J2.alloc(size_t((e->fi ? 13 : 9) - e->jpack) * e->ldo); e->d_r2.alloc(e->ldo);
     e->d_JcA.alloc(size_t(e->fi ? 12 : 8) * std::max(No, 1));
     e->k1_grid = std::max(1, std::min(e->nTiles, e->num_sms * K1_CTAS_PER_SM));
@@ -841,6 +844,7 @@ void do_set_problem(ba_engine* e, const ba_problem* P, const DevState* dev = nul
     CU_TRY(cudaStreamSynchronize(s));   // host staging vectors go out of scope
     e->traj.clear();
     e->scales_set = false;
+    e->pcg_pred = 0;
     e->has_problem = true;
 
     pt_.tick("p2p, view");
@@ -862,18 +866,16 @@ void do_set_problem(ba_engine* e, const ba_problem* P, const DevState* dev = nul
     e->stats[KID_K5].bytes = no * (jb + 8 + 5) + np * (48 + 4) + 96 * nc;
     e->stats[KID_K7].bytes = no * (jb + 8 + 16) + np * (48 + 24 + 24 + 4) + 48 * nc;
     e->stats[KID_K8].bytes = np * 72 + nc * 144;
-    e->stats[KID_PCGV].bytes = double(e->nf) * 8 * (14 + e->Sch.G * 2) + 288 * nc;
+    e->stats[KID_PCGV].bytes = double(e->nf) * 8 * 14 + 288 * nc;
     e->stats[KID_MISC].bytes = 0;
-    if (e->scatter_mode >= 4) {   // partial-row formulation: + 7 B/obs of schedule, 64 B written per (tile, camera) row, read back by the gather
+    e->stats[KID_GATHER].bytes = 0; e->stats[KID_TAIL].bytes = double(e->nf) * 8 * 12 + 288 * nc;
+    if (e->scatter_mode >= 4) {   // partial-row formulation: 16 B/obs of schedule, one packed row written per (tile, camera) pair, read back by the gather
         const double nr = e->RS.nRows;
         const double rb = 8.0 * bak::ROW_DOUBLES;   // bytes per partial row as stored
         e->stats[KID_K4].bytes = no * (jb + 16 + 16) + np * 24 + rb * nr + 16.0 * e->nTiles;
         e->stats[KID_K5].bytes = no * (jb + 16) + np * 48 + 48 * nc + rb * nr + 16.0 * e->nTiles;
-        e->stats[KID_PCGV].bytes = (rb + 4) * nr + double(e->nf) * 8 * 12 + 288 * nc;
-        if (e->fuse_gather) {   // the by-camera gather (row and row-list reads, y stores) runs inside K4/K5a
-            e->stats[KID_K4].bytes += (rb + 4) * nr + 48 * nc; e->stats[KID_K5].bytes += (rb + 4) * nr + 48 * nc;
-            e->stats[KID_PCGV].bytes -= (rb + 4) * nr;
-        }
+        e->stats[KID_GATHER].bytes = (rb + 4) * nr + 48 * nc;
+        e->stats[KID_PCGV].bytes = e->stats[KID_GATHER].bytes + e->stats[KID_TAIL].bytes;
     }
 }
 
@@ -882,10 +884,11 @@ void do_set_problem(ba_engine* e, const ba_problem* P, const DevState* dev = nul
 namespace {
 
 // ---- kernel sequences ----------------------------------------------------------------------------------------
-inline int cdiv(int a, int b) { return (a + b - 1) / b; }
+inline int cdiv(int a, int b) { return std::max(1, (a + b - 1) / b); }   // never a grid of 0 (every kernel bounds-checks its index)
 constexpr int kNormBlocks = 592;
 
 void read_scalars(ba_engine* e) {
+    launch_check(__FILE__, __LINE__);
     CU_TRY(cudaMemcpyAsync(e->h_scal, e->d_scal.p, sizeof(bak::Scalars), cudaMemcpyDeviceToHost, e->stream));
     g_d2h_bytes += int64_t(sizeof(bak::Scalars));
     CU_TRY(cudaStreamSynchronize(e->stream));
@@ -987,64 +990,56 @@ void launch_sweep(ba_engine* e, int kid, const double* xin, double* yout, const 
            else bak::k_schur_sweep<MODE, false, 0><<<e->nTiles, bak::TILE_OBS, 0, e->stream>>>(e->V, xin, yout, done, partial); }
 }
 
-// Camera-side product F^T(...) by the configured scatter.  Result: in `yout` for mode 1 (L2 atomics), otherwise in the
-// private copies e->d_scratch[0..*G_out) to be reduced by reduce_copies().
-template <int MODE, bool FI>
-void launch_pipe(ba_engine* e, const double* xin, const int* done, int* G_out) {
-    using Cfg = bak::PipeCfg<MODE, FI>;
-    static bool attr_set = false;
-    if (!attr_set) { CU_TRY(cudaFuncSetAttribute(bak::k_schur_pipe<MODE, FI>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(Cfg::SMEM))); attr_set = true; }
-    const int G = std::max(1, std::min(e->nTiles, e->num_sms * Cfg::CTAS_PER_SM));
-    KL(e), bak::k_schur_pipe<MODE, FI><<<G, Cfg::THREADS, Cfg::SMEM, e->stream>>>(e->V, e->Sch, xin, done);
-    *G_out = G;
+// K4 / K5a by the configured scatter: 1 = L2 atomics straight into `yout` (k_schur_sweep); 4 = partial rows, one CTA per
+// tile (k_schur_rows); 6 = partial rows, persistent streaming kernel (k_schur_stream).  4 and 6 leave the rows for the by-camera gather.
+template <int MODE, bool FI, int PK>
+void launch_stream(ba_engine* e, const double* xin, double* yout, const int* done, bool chain) {
+    using Cfg = bak::StreamCfg<MODE, FI, PK>;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(unsigned(std::max(1, std::min(e->num_sms, e->nTiles)))); cfg.blockDim = dim3(Cfg::THREADS);
+    cfg.dynamicSmemBytes = Cfg::SMEM; cfg.stream = e->stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = (chain && e->pdl) ? 1 : 0;
+    KL(e);
+    CU_TRY(cudaLaunchKernelEx(&cfg, bak::k_schur_stream<MODE, FI, PK>, e->V, e->RS, xin, yout, done));
 }
 
-// Persistent software-pipelined K4/K5a (ba_rows_pipe.cuh): G = CTAs that are co-resident, each walking tiles b, b+G, ...
-template <int MODE, bool FI>
-void launch_rows_pipe(ba_engine* e, const double* xin, double* yout, const int* done) {
-    using Cfg = bak::RowsPipeCfg<MODE, FI>;
-    static bool attr_set = false;
-    if (!attr_set) { CU_TRY(cudaFuncSetAttribute(bak::k_schur_rows_pipe<MODE, FI>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(Cfg::SMEM))); attr_set = true; }
-    const int G = std::max(1, std::min(e->nTiles, e->num_sms * Cfg::CTAS_PER_SM));
-    KL(e), bak::k_schur_rows_pipe<MODE, FI><<<G, bak::TILE_OBS, Cfg::SMEM, e->stream>>>(e->V, e->RS, xin, yout, done);
+template <int MODE, bool FI, int PK>
+void set_stream_attr() {
+    CU_TRY(cudaFuncSetAttribute(bak::k_schur_stream<MODE, FI, PK>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(bak::StreamCfg<MODE, FI, PK>::SMEM)));
+}
+// Once per engine (i.e. per device): the streaming kernels use more dynamic shared memory than the default limit.
+void set_stream_attrs(ba_engine* e) {
+    if (e->stream_attr_set) return;
+    set_stream_attr<bak::SWEEP_MATVEC, false, 0>(); set_stream_attr<bak::SWEEP_MATVEC, false, 1>();
+    set_stream_attr<bak::SWEEP_MATVEC, true, 0>();  set_stream_attr<bak::SWEEP_MATVEC, true, 1>();
+    set_stream_attr<bak::SWEEP_RHS, false, 0>();    set_stream_attr<bak::SWEEP_RHS, false, 1>();
+    set_stream_attr<bak::SWEEP_RHS, true, 0>();     set_stream_attr<bak::SWEEP_RHS, true, 1>();
+    e->stream_attr_set = true;
 }
 
 template <int MODE>
-void launch_scatter(ba_engine* e, int kid, const double* xin, double* yout, const int* done, int* G_out) {
-    *G_out = 0;
-    if (e->nTiles == 0) {   // a rank without observations: the fused gather has nobody to store its (zero) result
-        if (e->fuse_gather && e->scatter_mode == 4) CU_TRY(cudaMemsetAsync(yout, 0, size_t(6) * e->Nc * sizeof(double), e->stream));
-        return;
-    }
-    if (e->scatter_mode == 1) { launch_sweep<MODE>(e, kid, xin, yout, done, nullptr); return; }
+void launch_scatter(ba_engine* e, int kid, const double* xin, double* yout, const int* done) {
+    if (e->nTiles == 0) return;
+    if (e->scatter_eff == 1) { launch_sweep<MODE>(e, kid, xin, yout, done, nullptr); return; }
     const bool sample = kid != KID_K5 || e->stats[KID_K5].launches % e->k5_sample_stride == 0;
-    LaunchTimer t(e, kid, sample);
-    if (e->scatter_mode == 5) {
-        if (e->fi && e->Ng > 1) CU_TRY(cudaMemsetAsync(yout + 6 * e->Nc, 0, size_t(4) * e->Ng * sizeof(double), e->stream));
-        if (e->fi) launch_rows_pipe<MODE, true>(e, xin, yout, done);
-        else launch_rows_pipe<MODE, false>(e, xin, yout, done);
+    LaunchTimer t(e, kid, sample, kid == KID_K5 ? e->pcg_tag : -1);
+    if (e->fi && e->Ng > 1) CU_TRY(cudaMemsetAsync(yout + 6 * e->Nc, 0, size_t(4) * e->Ng * sizeof(double), e->stream));
+    // K5a goes down the PDL chain; K4 is an ordinary launch (both griddepcontrol instructions are no-ops there)
+    const bool chain = MODE == bak::SWEEP_MATVEC;
+    if (e->scatter_eff == 6) {
+        if (e->fi) { if (e->jpack) launch_stream<MODE, true, 1>(e, xin, yout, done, chain); else launch_stream<MODE, true, 0>(e, xin, yout, done, chain); }
+        else { if (e->jpack) launch_stream<MODE, false, 1>(e, xin, yout, done, chain); else launch_stream<MODE, false, 0>(e, xin, yout, done, chain); }
         return;
     }
-    if (e->scatter_mode == 4) {
-        if (e->fi && e->Ng > 1) CU_TRY(cudaMemsetAsync(yout + 6 * e->Nc, 0, size_t(4) * e->Ng * sizeof(double), e->stream));
-        // K5a goes down the PDL chain (launch_chain); K4 is an ordinary launch (both instructions are no-ops there)
-        const bool chain = MODE == bak::SWEEP_MATVEC;
-        auto go = [&](auto kern) {
-            if (chain) launch_chain(e, kern, dim3(e->nTiles), dim3(bak::TILE_OBS), e->V, e->RS, xin, yout, done);
-            else { KL(e); kern<<<e->nTiles, bak::TILE_OBS, 0, e->stream>>>(e->V, e->RS, xin, yout, done); }
-        };
-        if (e->fi) { if (e->jpack) go(bak::k_schur_rows<MODE, true, 1>); else go(bak::k_schur_rows<MODE, true, 0>); }
-        else { if (e->jpack) go(bak::k_schur_rows<MODE, false, 1>); else go(bak::k_schur_rows<MODE, false, 0>); }
-        return;
-    }
-    if (e->scatter_mode == 2) {
-        if (e->fi) KL(e), bak::k_schur_scatter<MODE, true><<<e->Sch.G, bak::TILE_OBS, 0, e->stream>>>(e->V, e->Sch, xin, done);
-        else KL(e), bak::k_schur_scatter<MODE, false><<<e->Sch.G, bak::TILE_OBS, 0, e->stream>>>(e->V, e->Sch, xin, done);
-        *G_out = e->Sch.G;
-    } else {
-        if (e->fi) launch_pipe<MODE, true>(e, xin, done, G_out);
-        else launch_pipe<MODE, false>(e, xin, done, G_out);
-    }
+    auto go = [&](auto kern) {
+        if (chain) launch_chain(e, kern, dim3(e->nTiles), dim3(bak::TILE_OBS), e->V, e->RS, xin, yout, done);
+        else { KL(e); kern<<<e->nTiles, bak::TILE_OBS, 0, e->stream>>>(e->V, e->RS, xin, yout, done); }
+    };
+    if (e->fi) { if (e->jpack) go(bak::k_schur_rows<MODE, true, 1>); else go(bak::k_schur_rows<MODE, true, 0>); }
+    else { if (e->jpack) go(bak::k_schur_rows<MODE, false, 1>); else go(bak::k_schur_rows<MODE, false, 0>); }
 }
 
 // One linear solve of the LM step at trust-region radius `radius` (K3, K4, PCG with K5, K7).  Leaves the step in
@@ -1053,9 +1048,9 @@ int solve_linear(ba_engine* e, double radius, double* rel_out, double lambda = 0
     cudaStream_t s = e->stream;
     bak::Scalars* sc = e->d_scal.p;
     const bak::LmParams lm{radius, e->opt.min_lm_diagonal, e->opt.max_lm_diagonal, e->opt.lm_policy == BA_POLICY_G2O ? 1 : 0, lambda};
-    const bool priv = e->scatter_mode == 2 || e->scatter_mode == 3;
-    const int vblocks = std::max(1, std::min(cdiv(e->nf, bak::PCG_BLOCK), 2 * e->num_sms));
-    const int cblocks = std::max(1, cdiv((e->Nc + e->Ng) * 8, bak::PCG_BLOCK));
+    const bool rowsm = e->scatter_eff >= 4;
+    const int gblocks = e->Nc + 1;
+    const dim3 gthreads(bak::GATHER_WARPS * 32);
     CU_TRY(cudaMemsetAsync(&sc->bad_lin, 0, sizeof(int), s));
     if (e->Np > 0) { LaunchTimer t(e, KID_K3P); KL(e), bak::k3_point_blocks<<<cdiv(e->Np, 256), 256, 0, s>>>(e->V, lm, &sc->bad_lin); }
     { LaunchTimer t(e, KID_K3C);
@@ -1066,28 +1061,11 @@ int solve_linear(ba_engine* e, double radius, double* rel_out, double lambda = 0
           allreduce_sum(e, e->d_sdiag.p, size_t(36) * e->Nc);
           KL(e), bak::k3_schur_jacobi_blocks<<<cdiv(e->Nc, 128), 128, 0, s>>>(e->Nc, e->Hcc(), e->d_Df2.p, e->d_sdiag.p, e->d_Minv.p);
       } }
-    // Source of k_pcg_q's reduction: mode 2 sums the G private copies directly (and re-zeroes them); mode 3 first folds
-    // them into kRedSlices slices with a wide grid (k_reduce_copies), the pipe kernel clears its own copy on entry.
-    auto reduce_src = [&](int G, const int* done, double*& src, int& nsrc) {
-        src = e->d_scratch.p; nsrc = G;
-        if (e->scatter_mode == 3 && G > 0) {
-            dim3 grid(cdiv(e->nf, 256), kRedSlices);
-            KL(e), bak::k_reduce_copies<<<grid, 256, 0, s>>>(e->nf, G, e->Sch.ldf, e->d_scratch.p, kRedSlices, e->d_redpart.p, done);
-            src = e->d_redpart.p; nsrc = kRedSlices;
-        }
-    };
     // reduced right-hand side b = F^T (r - E vp) = gc - F^T E vp
-    if (e->scatter_mode == 1) e->d_b.zero(s);
-    int G = 0;
-    launch_scatter<bak::SWEEP_RHS>(e, KID_K4, nullptr, e->d_b.p, nullptr, &G);
-    const bool rowsm = e->scatter_mode >= 4;
-    const int gblocks = e->Nc + 1;
-    if (rowsm && e->fuse_gather) {   // K4 delivered b itself (fused gather)
-    } else if (rowsm) { LaunchTimer t(e, KID_PCGV);
-        KL(e), bak::k_camera_gather<<<gblocks, bak::GATHER_WARPS * 32, 0, s>>>(e->Nc, e->Ng, e->fi, e->nTiles, e->RS, nullptr, nullptr, e->d_b.p, nullptr, nullptr, 0);
-    } else if (priv) { LaunchTimer t(e, KID_PCGV);
-        double* src; int nsrc; reduce_src(G, nullptr, src, nsrc);
-        KL(e), bak::k_pcg_q<<<vblocks, bak::PCG_BLOCK, 0, s>>>(e->nf, nsrc, e->Sch.ldf, src, nullptr, nullptr, e->d_b.p, nullptr, nullptr, 1, 0); }
+    if (!rowsm || e->nTiles == 0) e->d_b.zero(s);
+    launch_scatter<bak::SWEEP_RHS>(e, KID_K4, nullptr, e->d_b.p, nullptr);
+    if (rowsm && e->nTiles > 0) { LaunchTimer t(e, KID_GATHER);
+        KL(e), bak::k_camera_gather<<<gblocks, gthreads, 0, s>>>(e->Nc, e->Ng, e->fi, e->nTiles, e->RS, nullptr, nullptr, e->d_b.p, nullptr, nullptr, 0); }
     allreduce_sum(e, e->d_b.p, e->nf);
     if (e->dense) {   // direct solve (ba_dense.cuh): S formed densely, Cholesky with the right-hand side as an extra row, no host round trip
         const bak::DenseView& D = e->DV;
@@ -1124,57 +1102,67 @@ int solve_linear(ba_engine* e, double radius, double* rel_out, double lambda = 0
     const bak::PcgParams pp{e->opt.pcg_max_iterations, e->opt.pcg_forcing, e->opt.pcg_rel_tolerance, e->opt.eta};
     { LaunchTimer t(e, KID_PCGV);
       KL(e), bak::k_pcg_init2<<<1, 1024, 0, s>>>(e->nf, e->Nc, e->d_Minv.p, e->d_b.p, e->d_x.p, e->d_r.p, e->d_z.p, e->d_p.p, &sc->pcg); }
-    if (e->scatter_mode == 1) e->d_y.zero(s);
-    const int batch = 8;
+    // PCG iterations (K5a -> K5b -> cluster tail, a chain of programmatic dependent launches) go out in batches without host sync; a
+    // device-side `done` flag turns the rest of a batch into no-ops once the stop test fires, and the host reads the PCG state once
+    // per batch.  Fixed tolerance: iteration counts of consecutive linear solves differ by a few, so the first batch is the previous
+    // solve's count minus a margin and the remainder goes in eights (2-3 read-backs per linear solve).  Forcing sequence (a handful
+    // of iterations per solve): 2, 4, 8, 8, ...
+    int batch = e->opt.pcg_forcing ? 2 : (e->pcg_pred > 16 ? e->pcg_pred - 4 : 8);
+    const size_t pend0 = e->pending.size();
+    int launched = 0;
     bak::TailArgs ta{};
     ta.Nc = e->Nc; ta.Ng = e->Ng; ta.fi = e->fi; ta.Minv = e->d_Minv.p; ta.b = e->d_b.p; ta.Df2 = e->d_Df2.p;
     ta.y = e->d_y.p; ta.p = e->d_p.p; ta.x = e->d_x.p; ta.r = e->d_r.p; ta.z = e->d_z.p; ta.st = &sc->pcg; ta.pp = pp;
+    ta.dotp = e->d_part1.p; ta.ndot = gblocks;
     const bool multi = e->opt.world_size > 1;
+    const bool no_rows = !rowsm || e->nTiles == 0;   // y is accumulated in d_y by atomics (or stays zero on a rank without observations)
     for (;;) {
         for (int i = 0; i < batch; ++i) {
+            ++launched;
+            e->pcg_tag = launched;
             const bool sample = e->stats[KID_K5].launches % e->k5_sample_stride == 0;
-            double* ydst = e->d_y.p;
-            if (rowsm && e->fuse_gather && multi && e->p2p.on) {   // fused gather writes straight into this rank's exchange slot
-                ta.seq = ++e->p2p.seq; ta.P = e->p2p.view;
-                ydst = e->p2p.view.data[e->p2p.view.rank] + size_t(ta.seq & 1u) * e->p2p.view.ldf;
+            if (no_rows) e->d_y.zero(s);
+            launch_scatter<bak::SWEEP_MATVEC>(e, KID_K5, e->d_p.p, e->d_y.p, &sc->pcg.done);
+            LaunchTimer t(e, KID_PCGV, sample, launched);
+            // y from the rows (or already in d_y); what is left for the tail: mode 0 = q and the shares of p.q are there (one GPU),
+            // 1 = y is complete in local memory, 2 = pull the ranks' slots from peer memory (ba_p2p.cuh)
+            ta.mode = 1;
+            if (multi && e->p2p.on) {   // one-shot NVLink all-reduce: local gather here, flags + pull + sum inside the tail
+                ta.seq = ++e->p2p.seq; ta.P = e->p2p.view; ta.mode = 2;
+                LaunchTimer tg(e, KID_GATHER, sample, launched);
+                if (no_rows) {   // this rank's slot <- d_y
+                    double* mine = e->p2p.view.data[e->p2p.view.rank] + size_t(ta.seq & 1u) * e->p2p.view.ldf;
+                    CU_TRY(cudaMemcpyAsync(mine, e->d_y.p, size_t(e->nf) * sizeof(double), cudaMemcpyDeviceToDevice, s));
+                } else launch_chain(e, bak::k_camera_gather_push, dim3(gblocks), gthreads, e->Nc, e->Ng, e->fi, e->nTiles, e->RS, e->d_y.p, e->p2p.view, ta.seq, &sc->pcg, 1);
+            } else if (multi) {
+                { LaunchTimer tg(e, KID_GATHER, sample, launched);
+                  if (!no_rows) KL(e), bak::k_camera_gather<<<gblocks, gthreads, 0, s>>>(e->Nc, e->Ng, e->fi, e->nTiles, e->RS, nullptr, nullptr, e->d_y.p, nullptr, &sc->pcg, 0); }
+                allreduce_sum(e, e->d_y.p, e->nf);
+            } else if (!no_rows) {   // one GPU: the gather forms q and the shares of p.q as well
+                LaunchTimer tg(e, KID_GATHER, sample, launched);
+                launch_chain(e, bak::k_camera_gather, dim3(gblocks), gthreads, e->Nc, e->Ng, e->fi, e->nTiles, e->RS, e->d_Df2.p, e->d_p.p, e->d_y.p, e->d_part1.p, &sc->pcg, 1);
+                ta.mode = 0;
             }
-            launch_scatter<bak::SWEEP_MATVEC>(e, KID_K5, e->d_p.p, ydst, &sc->pcg.done, &G);
-            LaunchTimer t(e, KID_PCGV, sample);
-            double* src = nullptr; int nsrc = 0;
-            // y (and, on one GPU, q = y + Df2 p and alpha) from the scatter mode's own reduction; tail.mode says what is left to do
-            ta.mode = 0;
-            if (rowsm && e->fuse_gather) {
-                if (multi && e->p2p.on) ta.mode = 2;
-                else { if (multi) allreduce_sum(e, e->d_y.p, e->nf); ta.mode = 1; }
-            } else if (rowsm) {
-                if (multi && e->p2p.on) {   // one-shot NVLink all-reduce: local gather + flags here, the pull and the sum inside the tail (ba_p2p.cuh)
-                    ta.seq = ++e->p2p.seq; ta.P = e->p2p.view; ta.mode = 2;
-                    launch_chain(e, bak::k_camera_gather_push, dim3(gblocks), dim3(bak::GATHER_WARPS * 32), e->Nc, e->Ng, e->fi, e->nTiles, e->RS, e->d_y.p, e->p2p.view, ta.seq, &sc->pcg, 1);
-                } else if (multi) {
-                    KL(e), bak::k_camera_gather<<<gblocks, bak::GATHER_WARPS * 32, 0, s>>>(e->Nc, e->Ng, e->fi, e->nTiles, e->RS, nullptr, nullptr, e->d_y.p, nullptr, &sc->pcg, 0);
-                    allreduce_sum(e, e->d_y.p, e->nf);
-                    ta.mode = 1;
-                } else {   // one GPU: plain gather (no ticket); q, p.q and alpha are the tail's
-                    launch_chain(e, bak::k_camera_gather, dim3(gblocks), dim3(bak::GATHER_WARPS * 32), e->Nc, e->Ng, e->fi, e->nTiles, e->RS, nullptr, nullptr, e->d_y.p, nullptr, &sc->pcg, 0);
-                    ta.mode = 1;
-                }
-            } else {
-                if (priv) reduce_src(G, &sc->pcg.done, src, nsrc);
-                if (multi) {   // reduce the private copies, all-reduce across ranks; the dot product is the tail's
-                    if (priv) KL(e), bak::k_pcg_q<<<vblocks, bak::PCG_BLOCK, 0, s>>>(e->nf, nsrc, e->Sch.ldf, src, nullptr, nullptr, e->d_y.p, nullptr, nullptr, 1, 0);
-                    allreduce_sum(e, e->d_y.p, e->nf);
-                    ta.mode = 1;
-                } else {
-                    KL(e), bak::k_pcg_q<<<vblocks, bak::PCG_BLOCK, 0, s>>>(e->nf, nsrc, e->Sch.ldf, src, e->d_Df2.p, e->d_p.p, e->d_y.p, e->d_part1.p, &sc->pcg, priv ? 1 : 0, 1);
-                }
-            }
-            // x, r, z, rho, beta, stop test and the new search direction: one thread-block cluster (ba_pcg_cluster.cuh)
+            // q, alpha, x, r, z, rho, beta, stop test and the new search direction: one thread-block cluster (ba_pcg_cluster.cuh)
+            LaunchTimer tt(e, KID_TAIL, sample, launched);
             launch_chain(e, bak::k_pcg_tail, dim3(bak::TAIL_CL), dim3(bak::TAIL_THREADS), ta);
-            if (e->scatter_mode == 1) e->d_y.zero(s);
         }
         read_scalars(e);
         if (e->h_scal->bad_lin & 8) throw BaFail{BA_ERR_NCCL, "peer-memory all-reduce timed out waiting for another rank"};
         if (e->h_scal->pcg.done) break;
+        batch = e->opt.pcg_forcing ? std::min(2 * batch, 8) : 8;
+    }
+    e->pcg_tag = -1;
+    {   // launches after the stop test fired did no work: they are neither counted nor timed (ba_get_kernel_stats)
+        const int real = e->h_scal->pcg.k;
+        if (real > 0) e->pcg_pred = real;
+        if (launched > real) {
+            for (int kid : {KID_K5, KID_PCGV, KID_GATHER, KID_TAIL}) e->stats[kid].launches = std::max<int64_t>(0, e->stats[kid].launches - (launched - real));
+            for (size_t i = pend0; i < e->pending.size(); ++i) {
+                ba_engine::Pending& q = e->pending[i];
+                if (q.tag > real && q.kid >= 0) { --e->stats[q.kid].timed; q.kid = -1; }
+            }
+        }
     }
     *rel_out = e->h_scal->pcg.rel;
     if (e->h_scal->bad_lin || e->h_scal->pcg.done == 3) return -1;
@@ -1209,6 +1197,7 @@ void lm_solve(ba_engine* e) {
         S.termination = term; S.usable = (term != BA_TERM_FAILURE); S.final_cost = cost; S.num_iterations = int(e->traj.size());
         if (!e->traj.empty() && e->traj.back().radius > 0.0) e->last_radius = e->traj.back().radius;
         std::snprintf(S.message, sizeof S.message, "%s", msg);
+        launch_check(__FILE__, __LINE__);
         CU_TRY(cudaEventRecord(e->ev_t1, s));
         CU_TRY(cudaEventSynchronize(e->ev_t1));
         float ms = 0.f;
@@ -1318,6 +1307,7 @@ void lm_solve_g2o(ba_engine* e) {
     auto finish = [&](int term, const char* msg, double cost) {
         S.termination = term; S.usable = (term != BA_TERM_FAILURE); S.final_cost = cost; S.num_iterations = int(e->traj.size());
         std::snprintf(S.message, sizeof S.message, "%s", msg);
+        launch_check(__FILE__, __LINE__);
         CU_TRY(cudaEventRecord(e->ev_t1, s));
         CU_TRY(cudaEventSynchronize(e->ev_t1));
         float ms = 0.f;
@@ -1433,13 +1423,7 @@ int ba_create(const ba_options* opt, ba_engine** out) {
     if (opt->model != BA_MODEL_PINHOLE && opt->model != BA_MODEL_SNAVELY) return fail(nullptr, BA_ERR_INVALID_ARGUMENT, "unknown residual model");
     if (opt->lm_policy == BA_POLICY_G2O && opt->model != BA_MODEL_PINHOLE) return fail(nullptr, BA_ERR_UNSUPPORTED, "g2o policy: EdgeSE3ProjectXYZ is the pinhole model");
     if (opt->lm_policy == BA_POLICY_G2O && opt->intrinsics_free) return fail(nullptr, BA_ERR_UNSUPPORTED, "g2o policy: EdgeSE3ProjectXYZ has constant pinhole intrinsics (set intrinsics_free = 0)");
-    if (opt->preconditioner != BA_PRECOND_JACOBI) {
-        // BA_PRECOND_SCHUR_JACOBI is written (k_schur_diag, k3_schur_jacobi_blocks) but has not run on hardware yet: it stays behind an explicit
-        // opt-in until tests/test_engine_gpu.py::test_schur_jacobi_preconditioner has passed on a B200
-        const char* x = std::getenv("BA_EXPERIMENTAL_SCHUR_JACOBI");
-        if (opt->preconditioner != BA_PRECOND_SCHUR_JACOBI || !x || std::atoi(x) != 1)
-            return fail(nullptr, BA_ERR_UNSUPPORTED, "preconditioner not enabled in the CUDA engine (SCHUR_JACOBI: set BA_EXPERIMENTAL_SCHUR_JACOBI=1)");
-    }
+    if (opt->preconditioner != BA_PRECOND_JACOBI && opt->preconditioner != BA_PRECOND_SCHUR_JACOBI) return fail(nullptr, BA_ERR_INVALID_ARGUMENT, "unknown preconditioner");
     if (opt->world_size < 1 || opt->rank < 0 || opt->rank >= opt->world_size) return fail(nullptr, BA_ERR_INVALID_ARGUMENT, "bad rank/world_size");
     if (opt->world_size > 1 && !opt->nccl_unique_id) return fail(nullptr, BA_ERR_INVALID_ARGUMENT, "world_size > 1 needs nccl_unique_id");
     int ndev = 0;
@@ -1456,12 +1440,21 @@ int ba_create(const ba_options* opt, ba_engine** out) {
         cudaDeviceProp prop{};
         CU_TRY(cudaGetDeviceProperties(&prop, e->device));
         e->num_sms = prop.multiProcessorCount;
-        e->scatter_mode = (opt->scatter_mode >= 1 && opt->scatter_mode <= 5) ? opt->scatter_mode : 4;
+        e->scatter_mode = (opt->scatter_mode == 1 || opt->scatter_mode == 4 || opt->scatter_mode == 6) ? opt->scatter_mode : 0;   // 0: auto
+        set_stream_attrs(e);
         if (const char* g = std::getenv("BA_L2_FETCH")) CU_TRY(cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, size_t(std::atoi(g))));   // experiment knob: 32 / 64 / 128
         if (const char* v = std::getenv("BA_K5_SAMPLE")) e->k5_sample_stride = std::max(1, std::atoi(v));
         e->pdl = BA_PDL_DEFAULT;
         if (const char* v = std::getenv("BA_PDL")) e->pdl = std::atoi(v) ? 1 : 0;
-        if (prop.major < 10) throw BaFail{BA_ERR_CUDA, std::string("device ") + prop.name + " is not sm_100-class; this library holds sm_100a code only"};
+        // sm_100a images are architecture-specific: they run on compute capability 10.0 only (not on 10.3 / 12.x); probe one kernel as well
+        if (prop.major != 10 || prop.minor != 0)
+            throw BaFail{BA_ERR_CUDA, std::string("device ") + prop.name + " has compute capability " + std::to_string(prop.major) + "." + std::to_string(prop.minor) +
+                                          "; this library holds sm_100a code only (compute capability 10.0) and has no CPU fallback"};
+        {
+            cudaFuncAttributes fa{};
+            const cudaError_t pe = cudaFuncGetAttributes(&fa, bak::k0_camera_precompute);
+            if (pe != cudaSuccess) { cudaGetLastError(); throw BaFail{BA_ERR_CUDA, std::string("no sm_100a kernel image usable on ") + prop.name + ": " + cudaGetErrorString(pe)}; }
+        }
         if (opt->stream) e->stream = static_cast<cudaStream_t>(opt->stream);
         else { CU_TRY(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking)); e->own_stream = true; }
         CU_TRY(cudaMallocHost(reinterpret_cast<void**>(&e->h_scal), sizeof(bak::Scalars)));
@@ -1615,15 +1608,29 @@ int ba_get_trajectory(ba_engine* e, ba_iter_record* out, int32_t cap, int32_t* n
 int ba_get_structure(ba_engine* e, int32_t* perm_by_cam, int32_t* cam_off, int32_t* pt_off, int32_t* schur_pairs, int64_t pairs_cap, int64_t* n_pairs) {
     if (!e) return BA_ERR_INVALID_ARGUMENT;
     if (!e->has_problem) return fail(e, BA_ERR_NO_PROBLEM, "no problem set");
-    // Global canonical structure (independent of sharding), rebuilt on the host from the index arrays kept at set_problem.
+    // One GPU: the arrays the kernels consume, read back from the device (d_perm / d_cam_off / d_pt_off as the threaded counting sorts
+    // of ba_set_problem built them).  Several GPUs: every rank holds the schedule of its own shard only, so the global canonical
+    // structure (independent of sharding) is rebuilt on the host from the index arrays kept at ba_set_problem.
     const int Nc = e->Nc, Np = e->NpG, No = e->NoG;
     vector<int32_t> po(size_t(Np) + 1, 0), co(size_t(Nc) + 1, 0);
-    for (int o = 0; o < No; ++o) { ++po[e->h_obs_pt[o] + 1]; ++co[e->h_obs_cam[o] + 1]; }
-    for (int p = 0; p < Np; ++p) po[p + 1] += po[p];
-    for (int c = 0; c < Nc; ++c) co[c + 1] += co[c];
+    if (e->opt.world_size == 1) {
+        const int rc = guarded(e, [&] {
+            CU_TRY(cudaSetDevice(e->device));
+            CU_TRY(cudaStreamSynchronize(e->stream));
+            CU_TRY(cudaMemcpy(po.data(), e->d_pt_off.p, po.size() * sizeof(int32_t), cudaMemcpyDeviceToHost));
+            CU_TRY(cudaMemcpy(co.data(), e->d_cam_off.p, co.size() * sizeof(int32_t), cudaMemcpyDeviceToHost));
+            if (perm_by_cam && No) CU_TRY(cudaMemcpy(perm_by_cam, e->d_perm.p, size_t(No) * sizeof(int32_t), cudaMemcpyDeviceToHost));
+            g_d2h_bytes += int64_t(po.size() + co.size() + (perm_by_cam ? No : 0)) * 4;
+        });
+        if (rc != BA_OK) return rc;
+    } else {
+        for (int o = 0; o < No; ++o) { ++po[e->h_obs_pt[o] + 1]; ++co[e->h_obs_cam[o] + 1]; }
+        for (int p = 0; p < Np; ++p) po[p + 1] += po[p];
+        for (int c = 0; c < Nc; ++c) co[c + 1] += co[c];
+        if (perm_by_cam) { vector<int32_t> cur(co.begin(), co.end() - 1); for (int o = 0; o < No; ++o) perm_by_cam[cur[e->h_obs_cam[o]]++] = o; }
+    }
     if (pt_off) std::copy(po.begin(), po.end(), pt_off);
     if (cam_off) std::copy(co.begin(), co.end(), cam_off);
-    if (perm_by_cam) { vector<int32_t> cur(co.begin(), co.end() - 1); for (int o = 0; o < No; ++o) perm_by_cam[cur[e->h_obs_cam[o]]++] = o; }
     if (schur_pairs || n_pairs) {
         // co-visibility bitset, one row per pose: bit j of row i set iff i<j are both free and share a point
         const size_t words = (size_t(Nc) + 63) / 64;
@@ -1754,7 +1761,7 @@ void ba_destroy(ba_engine* e) {
         cudaStreamSetAttribute(e->stream, cudaStreamAttributeAccessPolicyWindow, &attr);
         cudaCtxResetPersistingL2Cache();
     }
-    teardown_p2p(e);
+    teardown_p2p(e, e->err.empty());   // collective: every rank destroys its handle (a handle that failed does not wait for the others)
     if (e->comm) g_nccl.CommDestroy(e->comm);
     for (auto& p : e->pending) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
     for (auto ev : e->ev_pool) cudaEventDestroy(ev);

@@ -8,14 +8,14 @@
 // the three scalars are reduced through distributed shared memory (every CTA writes its partial into its own shared memory, one
 // cluster barrier, every CTA adds the TAIL_CL partials in rank order: no global memory, no atomics, identical bits everywhere).
 //
-// Source of y (mode): 0 = the gather already produced q and alpha (single GPU, k_camera_gather with do_dot);
-//                     1 = y is in local memory, already all-reduced (NCCL path);
+// Source of y (mode): 0 = the gather already produced q = y + Df2 p and one share of p.q per gather CTA (dotp[0..ndot), single GPU):
+//                         every CTA adds the shares in index order (same bits everywhere, no cluster reduction, no second pass over y);
+//                     1 = y is in local memory, already all-reduced (NCCL path, atomics scatter);
 //                     2 = pull the W ranks' slots from peer memory and add them in rank order (ba_p2p.cuh), after waiting for the flags.
 #pragma once
 #include <cooperative_groups.h>
 
 #include "ba_p2p.cuh"
-#include "ba_scatter.cuh"
 
 namespace bak {
 
@@ -26,6 +26,7 @@ struct TailArgs {
     int Nc, Ng, fi, mode;
     const double* Minv; const double* b; const double* Df2;
     double* y; double* p; double* x; double* r; double* z;
+    const double* dotp; int ndot;        // mode 0: the gather CTAs' shares of p.q
     PcgState2* st;
     PcgParams pp;
     PeerView P;
@@ -121,6 +122,19 @@ __global__ void __cluster_dims__(TAIL_CL, 1, 1) __launch_bounds__(TAIL_THREADS) 
         if (!(pq > 0.0) || !isfinite(pq)) {      // breakdown: every CTA sees the same pq
             if (cl.block_rank() == 0 && threadIdx.x == 0) { st->done = 3; st->alpha = 0.0; }
             cl.sync();                           // nobody leaves while its shared memory may still be read
+            return;
+        }
+        alpha = rho / pq;
+    } else {
+        __shared__ double s_pq;
+        double acc = 0.0;
+        for (int i = threadIdx.x; i < A.ndot; i += TAIL_THREADS) acc += A.dotp[i];
+        acc = block_sum(acc, sred);
+        if (threadIdx.x == 0) s_pq = acc;
+        __syncthreads();
+        const double pq = s_pq;
+        if (!(pq > 0.0) || !isfinite(pq)) {      // breakdown: every CTA sees the same pq; no cluster barrier has been entered yet
+            if (cl.block_rank() == 0 && threadIdx.x == 0) { st->done = 3; st->alpha = 0.0; }
             return;
         }
         alpha = rho / pq;

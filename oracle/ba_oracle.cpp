@@ -821,7 +821,7 @@ int ba_get_observations(ba_engine* e, int32_t* obs_cam, int32_t* obs_pt, double*
     if (!e) return BA_ERR_INVALID_ARGUMENT;
     if (!e->has_problem) return fail(e, BA_ERR_NO_PROBLEM, "no problem set");
     if (n) *n = e->No;
-    const int m = std::min<int>(cap, e->No);
+    const int m = std::max(0, std::min<int>(cap, e->No));
     if (obs_cam) std::copy(e->obs_cam.begin(), e->obs_cam.begin() + m, obs_cam);
     if (obs_pt) std::copy(e->obs_pt.begin(), e->obs_pt.begin() + m, obs_pt);
     if (obs_uv) std::copy(e->obs_uv.begin(), e->obs_uv.begin() + size_t(2) * m, obs_uv);
