@@ -251,6 +251,13 @@ class Handle:
         self._check(self.lib.ba_linear_solver_in_use(self.h, C.byref(v)), "ba_linear_solver_in_use")
         return v.value
 
+    def execution_info(self):
+        """dict(linear_solver, scatter_mode, allreduce (0 one GPU, 1 NCCL, 2 NVLink peer memory), host_syncs of the last solve, tiles, rows)."""
+        buf = (C.c_int64 * 6)()
+        n = C.c_int32(0)
+        self._check(self.lib.ba_get_execution_info(self.h, buf, 6, C.byref(n)), "ba_get_execution_info")
+        return dict(zip(("linear_solver", "scatter_mode", "allreduce", "host_syncs", "tiles", "rows"), [int(v) for v in buf]))
+
     def set_profiling(self, mask, stride=1):
         """mask: False/0 off, True/1 every kernel, else a bit mask over kernel_stats() order; stride: time every n-th launch of
         the PCG-loop kernels only (events between launches serialise the chain's programmatic dependent launches)."""

@@ -242,6 +242,7 @@ struct ba_engine {
     } p2p;
     // profiling
     int64_t kernel_launches = 0;
+    int64_t host_syncs = 0;           // Scalars read-backs (stream synchronisations) of the current / last ba_solve
     unsigned profiling = 0;           // bit k set: time kernel id k with CUDA events
     struct Stat { int64_t launches = 0; int64_t timed = 0; double ms = 0.0; double bytes = 0.0; } stats[KID_COUNT];
     int pcg_tag = -1;                 // ordinal of the PCG iteration being launched (LaunchTimer tags; -1 outside the PCG loop)
@@ -889,6 +890,7 @@ constexpr int kNormBlocks = 592;
 
 void read_scalars(ba_engine* e) {
     launch_check(__FILE__, __LINE__);
+    ++e->host_syncs;
     CU_TRY(cudaMemcpyAsync(e->h_scal, e->d_scal.p, sizeof(bak::Scalars), cudaMemcpyDeviceToHost, e->stream));
     g_d2h_bytes += int64_t(sizeof(bak::Scalars));
     CU_TRY(cudaStreamSynchronize(e->stream));
@@ -1192,6 +1194,7 @@ void lm_solve(ba_engine* e) {
     S.num_residuals = 2 * e->NoG;
     e->traj.clear();
     e->kernel_launches = 0;
+    e->host_syncs = 0;
     CU_TRY(cudaEventRecord(e->ev_t0, s));
     auto finish = [&](int term, const char* msg, double cost) {
         S.termination = term; S.usable = (term != BA_TERM_FAILURE); S.final_cost = cost; S.num_iterations = int(e->traj.size());
@@ -1303,6 +1306,7 @@ void lm_solve_g2o(ba_engine* e) {
     S.num_residuals = 2 * e->NoG;
     e->traj.clear();
     e->kernel_launches = 0;
+    e->host_syncs = 0;
     CU_TRY(cudaEventRecord(e->ev_t0, s));
     auto finish = [&](int term, const char* msg, double cost) {
         S.termination = term; S.usable = (term != BA_TERM_FAILURE); S.final_cost = cost; S.num_iterations = int(e->traj.size());
@@ -1441,6 +1445,7 @@ int ba_create(const ba_options* opt, ba_engine** out) {
         CU_TRY(cudaGetDeviceProperties(&prop, e->device));
         e->num_sms = prop.multiProcessorCount;
         e->scatter_mode = (opt->scatter_mode == 1 || opt->scatter_mode == 4 || opt->scatter_mode == 6) ? opt->scatter_mode : 0;   // 0: auto
+        if (e->scatter_mode == 0) if (const char* v = std::getenv("BA_SCATTER_MODE")) { const int m = std::atoi(v); if (m == 1 || m == 4 || m == 6) e->scatter_mode = m; }   // A/B knob for auto
         set_stream_attrs(e);
         if (const char* g = std::getenv("BA_L2_FETCH")) CU_TRY(cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, size_t(std::atoi(g))));   // experiment knob: 32 / 64 / 128
         if (const char* v = std::getenv("BA_K5_SAMPLE")) e->k5_sample_stride = std::max(1, std::atoi(v));
@@ -1744,6 +1749,15 @@ int ba_nccl_unique_id(void* out128) {
     const int r = g_nccl.GetUniqueId(&id);
     if (r != 0) return fail(nullptr, BA_ERR_NCCL, std::string("ncclGetUniqueId: ") + g_nccl.GetErrorString(r));
     std::memcpy(out128, &id, sizeof id);
+    return BA_OK;
+}
+
+int ba_get_execution_info(ba_engine* e, int64_t* info, int32_t cap, int32_t* n) {
+    if (!e || !n) return BA_ERR_INVALID_ARGUMENT;
+    if (!e->has_problem) return fail(e, BA_ERR_NO_PROBLEM, "no problem set");
+    const int64_t v[6] = {e->dense ? BA_LINEAR_EXACT : BA_LINEAR_PCG, e->scatter_eff, e->opt.world_size > 1 ? (e->p2p.on ? 2 : 1) : 0, e->host_syncs, e->nTiles, e->RS.nRows};
+    *n = 6;
+    if (info) for (int i = 0; i < std::min<int>(cap, 6); ++i) info[i] = v[i];
     return BA_OK;
 }
 

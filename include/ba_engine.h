@@ -65,8 +65,7 @@ typedef enum ba_model { BA_MODEL_PINHOLE = 0, BA_MODEL_SNAVELY = 1 } ba_model;
  * reads AUTO as EXACT. */
 typedef enum ba_linear_solver { BA_LINEAR_EXACT = 0, BA_LINEAR_PCG = 1, BA_LINEAR_AUTO = 2 } ba_linear_solver;
 typedef enum ba_preconditioner { BA_PRECOND_JACOBI = 0 /* blockdiag(Hcc + Dc^2) */, BA_PRECOND_SCHUR_JACOBI = 1 /* blockdiag(S) */ } ba_preconditioner;
-/* The CUDA engine runs BA_PRECOND_JACOBI; its BA_PRECOND_SCHUR_JACOBI (k_schur_diag) is written but not yet validated on hardware and is
- * refused unless BA_EXPERIMENTAL_SCHUR_JACOBI=1 is set in the environment.  The CPU oracle implements both. */
+/* SCHUR_JACOBI costs one more by-camera pass per linear solve (k_schur_diag) and saves PCG iterations; engine and oracle implement both. */
 
 /* Which rule selects the first-order branch of AngleAxisRotatePoint. */
 typedef enum ba_taylor_rule { BA_TAYLOR_THETA2_LE_EPS = 0 /* theta^2 <= DBL_EPSILON */, BA_TAYLOR_THETA_IS_ZERO = 1 /* hypot()==0 */ } ba_taylor_rule;
@@ -126,7 +125,8 @@ typedef struct ba_options {
     int32_t world_size;                  /* 1 = single GPU */
     const void* nccl_unique_id;          /* world_size>1: 128-byte ncclUniqueId from ba_nccl_unique_id() on rank 0, broadcast by the caller */
     void*   stream;                      /* engine: cudaStream_t to run on (NULL: the engine creates its own) */
-    int32_t scatter_mode;                /* engine camera-side scatter: 0 = default (4), 1 = red.global.add.f64, 2 = private accumulators, 3 = 2 + bulk-copy pipeline, 4 = partial rows, 5 = 4 as a persistent cp.async pipeline (measured slower) */
+    int32_t scatter_mode;                /* engine camera-side scatter of K4/K5: 0 = auto (6 for problems with at least 4 tiles per SM, else 4), 1 = red.global.add.f64,
+                                            4 = partial rows + by-camera gather, one CTA per tile, 6 = the same rows from the persistent cp.async.bulk streaming kernel */
     int32_t p2p_allreduce;               /* multi-GPU all-reduce of the PCG matvec: 0 = auto (one-shot NVLink peer-memory all-reduce fused into the
                                             K5b gather when every peer buffer can be mapped with CUDA IPC, else NCCL), 1 = NCCL only, 2 = peer memory required */
     int32_t lm_policy;                   /* ba_lm_policy; default CERES */
@@ -233,6 +233,10 @@ int  ba_set_profiling_stride(ba_engine* e, int32_t stride);    /* time only ever
                                                                  * of the chain from the very measurement; ba_get_kernel_stats scales total_ms to all launches */
 int  ba_get_kernel_stats(ba_engine* e, ba_kernel_stat* out, int32_t cap, int32_t* n);
 int  ba_linear_solver_in_use(ba_engine* e, int32_t* solver);  /* after ba_set_problem: BA_LINEAR_EXACT or BA_LINEAR_PCG, what AUTO resolved to for this problem */
+/* Execution facts for reports (bench.py, tools): info[0] = linear solver in use (as ba_linear_solver_in_use), [1] = scatter mode in effect for
+ * the current problem (1, 4 or 6), [2] = all-reduce of the PCG matvec (0: one GPU, 1: NCCL, 2: one-shot NVLink peer memory), [3] = host
+ * synchronisations of the last ba_solve (Scalars read-backs), [4] = tiles and [5] = partial rows of this rank's shard.  The oracle reports zeros. */
+int  ba_get_execution_info(ba_engine* e, int64_t* info, int32_t cap, int32_t* n);
 int  ba_get_io_bytes(int64_t* h2d, int64_t* d2h);              /* cumulative host->device / device->host bytes moved by this library in this process */
 /* Host-only (no device needed): the point ranges of the multi-GPU sharding. Rank r owns points
  * [shard_pt[r], shard_pt[r+1]) and all their observations; ranges are contiguous, cut at point boundaries and

@@ -913,6 +913,12 @@ int ba_get_kernel_stats(ba_engine* e, ba_kernel_stat*, int32_t, int32_t* n) { if
 int ba_linear_solver_in_use(ba_engine* e, int32_t* solver) { if (!e || !solver) return BA_ERR_INVALID_ARGUMENT; *solver = e->opt.linear_solver == BA_LINEAR_PCG ? BA_LINEAR_PCG : BA_LINEAR_EXACT; return BA_OK; }
 int ba_shard_points(int32_t, int32_t, const int32_t*, int32_t, int32_t*) { return BA_ERR_UNSUPPORTED; }   // engine-side host logic; the oracle is single-process
 int ba_nccl_unique_id(void*) { return BA_ERR_UNSUPPORTED; }
+int ba_get_execution_info(ba_engine* e, int64_t* info, int32_t cap, int32_t* n) {
+    if (!e || !n) return BA_ERR_INVALID_ARGUMENT;
+    *n = 6;
+    if (info) for (int i = 0; i < std::min<int>(cap, 6); ++i) info[i] = 0;
+    return BA_OK;
+}
 int ba_get_io_bytes(int64_t* h2d, int64_t* d2h) { if (h2d) *h2d = 0; if (d2h) *d2h = 0; return BA_OK; }
 const char* ba_last_error(const ba_engine* e) { return e ? e->err.c_str() : g_create_error.c_str(); }
 const char* ba_backend(void) { return "cpu-oracle"; }

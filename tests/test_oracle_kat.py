@@ -322,3 +322,61 @@ def test_schur_jacobi_preconditioner_in_the_oracle(ba, oracle):
             assert a.step_is_successful == b.step_is_successful
             assert abs(a.cost - b.cost) <= 1e-9 * abs(b.cost)
     assert 0 < runs["schur"][0].total_pcg_iterations < runs["jacobi"][0].total_pcg_iterations
+
+
+def test_forcing_sequence_q_criterion(ba, oracle):
+    """KAT for the throughput mode's stop rule (Ceres' inexact-Newton Q-criterion, eta = 0.1): the oracle's PCG iteration count of the
+    first LM step equals that of an independent dense numpy PCG on the explicitly formed reduced system, with Q(x) = 1/2 x'Sx - b'x
+    evaluated from its definition (the oracle uses the identity Q = -1/2 x'(b + r))."""
+    P = ba.synth("tiny", seed=3)
+    Nc, Ng, Np, No = P.sizes
+    with oracle.create(oracle.default_options(intrinsics_free=0)) as h:
+        h.set_problem(P)
+        e = h.evaluate()
+    Jc, Jp, r = e["Jc"], e["Jp"], e["r"].reshape(-1)
+    F = np.zeros((2 * No, 6 * Nc)); E = np.zeros((2 * No, 3 * Np))
+    for o in range(No):
+        F[2 * o:2 * o + 2, 6 * P.obs_cam[o]:6 * P.obs_cam[o] + 6] = Jc[o]
+        E[2 * o:2 * o + 2, 3 * P.obs_pt[o]:3 * P.obs_pt[o] + 3] = Jp[o]
+    J = np.hstack([F, E])
+    s = 1.0 / (1.0 + np.sqrt((J * J).sum(axis=0)))                  # Jacobi scaling
+    Js = J * s
+    d2 = np.clip((Js * Js).sum(axis=0), 1e-6, 1e32) / 1e4           # LM diagonal at the initial radius
+    Fs, Es = Js[:, :6 * Nc], Js[:, 6 * Nc:]
+    B = Fs.T @ Fs + np.diag(d2[:6 * Nc])
+    C = Es.T @ Es + np.diag(d2[6 * Nc:])
+    W = Fs.T @ Es
+    Ci = np.linalg.inv(C)
+    S = B - W @ Ci @ W.T
+    b = Fs.T @ r - W @ Ci @ (Es.T @ r)
+    Minv = np.zeros_like(B)
+    for c in range(Nc):
+        sl = slice(6 * c, 6 * c + 6)
+        Minv[sl, sl] = np.linalg.inv(B[sl, sl])
+
+    def pcg_iterations(eta):
+        x = np.zeros_like(b); res = b.copy(); z = Minv @ res; p = z.copy(); rho = res @ z; Q0 = 0.0
+        for k in range(1, 500):
+            q = S @ p
+            alpha = rho / (p @ q)
+            x += alpha * p; res -= alpha * q
+            z = Minv @ res
+            rho_new = res @ z
+            Q1 = 0.5 * x @ S @ x - b @ x
+            if k * (Q1 - Q0) / Q1 < eta:
+                return k
+            Q0 = Q1
+            p = z + (rho_new / rho) * p; rho = rho_new
+        return 500
+
+    for eta in (0.1, 0.01, 1e-4):
+        with oracle.create(oracle.default_options(intrinsics_free=0, linear_solver=1, pcg_forcing=1, eta=eta, pcg_rel_tolerance=0.0, max_num_iterations=1)) as h:
+            h.set_problem(P)
+            h.solve()
+            t = h.trajectory()
+        assert t[1].pcg_iterations == pcg_iterations(eta), eta
+    # and the stop rule buys what it is for: far fewer iterations than the fixed 1e-12 tolerance
+    with oracle.create(oracle.default_options(intrinsics_free=0, linear_solver=1, max_num_iterations=1)) as h:
+        h.set_problem(P)
+        h.solve()
+        assert h.trajectory()[1].pcg_iterations > 3 * pcg_iterations(0.1)

@@ -8,5 +8,5 @@ for spec in "$@"; do
   if [ "$v" = "base" ]; then lib=""; else lib=$PWD/3dreconstruction_b200/csrc/libba_engine_$v.so; fi
   echo "== variant $spec"
   ( [ -n "$lib" ] && export BA_ENGINE_LIB=$lib; for kv in ${envs//,/ }; do export "$kv"; done
-    timeout -s KILL ${AB_TIMEOUT:-90} python tools/quick_gpu.py $SHAPE max_num_iterations=${AB_LM:-3} 2>&1 | grep -E "plain|K1_|K1c|K2c|K3p|K4|K5|PCG|K7|K8|warm|rror|Traceback"; echo "   rc=${PIPESTATUS[0]}" )
+    timeout -s KILL ${AB_TIMEOUT:-90} python tools/quick_gpu.py $SHAPE max_num_iterations=${AB_LM:-3} 2>&1 | grep -E "plain|K0_|K1_|K1c|K2c|K3p|K3c|K4|K5|PCG|K7|K8|misc|warm|rror|Traceback"; echo "   rc=${PIPESTATUS[0]}" )
 done

@@ -2,7 +2,10 @@
 import importlib, json, os, sys, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 ba = importlib.import_module("3dreconstruction_b200")
-PEAK = 6533.2e9
+PEAK = 6553.0e9
+_pk = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "MEASURED_PEAKS.json")
+if os.path.exists(_pk):
+    PEAK = float(json.load(open(_pk))["hbm_gbs"]) * 1e9
 name = sys.argv[1] if len(sys.argv) > 1 else "venice"
 opts = {}
 for a in sys.argv[2:]:
@@ -17,7 +20,7 @@ with ba.Engine(**base) as eng:
     print("warm: term", s.termination, s.message.decode(), "iters", s.num_iterations, "pcg", s.total_pcg_iterations, "cost %.9e -> %.9e" % (s.initial_cost, s.final_cost), "dev %.1f ms" % (s.solve_seconds * 1e3), flush=True)
     eng.reset_state()
     t = time.time(); s = eng.solve(); wall = time.time() - t
-    print("plain: dev %.1f ms wall %.1f ms  LM it/s %.2f" % (s.solve_seconds * 1e3, wall * 1e3, (s.num_iterations - 1) / s.solve_seconds), flush=True)
+    print("plain: dev %.1f ms wall %.1f ms  LM it/s %.2f  pcg %d  launches %d" % (s.solve_seconds * 1e3, wall * 1e3, (s.num_iterations - 1) / s.solve_seconds, s.total_pcg_iterations, s.kernel_launches), eng.execution_info(), flush=True)
     eng.reset_state(); eng.set_profiling(True)
     s = eng.solve()
     print("profiled: dev %.1f ms" % (s.solve_seconds * 1e3))
