@@ -870,7 +870,7 @@ void do_set_problem(ba_engine* e, const ba_problem* P, const DevState* dev = nul
     e->stats[KID_PCGV].bytes = double(e->nf) * 8 * 14 + 288 * nc;
     e->stats[KID_MISC].bytes = 0;
     e->stats[KID_GATHER].bytes = 0; e->stats[KID_TAIL].bytes = double(e->nf) * 8 * 12 + 288 * nc;
-    if (e->scatter_mode >= 4) {   // partial-row formulation: 16 B/obs of schedule, one packed row written per (tile, camera) pair, read back by the gather
+    if (e->scatter_eff >= 4) {   // partial-row formulation: 16 B/obs of schedule, one packed row written per (tile, camera) pair, read back by the gather
         const double nr = e->RS.nRows;
         const double rb = 8.0 * bak::ROW_DOUBLES;   // bytes per partial row as stored
         e->stats[KID_K4].bytes = no * (jb + 16 + 16) + np * 24 + rb * nr + 16.0 * e->nTiles;

@@ -164,9 +164,11 @@ __device__ __forceinline__ void tile_rows(const View& V, const RowSched& S, Tile
 }
 
 // One point with more than TILE_OBS observations (rare): two passes straight from global memory, every observation is its own row.
-// Whole tile group (128 threads) calls; p = the point.
+// Whole tile group (128 threads) calls; p = the point.  (Inlined on purpose: as a real call it takes the View by reference, which makes
+// every thread of every CTA spill the whole kernel-parameter struct to local memory at kernel entry — 25 STL per thread, measured
+// +30 % on K4/K5a.)
 template <int MODE, bool FI, int PK, class Bar>
-__device__ __noinline__ void tile_rows_long(const View& V, const RowSched& S, TileScratch& M, Bar bar, const int tid, const int o0, const int n,
+__device__ __forceinline__ void tile_rows_long(const View& V, const RowSched& S, TileScratch& M, Bar bar, const int tid, const int o0, const int n,
                                             const int hbase, const int p, const double* __restrict__ xin, double* __restrict__ atomic_out,
                                             double (&yi)[4]) {
     const int ioff = 6 * V.Nc;
@@ -380,7 +382,9 @@ k_camera_gather(int Nc, int Ng, int fi, int nTiles, RowSched S, const double* __
             double v = sw[threadIdx.x];
             const int j = 6 * c + threadIdx.x;
             double dot = 0.0;
-            if (qdot) { const double pj = p[j]; v += Df2[j] * pj; dot = pj * v; }
+            // p is the predecessor grid's output and this kernel's CTAs may share an SM with a successor's (the next K5a is launched while
+            // this grid still runs): read it past L1 (ld.global.cg) so that no L1 line of p exists that the PCG tail's update could leave stale
+            if (qdot) { const double pj = __ldcg(p + j); v += Df2[j] * pj; dot = pj * v; }
             y[j] = v;
             if (qdot) {   // lanes 0..5 of warp 0, fixed order
                 double s = 0.0;
@@ -394,7 +398,7 @@ k_camera_gather(int Nc, int Ng, int fi, int nTiles, RowSched S, const double* __
         if (st && st->done) return;
         double dot = 0.0;
         if (fi) gather_intrinsics(Nc, Ng, nTiles, S, y, [&](int j, double v) {
-            if (qdot) { const double pj = p[j]; v += Df2[j] * pj; dot += pj * v; }
+            if (qdot) { const double pj = __ldcg(p + j); v += Df2[j] * pj; dot += pj * v; }
             y[j] = v;
         });
         if (qdot) {   // lane 0 of each warp holds its entries' share

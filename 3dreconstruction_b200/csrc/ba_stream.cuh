@@ -83,13 +83,13 @@ k_schur_stream(View V, RowSched S, const double* __restrict__ xin, double* __res
     constexpr int NG = Cfg::NG, NST = Cfg::NST, NCOL = Cfg::NCOL;
     extern __shared__ __align__(128) unsigned char smem[];
     uint64_t* full = reinterpret_cast<uint64_t*>(smem);            // [NST] producer -> consumers (transaction count)
-    uint64_t* empty = full + NST;                                  // [NST] consumers -> producer (TILE_OBS arrivals)
+    uint64_t* empty = full + NST;                                  // [NST] consumers -> producer (one arrival per warp of the consuming group)
     unsigned char* scratch0 = smem + Cfg::BAR_BYTES;
     unsigned char* stage0 = scratch0 + NG * Cfg::SCR_STRIDE;
 
     pdl_trigger();
     if (threadIdx.x == 0) {
-        for (int s = 0; s < NST; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, TILE_OBS); }
+        for (int s = 0; s < NST; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, TILE_OBS / 32); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
@@ -150,10 +150,15 @@ k_schur_stream(View V, RowSched S, const double* __restrict__ xin, double* __res
     const BarGroup bar{1 + grp};
     pdl_wait();
     if (done_flag && ld_volatile_s32(done_flag)) return;
+    // one arrival per warp hands a stage back: the warp's shared-memory reads and its lane 0's mbarrier arrive go down the same in-order
+    // pipe (128 same-address arrivals per tile cost more than the copies they protect)
+    auto release = [&](int s) { __syncwarp(); if (lane == 0) mbar_arrive(empty + s); };
+    int4 ti_next = grp < my ? __ldg(S.tile_info + blockIdx.x + size_t(grp) * G) : make_int4(0, 0, 0, 0);
     for (int i = grp; i < my; i += NG) {
         const int t = blockIdx.x + i * G;
         const int s = i % NST, use = i / NST;
-        const int4 ti = __ldg(S.tile_info + t);
+        const int4 ti = ti_next;
+        if (i + NG < my) ti_next = __ldg(S.tile_info + t + size_t(NG) * G);      // the next tile's record is in flight during this tile
         const int o0 = ti.x, n = ti.y & 0xffffff, hbase = ti.z, pfirst = ti.w;
         double yi[4] = {0, 0, 0, 0};
         mbar_wait(full + s, unsigned(use) & 1u);
@@ -182,10 +187,10 @@ k_schur_stream(View V, RowSched S, const double* __restrict__ xin, double* __res
                 const double2* H = reinterpret_cast<const double2*>(st + Cfg::AUX_OFF) + 3 * tid;
                 R.h0 = H[0]; R.h1 = H[1]; R.h2 = H[2];
             }
-            mbar_arrive(empty + s);                    // operands are in registers: the stage can be refilled
+            release(s);                                // operands are in registers: the stage can be refilled
             tile_rows<MODE, FI>(V, S, M, bar, tid, n, hbase, pfirst, R, xin, atomic_out, yi);
         } else {
-            mbar_arrive(empty + s);
+            release(s);
             tile_rows_long<MODE, FI, PK>(V, S, M, bar, tid, o0, n, hbase, pfirst, xin, atomic_out, yi);
         }
         if (FI && V.Ng == 1) tile_intr_store(S, M, bar, tid, t, yi);
