@@ -245,6 +245,7 @@ struct ba_engine {
     int64_t host_syncs = 0;           // Scalars read-backs (stream synchronisations) of the current / last ba_solve
     unsigned profiling = 0;           // bit k set: time kernel id k with CUDA events
     struct Stat { int64_t launches = 0; int64_t timed = 0; double ms = 0.0; double bytes = 0.0; } stats[KID_COUNT];
+    int dbg_tail1 = 0;                // BA_TAIL_MODE1
     int pcg_tag = -1;                 // ordinal of the PCG iteration being launched (LaunchTimer tags; -1 outside the PCG loop)
     int pcg_pred = 0;                 // PCG iterations of the previous linear solve on this handle (first batch size)
     int k5_sample_stride = 1;         // time every n-th K5 launch only (events between two launches serialise them; BA_K5_SAMPLE)
@@ -682,16 +683,20 @@ void do_set_problem(ba_engine* e, const ba_problem* P, const DevState* dev = nul
                 if (n > bak::TILE_OBS) { hbase[t + 1] = n; continue; }   // long-point tile: one row per observation, no schedule
                 for (int i = 0; i < n; ++i) key[i] = uint32_t(ocam[o0 + i]) << 9 | uint32_t(i);   // unique keys: std::sort == stable sort by camera
                 std::sort(key, key + n);
+                // Rows: one per maximal run of equal cameras INSIDE a warp's 32 sorted positions (a camera segment that crosses a
+                // 32-boundary gives one row per warp it touches: the fold is a warp-segmented shuffle reduction, ba_rows.cuh).  For the
+                // head of every run: camera | run length << 22 and its row number in the tile; for every position: how many positions
+                // of its run follow it (`lvl1` field of the record).
                 int rank = 0;
                 for (int j = 0; j < n;) {
                     const int cam = int(key[j] >> 9);
                     int k = j;
                     while (k < n && int(key[k] >> 9) == cam) { slot[o0 + (key[k] & 511u)] = static_cast<unsigned char>(k); hpos[o0 + (key[k] & 511u)] = static_cast<unsigned char>(j); ++k; }
-                    spack[o0 + j] = cam | ((k - j) << 22);
-                    hrank[o0 + j] = static_cast<unsigned char>(rank++);
-                    for (int q = j; q < k;) {             // chunk leaders: the head, then every multiple of L1_CHUNK inside the segment
-                        const int nxt = std::min((q / bak::L1_CHUNK + 1) * bak::L1_CHUNK, k);
-                        lvl1[o0 + q] = static_cast<unsigned char>(nxt - q);
+                    for (int q = j; q < k;) {
+                        const int nxt = std::min((q / 32 + 1) * 32, k);     // end of this run: the segment's end or the warp boundary
+                        spack[o0 + q] = cam | ((nxt - q) << 22);
+                        hrank[o0 + q] = static_cast<unsigned char>(rank++);
+                        for (int r = q; r < nxt; ++r) lvl1[o0 + r] = static_cast<unsigned char>(nxt - 1 - r);
                         q = nxt;
                     }
                     j = k;
@@ -1140,6 +1145,9 @@ int solve_linear(ba_engine* e, double radius, double* rel_out, double lambda = 0
                 { LaunchTimer tg(e, KID_GATHER, sample, launched);
                   if (!no_rows) KL(e), bak::k_camera_gather<<<gblocks, gthreads, 0, s>>>(e->Nc, e->Ng, e->fi, e->nTiles, e->RS, nullptr, nullptr, e->d_y.p, nullptr, &sc->pcg, 0); }
                 allreduce_sum(e, e->d_y.p, e->nf);
+            } else if (!no_rows && e->dbg_tail1) {   // BA_TAIL_MODE1=1 (bisecting aid): plain gather, q and p.q by the tail's cluster reduction
+                LaunchTimer tg(e, KID_GATHER, sample, launched);
+                launch_chain(e, bak::k_camera_gather, dim3(gblocks), gthreads, e->Nc, e->Ng, e->fi, e->nTiles, e->RS, nullptr, nullptr, e->d_y.p, nullptr, &sc->pcg, 0);
             } else if (!no_rows) {   // one GPU: the gather forms q and the shares of p.q as well
                 LaunchTimer tg(e, KID_GATHER, sample, launched);
                 launch_chain(e, bak::k_camera_gather, dim3(gblocks), gthreads, e->Nc, e->Ng, e->fi, e->nTiles, e->RS, e->d_Df2.p, e->d_p.p, e->d_y.p, e->d_part1.p, &sc->pcg, 1);
@@ -1451,6 +1459,7 @@ int ba_create(const ba_options* opt, ba_engine** out) {
         if (const char* v = std::getenv("BA_K5_SAMPLE")) e->k5_sample_stride = std::max(1, std::atoi(v));
         e->pdl = BA_PDL_DEFAULT;
         if (const char* v = std::getenv("BA_PDL")) e->pdl = std::atoi(v) ? 1 : 0;
+        if (const char* v = std::getenv("BA_TAIL_MODE1")) e->dbg_tail1 = std::atoi(v) ? 1 : 0;
         // sm_100a images are architecture-specific: they run on compute capability 10.0 only (not on 10.3 / 12.x); probe one kernel as well
         if (prop.major != 10 || prop.minor != 0)
             throw BaFail{BA_ERR_CUDA, std::string("device ") + prop.name + " has compute capability " + std::to_string(prop.major) + "." + std::to_string(prop.minor) +

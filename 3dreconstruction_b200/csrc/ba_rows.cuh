@@ -9,8 +9,8 @@
 //
 // Tile math: thread i = observation i of the tile.  u = Jc p[c] (+ Ji p[g]);  per point W = sum Jp^T u through shared memory (points
 // are contiguous, thread j sums point j), v = Hinv W;  t = u - Jp v;  the 6-vector Jc^T t is written to shared memory at the
-// observation's rank in the tile's static camera-sorted order; segment heads fold their segment (two-level serial sum, fixed order)
-// and store one packed 48-byte row per distinct (tile, camera).  No atomics, no read-modify-write.
+// observation's rank in the tile's static camera-sorted order; each warp then folds 32 sorted positions with a segmented shuffle
+// reduction (fixed tree) and the head of every run of one camera stores one packed 48-byte row.  No atomics, no read-modify-write.
 #pragma once
 #include "ba_pcg.cuh"
 
@@ -20,7 +20,6 @@ namespace bak {
 #define BA_ROW_DOUBLES 6
 #endif
 constexpr int ROW_DOUBLES = BA_ROW_DOUBLES;    // 6: packed 48-byte rows; 8: 64-byte rows (two whole sectors; measured 5 % slower end to end: the pad is written every iteration)
-constexpr int L1_CHUNK = 8;                    // level-1 chunk of the in-tile segmented sum
 constexpr int GATHER_WARPS = 4;                // warps per CTA of the by-camera gather (K5b)
 constexpr int TILE_MAX_PTS = 64;               // points per tile (the streaming kernel reserves 48 bytes of Hinv per point in every stage)
 
@@ -30,9 +29,10 @@ __device__ __forceinline__ double2 row_load(const double2* p) { return __ldcg(p)
 struct RowSched {
     // One 16-byte record per tile position i = o0 + tid:
     //   .x  camera of observation i | sorted position of the head of its camera segment << 24
-    //   .y  slot | lvl1 << 8 | hrank << 16 | lpt << 24   (observation i: rank in the tile's camera-sorted order; sorted position
-    //       tid: rows to fold in level 1, index of this segment head among the tile's heads; observation i: tile-local point)
-    //   .z  sorted position tid: camera | segment length << 22 at segment heads, -1 elsewhere
+    //   .y  slot | rem << 8 | hrank << 16 | lpt << 24   (observation i: rank in the tile's camera-sorted order; sorted position
+    //       tid: positions of its run after it, row number of the run in the tile; observation i: tile-local point)
+    //   .z  sorted position tid: camera | run length << 22 at the head of a run, -1 elsewhere  (run = maximal stretch of one camera
+    //       inside a warp's 32 sorted positions; one partial row per run)
     //   .w  tile-local point tid: first observation | observation count << 16 (0 when tid >= points in tile)
     const int4* tmeta;            // [No]
     const int4* tile_info;        // [nTiles] {o0, n | points << 24 (points = 0 for a long-point tile), first compact row, first local point}
@@ -136,30 +136,28 @@ __device__ __forceinline__ void tile_rows(const View& V, const RowSched& S, Tile
         }
     }
     bar();
-    // level 1: chunk leaders (segment heads and every 8th sorted position) fold their <= 8 rows into their own row
-    if (n1 > 1) {
-        double2* row = reinterpret_cast<double2*>(M.sC[tid]);
-        double2 a = row[0], bq = row[1], cq = row[2];
-        for (int i = 1; i < n1; ++i) {
-            const double2 a2 = row[3 * i], b2 = row[3 * i + 1], c2 = row[3 * i + 2];
-            a.x += a2.x; a.y += a2.y; bq.x += b2.x; bq.y += b2.y; cq.x += c2.x; cq.y += c2.y;
+    // Fold over the camera-sorted rows, one warp per 32 sorted positions: a segmented shuffle reduction (fixed tree => bit-reproducible).
+    // After the step with distance d a lane holds the sum of the rows [lane, min(lane + 2d - 1, end of its run)]; `rem` = positions of
+    // the run after this one (static schedule).  The head of every run stores one compact row.  (The first version folded serially
+    // through shared memory in two levels: ncu showed 60 % of the kernel's shared-memory wavefronts and its longest dependent chains there.)
+    {
+        const int rem = n1;
+        double2 a = make_double2(0.0, 0.0), bq = a, cq = a;
+        if (act) {
+            const double2* row = reinterpret_cast<const double2*>(M.sC[tid]);
+            a = row[0]; bq = row[1]; cq = row[2];
         }
-        row[0] = a; row[1] = bq; row[2] = cq;
-    }
-    bar();
-    // level 2: each segment head adds the chunk leaders of its segment and writes one compact row
-    if (pk >= 0) {
-        const int len = pk >> 22;
-        const int j = tid, end = j + len;
-        const double2* row = reinterpret_cast<const double2*>(M.sC[j]);
-        double2 a = row[0], bq = row[1], cq = row[2];
-        for (int q = (j / L1_CHUNK + 1) * L1_CHUNK; q < end; q += L1_CHUNK) {
-            const double2* r2 = reinterpret_cast<const double2*>(M.sC[q]);
-            const double2 a2 = r2[0], b2 = r2[1], c2 = r2[2];
-            a.x += a2.x; a.y += a2.y; bq.x += b2.x; bq.y += b2.y; cq.x += c2.x; cq.y += c2.y;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const double ax = __shfl_down_sync(0xffffffffu, a.x, d), ay = __shfl_down_sync(0xffffffffu, a.y, d);
+            const double bx = __shfl_down_sync(0xffffffffu, bq.x, d), by = __shfl_down_sync(0xffffffffu, bq.y, d);
+            const double cx = __shfl_down_sync(0xffffffffu, cq.x, d), cy = __shfl_down_sync(0xffffffffu, cq.y, d);
+            if (d <= rem) { a.x += ax; a.y += ay; bq.x += bx; bq.y += by; cq.x += cx; cq.y += cy; }
         }
-        double2* dst = reinterpret_cast<double2*>(S.rows + size_t(ROW_DOUBLES) * (hbase + hrank));
-        row_store(dst, a); row_store(dst + 1, bq); row_store(dst + 2, cq);
+        if (pk >= 0) {
+            double2* dst = reinterpret_cast<double2*>(S.rows + size_t(ROW_DOUBLES) * (hbase + hrank));
+            row_store(dst, a); row_store(dst + 1, bq); row_store(dst + 2, cq);
+        }
     }
 }
 
@@ -298,10 +296,13 @@ k_schur_rows(View V, RowSched S, const double* __restrict__ xin, double* __restr
 // griddepcontrol.wait, i.e. while K5a is still running; after the wait there is no index -> row dependency left, only row loads,
 // GATHER_UNR of them in flight per lane.
 #ifndef BA_GATHER_UNR
-#define BA_GATHER_UNR 8
+#define BA_GATHER_UNR 4
 #endif
 #ifndef BA_GATHER_MINB
-#define BA_GATHER_MINB 12      // min CTAs/SM: all 1779 CTAs of the Venice shape resident at once
+#define BA_GATHER_MINB 16      // min CTAs/SM (32 registers): all 1779 CTAs of the Venice shape are ONE wave (148 x 16 = 2368).  With 12 per SM
+                               // (1776 slots) three CTAs had to wait for a first-wave CTA to finish, and the PCG tail -- a programmatic dependent
+                               // launch that needs every gather CTA started -- waited with them: ~45 us per PCG iteration behind the streaming
+                               // kernel, whose CTAs leave no room for early gather CTAs.
 #endif
 constexpr int GATHER_IDX_CAP = 1536;   // row ids staged per CTA (6 KB); longer lists read the remainder from global memory
 
