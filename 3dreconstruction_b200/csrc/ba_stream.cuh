@@ -1,4 +1,4 @@
-// ba_stream.cuh — K4/K5a as a persistent, warp-specialised streaming kernel (scatter_mode 6, the default).
+// ba_stream.cuh — K4/K5a as a persistent, warp-specialised streaming kernel (scatter_mode 6, an experimental opt-in; see ba_engine.cu: do_set_problem for why it is not the default).
 //
 // Same tile math, same static schedule and bit-identical partial rows as k_schur_rows (ba_rows.cuh); what changes is how the bytes
 // arrive.  ncu on the CTA-per-tile shape shows it latency-exposed, not bandwidth-bound (0.68 of the measured HBM peak at 35 % warps

@@ -125,8 +125,9 @@ typedef struct ba_options {
     int32_t world_size;                  /* 1 = single GPU */
     const void* nccl_unique_id;          /* world_size>1: 128-byte ncclUniqueId from ba_nccl_unique_id() on rank 0, broadcast by the caller */
     void*   stream;                      /* engine: cudaStream_t to run on (NULL: the engine creates its own) */
-    int32_t scatter_mode;                /* engine camera-side scatter of K4/K5: 0 = auto (6 for problems with at least 4 tiles per SM, else 4), 1 = red.global.add.f64,
-                                            4 = partial rows + by-camera gather, one CTA per tile, 6 = the same rows from the persistent cp.async.bulk streaming kernel */
+    int32_t scatter_mode;                /* engine camera-side scatter of K4/K5: 0 = default (4), 1 = red.global.add.f64, 4 = partial rows + by-camera gather,
+                                            one CTA per tile, 6 = the same rows from the persistent cp.async.bulk streaming kernel (experimental opt-in:
+                                            bit-identical to 4 on the small shapes, slower per PCG iteration and not reproducible on the Final-13682 shape) */
     int32_t p2p_allreduce;               /* multi-GPU all-reduce of the PCG matvec: 0 = auto (one-shot NVLink peer-memory all-reduce fused into the
                                             K5b gather when every peer buffer can be mapped with CUDA IPC, else NCCL), 1 = NCCL only, 2 = peer memory required */
     int32_t lm_policy;                   /* ba_lm_policy; default CERES */
