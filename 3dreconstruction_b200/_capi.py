@@ -182,6 +182,7 @@ ENGINE_SYMBOLS = [
     ("ba_linear_solver_in_use", C.c_int, [C.c_void_p, c_int32_p]),
     ("ba_get_kernel_stats", C.c_int, [C.c_void_p, C.POINTER(BAKernelStat), C.c_int32, c_int32_p]),
     ("ba_get_execution_info", C.c_int, [C.c_void_p, C.POINTER(C.c_int64), C.c_int32, c_int32_p]),
+    ("ba_cost_noalloc", C.c_int, [C.c_int32, C.c_void_p, C.c_int32, C.c_int32, C.c_double, C.c_int32, C.c_int32, C.c_int32, C.c_int32] + [C.c_void_p] * 9),
     ("ba_get_io_bytes", C.c_int, [C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     ("ba_shard_points", C.c_int, [C.c_int32, C.c_int32, c_int32_p, C.c_int32, c_int32_p]),
     ("ba_nccl_unique_id", C.c_int, [C.c_void_p]),

@@ -1799,3 +1799,114 @@ void ba_destroy(ba_engine* e) {
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------------------------------------------------
+// ba_cost_noalloc — an entry point that allocates nothing (include/ba_engine.h).  No counterpart in the reference: added
+// for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).
+// It is the candidate-cost evaluation (K0 camera precompute + a K1'-style residual / robust-loss sweep, the same device functions the
+// LM loop uses) with its scratch memory — the per-camera records and the per-block partial sums — in ONE file-scope device array of a
+// fixed, modest size instead of engine-owned cudaMalloc buffers.  Every GPU that loads this library holds the array until exit.
+// In host code `g_noalloc_scratch` is only a stand-in for the symbol, not a device address: its address is looked up once per device
+// with cudaGetSymbolAddress (that device current) and that pointer is what the kernels get.
+namespace {
+constexpr int kNoallocBlocks = 1184;                                             // 148 SMs x 8 CTAs of 256 threads, grid-stride
+constexpr size_t kNoallocCamDoubles = size_t(BA_NOALLOC_MAX_CAMERAS) * bak::CAMREC;
+constexpr size_t kNoallocDoubles = kNoallocCamDoubles + 2048;                    // + block partials (1184) + ticket word, padded
+}  // namespace
+static __device__ __align__(256) double g_noalloc_scratch[kNoallocDoubles];     // 672 KB per device
+
+namespace {
+// Residual + robust loss of every observation (grid-stride), one partial per block; the last block to finish (ticket) adds the partials in
+// index order, so the result does not depend on block scheduling.  `ticket` must be zero on entry (cleared by the host per call).
+template <int MODEL>
+__global__ void __launch_bounds__(256)
+k_cost_static(int No, int Ng, const double* __restrict__ camrec, const double* __restrict__ intr, const int* __restrict__ cam_group,
+              const double* __restrict__ pt, const int* __restrict__ obs_cam, const int* __restrict__ obs_pt, const double2* __restrict__ obs_uv,
+              bak::RobustParams rp, double* __restrict__ partial, unsigned int* __restrict__ ticket, double* __restrict__ cost_out,
+              int* __restrict__ bad_out) {
+    __shared__ double sred[32];
+    __shared__ bool last;
+    __shared__ int sbad;
+    if (threadIdx.x == 0) sbad = 0;
+    __syncthreads();
+    double cost = 0.0;
+    int bad = 0;
+    for (int o = blockIdx.x * blockDim.x + threadIdx.x; o < No; o += gridDim.x * blockDim.x) {
+        const int c = obs_cam[o], p = obs_pt[o];
+        bak::Proj q;
+        double cr[12];   // R, t
+        bak::load_camrec<6>(camrec, c, cr);
+        bak::project_obs<MODEL>(cr, pt + 3 * size_t(p), intr + (Ng == 1 ? 0 : 4 * cam_group[c]), __ldg(obs_uv + o), q);
+        double w;
+        const double rho = bak::robust(rp, q.r0 * q.r0 + q.r1 * q.r1, w);
+        if (!isfinite(rho)) bad = 1;
+        cost += 0.5 * rho;
+    }
+    if (bad) atomicOr(&sbad, 1);
+    const double cs = bak::block_sum(cost, sred);
+    if (threadIdx.x == 0) {
+        partial[blockIdx.x] = cs;
+        if (sbad) atomicOr(bad_out, 1);
+        __threadfence();
+        last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (!last) return;
+    __threadfence();
+    double s = 0.0;
+    for (int i = threadIdx.x; i < int(gridDim.x); i += blockDim.x) s += __ldcg(partial + i);
+    s = bak::block_sum(s, sred);
+    if (threadIdx.x == 0) *cost_out = s;
+}
+
+std::mutex g_noalloc_mu;
+double* g_noalloc_ptr[64] = {};   // device address of g_noalloc_scratch, per device ordinal
+}  // namespace
+
+extern "C" int ba_cost_noalloc(int32_t device, void* stream, int32_t model, int32_t robust_kind, double robust_a, int32_t taylor_rule,
+                               int32_t num_cameras, int32_t num_groups, int32_t num_observations, const double* d_pose, const double* d_intr,
+                               const int32_t* d_cam_group, const double* d_pt, const int32_t* d_obs_cam, const int32_t* d_obs_pt,
+                               const double* d_obs_uv, double* d_cost, int32_t* d_bad) {
+    if (num_cameras < 0 || num_groups < 1 || num_observations < 0) return fail(nullptr, BA_ERR_INVALID_ARGUMENT, "ba_cost_noalloc: negative size or no intrinsics group");
+    if (num_cameras > BA_NOALLOC_MAX_CAMERAS) {
+        char b[200];
+        std::snprintf(b, sizeof b, "ba_cost_noalloc: %d cameras exceed the static scratch of this entry point (BA_NOALLOC_MAX_CAMERAS = %d); use a ba_engine handle",
+                      int(num_cameras), int(BA_NOALLOC_MAX_CAMERAS));
+        return fail(nullptr, BA_ERR_INVALID_ARGUMENT, b);
+    }
+    if (model != BA_MODEL_PINHOLE && model != BA_MODEL_SNAVELY) return fail(nullptr, BA_ERR_INVALID_ARGUMENT, "ba_cost_noalloc: unknown residual model");
+    if (!d_cost || !d_bad || (num_cameras && (!d_pose || !d_cam_group)) || !d_intr || (num_observations && (!d_pt || !d_obs_cam || !d_obs_pt || !d_obs_uv)))
+        return fail(nullptr, BA_ERR_INVALID_ARGUMENT, "ba_cost_noalloc: null device pointer");
+    if (device < 0 || device >= 64) return fail(nullptr, BA_ERR_INVALID_ARGUMENT, "ba_cost_noalloc: device ordinal out of range");
+    return guarded(nullptr, [&] {
+        int prev = -1;
+        CU_TRY(cudaGetDevice(&prev));
+        struct Restore { int d; ~Restore() { if (d >= 0) cudaSetDevice(d); } } restore{prev == device ? -1 : prev};
+        CU_TRY(cudaSetDevice(device));
+        double* scratch = nullptr;
+        {   // once per device, with that device current: the device address of the symbol
+            std::lock_guard<std::mutex> g(g_noalloc_mu);
+            if (!g_noalloc_ptr[device]) {
+                void* p = nullptr;
+                CU_TRY(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+                g_noalloc_ptr[device] = static_cast<double*>(p);
+            }
+            scratch = g_noalloc_ptr[device];
+        }
+        cudaStream_t s = static_cast<cudaStream_t>(stream);
+        double* camrec = scratch;
+        double* partial = scratch + kNoallocCamDoubles;
+        unsigned int* ticket = reinterpret_cast<unsigned int*>(partial + kNoallocBlocks);
+        // the array keeps the last call's contents: the ticket and the outputs must start at zero; records and partials are overwritten before use
+        CU_TRY(cudaMemsetAsync(ticket, 0, sizeof(unsigned int), s));
+        CU_TRY(cudaMemsetAsync(d_bad, 0, sizeof(int32_t), s));
+        if (num_cameras > 0) bak::k0_camera_precompute<<<cdiv(num_cameras, 128), 128, 0, s>>>(num_cameras, d_pose, camrec, taylor_rule);
+        CU_TRY(cudaGetLastError());
+        const int blocks = std::max(1, std::min(kNoallocBlocks, cdiv(num_observations, 256)));
+        const bak::RobustParams rp{robust_kind, robust_a};
+        const double2* uv = reinterpret_cast<const double2*>(d_obs_uv);
+        if (model == BA_MODEL_SNAVELY) k_cost_static<1><<<blocks, 256, 0, s>>>(num_observations, num_groups, camrec, d_intr, d_cam_group, d_pt, d_obs_cam, d_obs_pt, uv, rp, partial, ticket, d_cost, d_bad);
+        else k_cost_static<0><<<blocks, 256, 0, s>>>(num_observations, num_groups, camrec, d_intr, d_cam_group, d_pt, d_obs_cam, d_obs_pt, uv, rp, partial, ticket, d_cost, d_bad);
+        CU_TRY(cudaGetLastError());
+    });
+}

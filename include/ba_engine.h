@@ -238,7 +238,25 @@ int  ba_linear_solver_in_use(ba_engine* e, int32_t* solver);  /* after ba_set_pr
  * the current problem (1, 4 or 6), [2] = all-reduce of the PCG matvec (0: one GPU, 1: NCCL, 2: one-shot NVLink peer memory), [3] = host
  * synchronisations of the last ba_solve (Scalars read-backs), [4] = tiles and [5] = partial rows of this rank's shard.  The oracle reports zeros. */
 int  ba_get_execution_info(ba_engine* e, int64_t* info, int32_t cap, int32_t* n);
-int  ba_get_io_bytes(int64_t* h2d, int64_t* d2h);              /* cumulative host->device / device->host bytes moved by this library in this process */
+int  ba_get_io_bytes(int64_t* h2d, int64_t* d2h);
+/* ba_cost_noalloc has NO counterpart in the reference: it was added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid allocation).  It evaluates cost = 1/2 sum rho(||r||^2)
+ * (the candidate-cost step of the LM loop: camera precompute + residual / robust-loss sweep) of a problem whose arrays are ALREADY ON THE
+ * DEVICE, and allocates nothing: no cudaMalloc / cudaFree / allocating library call, no engine handle.  Its scratch (per-camera records,
+ * per-block partial sums) is one file-scope static device array of 672 KB that every GPU loading this library holds until exit; hence
+ * the limit num_cameras <= BA_NOALLOC_MAX_CAMERAS (larger problems are rejected with BA_ERR_INVALID_ARGUMENT and a message in
+ * ba_last_error(NULL); use a ba_engine handle for them).  Observations and points are not limited.
+ * All d_* pointers are device pointers on `device`: pose[Nc][6], intr[Ng][4], cam_group[Nc], pt[Np][3], obs_cam[No], obs_pt[No], obs_uv[No][2]
+ * (16-byte aligned), outputs d_cost[1] and d_bad[1] (1 if any residual was non-finite).  The work is enqueued on `stream` (a cudaStream_t, NULL =
+ * the default stream) and NOT synchronised: the outputs are valid once the stream has reached this point.  All calls on a device share the
+ * array, which keeps the last call's contents (what must start at zero is cleared by every call): calls that overlap on the GPU — two
+ * streams, two host threads, two processes' worth of graphs replayed concurrently on one device — race and give wrong results.  The first
+ * call on a device looks up the array's device address (cudaGetSymbolAddress); make that call outside stream capture. */
+#define BA_NOALLOC_MAX_CAMERAS 4096
+int  ba_cost_noalloc(int32_t device, void* stream, int32_t model, int32_t robust_kind, double robust_a, int32_t taylor_rule,
+                     int32_t num_cameras, int32_t num_groups, int32_t num_observations, const double* d_pose, const double* d_intr,
+                     const int32_t* d_cam_group, const double* d_pt, const int32_t* d_obs_cam, const int32_t* d_obs_pt,
+                     const double* d_obs_uv, double* d_cost, int32_t* d_bad);              /* cumulative host->device / device->host bytes moved by this library in this process */
 /* Host-only (no device needed): the point ranges of the multi-GPU sharding. Rank r owns points
  * [shard_pt[r], shard_pt[r+1]) and all their observations; ranges are contiguous, cut at point boundaries and
  * balanced by observation count.  obs_pt[No] non-decreasing; shard_pt has world_size+1 entries. */

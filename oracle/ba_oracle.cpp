@@ -919,6 +919,10 @@ int ba_get_execution_info(ba_engine* e, int64_t* info, int32_t cap, int32_t* n) 
     if (info) for (int i = 0; i < std::min<int>(cap, 6); ++i) info[i] = 0;
     return BA_OK;
 }
+int ba_cost_noalloc(int32_t, void*, int32_t, int32_t, double, int32_t, int32_t, int32_t, int32_t, const double*, const double*, const int32_t*,
+                    const double*, const int32_t*, const int32_t*, const double*, double*, int32_t*) {
+    return fail(nullptr, BA_ERR_UNSUPPORTED, "ba_cost_noalloc is a device entry point of the CUDA engine; the CPU oracle has no device");
+}
 int ba_get_io_bytes(int64_t* h2d, int64_t* d2h) { if (h2d) *h2d = 0; if (d2h) *d2h = 0; return BA_OK; }
 const char* ba_last_error(const ba_engine* e) { return e ? e->err.c_str() : g_create_error.c_str(); }
 const char* ba_backend(void) { return "cpu-oracle"; }
