@@ -99,7 +99,7 @@ def load_golden(args):
     import numpy as np
     name = {"venice": "venice_exact", "final": "final_pcg"}.get(args.workload)
     path = os.path.join(ROOT, "tests", "golden", f"{name}_oracle_trajectory_large.npz") if name else None
-    if not path or not os.path.exists(path) or args.max_lm_iterations != 50:
+    if not path or not os.path.exists(path):
         return None, None
     return np.load(path), os.path.basename(path)
 

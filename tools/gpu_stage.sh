@@ -19,6 +19,16 @@ ab)
   SHAPE=$1; shift
   tools/ab.sh $SHAPE "$@" 2>&1 | tee $OUT/${TAG}_ab_$SHAPE.txt
   ;;
+mg)   # tools/gpu_stage.sh mg <tag> <N> [workload ...]: multi-GPU parity check, per-rank kernel table and bench lines at N GPUs (gpurun --gpus N)
+  N=$1; shift
+  TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1"
+  timeout -s KILL 600 $TR --master-port 29511 tools/multi_gpu_check.py ladybug trafalgar > $OUT/${TAG}_multi_gpu_check_n$N.txt 2>&1; echo "multi_gpu_check rc=$?"; grep -E "OK|MISMATCH|rror" $OUT/${TAG}_multi_gpu_check_n$N.txt | tail -12
+  for W in "${@:-venice}"; do
+    timeout -s KILL 400 $TR --master-port 29513 tools/multi_gpu_stats.py $W 3 0 > $OUT/${TAG}_multi_gpu_stats_${W}_n$N.txt 2>&1; echo "stats $W rc=$?"; grep -vE "^W|^\*|warn" $OUT/${TAG}_multi_gpu_stats_${W}_n$N.txt | tail -40
+    ST=3; [ "$W" = "final" ] && ST=2
+    timeout -s KILL 900 $TR --master-port 29515 bench.py --gpus $N --steps $ST --warmup 3 --workload $W > $OUT/${TAG}_bench_${W}_n$N.json 2> $OUT/${TAG}_bench_${W}_n$N.err; echo "bench $W rc=$?"; tail -2 $OUT/${TAG}_bench_${W}_n$N.err; cat $OUT/${TAG}_bench_${W}_n$N.json
+  done
+  ;;
 profile)
   tools/gpu_profile.sh $TAG
   ;;
