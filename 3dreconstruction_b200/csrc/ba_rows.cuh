@@ -41,6 +41,13 @@ struct RowSched {
     const int* cam_row_off;       // [Nc+1] by-camera view of the rows
     const int* cam_rows;          // [nRows] compact row ids, ascending
     int nRows;
+    // warp-packed tiles (scatter_mode 7, ba_wp.cuh): 256 positions per tile = 8 warps x 32 lanes, every warp holds whole points
+    const int2* wpA;              // [nTilesWP][256] per position: .x = camera | slot << 24;  .y = head lane | seg_rem << 5 | point rank << 10 | rem << 15 | hrank << 20
+    const int* wpB;               // [nTilesWP][256] sorted position: camera | run length << 22 at the head of a run, -1 elsewhere
+    const int4* winfo;            // [nTilesWP][8]   per warp: {first observation, observations | points << 8, first local point, 0}
+    const int4* tile_info2;       // [nTilesWP]      {observations of the tile (| WP_LONG: one point with more than 32 observations), first compact row,
+                                  //                  long tile: first observation, long tile: the point}
+    int nTilesWP;
 };
 
 // barrier policies of the tile math: the whole CTA (k_schur_rows) or one 128-thread consumer group (k_schur_stream)
@@ -57,14 +64,15 @@ struct TileScratch {   // 12 KB per tile in flight
     double sred[8];
 };
 
-// Sum over the 128 threads of a tile (fixed tree); valid in every thread.
-template <class Bar>
+// Sum over the NT threads of a tile (fixed tree); valid in every thread.
+template <int NT = TILE_OBS, class Bar>
 __device__ __forceinline__ double tile_sum(double v, double* sred, Bar bar, int tid) {
     v = warp_sum(v);
     bar();
     if ((tid & 31) == 0) sred[tid >> 5] = v;
     bar();
-    return (sred[0] + sred[1]) + (sred[2] + sred[3]);
+    if (NT == 128) return (sred[0] + sred[1]) + (sred[2] + sred[3]);
+    return ((sred[0] + sred[1]) + (sred[2] + sred[3])) + ((sred[4] + sred[5]) + (sred[6] + sred[7]));
 }
 
 // The operands of one tile position, in registers.
@@ -165,8 +173,8 @@ __device__ __forceinline__ void tile_rows(const View& V, const RowSched& S, Tile
 // Whole tile group (128 threads) calls; p = the point.  (Inlined on purpose: as a real call it takes the View by reference, which makes
 // every thread of every CTA spill the whole kernel-parameter struct to local memory at kernel entry — 25 STL per thread, measured
 // +30 % on K4/K5a.)
-template <int MODE, bool FI, int PK, class Bar>
-__device__ __forceinline__ void tile_rows_long(const View& V, const RowSched& S, TileScratch& M, Bar bar, const int tid, const int o0, const int n,
+template <int MODE, bool FI, int PK, int NT = TILE_OBS, class Bar>
+__device__ __forceinline__ void tile_rows_long(const View& V, const RowSched& S, double* sred, Bar bar, const int tid, const int o0, const int n,
                                             const int hbase, const int p, const double* __restrict__ xin, double* __restrict__ atomic_out,
                                             double (&yi)[4]) {
     const int ioff = 6 * V.Nc;
@@ -174,7 +182,7 @@ __device__ __forceinline__ void tile_rows_long(const View& V, const RowSched& S,
     double v[3];
     if (MODE == SWEEP_MATVEC) {
         double W[3] = {0, 0, 0};
-        for (int o = o0 + tid; o < o1; o += TILE_OBS) {
+        for (int o = o0 + tid; o < o1; o += NT) {
             const int c = V.obs_cam[o];
             const double2* J = V.J2 + o;
             double2 u = make_double2(0.0, 0.0);
@@ -195,11 +203,11 @@ __device__ __forceinline__ void tile_rows_long(const View& V, const RowSched& S,
         }
         double w[3];
 #pragma unroll
-        for (int a = 0; a < 3; ++a) w[a] = tile_sum(W[a], M.sred, bar, tid);
+        for (int a = 0; a < 3; ++a) w[a] = tile_sum<NT>(W[a], sred, bar, tid);
         const double* H = V.Hinv + 6 * size_t(p);
         v[0] = H[0] * w[0] + H[1] * w[1] + H[2] * w[2]; v[1] = H[1] * w[0] + H[3] * w[1] + H[4] * w[2]; v[2] = H[2] * w[0] + H[4] * w[1] + H[5] * w[2];
     } else { v[0] = V.vp[3 * size_t(p)]; v[1] = V.vp[3 * size_t(p) + 1]; v[2] = V.vp[3 * size_t(p) + 2]; }
-    for (int o = o0 + tid; o < o1; o += TILE_OBS) {
+    for (int o = o0 + tid; o < o1; o += NT) {
         const int c = V.obs_cam[o];
         const int g = FI ? V.cam_group[c] : 0;
         const double2* J = V.J2 + o;
@@ -237,10 +245,10 @@ __device__ __forceinline__ void tile_rows_long(const View& V, const RowSched& S,
 }
 
 // One shared intrinsics group: the tile's partial of the intrinsics entries, summed in tile order by k_camera_gather.
-template <class Bar>
-__device__ __forceinline__ void tile_intr_store(const RowSched& S, TileScratch& M, Bar bar, int tid, int t, const double (&yi)[4]) {
+template <int NT = TILE_OBS, class Bar>
+__device__ __forceinline__ void tile_intr_store(const RowSched& S, double* sred, Bar bar, int tid, int t, const double (&yi)[4]) {
 #pragma unroll
-    for (int k = 0; k < 4; ++k) { const double s = tile_sum(yi[k], M.sred, bar, tid); if (tid == 0) S.tile_intr[4 * size_t(t) + k] = s; }
+    for (int k = 0; k < 4; ++k) { const double s = tile_sum<NT>(yi[k], sred, bar, tid); if (tid == 0) S.tile_intr[4 * size_t(t) + k] = s; }
 }
 
 #ifndef BA_K5A_MINB
@@ -283,9 +291,9 @@ k_schur_rows(View V, RowSched S, const double* __restrict__ xin, double* __restr
     } else {
         pdl_wait();
         if (done_flag && *done_flag) return;
-        tile_rows_long<MODE, FI, PK>(V, S, M, BarCta{}, tid, o0, n, hbase, pfirst, xin, atomic_out, yi);
+        tile_rows_long<MODE, FI, PK>(V, S, M.sred, BarCta{}, tid, o0, n, hbase, pfirst, xin, atomic_out, yi);
     }
-    if (FI && V.Ng == 1) tile_intr_store(S, M, BarCta{}, tid, t, yi);
+    if (FI && V.Ng == 1) tile_intr_store(S, M.sred, BarCta{}, tid, t, yi);
 }
 
 // ---------------------------------------------------------------------------------------------------------

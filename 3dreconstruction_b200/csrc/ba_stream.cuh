@@ -187,13 +187,22 @@ k_schur_stream(View V, RowSched S, const double* __restrict__ xin, double* __res
                 const double2* H = reinterpret_cast<const double2*>(st + Cfg::AUX_OFF) + 3 * tid;
                 R.h0 = H[0]; R.h1 = H[1]; R.h2 = H[2];
             }
+            // The stage may only be handed back once the shared-memory reads above have RETURNED: ptxas puts no scoreboard wait between the
+            // LDS instructions and the mbarrier arrive (nothing in the arrive reads their destination registers), so an arrive issued
+            // right behind them can overtake them in the memory pipe and the producer's next bulk copy lands on bytes that are still being
+            // read (seen as PCG runs that differ from launch to launch on the Final-13682 shape).  A branch on a value formed from the last
+            // loads of every kind makes the warp wait for them first; shared-memory loads of one warp return in order.
+            {
+                const double touch = R.jp[2].y + R.jc[5].y + R.h2.y + R.rr.y + double(R.tm.w);
+                if (touch == -1.2345678901234567e+301) atomicAdd(&S.rows[0], touch);      // never taken; keeps the dependency alive
+            }
             release(s);                                // operands are in registers: the stage can be refilled
             tile_rows<MODE, FI>(V, S, M, bar, tid, n, hbase, pfirst, R, xin, atomic_out, yi);
         } else {
             release(s);
-            tile_rows_long<MODE, FI, PK>(V, S, M, bar, tid, o0, n, hbase, pfirst, xin, atomic_out, yi);
+            tile_rows_long<MODE, FI, PK>(V, S, M.sred, bar, tid, o0, n, hbase, pfirst, xin, atomic_out, yi);
         }
-        if (FI && V.Ng == 1) tile_intr_store(S, M, bar, tid, t, yi);
+        if (FI && V.Ng == 1) tile_intr_store(S, M.sred, bar, tid, t, yi);
         // The next tile of this group may overwrite sC (RHS: right away) or sW/sred while slower threads still read them
         if (MODE == SWEEP_RHS || n > TILE_OBS) bar();
     }

@@ -172,6 +172,7 @@ def run_ours(args, rank, world, local_rank):
     dev = torch.device("cuda", local_rank)
     lib = ba.engine_library()   # raises if the CUDA extension is missing: no fallback
     if world > 1:
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # keep NCCL's version banner off stdout: rank 0 prints ONE JSON line there
         dist.init_process_group("nccl", device_id=dev)
 
     def barrier():

@@ -84,12 +84,12 @@ def test_trajectory_parity(ba, oracle, name, fi, solver):
     assert rel_err(xe[1], xo[1]) <= STATE_RTOL
 
 
-@pytest.mark.parametrize("mode", [1, 4, 6])
-@pytest.mark.parametrize("fi", [0, 1])
-def test_scatter_modes(ba, oracle, mode, fi):
-    """The camera-side scatter implementations (1: L2 atomics, 4: partial rows with one CTA per tile, 6: partial rows from the persistent
-    cp.async.bulk streaming kernel) agree with the oracle."""
-    P = ba.synth("ladybug", seed=123)
+@pytest.mark.parametrize("mode", [1, 4, 6, 7])
+@pytest.mark.parametrize("shape,fi", [("ladybug", 0), ("ladybug", 1), ("trafalgar", 0)])
+def test_scatter_modes(ba, oracle, mode, shape, fi):
+    """The camera-side scatter implementations (1: L2 atomics, 4: partial rows with one CTA per tile, 6: the same rows from the persistent
+    cp.async.bulk streaming kernel, 7: partial rows on warp-packed tiles) agree with the oracle."""
+    P = ba.synth(shape, seed=123)
     (se, te, xe), (so, to, xo) = solve_both(ba, oracle, P, intrinsics_free=fi, max_num_iterations=6, scatter_mode=mode, engine_solver=1)
     assert_trajectory_parity(te, to)
 
@@ -184,16 +184,17 @@ def test_reset_state_reproduces(ba):
     assert s1.num_iterations == s2.num_iterations
 
 
-@pytest.mark.parametrize("solver", [0, 1])
-def test_long_track_and_ragged(ba, oracle, solver):
-    """A point seen by more cameras than one tile holds (long-point path), empty points and an unobserved camera."""
+@pytest.mark.parametrize("solver,scatter", [(0, 0), (1, 4), (1, 6), (1, 7)])
+def test_long_track_and_ragged(ba, oracle, solver, scatter):
+    """A point seen by more cameras than one tile holds (long-point path of every K4/K5 kernel; with scatter_mode 7 also the point of
+    33..256 observations that cannot live in one warp), empty points and an unobserved camera."""
     P = ba.synth(num_cameras=300, num_points=60, num_observations=60 * 2 + 298 + 100, seed=5, max_track=300)
     # make point 0 visible from every camera: rebuild the observation list by hand
     rng = np.random.default_rng(3)
     Nc, Np = 300, 60
     cams, pts = [], []
     for p in range(Np):
-        k = Nc if p == 0 else int(rng.integers(2, 6))
+        k = Nc if p == 0 else (40 if p == 20 else int(rng.integers(2, 6)))
         cs = np.sort(rng.choice(Nc - 1, size=min(k, Nc - 1), replace=False))   # camera Nc-1 is never observed
         if p in (7, 8):
             continue                                                            # points 7 and 8 have no observation
@@ -212,7 +213,7 @@ def test_long_track_and_ragged(ba, oracle, solver):
         uv[i] = [P.intr[0, 0] * Pc[0] / Pc[2] + P.intr[0, 2], P.intr[0, 1] * Pc[1] / Pc[2] + P.intr[0, 3]]
     uv += rng.normal(0, 0.5, uv.shape)
     Q = ba.Problem(pose=P.pose, intr=P.intr, cam_group=P.cam_group, cam_fixed=P.cam_fixed, pt=P.pt, obs_cam=obs_cam, obs_pt=obs_pt, obs_uv=uv)
-    (se, te, xe), (so, to, xo) = solve_both(ba, oracle, Q, intrinsics_free=1, max_num_iterations=6, engine_solver=solver)
+    (se, te, xe), (so, to, xo) = solve_both(ba, oracle, Q, intrinsics_free=1, max_num_iterations=6, engine_solver=solver, scatter_mode=scatter)
     assert_trajectory_parity(te, to)
     # untouched parameters stay bit-identical
     assert np.array_equal(xe[2][7], Q.pt[7]) and np.array_equal(xe[2][8], Q.pt[8])

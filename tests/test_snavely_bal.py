@@ -111,7 +111,7 @@ def test_engine_snavely_residual_and_jacobian(ba):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("fi,solver,scatter", [(0, 2, 0), (1, 2, 0), (0, 1, 6), (1, 1, 6), (0, 1, 4)])
+@pytest.mark.parametrize("fi,solver,scatter", [(0, 2, 0), (1, 2, 0), (0, 1, 6), (1, 1, 6), (0, 1, 4), (0, 1, 7), (1, 1, 7)])
 def test_engine_snavely_trajectory_parity(ba, oracle, fi, solver, scatter):
     """solver 2 = AUTO (direct solve at this size); solver 1 = PCG with the streaming (6) / CTA-per-tile (4) matvec: nine stored Jacobian columns."""
     P = snavely_problem(ba, "ladybug", seed=2)
