@@ -254,6 +254,7 @@ struct ba_engine {
     unsigned profiling = 0;           // bit k set: time kernel id k with CUDA events
     struct Stat { int64_t launches = 0; int64_t timed = 0; double ms = 0.0; double bytes = 0.0; } stats[KID_COUNT];
     int dbg_tail1 = 0;                // BA_TAIL_MODE1
+    int p2p_wide = 1;                 // peer-memory all-reduce: pull on many SMs in a kernel of its own (1, default) or inside the PCG tail's cluster (0; BA_P2P_WIDE)
     int pcg_tag = -1;                 // ordinal of the PCG iteration being launched (LaunchTimer tags; -1 outside the PCG loop)
     int pcg_pred = 0;                 // PCG iterations of the previous linear solve on this handle (first batch size)
     int k5_sample_stride = 1;         // time every n-th K5 launch only (events between two launches serialise them; BA_K5_SAMPLE)
@@ -1267,6 +1268,11 @@ int solve_linear(ba_engine* e, double radius, double* rel_out, double lambda = 0
                     double* mine = e->p2p.view.data[e->p2p.view.rank] + size_t(ta.seq & 1u) * e->p2p.view.ldf;
                     CU_TRY(cudaMemcpyAsync(mine, e->d_y.p, size_t(e->nf) * sizeof(double), cudaMemcpyDeviceToDevice, s));
                 } else launch_chain(e, bak::k_camera_gather_push, dim3(gblocks), gthreads, e->Nc, e->Ng, e->fi, (e->scatter_eff == 7 ? e->nTilesWP : e->nTiles), e->RS, e->d_y.p, e->p2p.view, ta.seq, &sc->pcg, 1);
+                if (e->p2p_wide) {   // pull and sum the W slots on many SMs (ba_p2p.cuh: k_allreduce_pull); the tail then finds y complete in local memory
+                    const int pblocks = std::max(1, std::min(2 * e->num_sms, cdiv((e->nf + 1) / 2, bak::PULL_THREADS)));
+                    launch_chain(e, bak::k_allreduce_pull, dim3(pblocks), dim3(bak::PULL_THREADS), e->nf, e->p2p.view, ta.seq, e->d_y.p, &sc->pcg, 1);
+                    ta.mode = 1;
+                }
             } else if (multi) {
                 { LaunchTimer tg(e, KID_GATHER, sample, launched);
                   if (!no_rows) KL(e), bak::k_camera_gather<<<gblocks, gthreads, 0, s>>>(e->Nc, e->Ng, e->fi, (e->scatter_eff == 7 ? e->nTilesWP : e->nTiles), e->RS, nullptr, nullptr, e->d_y.p, nullptr, &sc->pcg, 0); }
@@ -1587,6 +1593,7 @@ int ba_create(const ba_options* opt, ba_engine** out) {
         e->pdl = BA_PDL_DEFAULT;
         if (const char* v = std::getenv("BA_PDL")) e->pdl = std::atoi(v) ? 1 : 0;
         if (const char* v = std::getenv("BA_TAIL_MODE1")) e->dbg_tail1 = std::atoi(v) ? 1 : 0;
+        if (const char* v = std::getenv("BA_P2P_WIDE")) e->p2p_wide = std::atoi(v) ? 1 : 0;
         // sm_100a images are architecture-specific: they run on compute capability 10.0 only (not on 10.3 / 12.x); probe one kernel as well
         if (prop.major != 10 || prop.minor != 0)
             throw BaFail{BA_ERR_CUDA, std::string("device ") + prop.name + " has compute capability " + std::to_string(prop.major) + "." + std::to_string(prop.minor) +

@@ -64,4 +64,47 @@ k_camera_gather_push(int Nc, int Ng, int fi, int nTiles, RowSched S, const doubl
     // no ticket, no flag: the kernel boundary orders these stores before the tail kernel, which publishes the flags (ba_pcg_cluster.cuh)
 }
 
+// The pull of the one-shot all-reduce as a kernel of its own, on MANY SMs.  Inside the PCG tail (one cluster of 8 CTAs) the pull of W slots
+// is bound by what 8 SMs can keep in flight over NVLink: 88 us per PCG iteration on the Final-13682 shape at 8 GPUs (W x 657 KB), the one
+// term that does not shrink with the shard.  Here: block 0 fences once at system scope and publishes this rank's flag on every rank (the
+// kernel boundary ordered the gather's stores), every block waits (local memory) until all W ranks have published this sequence number,
+// then pulls ITS slice of all W slots (16-byte ld.relaxed.sys, all W loads of a thread in flight together), adds them in rank order (the same
+// order on every rank: bit-identical y everywhere) and stores y locally.  The tail then runs in mode 1 (y complete in local memory).
+// The grid is small enough to be co-resident (<= 2 blocks per SM), so the blocks that spin cannot keep block 0 from running.
+constexpr int PULL_THREADS = 256;
+
+__device__ __forceinline__ double2 ld_relaxed_sys_v2f64(const double* p) {
+    double2 v;
+    asm volatile("ld.relaxed.sys.global.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "l"(p) : "memory");
+    return v;
+}
+
+__global__ void __launch_bounds__(PULL_THREADS)
+k_allreduce_pull(int nf, PeerView P, unsigned int seq, double* __restrict__ y, const PcgState2* __restrict__ st, int check_done) {
+    pdl_trigger();
+    pdl_wait();
+    if (check_done && st->done) return;
+    if (blockIdx.x == 0 && threadIdx.x < P.W) { __threadfence_system(); st_release_sys(P.flags[threadIdx.x] + P.rank, seq); }
+    if (threadIdx.x < P.W) {
+        const unsigned int* f = P.flags[P.rank] + threadIdx.x;
+        const long long t0 = clock64();
+        while (int(ld_acquire_sys(f) - seq) < 0) {
+            if ((*reinterpret_cast<volatile int*>(P.timeout_flag) & 8) || clock64() - t0 > 4000000000LL) { atomicOr(P.timeout_flag, 8); break; }   // ~2 s: a peer died; never hang the GPU
+        }
+    }
+    __syncthreads();
+    const size_t off = size_t(seq & 1u) * P.ldf;                 // ldf is a multiple of 16 doubles: slots and pairs are 16-byte aligned
+    const int npair = (nf + 1) / 2;                              // the slot is padded to ldf >= nf + 1
+    for (int i = blockIdx.x * PULL_THREADS + threadIdx.x; i < npair; i += gridDim.x * PULL_THREADS) {
+        double2 v[P2P_MAX_RANKS];
+#pragma unroll
+        for (int r = 0; r < P2P_MAX_RANKS; ++r) v[r] = r < P.W ? ld_relaxed_sys_v2f64(P.data[r] + off + 2 * size_t(i)) : make_double2(0.0, 0.0);
+        double2 s = make_double2(0.0, 0.0);
+#pragma unroll
+        for (int r = 0; r < P2P_MAX_RANKS; ++r) if (r < P.W) { s.x += v[r].x; s.y += v[r].y; }
+        if (2 * i + 1 < nf) *reinterpret_cast<double2*>(y + 2 * size_t(i)) = s;
+        else y[2 * size_t(i)] = s.x;
+    }
+}
+
 }  // namespace bak

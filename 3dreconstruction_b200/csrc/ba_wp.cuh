@@ -16,12 +16,15 @@
 
 namespace bak {
 
-constexpr int WP_THREADS = 256;
+#ifndef BA_WP_THREADS
+#define BA_WP_THREADS 256             // positions (threads) per tile: 256 or 128 (A/B knob)
+#endif
+constexpr int WP_THREADS = BA_WP_THREADS;
 constexpr int WP_WARPS = WP_THREADS / 32;
 constexpr int WP_LONG = 1 << 30;      // tile_info2.x flag: the tile is one point with more than 32 observations
 
 #ifndef BA_WP_MINB
-#define BA_WP_MINB 3                  // CTAs/SM for ptxas: 3 x 256 threads = 80 registers
+#define BA_WP_MINB (768 / BA_WP_THREADS)   // CTAs/SM for ptxas: 768 threads = 80 registers
 #endif
 
 template <int MODE, bool FI, int PK>
