@@ -30,8 +30,9 @@
 
 #include "ba_kernels.cuh"
 #include "ba_rows.cuh"
+#ifdef BA_WITH_STREAM          // the persistent cp.async.bulk streaming kernel (scatter_mode 6) is an experiment kept out of the default build
 #include "ba_stream.cuh"
-#include "ba_wp.cuh"
+#endif
 #include "ba_p2p.cuh"
 #include "ba_dense.cuh"
 #include "ba_pcg_cluster.cuh"
@@ -152,9 +153,6 @@ template <class T> using pvec = std::vector<T, PinnedAlloc<T>>;
 
 struct HostScratch {   // ba_set_problem's work arrays (capacity survives between calls)
     pvec<int4> tmeta;
-    pvec<int2> wpA;
-    pvec<int32_t> wpB;
-    std::vector<int4> winfo, tinfo2;
     pvec<int32_t> perm, obs_pt, crows;
     std::vector<unsigned char> slot, lvl1, hrank, hpos;
     std::vector<int32_t> spack, row_cam, hbase, tpts;
@@ -221,10 +219,6 @@ struct ba_engine {
     int chol_grid = 1;
     // per-(tile, camera) partial rows + by-camera gather (ba_rows.cuh, ba_stream.cuh)
     DevBuf<int4> d_tmeta, d_tile_info;
-    DevBuf<int2> d_wpA;                // warp-packed tiles (scatter_mode 7, ba_wp.cuh)
-    DevBuf<int> d_wpB;
-    DevBuf<int4> d_winfo, d_tinfo2;
-    int nTilesWP = 0;
     HostScratch hs;
     DevBuf<int> d_cam_row_off, d_cam_rows;
     DevBuf<double> d_rows, d_tile_intr;
@@ -254,7 +248,8 @@ struct ba_engine {
     unsigned profiling = 0;           // bit k set: time kernel id k with CUDA events
     struct Stat { int64_t launches = 0; int64_t timed = 0; double ms = 0.0; double bytes = 0.0; } stats[KID_COUNT];
     int dbg_tail1 = 0;                // BA_TAIL_MODE1
-    int p2p_wide = 1;                 // peer-memory all-reduce: pull on many SMs in a kernel of its own (1, default) or inside the PCG tail's cluster (0; BA_P2P_WIDE)
+    int p2p_wide = -1;                // peer-memory all-reduce: pull on many SMs in a kernel of its own (1) or inside the PCG tail's cluster (0); -1 (default): the
+                                      // kernel of its own from 4 ranks on (at 2 ranks the extra launch costs what the wider pull saves); BA_P2P_WIDE overrides
     int pcg_tag = -1;                 // ordinal of the PCG iteration being launched (LaunchTimer tags; -1 outside the PCG loop)
     int pcg_pred = 0;                 // PCG iterations of the previous linear solve on this handle (first batch size)
     int k5_sample_stride = 1;         // time every n-th K5 launch only (events between two launches serialise them; BA_K5_SAMPLE)
@@ -378,97 +373,6 @@ void build_tiles(const vector<int32_t>& pt_off, int Np, vector<int32_t>& tile_of
         if (pstart < 0) pstart = p;
     }
     if (tile_off.back() != pt_off[Np]) tile_off.push_back(pt_off[Np]);
-}
-
-// Static schedule of the warp-packed tiles (scatter_mode 7, ba_wp.cuh).  Points are dealt in order to warps of 32 lanes (a point never
-// straddles two warps; an unobserved point closes the open warp so that a warp's points are consecutive ids) and warps to tiles of 8; a
-// point with more than 32 observations becomes a tile of its own (generic path).  Per tile: stable sort of its observations by camera
-// (rank = `slot`), rows = maximal runs of one camera inside 32 consecutive sorted positions.  Fills hs.winfo / tinfo2 / wpA / wpB and the
-// row numbering hs.hbase / hs.row_cam that the common code turns into the by-camera row lists.
-void build_wp_schedule(ba_engine* e, const int32_t* ocam, const vector<int32_t>& pt_off, int Np, HostScratch& hs) {
-    constexpr int W = bak::WP_WARPS, T = bak::WP_THREADS;
-    vector<int4>& winfo = hs.winfo; vector<int4>& tinfo2 = hs.tinfo2;
-    winfo.clear(); tinfo2.clear();
-    int cur = -1, lanes = 32, tile_warps = W;      // open warp (index into winfo), lanes used in it, warps used in the open tile
-    auto new_tile = [&] { tinfo2.push_back(make_int4(0, 0, 0, 0)); winfo.resize(winfo.size() + W, make_int4(0, 0, 0, 0)); tile_warps = 0; };
-    for (int p = 0; p < Np; ++p) {
-        const int a = pt_off[p], k = pt_off[p + 1] - a;
-        if (k == 0) { lanes = 32; continue; }
-        if (k > 32) {
-            new_tile();
-            tinfo2.back() = make_int4(k | bak::WP_LONG, 0, a, p);
-            tile_warps = W; lanes = 32;
-            continue;
-        }
-        if (lanes + k > 32) {
-            if (tile_warps == W) new_tile();
-            cur = int(tinfo2.size() - 1) * W + tile_warps++;
-            winfo[cur] = make_int4(a, 0, p, 0);
-            lanes = 0;
-        }
-        lanes += k;
-        winfo[cur].y = lanes | (((winfo[cur].y >> 8) + 1) << 8);
-        tinfo2.back().x += k;
-    }
-    const int nT = int(tinfo2.size());
-    hs.wpA.resize(std::max<size_t>(size_t(nT) * T, 1)); hs.wpB.resize(std::max<size_t>(size_t(nT) * T, 1));
-    std::vector<int32_t>& hbase = hs.hbase;
-    hbase.assign(size_t(nT) + 1, 0);
-    parallel_ranges(nT, [&](int t0, int t1) {
-        uint32_t key[T];
-        int pos_of[T], obs_of[T];     // dense index (position order) -> padded position / observation
-        for (int t = t0; t < t1; ++t) {
-            int2* A = hs.wpA.data() + size_t(t) * T; int32_t* B = hs.wpB.data() + size_t(t) * T;
-            for (int q = 0; q < T; ++q) { A[q] = make_int2(0, 0); B[q] = -1; }
-            if (tinfo2[t].x & bak::WP_LONG) { hbase[t + 1] = tinfo2[t].x & (bak::WP_LONG - 1); continue; }   // one row per observation
-            int n = 0;
-            for (int w = 0; w < W; ++w) {
-                const int4 wi = winfo[size_t(t) * W + w];
-                const int nw = wi.y & 0xff;
-                for (int l = 0; l < nw; ++l) {
-                    const int o = wi.x + l, q = w * 32 + l;
-                    pos_of[n] = q; obs_of[n] = o;
-                    key[n] = uint32_t(ocam[o]) << 9 | uint32_t(n);      // unique keys: std::sort == stable sort by camera
-                    ++n;
-                }
-                // point fields of the warp's lanes: first lane of the point, lanes of the point after this one, rank of the point in the warp
-                int pr = 0;
-                for (int l = 0; l < nw; ++pr) {
-                    const int pa = pt_off[wi.z + pr], pb = pt_off[wi.z + pr + 1];
-                    const int hl = pa - wi.x;
-                    for (int o = pa; o < pb; ++o, ++l) A[w * 32 + l].y = hl | (pb - 1 - o) << 5 | pr << 10;
-                }
-            }
-            std::sort(key, key + n);
-            int rank = 0;
-            for (int j = 0; j < n;) {
-                const int cam = int(key[j] >> 9);
-                int k = j;
-                while (k < n && int(key[k] >> 9) == cam) { A[pos_of[key[k] & 511u]].x = int(unsigned(cam) | unsigned(k) << 24); ++k; }
-                for (int q = j; q < k;) {
-                    const int nxt = std::min((q / 32 + 1) * 32, k);     // end of this run: the segment's end or the warp boundary
-                    B[q] = cam | ((nxt - q) << 22);
-                    for (int r = q; r < nxt; ++r) A[r].y |= (nxt - 1 - r) << 15 | (r == q ? rank << 20 : 0);
-                    ++rank;
-                    q = nxt;
-                }
-                j = k;
-            }
-            hbase[t + 1] = rank;
-        }
-    });
-    for (int t = 0; t < nT; ++t) { tinfo2[t].y = hbase[t]; hbase[t + 1] += hbase[t]; }
-    std::vector<int32_t>& row_cam = hs.row_cam;
-    row_cam.resize(hbase[nT]);
-    parallel_ranges(nT, [&](int t0, int t1) {
-        for (int t = t0; t < t1; ++t) {
-            int32_t* rc = row_cam.data() + hbase[t];
-            if (tinfo2[t].x & bak::WP_LONG) { const int n = tinfo2[t].x & (bak::WP_LONG - 1); for (int i = 0; i < n; ++i) rc[i] = ocam[tinfo2[t].z + i]; continue; }
-            const int32_t* B = hs.wpB.data() + size_t(t) * T;
-            for (int q = 0; q < tinfo2[t].x;) { *rc++ = B[q] & 0x3fffff; q += B[q] >> 22; }
-        }
-    });
-    (void)e;
 }
 
 // Two phases (CUDA IPC: freeing an exported allocation while a peer still has it mapped is undefined): every rank first closes the
@@ -777,9 +681,6 @@ void do_set_problem(ba_engine* e, const ba_problem* P, const DevState* dev = nul
         std::vector<unsigned char>&lvl1 = hs.lvl1, &hrank = hs.hrank, &hpos = hs.hpos;
         lvl1.resize(std::max(No, 1)); hrank.resize(std::max(No, 1)); hpos.resize(std::max(No, 1));
         std::vector<int32_t>&hbase = hs.hbase, &row_cam = hs.row_cam;
-        const bool wp = e->scatter_eff == 7;
-        if (wp) build_wp_schedule(e, ocam, pt_off, Np, hs);
-        else {
         hbase.assign(size_t(e->nTiles) + 1, 0);
         parallel_ranges(e->nTiles, [&](int t0, int t1) {
             uint32_t key[bak::TILE_OBS];
@@ -820,7 +721,6 @@ void do_set_problem(ba_engine* e, const ba_problem* P, const DevState* dev = nul
                 for (int j = 0; j < n;) { const int pk = spack[o0 + j]; *rc++ = pk & 0x3fffff; j += pk >> 22; }
             }
         });
-        }
         const int nRows = int(row_cam.size());
         vector<int32_t> cro(size_t(Nc) + 1, 0);
         pvec<int32_t>& crows = hs.crows; crows.resize(std::max(nRows, 1));
@@ -836,9 +736,9 @@ void do_set_problem(ba_engine* e, const ba_problem* P, const DevState* dev = nul
             parallel_chunks(nRows, nt3, [&](int k, int a, int b) { int32_t* cur = hist.data() + size_t(k) * Nc; for (int r = a; r < b; ++r) crows[cur[row_cam[r]]++] = r; });
         }
         // pack the per-position records (RowSched::tmeta) and per-tile records (RowSched::tile_info)
-        pvec<int4>& tmeta = hs.tmeta; tmeta.resize(wp ? 1 : std::max(No, 1));
-        vector<int4> tinfo(wp ? 1 : std::max(e->nTiles, 1));
-        if (!wp) parallel_ranges(e->nTiles, [&](int t0, int t1) {
+        pvec<int4>& tmeta = hs.tmeta; tmeta.resize(std::max(No, 1));
+        vector<int4> tinfo(std::max(e->nTiles, 1));
+        parallel_ranges(e->nTiles, [&](int t0, int t1) {
           for (int t = t0; t < t1; ++t) {
             const int o0 = tile_off[t], n = tile_off[t + 1] - o0;
             const int pfirst = obs_pt[o0];
@@ -856,12 +756,7 @@ void do_set_problem(ba_engine* e, const ba_problem* P, const DevState* dev = nul
           }
         });
         pt_.tick("row schedule (host threads)");
-        e->nTilesWP = 0;
-        if (wp) {
-            e->nTilesWP = int(hs.tinfo2.size());
-            e->d_wpA.upload(hs.wpA.data(), hs.wpA.size(), s); e->d_wpB.upload(hs.wpB.data(), hs.wpB.size(), s);
-            e->d_winfo.upload(hs.winfo.data(), hs.winfo.size(), s); e->d_tinfo2.upload(hs.tinfo2.data(), hs.tinfo2.size(), s);
-        } else { e->d_tmeta.upload(tmeta.data(), No, s); e->d_tile_info.upload(tinfo.data(), tinfo.size(), s); }
+        e->d_tmeta.upload(tmeta.data(), No, s); e->d_tile_info.upload(tinfo.data(), tinfo.size(), s);
         e->d_cam_row_off.upload(cro.data(), cro.size(), s); e->d_cam_rows.upload(crows.data(), nRows, s);
         e->d_rows.alloc(size_t(nRows) * bak::ROW_DOUBLES); e->d_rows.zero(s);
         // The rows are written by K5a and read back by the gather a few microseconds later, every PCG iteration: ask L2 to keep them
@@ -889,12 +784,11 @@ void do_set_problem(ba_engine* e, const ba_problem* P, const DevState* dev = nul
             }
             if (on || e->l2_window_ever) { CU_TRY(cudaStreamSetAttribute(e->stream, cudaStreamAttributeAccessPolicyWindow, &attr)); e->l2_window_ever = true; }
         }
-        e->d_tile_intr.alloc(size_t(4) * std::max(std::max(e->nTiles, e->nTilesWP), 1)); e->d_tile_intr.zero(s);
+        e->d_tile_intr.alloc(size_t(4) * std::max(e->nTiles, 1)); e->d_tile_intr.zero(s);
         CU_TRY(cudaStreamSynchronize(s));
         bak::RowSched& RS = e->RS;
         RS.tmeta = e->d_tmeta.p; RS.tile_info = e->d_tile_info.p;
         RS.rows = e->d_rows.p; RS.tile_intr = e->d_tile_intr.p; RS.cam_row_off = e->d_cam_row_off.p; RS.cam_rows = e->d_cam_rows.p; RS.nRows = nRows;
-        RS.wpA = e->d_wpA.p; RS.wpB = e->d_wpB.p; RS.winfo = e->d_winfo.p; RS.tile_info2 = e->d_tinfo2.p; RS.nTilesWP = e->nTilesWP;
     }
     pt_.tick("schedule uploads, rows alloc");
     e->d_tile_off.upload(tile_off.data(), tile_off.size(), s);
@@ -993,11 +887,6 @@ void do_set_problem(ba_engine* e, const ba_problem* P, const DevState* dev = nul
         const double rb = 8.0 * bak::ROW_DOUBLES;   // bytes per partial row as stored
         e->stats[KID_K4].bytes = no * (jb + 16 + 16) + np * 24 + rb * nr + 16.0 * e->nTiles;
         e->stats[KID_K5].bytes = no * (jb + 16) + np * 48 + 48 * nc + rb * nr + 16.0 * e->nTiles;
-        if (e->scatter_eff == 7) {   // warp-packed tiles: 12 B of schedule per (padded) position, 9 x 16 B of records per tile
-            const double sched = 12.0 * bak::WP_THREADS * e->nTilesWP + 144.0 * e->nTilesWP;
-            e->stats[KID_K4].bytes = no * (jb + 16) + np * 24 + rb * nr + sched;
-            e->stats[KID_K5].bytes = no * jb + np * 48 + 48 * nc + rb * nr + sched;
-        }
         e->stats[KID_GATHER].bytes = (rb + 4) * nr + 48 * nc;
         e->stats[KID_PCGV].bytes = e->stats[KID_GATHER].bytes + e->stats[KID_TAIL].bytes;
     }
@@ -1117,6 +1006,7 @@ void launch_sweep(ba_engine* e, int kid, const double* xin, double* yout, const 
 
 // K4 / K5a by the configured scatter: 1 = L2 atomics straight into `yout` (k_schur_sweep); 4 = partial rows, one CTA per
 // tile (k_schur_rows); 6 = partial rows, persistent streaming kernel (k_schur_stream).  4 and 6 leave the rows for the by-camera gather.
+#ifdef BA_WITH_STREAM
 template <int MODE, bool FI, int PK>
 void launch_stream(ba_engine* e, const double* xin, double* yout, const int* done, bool chain) {
     using Cfg = bak::StreamCfg<MODE, FI, PK>;
@@ -1145,6 +1035,8 @@ void set_stream_attrs(ba_engine* e) {
     e->stream_attr_set = true;
 }
 
+#endif
+
 template <int MODE>
 void launch_scatter(ba_engine* e, int kid, const double* xin, double* yout, const int* done) {
     if (e->nTiles == 0) return;
@@ -1154,20 +1046,13 @@ void launch_scatter(ba_engine* e, int kid, const double* xin, double* yout, cons
     if (e->fi && e->Ng > 1) CU_TRY(cudaMemsetAsync(yout + 6 * e->Nc, 0, size_t(4) * e->Ng * sizeof(double), e->stream));
     // K5a goes down the PDL chain; K4 is an ordinary launch (both griddepcontrol instructions are no-ops there)
     const bool chain = MODE == bak::SWEEP_MATVEC;
-    if (e->scatter_eff == 7) {   // warp-packed tiles (ba_wp.cuh)
-        auto go = [&](auto kern) {
-            if (chain) launch_chain(e, kern, dim3(e->nTilesWP), dim3(bak::WP_THREADS), e->V, e->RS, xin, yout, done);
-            else { KL(e); kern<<<e->nTilesWP, bak::WP_THREADS, 0, e->stream>>>(e->V, e->RS, xin, yout, done); }
-        };
-        if (e->fi) { if (e->jpack) go(bak::k_schur_wp<MODE, true, 1>); else go(bak::k_schur_wp<MODE, true, 0>); }
-        else { if (e->jpack) go(bak::k_schur_wp<MODE, false, 1>); else go(bak::k_schur_wp<MODE, false, 0>); }
-        return;
-    }
+#ifdef BA_WITH_STREAM
     if (e->scatter_eff == 6) {
         if (e->fi) { if (e->jpack) launch_stream<MODE, true, 1>(e, xin, yout, done, chain); else launch_stream<MODE, true, 0>(e, xin, yout, done, chain); }
         else { if (e->jpack) launch_stream<MODE, false, 1>(e, xin, yout, done, chain); else launch_stream<MODE, false, 0>(e, xin, yout, done, chain); }
         return;
     }
+#endif
     auto go = [&](auto kern) {
         if (chain) launch_chain(e, kern, dim3(e->nTiles), dim3(bak::TILE_OBS), e->V, e->RS, xin, yout, done);
         else { KL(e); kern<<<e->nTiles, bak::TILE_OBS, 0, e->stream>>>(e->V, e->RS, xin, yout, done); }
@@ -1199,7 +1084,7 @@ int solve_linear(ba_engine* e, double radius, double* rel_out, double lambda = 0
     if (!rowsm || e->nTiles == 0) e->d_b.zero(s);
     launch_scatter<bak::SWEEP_RHS>(e, KID_K4, nullptr, e->d_b.p, nullptr);
     if (rowsm && e->nTiles > 0) { LaunchTimer t(e, KID_GATHER);
-        KL(e), bak::k_camera_gather<<<gblocks, gthreads, 0, s>>>(e->Nc, e->Ng, e->fi, (e->scatter_eff == 7 ? e->nTilesWP : e->nTiles), e->RS, nullptr, nullptr, e->d_b.p, nullptr, nullptr, 0); }
+        KL(e), bak::k_camera_gather<<<gblocks, gthreads, 0, s>>>(e->Nc, e->Ng, e->fi, e->nTiles, e->RS, nullptr, nullptr, e->d_b.p, nullptr, nullptr, 0); }
     allreduce_sum(e, e->d_b.p, e->nf);
     if (e->dense) {   // direct solve (ba_dense.cuh): S formed densely, Cholesky with the right-hand side as an extra row, no host round trip
         const bak::DenseView& D = e->DV;
@@ -1267,22 +1152,22 @@ int solve_linear(ba_engine* e, double radius, double* rel_out, double lambda = 0
                 if (no_rows) {   // this rank's slot <- d_y
                     double* mine = e->p2p.view.data[e->p2p.view.rank] + size_t(ta.seq & 1u) * e->p2p.view.ldf;
                     CU_TRY(cudaMemcpyAsync(mine, e->d_y.p, size_t(e->nf) * sizeof(double), cudaMemcpyDeviceToDevice, s));
-                } else launch_chain(e, bak::k_camera_gather_push, dim3(gblocks), gthreads, e->Nc, e->Ng, e->fi, (e->scatter_eff == 7 ? e->nTilesWP : e->nTiles), e->RS, e->d_y.p, e->p2p.view, ta.seq, &sc->pcg, 1);
-                if (e->p2p_wide) {   // pull and sum the W slots on many SMs (ba_p2p.cuh: k_allreduce_pull); the tail then finds y complete in local memory
+                } else launch_chain(e, bak::k_camera_gather_push, dim3(gblocks), gthreads, e->Nc, e->Ng, e->fi, e->nTiles, e->RS, e->d_y.p, e->p2p.view, ta.seq, &sc->pcg, 1);
+                if (e->p2p_wide == 1 || (e->p2p_wide < 0 && e->opt.world_size >= 4)) {   // pull and sum the W slots on many SMs (ba_p2p.cuh: k_allreduce_pull); the tail then finds y complete in local memory
                     const int pblocks = std::max(1, std::min(2 * e->num_sms, cdiv((e->nf + 1) / 2, bak::PULL_THREADS)));
                     launch_chain(e, bak::k_allreduce_pull, dim3(pblocks), dim3(bak::PULL_THREADS), e->nf, e->p2p.view, ta.seq, e->d_y.p, &sc->pcg, 1);
                     ta.mode = 1;
                 }
             } else if (multi) {
                 { LaunchTimer tg(e, KID_GATHER, sample, launched);
-                  if (!no_rows) KL(e), bak::k_camera_gather<<<gblocks, gthreads, 0, s>>>(e->Nc, e->Ng, e->fi, (e->scatter_eff == 7 ? e->nTilesWP : e->nTiles), e->RS, nullptr, nullptr, e->d_y.p, nullptr, &sc->pcg, 0); }
+                  if (!no_rows) KL(e), bak::k_camera_gather<<<gblocks, gthreads, 0, s>>>(e->Nc, e->Ng, e->fi, e->nTiles, e->RS, nullptr, nullptr, e->d_y.p, nullptr, &sc->pcg, 0); }
                 allreduce_sum(e, e->d_y.p, e->nf);
             } else if (!no_rows && e->dbg_tail1) {   // BA_TAIL_MODE1=1 (bisecting aid): plain gather, q and p.q by the tail's cluster reduction
                 LaunchTimer tg(e, KID_GATHER, sample, launched);
-                launch_chain(e, bak::k_camera_gather, dim3(gblocks), gthreads, e->Nc, e->Ng, e->fi, (e->scatter_eff == 7 ? e->nTilesWP : e->nTiles), e->RS, nullptr, nullptr, e->d_y.p, nullptr, &sc->pcg, 0);
+                launch_chain(e, bak::k_camera_gather, dim3(gblocks), gthreads, e->Nc, e->Ng, e->fi, e->nTiles, e->RS, nullptr, nullptr, e->d_y.p, nullptr, &sc->pcg, 0);
             } else if (!no_rows) {   // one GPU: the gather forms q and the shares of p.q as well
                 LaunchTimer tg(e, KID_GATHER, sample, launched);
-                launch_chain(e, bak::k_camera_gather, dim3(gblocks), gthreads, e->Nc, e->Ng, e->fi, (e->scatter_eff == 7 ? e->nTilesWP : e->nTiles), e->RS, e->d_Df2.p, e->d_p.p, e->d_y.p, e->d_part1.p, &sc->pcg, 1);
+                launch_chain(e, bak::k_camera_gather, dim3(gblocks), gthreads, e->Nc, e->Ng, e->fi, e->nTiles, e->RS, e->d_Df2.p, e->d_p.p, e->d_y.p, e->d_part1.p, &sc->pcg, 1);
                 ta.mode = 0;
             }
             // q, alpha, x, r, z, rho, beta, stop test and the new search direction: one thread-block cluster (ba_pcg_cluster.cuh)
@@ -1584,10 +1469,14 @@ int ba_create(const ba_options* opt, ba_engine** out) {
         cudaDeviceProp prop{};
         CU_TRY(cudaGetDeviceProperties(&prop, e->device));
         e->num_sms = prop.multiProcessorCount;
-        auto known = [](int m) { return m == 1 || m == 4 || m == 6 || m == 7; };
+        auto known = [](int m) { return m == 1 || m == 4 || m == 6; };
         e->scatter_mode = known(opt->scatter_mode) ? opt->scatter_mode : 0;   // 0: default
         if (e->scatter_mode == 0) if (const char* v = std::getenv("BA_SCATTER_MODE")) { const int m = std::atoi(v); if (known(m)) e->scatter_mode = m; }   // A/B knob for the default
+#ifdef BA_WITH_STREAM
         set_stream_attrs(e);
+#else
+        if (e->scatter_mode == 6) throw BaFail{BA_ERR_UNSUPPORTED, "scatter_mode 6 (the cp.async.bulk streaming kernel) is not compiled into this library (build with -DBA_WITH_STREAM)"};
+#endif
         if (const char* g = std::getenv("BA_L2_FETCH")) CU_TRY(cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, size_t(std::atoi(g))));   // experiment knob: 32 / 64 / 128
         if (const char* v = std::getenv("BA_K5_SAMPLE")) e->k5_sample_stride = std::max(1, std::atoi(v));
         e->pdl = BA_PDL_DEFAULT;

@@ -41,13 +41,6 @@ struct RowSched {
     const int* cam_row_off;       // [Nc+1] by-camera view of the rows
     const int* cam_rows;          // [nRows] compact row ids, ascending
     int nRows;
-    // warp-packed tiles (scatter_mode 7, ba_wp.cuh): 256 positions per tile = 8 warps x 32 lanes, every warp holds whole points
-    const int2* wpA;              // [nTilesWP][256] per position: .x = camera | slot << 24;  .y = head lane | seg_rem << 5 | point rank << 10 | rem << 15 | hrank << 20
-    const int* wpB;               // [nTilesWP][256] sorted position: camera | run length << 22 at the head of a run, -1 elsewhere
-    const int4* winfo;            // [nTilesWP][8]   per warp: {first observation, observations | points << 8, first local point, 0}
-    const int4* tile_info2;       // [nTilesWP]      {observations of the tile (| WP_LONG: one point with more than 32 observations), first compact row,
-                                  //                  long tile: first observation, long tile: the point}
-    int nTilesWP;
 };
 
 // barrier policies of the tile math: the whole CTA (k_schur_rows) or one 128-thread consumer group (k_schur_stream)
