@@ -967,13 +967,14 @@ void candidate_cost(ba_engine* e) {
     CU_TRY(cudaMemsetAsync(&sc->bad_cand, 0, sizeof(int), s));
     { LaunchTimer t(e, KID_K0);
       KL(e), bak::k0_camera_precompute<<<cdiv(e->Nc, 128), 128, 0, s>>>(e->Nc, e->d_cpose.p, e->d_ccamrec.p, e->opt.taylor_rule); }
-    if (e->nTiles > 0) {
+    const int cblocks = e->No > 0 ? std::min(std::min(cdiv(e->No, bak::K1C_THREADS), e->num_sms * bak::K1C_CTAS_PER_SM), 2048) : 0;   // <= 2048 partials (d_part0)
+    if (cblocks > 0) {
         LaunchTimer t(e, KID_K1C);
-        if (e->opt.model == BA_MODEL_SNAVELY) KL(e), bak::k1c_candidate_cost<1><<<e->nTiles, bak::TILE_OBS, 0, s>>>(e->V, e->d_ccamrec.p, e->d_cintr.p, e->d_cpt.p, rp, e->d_part0.p, &sc->bad_cand);
-        else KL(e), bak::k1c_candidate_cost<0><<<e->nTiles, bak::TILE_OBS, 0, s>>>(e->V, e->d_ccamrec.p, e->d_cintr.p, e->d_cpt.p, rp, e->d_part0.p, &sc->bad_cand);
+        if (e->opt.model == BA_MODEL_SNAVELY) KL(e), bak::k1c_candidate_cost<1><<<cblocks, bak::K1C_THREADS, 0, s>>>(e->V, e->d_ccamrec.p, e->d_cintr.p, e->d_cpt.p, rp, e->d_part0.p, &sc->bad_cand);
+        else KL(e), bak::k1c_candidate_cost<0><<<cblocks, bak::K1C_THREADS, 0, s>>>(e->V, e->d_ccamrec.p, e->d_cintr.p, e->d_cpt.p, rp, e->d_part0.p, &sc->bad_cand);
     }
     { LaunchTimer t(e, KID_MISC);
-      KL(e), bak::k_reduce_partials<<<1, 1024, 0, s>>>(e->d_part0.p, e->nTiles, &sc->ccost); }
+      KL(e), bak::k_reduce_partials<<<1, 1024, 0, s>>>(e->d_part0.p, cblocks, &sc->ccost); }
 }
 
 // Launch along the PCG chain (K5a -> K5b -> tail -> K5a ...) with programmatic dependent launch: the next kernel's CTAs are scheduled

@@ -526,31 +526,44 @@ k1_residual_jacobian(View V, const double* __restrict__ camrec, const double* __
     if (threadIdx.x == 0) cost_partial[blockIdx.x] = cs;
 }
 
-// K1' — candidate cost: residual + rho only.  Reads 24 No + 24 Np + 160 Nc, writes one partial per tile.
+// K1' — candidate cost: residual + rho only.  Reads 24 No + 24 Np + 160 Nc, writes one partial per CTA.
+// Persistent grid-stride sweep (K1C_CTAS_PER_SM CTAs of 256 threads per SM): the observation's index data (camera, point, pixel) of the
+// NEXT trip is loaded while the current trip's gathers (camera record, point) and arithmetic run, so a trip costs one gather latency, not
+// two dependent ones.  (The first version was one short CTA per tile: 40 096 CTAs of three dependent loads and a block reduction each ran at
+// 0.27 of the HBM roofline, bound by CTA turnover.)
+constexpr int K1C_THREADS = 256;
+constexpr int K1C_CTAS_PER_SM = 8;
 template <int MODEL>
-__global__ void __launch_bounds__(TILE_OBS)
+__global__ void __launch_bounds__(K1C_THREADS)
 k1c_candidate_cost(View V, const double* __restrict__ camrec, const double* __restrict__ intr, const double* __restrict__ pt,
                    RobustParams rp, double* __restrict__ cost_partial, int* __restrict__ bad_flag) {
     __shared__ double sred[32];
-    const int t = blockIdx.x;
-    const int o0 = V.tile_off[t], o1 = V.tile_off[t + 1];
+    const int stride = gridDim.x * K1C_THREADS;
     double cost = 0.0;
     int bad = 0;
-    for (int o = o0 + threadIdx.x; o < o1; o += TILE_OBS) {
-        const int c = V.obs_cam[o], p = V.obs_pt[o];
+    int o = blockIdx.x * K1C_THREADS + threadIdx.x;
+    int c = 0, p = 0;
+    double2 uv = make_double2(0.0, 0.0);
+    if (o < V.No) { c = __ldg(V.obs_cam + o); p = __ldg(V.obs_pt + o); uv = ldg2(V.obs_uv + o); }
+    while (o < V.No) {
+        const int on = o + stride;
+        int cn = 0, pn = 0;
+        double2 uvn = make_double2(0.0, 0.0);
+        if (on < V.No) { cn = __ldg(V.obs_cam + on); pn = __ldg(V.obs_pt + on); uvn = ldg2(V.obs_uv + on); }
         Proj q;
         double cr[12];   // R, t
         load_camrec<6>(camrec, c, cr);
-        project_obs<MODEL>(cr, pt + 3 * size_t(p), intr + (V.Ng == 1 ? 0 : 4 * V.cam_group[c]), ldg2(V.obs_uv + o), q);
+        project_obs<MODEL>(cr, pt + 3 * size_t(p), intr + (V.Ng == 1 ? 0 : 4 * V.cam_group[c]), uv, q);
         const double s = q.r0 * q.r0 + q.r1 * q.r1;
         double w;
         const double rho = robust(rp, s, w);
         if (!isfinite(rho)) bad = 1;
         cost += 0.5 * rho;
+        o = on; c = cn; p = pn; uv = uvn;
     }
     if (bad) atomicOr(bad_flag, 1);
     const double cs = block_sum(cost, sred);
-    if (threadIdx.x == 0) cost_partial[t] = cs;
+    if (threadIdx.x == 0) cost_partial[blockIdx.x] = cs;
 }
 
 // Deterministic final reduction of per-tile partials (fixed order for a fixed launch shape).
