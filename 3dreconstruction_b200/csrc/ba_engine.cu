@@ -249,7 +249,9 @@ struct ba_engine {
     struct Stat { int64_t launches = 0; int64_t timed = 0; double ms = 0.0; double bytes = 0.0; } stats[KID_COUNT];
     int dbg_tail1 = 0;                // BA_TAIL_MODE1
     int p2p_wide = -1;                // peer-memory all-reduce: pull on many SMs in a kernel of its own (1) or inside the PCG tail's cluster (0); -1 (default): the
-                                      // kernel of its own from 4 ranks on (at 2 ranks the extra launch costs what the wider pull saves); BA_P2P_WIDE overrides
+                                      // kernel of its own from 4 ranks and 32768 reduced unknowns on.  Measured at 8 GPUs (profiles/r2i_pull_ab_n8.txt): Final-13682
+                                      // (82 092 unknowns) 274.7 -> 259.6 us per PCG iteration, Venice (10 668) 60.8 -> 64.2 us (the extra launch costs more than the
+                                      // wider pull saves); at 2 GPUs no difference.  BA_P2P_WIDE overrides.
     int pcg_tag = -1;                 // ordinal of the PCG iteration being launched (LaunchTimer tags; -1 outside the PCG loop)
     int pcg_pred = 0;                 // PCG iterations of the previous linear solve on this handle (first batch size)
     int k5_sample_stride = 1;         // time every n-th K5 launch only (events between two launches serialise them; BA_K5_SAMPLE)
@@ -1154,7 +1156,7 @@ int solve_linear(ba_engine* e, double radius, double* rel_out, double lambda = 0
                     double* mine = e->p2p.view.data[e->p2p.view.rank] + size_t(ta.seq & 1u) * e->p2p.view.ldf;
                     CU_TRY(cudaMemcpyAsync(mine, e->d_y.p, size_t(e->nf) * sizeof(double), cudaMemcpyDeviceToDevice, s));
                 } else launch_chain(e, bak::k_camera_gather_push, dim3(gblocks), gthreads, e->Nc, e->Ng, e->fi, e->nTiles, e->RS, e->d_y.p, e->p2p.view, ta.seq, &sc->pcg, 1);
-                if (e->p2p_wide == 1 || (e->p2p_wide < 0 && e->opt.world_size >= 4)) {   // pull and sum the W slots on many SMs (ba_p2p.cuh: k_allreduce_pull); the tail then finds y complete in local memory
+                if (e->p2p_wide == 1 || (e->p2p_wide < 0 && e->opt.world_size >= 4 && e->nf >= 32768)) {   // pull and sum the W slots on many SMs (ba_p2p.cuh: k_allreduce_pull); the tail then finds y complete in local memory
                     const int pblocks = std::max(1, std::min(2 * e->num_sms, cdiv((e->nf + 1) / 2, bak::PULL_THREADS)));
                     launch_chain(e, bak::k_allreduce_pull, dim3(pblocks), dim3(bak::PULL_THREADS), e->nf, e->p2p.view, ta.seq, e->d_y.p, &sc->pcg, 1);
                     ta.mode = 1;
