@@ -1300,6 +1300,9 @@ void lm_solve(ba_engine* e) {
         if (H->bad_cand || !std::isfinite(ccost)) ccost = std::numeric_limits<double>::max();
         R.candidate_cost = ccost;
         R.step_norm = std::sqrt(H->step2_pt + H->step2_f);
+        // TrustRegionMinimizer::ParameterToleranceReached / FunctionToleranceReached, in this order, before the accept test, on every valid
+        // step: Ceres 2.2 has NO "at least one successful step" guard on these two tests (SURVEY 8 a-LM lists one; that guard is not in the
+        // 2.2 minimizer and is deliberately not implemented here) — restated from the published source, not pinned by a Ceres run.
         if (R.step_norm <= O.parameter_tolerance * (x_norm + O.parameter_tolerance)) { finish(BA_TERM_CONVERGENCE, "parameter tolerance reached", cost); return; }
         if (std::fabs(cost - ccost) <= O.function_tolerance * cost) { finish(BA_TERM_CONVERGENCE, "function tolerance reached", cost); return; }
         R.relative_decrease = (ccost >= std::numeric_limits<double>::max()) ? std::numeric_limits<double>::lowest() : (cost - ccost) / R.model_cost_change;

@@ -704,6 +704,9 @@ int lm_solve(ba_engine* e) {
         if (!evaluate(e, cpose.data(), cintr.data(), cpt.data(), false, &ccost, nullptr, nullptr, nullptr, nullptr, false)) ccost = std::numeric_limits<double>::max();
         R.candidate_cost = ccost;
         R.step_norm = FN.norm([&](int kind, int i) { return kind == 0 ? pose[i] - cpose[i] : kind == 1 ? intr[i] - cintr[i] : pt[i] - cpt[i]; });
+        // TrustRegionMinimizer::ParameterToleranceReached / FunctionToleranceReached, in this order, before the accept test, on every valid
+        // step: Ceres 2.2 has NO "at least one successful step" guard on these two tests (SURVEY 8 a-LM lists one; that guard is not in the
+        // 2.2 minimizer and is deliberately not implemented here) — restated from the published source, not pinned by a Ceres run.
         if (R.step_norm <= O.parameter_tolerance * (x_norm + O.parameter_tolerance)) return finish(BA_TERM_CONVERGENCE, "parameter tolerance reached", cost);
         if (std::fabs(cost - ccost) <= O.function_tolerance * cost) return finish(BA_TERM_CONVERGENCE, "function tolerance reached", cost);
         R.relative_decrease = (ccost >= std::numeric_limits<double>::max()) ? std::numeric_limits<double>::lowest() : (cost - ccost) / mcc;
