@@ -202,7 +202,10 @@ int  ba_reset_state(ba_engine* e);                            /* restore the par
  * 176-186).  ba_append grows the problem held by the handle instead: the state already on the device (the result of the last
  * ba_solve) is kept, new poses / Camera groups / points are appended after the existing ones (ids continue), new observations
  * may reference old and new ids in any order and are merged into point order (within a point: existing observations first, then
- * the new ones in the order given).  The merged state becomes the one ba_reset_state restores.  Single GPU only. */
+ * the new ones in the order given).  The merged state becomes the one ba_reset_state restores.  Single GPU only.
+ * The delta is validated before anything changes (a rejected delta leaves the handle as it was); if the rebuild itself fails afterwards
+ * (out of device memory, BA_LINEAR_EXACT limits exceeded by the grown problem, a CUDA error) the handle holds NO problem any more:
+ * ba_solve then returns BA_ERR_NO_PROBLEM and the caller starts again with ba_set_problem (IncrementalBundleAdjuster does). */
 typedef struct ba_delta {
     int32_t num_new_cameras;      const double* pose;  const int32_t* cam_group;  const uint8_t* cam_fixed;
     int32_t num_new_groups;       const double* intr;
