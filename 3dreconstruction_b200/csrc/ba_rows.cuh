@@ -92,8 +92,12 @@ __device__ __forceinline__ void tile_rows(const View& V, const RowSched& S, Tile
     double2 u = make_double2(0.0, 0.0), tt = make_double2(0.0, 0.0);
     if (MODE == SWEEP_MATVEC) {
         if (act) {
+#ifdef BA_EXP_NO_PGATHER      // timing experiment only (wrong results): what the divergent gather of p[c] costs
+            const double2 x0 = make_double2(1.0, 0.5), x1 = make_double2(0.25, 2.0), x2 = make_double2(1.5, 0.75);
+#else
             const double2* xc = reinterpret_cast<const double2*>(xin + 6 * c);
             const double2 x0 = __ldg(xc), x1 = __ldg(xc + 1), x2 = __ldg(xc + 2);      // (one 32-byte + one 16-byte load by the parity of c measured 1 % slower)
+#endif
             u.x = R.jc[0].x * x0.x + R.jc[1].x * x0.y + R.jc[2].x * x1.x + R.jc[3].x * x1.y + R.jc[4].x * x2.x + R.jc[5].x * x2.y;
             u.y = R.jc[0].y * x0.x + R.jc[1].y * x0.y + R.jc[2].y * x1.x + R.jc[3].y * x1.y + R.jc[4].y * x2.x + R.jc[5].y * x2.y;
             if (FI) {
@@ -103,6 +107,7 @@ __device__ __forceinline__ void tile_rows(const View& V, const RowSched& S, Tile
 #pragma unroll
             for (int a = 0; a < 3; ++a) M.sW[tid][a] = R.jp[a].x * u.x + R.jp[a].y * u.y;
         }
+#ifndef BA_EXP_NO_POINT      // timing experiment only (wrong results): what the per-point phase (two barriers, shared-memory exchange) costs
         bar();
         if (npt_obs > 0) {
             double W0 = 0, W1 = 0, W2 = 0;
@@ -117,6 +122,9 @@ __device__ __forceinline__ void tile_rows(const View& V, const RowSched& S, Tile
             tt.x = u.x - (R.jp[0].x * v[0] + R.jp[1].x * v[1] + R.jp[2].x * v[2]);
             tt.y = u.y - (R.jp[0].y * v[0] + R.jp[1].y * v[1] + R.jp[2].y * v[2]);
         }
+#else
+        if (act) { tt.x = u.x - (R.jp[0].x * R.h0.x + R.jp[1].x * R.h1.x + R.jp[2].x * R.h2.x); tt.y = u.y - (R.jp[0].y * R.h0.y + R.jp[1].y * R.h1.y + R.jp[2].y * R.h2.y); }
+#endif
     } else if (act) {   // SWEEP_RHS: t = r - E vp
         const double* v = V.vp + 3 * size_t(pfirst + lpt);
         tt.x = R.rr.x - (R.jp[0].x * v[0] + R.jp[1].x * v[1] + R.jp[2].x * v[2]);
