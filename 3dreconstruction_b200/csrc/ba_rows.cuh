@@ -104,14 +104,29 @@ __device__ __forceinline__ void tile_rows(const View& V, const RowSched& S, Tile
 #pragma unroll
                 for (int k = 0; k < 4; ++k) { const double xv = __ldg(xin + ioff + 4 * g + k); u.x += R.ji[k].x * xv; u.y += R.ji[k].y * xv; }
             }
-#pragma unroll
-            for (int a = 0; a < 3; ++a) M.sW[tid][a] = R.jp[a].x * u.x + R.jp[a].y * u.y;
         }
 #ifndef BA_EXP_NO_POINT      // timing experiment only (wrong results): what the per-point phase (two barriers, shared-memory exchange) costs
+        // W_p = sum over the point's observations of Jp^T u.  First inside the warp: the lanes of one point are contiguous, so a segmented
+        // shuffle reduction (fixed tree, only as many steps as the longest run in this warp needs) leaves the sum of every run in its first
+        // lane; only those lanes go through shared memory, and the point thread adds one value per warp its point touches (1.1 on average)
+        // instead of walking all its observations serially (5 on average, up to 40: the tile's critical path between the two barriers).
+        {
+            double w0 = 0.0, w1 = 0.0, w2 = 0.0;
+            if (act) { w0 = R.jp[0].x * u.x + R.jp[0].y * u.y; w1 = R.jp[1].x * u.x + R.jp[1].y * u.y; w2 = R.jp[2].x * u.x + R.jp[2].y * u.y; }
+            const unsigned same = __match_any_sync(0xffffffffu, act ? lpt : 0xffff);      // lanes of my point in this warp (contiguous)
+            const int lane = tid & 31;
+            const int segrem = __popc(same >> lane) - 1;                                   // lanes of the run after this one
+            const int maxseg = __reduce_max_sync(0xffffffffu, segrem);
+            for (int d = 1; d <= maxseg; d <<= 1) {
+                const double a0 = __shfl_down_sync(0xffffffffu, w0, d), a1 = __shfl_down_sync(0xffffffffu, w1, d), a2 = __shfl_down_sync(0xffffffffu, w2, d);
+                if (d <= segrem) { w0 += a0; w1 += a1; w2 += a2; }
+            }
+            if (act && (same & ((1u << lane) - 1u)) == 0) { M.sW[tid][0] = w0; M.sW[tid][1] = w1; M.sW[tid][2] = w2; }   // first lane of its run
+        }
         bar();
         if (npt_obs > 0) {
-            double W0 = 0, W1 = 0, W2 = 0;
-            for (int i = pstart, e = pstart + npt_obs; i < e; ++i) { W0 += M.sW[i][0]; W1 += M.sW[i][1]; W2 += M.sW[i][2]; }
+            double W0 = M.sW[pstart][0], W1 = M.sW[pstart][1], W2 = M.sW[pstart][2];
+            for (int i = (pstart / 32 + 1) * 32, e = pstart + npt_obs; i < e; i += 32) { W0 += M.sW[i][0]; W1 += M.sW[i][1]; W2 += M.sW[i][2]; }
             M.sV[tid][0] = R.h0.x * W0 + R.h0.y * W1 + R.h1.x * W2;      // Hinv rows (H0,H1,H2) (H1,H3,H4) (H2,H4,H5)
             M.sV[tid][1] = R.h0.y * W0 + R.h1.y * W1 + R.h2.x * W2;
             M.sV[tid][2] = R.h1.x * W0 + R.h2.x * W1 + R.h2.y * W2;
