@@ -197,6 +197,7 @@ struct ba_engine {
     DevBuf<double2> d_J2, d_r2, d_JcA;
     int k1_grid = 1;
     DevBuf<double> d_Hpp, d_gp, d_Hinv, d_vp, d_yp, d_sc_pt;
+    DevBuf<double> d_G, d_vt;         // pose-factored matvec: per-camera 6x6 factors, vt = [G_c p_c | intrinsics entries of p]
     DevBuf<double> d_red;        // [Hcc 36Nc | gc 6Nc | Hii 16Ng | gi 4Ng] — one all-reduce per evaluation
     DevBuf<double> d_sc_f, d_Df2, d_Minv, d_b, d_x, d_r, d_z, d_p, d_y;
     DevBuf<double> d_sdiag;           // Schur-Jacobi: per-pose correction blocks (k_schur_diag)
@@ -248,6 +249,8 @@ struct ba_engine {
     unsigned profiling = 0;           // bit k set: time kernel id k with CUDA events
     struct Stat { int64_t launches = 0; int64_t timed = 0; double ms = 0.0; double bytes = 0.0; } stats[KID_COUNT];
     int dbg_tail1 = 0;                // BA_TAIL_MODE1
+    int factored_opt = 1;             // BA_POSE_FACTORED (default 1): K5a streams Jp only (ba_rows.cuh: k_pose_factors); 0 = explicit Jc and Jp (bisecting / A-B)
+    int factored = 0;                 // in effect for the current problem (partial rows, one CTA per tile, PCG)
     int p2p_wide = -1;                // peer-memory all-reduce: pull on many SMs in a kernel of its own (1) or inside the PCG tail's cluster (0); -1 (default): the
                                       // kernel of its own from 4 ranks and 32768 reduced unknowns on.  Measured at 8 GPUs (profiles/r2i_pull_ab_n8.txt): Final-13682
                                       // (82 092 unknowns) 274.7 -> 259.6 us per PCG iteration, Venice (10 668) 60.8 -> 64.2 us (the extra launch costs more than the
@@ -837,6 +840,8 @@ void do_set_problem(ba_engine* e, const ba_problem* P, const DevState* dev = nul
     e->d_red.alloc(e->red_count());
     for (auto* b : {&e->d_sc_f, &e->d_Df2, &e->d_b, &e->d_x, &e->d_r, &e->d_z, &e->d_p, &e->d_y}) b->alloc(e->nf);
     e->d_Minv.alloc(size_t(36) * Nc + size_t(16) * Ng);
+    e->factored = (e->factored_opt && e->scatter_eff == 4 && Nc > 0) ? 1 : 0;
+    if (e->factored) { e->d_G.alloc(size_t(36) * Nc); e->d_vt.alloc(size_t(e->nf) + size_t(bak::VT_STRIDE - 6) * Nc); e->d_vt.zero(s); }
     const size_t nparts = std::max<size_t>(std::max(e->nTiles, Nc + 8), 2048);
     e->d_part0.alloc(nparts); e->d_part1.alloc(nparts);
     e->d_scal.alloc(1);
@@ -889,6 +894,8 @@ void do_set_problem(ba_engine* e, const ba_problem* P, const DevState* dev = nul
         const double rb = 8.0 * bak::ROW_DOUBLES;   // bytes per partial row as stored
         e->stats[KID_K4].bytes = no * (jb + 16 + 16) + np * 24 + rb * nr + 16.0 * e->nTiles;
         e->stats[KID_K5].bytes = no * (jb + 16) + np * 48 + 48 * nc + rb * nr + 16.0 * e->nTiles;
+        if (e->factored)   // pose-factored: Jp (48 B) [+ Ji 64 B] and the schedule record per observation, Hinv and the point per point, vt per camera
+            e->stats[KID_K5].bytes = no * (48.0 + (e->fi ? 64.0 : 0.0) + 16) + np * (48 + 24) + 48 * nc + rb * nr + 16.0 * e->nTiles;
         e->stats[KID_GATHER].bytes = (rb + 4) * nr + 48 * nc;
         e->stats[KID_PCGV].bytes = e->stats[KID_GATHER].bytes + e->stats[KID_TAIL].bytes;
     }
@@ -917,7 +924,8 @@ void evaluate_full(ba_engine* e) {
     const bak::RobustParams rp{e->opt.robust_kind, e->opt.robust_a};
     CU_TRY(cudaMemsetAsync(&sc->bad_eval, 0, sizeof(int), s));
     { LaunchTimer t(e, KID_K0);
-      KL(e), bak::k0_camera_precompute<<<cdiv(e->Nc, 128), 128, 0, s>>>(e->Nc, e->d_pose.p, e->d_camrec.p, e->opt.taylor_rule); }
+      KL(e), bak::k0_camera_precompute<<<cdiv(e->Nc, 128), 128, 0, s>>>(e->Nc, e->d_pose.p, e->d_camrec.p, e->opt.taylor_rule);
+      if (e->factored) KL(e), bak::k_pose_factors<<<cdiv(e->Nc, 128), 128, 0, s>>>(e->Nc, e->d_camrec.p, e->d_cam_free.p, e->V.left_twist, e->d_G.p); }
     if (e->nTiles > 0) {
         LaunchTimer t(e, KID_K1);
         if (e->opt.model == BA_MODEL_SNAVELY) KL(e), bak::k1_residual_jacobian<1><<<e->k1_grid, bak::TILE_OBS, 0, s>>>(e->V, e->d_camrec.p, e->d_intr.p, e->d_pt.p, rp, e->d_part0.p, &sc->bad_eval);
@@ -1056,6 +1064,12 @@ void launch_scatter(ba_engine* e, int kid, const double* xin, double* yout, cons
         return;
     }
 #endif
+    if (chain && e->factored) {   // K5a, pose-factored: gathers vt = G p (written by the PCG tail) instead of p, reads the points of the linearisation
+        auto gof = [&](auto kern) { launch_chain(e, kern, dim3(e->nTiles), dim3(bak::TILE_OBS), e->V, e->RS, e->d_vt.p, e->d_pt.p, yout, done); };
+        if (e->fi) { if (e->jpack) gof(bak::k_schur_rows_f<true, 1>); else gof(bak::k_schur_rows_f<true, 0>); }
+        else { if (e->jpack) gof(bak::k_schur_rows_f<false, 1>); else gof(bak::k_schur_rows_f<false, 0>); }
+        return;
+    }
     auto go = [&](auto kern) {
         if (chain) launch_chain(e, kern, dim3(e->nTiles), dim3(bak::TILE_OBS), e->V, e->RS, xin, yout, done);
         else { KL(e); kern<<<e->nTiles, bak::TILE_OBS, 0, e->stream>>>(e->V, e->RS, xin, yout, done); }
@@ -1087,7 +1101,7 @@ int solve_linear(ba_engine* e, double radius, double* rel_out, double lambda = 0
     if (!rowsm || e->nTiles == 0) e->d_b.zero(s);
     launch_scatter<bak::SWEEP_RHS>(e, KID_K4, nullptr, e->d_b.p, nullptr);
     if (rowsm && e->nTiles > 0) { LaunchTimer t(e, KID_GATHER);
-        KL(e), bak::k_camera_gather<<<gblocks, gthreads, 0, s>>>(e->Nc, e->Ng, e->fi, e->nTiles, e->RS, nullptr, nullptr, e->d_b.p, nullptr, nullptr, 0); }
+        KL(e), bak::k_camera_gather<<<gblocks, gthreads, 0, s>>>(e->Nc, e->Ng, e->fi, e->nTiles, e->RS, nullptr, nullptr, e->d_b.p, nullptr, nullptr, 0, nullptr); }
     allreduce_sum(e, e->d_b.p, e->nf);
     if (e->dense) {   // direct solve (ba_dense.cuh): S formed densely, Cholesky with the right-hand side as an extra row, no host round trip
         const bak::DenseView& D = e->DV;
@@ -1122,8 +1136,9 @@ int solve_linear(ba_engine* e, double radius, double* rel_out, double lambda = 0
         return 0;   // failure (bad_lin) is seen by the caller's next read-back
     }
     const bak::PcgParams pp{e->opt.pcg_max_iterations, e->opt.pcg_forcing, e->opt.pcg_rel_tolerance, e->opt.eta};
+    const double* Gf = e->factored ? e->d_G.p : nullptr;   // pose-factored K5a: its rows are multiplied by G_c^T in the gather, the tail hands vt = G p back
     { LaunchTimer t(e, KID_PCGV);
-      KL(e), bak::k_pcg_init2<<<1, 1024, 0, s>>>(e->nf, e->Nc, e->d_Minv.p, e->d_b.p, e->d_x.p, e->d_r.p, e->d_z.p, e->d_p.p, &sc->pcg); }
+      KL(e), bak::k_pcg_init2<<<1, 1024, 0, s>>>(e->nf, e->Nc, e->d_Minv.p, e->d_b.p, e->d_x.p, e->d_r.p, e->d_z.p, e->d_p.p, &sc->pcg, Gf, e->factored ? e->d_vt.p : nullptr); }
     // PCG iterations (K5a -> K5b -> cluster tail, a chain of programmatic dependent launches) go out in batches without host sync; a
     // device-side `done` flag turns the rest of a batch into no-ops once the stop test fires, and the host reads the PCG state once
     // per batch.  Fixed tolerance: iteration counts of consecutive linear solves differ by a few, so the first batch is the previous
@@ -1136,6 +1151,7 @@ int solve_linear(ba_engine* e, double radius, double* rel_out, double lambda = 0
     ta.Nc = e->Nc; ta.Ng = e->Ng; ta.fi = e->fi; ta.Minv = e->d_Minv.p; ta.b = e->d_b.p; ta.Df2 = e->d_Df2.p;
     ta.y = e->d_y.p; ta.p = e->d_p.p; ta.x = e->d_x.p; ta.r = e->d_r.p; ta.z = e->d_z.p; ta.st = &sc->pcg; ta.pp = pp;
     ta.dotp = e->d_part1.p; ta.ndot = gblocks;
+    ta.G = Gf; ta.vt = e->factored ? e->d_vt.p : nullptr;
     const bool multi = e->opt.world_size > 1;
     const bool no_rows = !rowsm || e->nTiles == 0;   // y is accumulated in d_y by atomics (or stays zero on a rank without observations)
     for (;;) {
@@ -1155,7 +1171,7 @@ int solve_linear(ba_engine* e, double radius, double* rel_out, double lambda = 0
                 if (no_rows) {   // this rank's slot <- d_y
                     double* mine = e->p2p.view.data[e->p2p.view.rank] + size_t(ta.seq & 1u) * e->p2p.view.ldf;
                     CU_TRY(cudaMemcpyAsync(mine, e->d_y.p, size_t(e->nf) * sizeof(double), cudaMemcpyDeviceToDevice, s));
-                } else launch_chain(e, bak::k_camera_gather_push, dim3(gblocks), gthreads, e->Nc, e->Ng, e->fi, e->nTiles, e->RS, e->d_y.p, e->p2p.view, ta.seq, &sc->pcg, 1);
+                } else launch_chain(e, bak::k_camera_gather_push, dim3(gblocks), gthreads, e->Nc, e->Ng, e->fi, e->nTiles, e->RS, e->d_y.p, e->p2p.view, ta.seq, &sc->pcg, 1, Gf);
                 if (e->p2p_wide == 1 || (e->p2p_wide < 0 && e->opt.world_size >= 4 && e->nf >= 32768)) {   // pull and sum the W slots on many SMs (ba_p2p.cuh: k_allreduce_pull); the tail then finds y complete in local memory
                     const int pblocks = std::max(1, std::min(2 * e->num_sms, cdiv((e->nf + 1) / 2, bak::PULL_THREADS)));
                     launch_chain(e, bak::k_allreduce_pull, dim3(pblocks), dim3(bak::PULL_THREADS), e->nf, e->p2p.view, ta.seq, e->d_y.p, &sc->pcg, 1);
@@ -1163,14 +1179,14 @@ int solve_linear(ba_engine* e, double radius, double* rel_out, double lambda = 0
                 }
             } else if (multi) {
                 { LaunchTimer tg(e, KID_GATHER, sample, launched);
-                  if (!no_rows) KL(e), bak::k_camera_gather<<<gblocks, gthreads, 0, s>>>(e->Nc, e->Ng, e->fi, e->nTiles, e->RS, nullptr, nullptr, e->d_y.p, nullptr, &sc->pcg, 0); }
+                  if (!no_rows) KL(e), bak::k_camera_gather<<<gblocks, gthreads, 0, s>>>(e->Nc, e->Ng, e->fi, e->nTiles, e->RS, nullptr, nullptr, e->d_y.p, nullptr, &sc->pcg, 0, Gf); }
                 allreduce_sum(e, e->d_y.p, e->nf);
             } else if (!no_rows && e->dbg_tail1) {   // BA_TAIL_MODE1=1 (bisecting aid): plain gather, q and p.q by the tail's cluster reduction
                 LaunchTimer tg(e, KID_GATHER, sample, launched);
-                launch_chain(e, bak::k_camera_gather, dim3(gblocks), gthreads, e->Nc, e->Ng, e->fi, e->nTiles, e->RS, nullptr, nullptr, e->d_y.p, nullptr, &sc->pcg, 0);
+                launch_chain(e, bak::k_camera_gather, dim3(gblocks), gthreads, e->Nc, e->Ng, e->fi, e->nTiles, e->RS, nullptr, nullptr, e->d_y.p, nullptr, &sc->pcg, 0, Gf);
             } else if (!no_rows) {   // one GPU: the gather forms q and the shares of p.q as well
                 LaunchTimer tg(e, KID_GATHER, sample, launched);
-                launch_chain(e, bak::k_camera_gather, dim3(gblocks), gthreads, e->Nc, e->Ng, e->fi, e->nTiles, e->RS, e->d_Df2.p, e->d_p.p, e->d_y.p, e->d_part1.p, &sc->pcg, 1);
+                launch_chain(e, bak::k_camera_gather, dim3(gblocks), gthreads, e->Nc, e->Ng, e->fi, e->nTiles, e->RS, e->d_Df2.p, e->d_p.p, e->d_y.p, e->d_part1.p, &sc->pcg, 1, Gf);
                 ta.mode = 0;
             }
             // q, alpha, x, r, z, rho, beta, stop test and the new search direction: one thread-block cluster (ba_pcg_cluster.cuh)
@@ -1488,6 +1504,7 @@ int ba_create(const ba_options* opt, ba_engine** out) {
         e->pdl = BA_PDL_DEFAULT;
         if (const char* v = std::getenv("BA_PDL")) e->pdl = std::atoi(v) ? 1 : 0;
         if (const char* v = std::getenv("BA_TAIL_MODE1")) e->dbg_tail1 = std::atoi(v) ? 1 : 0;
+        if (const char* v = std::getenv("BA_POSE_FACTORED")) e->factored_opt = std::atoi(v) ? 1 : 0;
         if (const char* v = std::getenv("BA_P2P_WIDE")) e->p2p_wide = std::atoi(v) ? 1 : 0;
         // sm_100a images are architecture-specific: they run on compute capability 10.0 only (not on 10.3 / 12.x); probe one kernel as well
         if (prop.major != 10 || prop.minor != 0)
@@ -1793,9 +1810,10 @@ int ba_nccl_unique_id(void* out128) {
 int ba_get_execution_info(ba_engine* e, int64_t* info, int32_t cap, int32_t* n) {
     if (!e || !n) return BA_ERR_INVALID_ARGUMENT;
     if (!e->has_problem) return fail(e, BA_ERR_NO_PROBLEM, "no problem set");
-    const int64_t v[6] = {e->dense ? BA_LINEAR_EXACT : BA_LINEAR_PCG, e->scatter_eff, e->opt.world_size > 1 ? (e->p2p.on ? 2 : 1) : 0, e->host_syncs, e->nTiles, e->RS.nRows};
-    *n = 6;
-    if (info) for (int i = 0; i < std::min<int>(cap, 6); ++i) info[i] = v[i];
+    const int64_t v[7] = {e->dense ? BA_LINEAR_EXACT : BA_LINEAR_PCG, e->scatter_eff, e->opt.world_size > 1 ? (e->p2p.on ? 2 : 1) : 0, e->host_syncs, e->nTiles, e->RS.nRows,
+                          (e->factored && !e->dense) ? 1 : 0};
+    *n = 7;
+    if (info) for (int i = 0; i < std::min<int>(cap, 7); ++i) info[i] = v[i];
     return BA_OK;
 }
 

@@ -44,17 +44,20 @@ __device__ __forceinline__ double ld_relaxed_sys_f64(const double* p) {   // hom
 
 __global__ void __launch_bounds__(GATHER_WARPS * 32, BA_GATHER_MINB)
 k_camera_gather_push(int Nc, int Ng, int fi, int nTiles, RowSched S, const double* __restrict__ ylocal_rw, PeerView P, unsigned int seq,
-                     const PcgState2* __restrict__ st, int check_done) {
+                     const PcgState2* __restrict__ st, int check_done, const double* __restrict__ G) {
     __shared__ double sw[6];
     __shared__ int sidx[GATHER_IDX_CAP];
+    __shared__ double sG[36];
     pdl_trigger();
     double* const mine = P.data[P.rank] + size_t(seq & 1u) * P.ldf;
     const int c = blockIdx.x;
     if (c < Nc) {
+        if (G && threadIdx.x < 36) sG[threadIdx.x] = __ldg(G + 36 * size_t(c) + threadIdx.x);
         if (!camera_row_sum(S, c, sw, sidx, check_done ? &st->done : nullptr)) return;
-        if (threadIdx.x < 3) {   // thread h: 16 bytes of this camera's 6-vector
-            const int h = threadIdx.x;
-            __stcg(reinterpret_cast<double2*>(mine + 6 * size_t(c) + 2 * h), make_double2(sw[2 * h], sw[2 * h + 1]));
+        if (threadIdx.x < 3) {   // thread h: 16 bytes of this camera's 6-vector (pose-factored rows: of G_c^T times the row sum; linear, so
+            const int h = threadIdx.x;   // every rank applies it to its own partial before the all-reduce)
+            const double lo = G ? pose_factor_apply_t(sG, sw, 2 * h) : sw[2 * h], hi = G ? pose_factor_apply_t(sG, sw, 2 * h + 1) : sw[2 * h + 1];
+            __stcg(reinterpret_cast<double2*>(mine + 6 * size_t(c) + 2 * h), make_double2(lo, hi));
         }
     } else {
         pdl_wait();

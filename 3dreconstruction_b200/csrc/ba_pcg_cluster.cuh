@@ -27,6 +27,7 @@ struct TailArgs {
     const double* Minv; const double* b; const double* Df2;
     double* y; double* p; double* x; double* r; double* z;
     const double* dotp; int ndot;        // mode 0: the gather CTAs' shares of p.q
+    const double* G; double* vt;         // pose-factored matvec (ba_rows.cuh: k_pose_factors): vt = [G_c p_c | p of the intrinsics entries], or null
     PcgState2* st;
     PcgParams pp;
     PeerView P;
@@ -189,10 +190,23 @@ __global__ void __cluster_dims__(TAIL_CL, 1, 1) __launch_bounds__(TAIL_THREADS) 
     if (!isfinite(rho_new)) done = 3;
     const double beta = rho_new / rho;
     if (!done) {
-        for (int blk = b0 + grp; blk < b1; blk += NGRP) {
-            const bool cam = blk < Nc;
-            const int n = cam ? 6 : 4, j = (cam ? 6 * blk : 6 * Nc + 4 * (blk - Nc)) + sub;
-            if (sub < n) A.p[j] = A.z[j] + beta * A.p[j];
+        for (int base = b0; base < b1; base += NGRP) {   // whole warps iterate together (width-8 shuffles below)
+            const int blk = base + grp;
+            const bool valid = blk < b1, cam = blk < Nc;
+            const int n = cam ? 6 : 4, off = cam ? 6 * blk : 6 * Nc + 4 * (blk - Nc);
+            const bool act = valid && sub < n;
+            double pn = 0.0;
+            if (act) { pn = A.z[off + sub] + beta * A.p[off + sub]; A.p[off + sub] = pn; }
+            if (A.vt) {   // what the next pose-factored K5a gathers instead of p: row `sub` of G_c times the new p_c
+                const double* Gr = (act && cam) ? A.G + 36 * size_t(blk) + 6 * sub : nullptr;
+                double vv = 0.0;
+#pragma unroll
+                for (int k = 0; k < 6; ++k) {
+                    const double pk = __shfl_sync(0xffffffffu, pn, k, 8);
+                    if (Gr) vv += Gr[k] * pk;
+                }
+                if (act) A.vt[cam ? VT_STRIDE * size_t(blk) + sub : off + (VT_STRIDE - 6) * Nc + sub] = cam ? vv : pn;
+            }
         }
     }
     cl.sync();            // every CTA has read st->k, st->rho0, st->Q0 and every partial before anything is overwritten or freed

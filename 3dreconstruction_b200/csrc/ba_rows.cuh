@@ -171,8 +171,8 @@ __device__ __forceinline__ void tile_rows(const View& V, const RowSched& S, Tile
             const double2* row = reinterpret_cast<const double2*>(M.sC[tid]);
             a = row[0]; bq = row[1]; cq = row[2];
         }
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
+        const int maxrem = __reduce_max_sync(0xffffffffu, act ? rem : 0);   // shuffles share the shared-memory data pipe: only the steps the longest run needs
+        for (int d = 1; d <= maxrem; d <<= 1) {
             const double ax = __shfl_down_sync(0xffffffffu, a.x, d), ay = __shfl_down_sync(0xffffffffu, a.y, d);
             const double bx = __shfl_down_sync(0xffffffffu, bq.x, d), by = __shfl_down_sync(0xffffffffu, bq.y, d);
             const double cx = __shfl_down_sync(0xffffffffu, cq.x, d), cy = __shfl_down_sync(0xffffffffu, cq.y, d);
@@ -267,6 +267,66 @@ __device__ __forceinline__ void tile_intr_store(const RowSched& S, double* sred,
     for (int k = 0; k < 4; ++k) { const double s = tile_sum<NT>(yi[k], sred, bar, tid); if (tid == 0) S.tile_intr[4 * size_t(t) + k] = s; }
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// Pose-factored Schur product.  Both models reach the pose only through P = R X + t, so with A = d(residual)/dP
+// the stored point columns are Jp = w A R and the pose columns are Jc = w A dP/d(pose) = Jp K(X) G_c with
+//     K(X) = [ -[X]x | I ]   (3x6, the POINT in world coordinates),   K(X) (v; tau) = v x X + tau,
+//     G_c  = [ J_r(aa) 0 ; 0 R^T ]                      angle-axis + translation (Ceres policy; J_r = right Jacobian of SO(3)),
+//     G_c  = [ R^T 0 ; -[R^T t]x R^T  R^T ]             left twist (g2o policy),        G_c = 0 for a constant pose.
+// The PCG matvec therefore needs, per observation, only Jp (48 bytes) instead of Jc and Jp (128 / 144 bytes): the PCG tail hands over
+// vt[c] = G_c p[c] (6 doubles per camera, what K5a gathers instead of p[c]); K5a forms u = Jp (v x X + tau), runs the same per-point
+// phase, and folds K(X)^T Jp^T t = (X x g ; g), g = Jp^T t, into the same partial rows; the by-camera gather multiplies each camera's
+// row sum by G_c^T once.  Mathematically the same operator; in floating point it differs from the explicit product by rounding
+// (1e-16 relative per term) -- and by O(|aa|) <= 1.5e-8 relative for a camera on Ceres' first-order rotation branch with aa != 0
+// (there the stored derivative is -[X]x rather than -R [X]x J_r); K4, K7 and the Hessian blocks keep the explicit columns.
+__global__ void k_pose_factors(int Nc, const double* __restrict__ camrec, const unsigned char* __restrict__ cam_free, int left_twist,
+                               double* __restrict__ G) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= Nc) return;
+    double g[36];
+#pragma unroll
+    for (int k = 0; k < 36; ++k) g[k] = 0.0;
+    if (cam_free[c]) {
+        const double* cr = camrec + size_t(c) * CAMREC;
+        double R[9];
+#pragma unroll
+        for (int k = 0; k < 9; ++k) R[k] = cr[CR_R + k];
+#pragma unroll
+        for (int i = 0; i < 3; ++i)
+#pragma unroll
+            for (int j = 0; j < 3; ++j) g[6 * (3 + i) + 3 + j] = R[3 * j + i];            // lower right: R^T
+        if (left_twist) {
+            const double t0 = cr[CR_T], t1 = cr[CR_T + 1], t2 = cr[CR_T + 2];
+            const double s0 = R[0] * t0 + R[3] * t1 + R[6] * t2, s1 = R[1] * t0 + R[4] * t1 + R[7] * t2, s2 = R[2] * t0 + R[5] * t1 + R[8] * t2;   // R^T t
+#pragma unroll
+            for (int j = 0; j < 3; ++j) {
+                const double r0 = R[3 * j], r1 = R[3 * j + 1], r2 = R[3 * j + 2];           // column j of R^T
+                g[6 * 0 + j] = r0; g[6 * 1 + j] = r1; g[6 * 2 + j] = r2;                    // upper left: R^T
+                g[6 * 3 + j] = r1 * s2 - r2 * s1;                                           // lower left: column j of -[s]x R^T = (R^T e_j) x s
+                g[6 * 4 + j] = r2 * s0 - r0 * s2;
+                g[6 * 5 + j] = r0 * s1 - r1 * s0;
+            }
+        } else {
+            // J_r = I - b [aa]x + cc [aa]x^2,  b = (1 - cos th)/th^2 (K0),  cc = (th - sin th)/th^3 = (1 - a)/th^2
+            const double ax = cr[CR_AA], ay = cr[CR_AA + 1], az = cr[CR_AA + 2];
+            const double th2 = ax * ax + ay * ay + az * az;
+            const double a = cr[CR_A], b = cr[CR_B];
+            double cc;
+            if (cr[CR_C1] == 0.0) cc = 0.0;          // K0's first-order branch (a = 1, b = 0, c1 = 0): d(RX)/d(aa) = -[X]x, i.e. J_r = I
+            else if (th2 < 0.25) cc = 1.0 / 6 + th2 * (-1.0 / 120 + th2 * (1.0 / 5040 + th2 * (-1.0 / 362880 + th2 * (1.0 / 39916800 + th2 * (-1.0 / 6227020800.0 +
+                                      th2 * (1.0 / 1307674368000.0 + th2 * (-1.0 / 355687428096000.0)))))));
+            else cc = (1.0 - a) / th2;
+            const double d = 1.0 - cc * th2;
+            g[0] = d + cc * ax * ax;        g[1] = b * az + cc * ax * ay;   g[2] = -b * ay + cc * ax * az;
+            g[6] = -b * az + cc * ay * ax;  g[7] = d + cc * ay * ay;        g[8] = b * ax + cc * ay * az;
+            g[12] = b * ay + cc * az * ax;  g[13] = -b * ax + cc * az * ay; g[14] = d + cc * az * az;
+        }
+    }
+    double* o = G + 36 * size_t(c);
+#pragma unroll
+    for (int k = 0; k < 36; ++k) o[k] = g[k];
+}
+
 #ifndef BA_K5A_MINB
 #define BA_K5A_MINB 6          // min CTAs/SM for ptxas: 6 = 80 registers, no spills
 #endif
@@ -308,6 +368,246 @@ k_schur_rows(View V, RowSched S, const double* __restrict__ xin, double* __restr
         pdl_wait();
         if (done_flag && *done_flag) return;
         tile_rows_long<MODE, FI, PK>(V, S, M.sred, BarCta{}, tid, o0, n, hbase, pfirst, xin, atomic_out, yi);
+    }
+    if (FI && V.Ng == 1) tile_intr_store(S, M.sred, BarCta{}, tid, t, yi);
+}
+
+// K5a, pose-factored (see k_pose_factors): one CTA per tile, the same schedule, the same per-point phase and camera fold as k_schur_rows;
+// streams Jp only.  vt = [G_c p_c per camera, padded to VT_STRIDE doubles | p of the intrinsics entries], pt = the points of the
+// linearisation (tile-local rows).
+// ncu (profiles/r3c): with 64 bytes per observation this kernel is bound by the L1/shared-memory pipe (93 % busy, DRAM 36 %), i.e. by the
+// number of L1 tag requests and shared-memory wavefronts per tile, not by latency or occupancy (12 CTAs/SM and an L2 prefetch of the
+// tile two waves ahead were both measured slower than 8 CTAs/SM without).  Hence: vt records padded to 64 bytes and fetched with two
+// 32-byte loads (one line per lane instead of three 16-byte requests that straddle lines), the points read per observation straight from
+// global memory (lanes of one point share the request), Hinv in registers (or a conflict-free transposed shared-memory copy).
+#ifndef BA_K5F_MINB
+#define BA_K5F_MINB 8
+#endif
+#ifndef BA_K5F_XSMEM
+#define BA_K5F_XSMEM 0      // 1: the tile's points through shared memory (cp.async by the point threads, one more barrier)
+#endif
+#ifndef BA_K5F_HSMEM
+#define BA_K5F_HSMEM 0      // 1: Hinv through shared memory (transposed, conflict-free) instead of 12 registers
+#endif
+constexpr int K5F_CTAS_PER_SM = BA_K5F_MINB;
+struct TileScratchF {
+    alignas(16) double sC[TILE_OBS][6];     // camera-sorted 6-vectors; its first half doubles as sW (per-run point sums) before the second barrier
+    double sV[TILE_MAX_PTS][3];
+    double sred[8];
+#if BA_K5F_HSMEM
+    alignas(16) double2 sH[3][TILE_MAX_PTS];
+#endif
+#if BA_K5F_XSMEM
+    double sX[TILE_MAX_PTS][3];
+#endif
+};
+__device__ __forceinline__ void cp_async8(void* smem_dst, const void* gsrc) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(static_cast<uint32_t>(__cvta_generic_to_shared(smem_dst))), "l"(gsrc) : "memory");
+}
+
+template <bool FI, int PK>
+__global__ void __launch_bounds__(TILE_OBS, BA_K5F_MINB)
+k_schur_rows_f(View V, RowSched S, const double* __restrict__ vt, const double* __restrict__ pt, double* __restrict__ atomic_out,
+               const int* __restrict__ done_flag) {
+    __shared__ TileScratchF M;
+    pdl_trigger();
+    const int t = blockIdx.x;
+    const int4 ti = __ldg(S.tile_info + t);
+    const int o0 = ti.x, n = ti.y & 0xffffff, hbase = ti.z, pfirst = ti.w;
+    const int ioff = VT_STRIDE * V.Nc;      // intrinsics entries of vt
+    const int yoff = 6 * V.Nc;              // ... and of the output vector
+    double yi[4] = {0, 0, 0, 0};
+    const int tid = threadIdx.x;
+    if (n <= TILE_OBS) {
+        // ---- everything static during a linear solve is requested before the dependency wait: schedule record, Jp, the points, Hinv ----
+        const bool act = tid < n;
+        const int npts = int(unsigned(ti.y) >> 24);
+        int4 tm = make_int4(0, 0, -1, 0);
+        double2 jp[3], ji[4];
+        jp[0] = jp[1] = jp[2] = make_double2(0.0, 0.0);
+        double X0 = 0.0, X1 = 0.0, X2 = 0.0;
+        double2 h0 = make_double2(0.0, 0.0), h1 = h0, h2 = h0;
+        if (tid < npts) {   // this thread as a point thread (addressed from tile_info alone: no dependency on the schedule record)
+            const double2* H = reinterpret_cast<const double2*>(V.Hinv + 6 * size_t(pfirst + tid));
+#if BA_K5F_HSMEM
+            cp_async16(&M.sH[0][tid], H); cp_async16(&M.sH[1][tid], H + 1); cp_async16(&M.sH[2][tid], H + 2);
+#else
+            h0 = __ldg(H); h1 = __ldg(H + 1); h2 = __ldg(H + 2);
+#endif
+#if BA_K5F_XSMEM
+            const double* Xp = pt + 3 * size_t(pfirst + tid);
+            cp_async8(&M.sX[tid][0], Xp); cp_async8(&M.sX[tid][1], Xp + 1); cp_async8(&M.sX[tid][2], Xp + 2);
+#endif
+        }
+        if (act) {
+            const int o = o0 + tid;
+            tm = ldg4s(S.tmeta + o);
+            const double2* J = V.J2 + o;
+            load_jp<PK>(V, J, jp);
+            if (FI) load_ji<PK>(V, J, ji);
+#if !BA_K5F_XSMEM
+            const double* Xp = pt + 3 * size_t(pfirst + ((tm.y >> 24) & 0xff));
+            X0 = __ldg(Xp); X1 = __ldg(Xp + 1); X2 = __ldg(Xp + 2);
+#endif
+        }
+#if BA_K5F_HSMEM || BA_K5F_XSMEM
+        cp_async_commit();
+        cp_async_wait_all();
+        __syncthreads();
+#endif
+        pdl_wait();
+        if (done_flag && *done_flag) return;
+        const int npt_obs = tm.w >> 16, pstart = tm.w & 0xffff;   // this thread as a point thread
+        const int c = tm.x & 0xffffff;
+        const int slot = tm.y & 0xff, rem = (tm.y >> 8) & 0xff, hrank = (tm.y >> 16) & 0xff, lpt = (tm.y >> 24) & 0xff;
+        const int g = (FI && act) ? V.cam_group[c] : 0;
+        double2 u = make_double2(0.0, 0.0);
+        double w0 = 0.0, w1 = 0.0, w2 = 0.0;
+        if (act) {
+            double x[8];                               // v = x[0..2], tau = x[3..5]
+#if BA_K5F_VT256
+            ldg256(vt + VT_STRIDE * size_t(c), x); ldg256(vt + VT_STRIDE * size_t(c) + 4, x + 4);
+#else
+            {
+                const double2* xc = reinterpret_cast<const double2*>(vt + VT_STRIDE * size_t(c));
+                const double2 q0 = __ldg(xc), q1 = __ldg(xc + 1), q2 = __ldg(xc + 2);
+                x[0] = q0.x; x[1] = q0.y; x[2] = q1.x; x[3] = q1.y; x[4] = q2.x; x[5] = q2.y;
+            }
+#endif
+#if BA_K5F_XSMEM
+            X0 = M.sX[lpt][0]; X1 = M.sX[lpt][1]; X2 = M.sX[lpt][2];
+#endif
+            const double d0 = x[1] * X2 - x[2] * X1 + x[3];
+            const double d1 = x[2] * X0 - x[0] * X2 + x[4];
+            const double d2 = x[0] * X1 - x[1] * X0 + x[5];
+            u.x = jp[0].x * d0 + jp[1].x * d1 + jp[2].x * d2;
+            u.y = jp[0].y * d0 + jp[1].y * d1 + jp[2].y * d2;
+            if (FI) {
+#pragma unroll
+                for (int k = 0; k < 4; ++k) { const double xv = __ldg(vt + ioff + 4 * g + k); u.x += ji[k].x * xv; u.y += ji[k].y * xv; }
+            }
+            w0 = jp[0].x * u.x + jp[0].y * u.y; w1 = jp[1].x * u.x + jp[1].y * u.y; w2 = jp[2].x * u.x + jp[2].y * u.y;
+        }
+        double (*sW)[3] = reinterpret_cast<double (*)[3]>(&M.sC[0][0]);
+        {   // per-point sums: segmented shuffle reduction inside the warp, one shared-memory value per run (as in tile_rows)
+            const unsigned same = __match_any_sync(0xffffffffu, act ? lpt : 0xffff);
+            const int lane = tid & 31;
+            const int segrem = __popc(same >> lane) - 1;
+            const int maxseg = __reduce_max_sync(0xffffffffu, segrem);
+            for (int d = 1; d <= maxseg; d <<= 1) {
+                const double a0 = __shfl_down_sync(0xffffffffu, w0, d), a1 = __shfl_down_sync(0xffffffffu, w1, d), a2 = __shfl_down_sync(0xffffffffu, w2, d);
+                if (d <= segrem) { w0 += a0; w1 += a1; w2 += a2; }
+            }
+            if (act && (same & ((1u << lane) - 1u)) == 0) { sW[tid][0] = w0; sW[tid][1] = w1; sW[tid][2] = w2; }
+        }
+        __syncthreads();
+        if (npt_obs > 0) {
+            double W0 = sW[pstart][0], W1 = sW[pstart][1], W2 = sW[pstart][2];
+            for (int i = (pstart / 32 + 1) * 32, e = pstart + npt_obs; i < e; i += 32) { W0 += sW[i][0]; W1 += sW[i][1]; W2 += sW[i][2]; }
+#if BA_K5F_HSMEM
+            h0 = M.sH[0][tid]; h1 = M.sH[1][tid]; h2 = M.sH[2][tid];
+#endif
+            // (H0,H1) (H2,H3) (H4,H5); Hinv rows (H0,H1,H2) (H1,H3,H4) (H2,H4,H5)
+            M.sV[tid][0] = h0.x * W0 + h0.y * W1 + h1.x * W2;
+            M.sV[tid][1] = h0.y * W0 + h1.y * W1 + h2.x * W2;
+            M.sV[tid][2] = h1.x * W0 + h2.x * W1 + h2.y * W2;
+        }
+        __syncthreads();
+        if (act) {
+            const double* v = M.sV[lpt];
+            const double tx = u.x - (jp[0].x * v[0] + jp[1].x * v[1] + jp[2].x * v[2]);
+            const double ty = u.y - (jp[0].y * v[0] + jp[1].y * v[1] + jp[2].y * v[2]);
+            const double g0 = jp[0].x * tx + jp[0].y * ty, g1 = jp[1].x * tx + jp[1].y * ty, g2 = jp[2].x * tx + jp[2].y * ty;
+#if BA_K5F_XSMEM
+            X0 = M.sX[lpt][0]; X1 = M.sX[lpt][1]; X2 = M.sX[lpt][2];
+#endif
+            double2* sc = reinterpret_cast<double2*>(M.sC[slot]);
+            sc[0] = make_double2(X1 * g2 - X2 * g1, X2 * g0 - X0 * g2);
+            sc[1] = make_double2(X0 * g1 - X1 * g0, g0);
+            sc[2] = make_double2(g1, g2);
+            if (FI) {
+#pragma unroll
+                for (int k = 0; k < 4; ++k) yi[k] = ji[k].x * tx + ji[k].y * ty;
+                if (V.Ng > 1) {
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) red_add(atomic_out + yoff + 4 * g + k, yi[k]);
+                }
+            }
+        }
+        __syncthreads();
+        {   // camera fold over 32 sorted positions (as in tile_rows)
+            double2 a = make_double2(0.0, 0.0), bq = a, cq = a;
+            if (act) {
+                const double2* row = reinterpret_cast<const double2*>(M.sC[tid]);
+                a = row[0]; bq = row[1]; cq = row[2];
+            }
+            // shuffles share the shared-memory data pipe, the unit this kernel saturates: only as many steps as the longest run of this warp needs
+            const int maxrem = __reduce_max_sync(0xffffffffu, act ? rem : 0);
+            for (int d = 1; d <= maxrem; d <<= 1) {
+                const double ax = __shfl_down_sync(0xffffffffu, a.x, d), ay = __shfl_down_sync(0xffffffffu, a.y, d);
+                const double bx = __shfl_down_sync(0xffffffffu, bq.x, d), by = __shfl_down_sync(0xffffffffu, bq.y, d);
+                const double cx = __shfl_down_sync(0xffffffffu, cq.x, d), cy = __shfl_down_sync(0xffffffffu, cq.y, d);
+                if (d <= rem) { a.x += ax; a.y += ay; bq.x += bx; bq.y += by; cq.x += cx; cq.y += cy; }
+            }
+            if (tm.z >= 0) {
+                double2* dst = reinterpret_cast<double2*>(S.rows + size_t(ROW_DOUBLES) * (hbase + hrank));
+                row_store(dst, a); row_store(dst + 1, bq); row_store(dst + 2, cq);
+            }
+        }
+    } else {
+        // one point with more than TILE_OBS observations: two passes from global memory, every observation its own row
+        pdl_wait();
+        if (done_flag && *done_flag) return;
+        const int o1 = o0 + n;
+        const double X0 = pt[3 * size_t(pfirst)], X1 = pt[3 * size_t(pfirst) + 1], X2 = pt[3 * size_t(pfirst) + 2];
+        auto forward = [&](int o, int c, const double2 (&jp)[3]) {
+            const double* x = vt + VT_STRIDE * size_t(c);
+            const double d0 = x[1] * X2 - x[2] * X1 + x[3], d1 = x[2] * X0 - x[0] * X2 + x[4], d2 = x[0] * X1 - x[1] * X0 + x[5];
+            double2 u = make_double2(jp[0].x * d0 + jp[1].x * d1 + jp[2].x * d2, jp[0].y * d0 + jp[1].y * d1 + jp[2].y * d2);
+            if (FI) {
+                const int g = V.cam_group[c];
+                double2 ji[4];
+                load_ji<PK>(V, V.J2 + o, ji);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) { const double xv = vt[ioff + 4 * g + k]; u.x += ji[k].x * xv; u.y += ji[k].y * xv; }
+            }
+            return u;
+        };
+        double W[3] = {0, 0, 0};
+        for (int o = o0 + tid; o < o1; o += TILE_OBS) {
+            double2 jp[3];
+            load_jp<PK>(V, V.J2 + o, jp);
+            const double2 u = forward(o, V.obs_cam[o], jp);
+#pragma unroll
+            for (int a = 0; a < 3; ++a) W[a] += jp[a].x * u.x + jp[a].y * u.y;
+        }
+        double w[3];
+#pragma unroll
+        for (int a = 0; a < 3; ++a) w[a] = tile_sum(W[a], M.sred, BarCta{}, tid);
+        const double* H = V.Hinv + 6 * size_t(pfirst);
+        const double v0 = H[0] * w[0] + H[1] * w[1] + H[2] * w[2], v1 = H[1] * w[0] + H[3] * w[1] + H[4] * w[2], v2 = H[2] * w[0] + H[4] * w[1] + H[5] * w[2];
+        for (int o = o0 + tid; o < o1; o += TILE_OBS) {
+            const int c = V.obs_cam[o];
+            double2 jp[3];
+            load_jp<PK>(V, V.J2 + o, jp);
+            const double2 u = forward(o, c, jp);
+            const double tx = u.x - (jp[0].x * v0 + jp[1].x * v1 + jp[2].x * v2), ty = u.y - (jp[0].y * v0 + jp[1].y * v1 + jp[2].y * v2);
+            const double g0 = jp[0].x * tx + jp[0].y * ty, g1 = jp[1].x * tx + jp[1].y * ty, g2 = jp[2].x * tx + jp[2].y * ty;
+            double2* dst = reinterpret_cast<double2*>(S.rows + size_t(ROW_DOUBLES) * (hbase + (o - o0)));
+            row_store(dst, make_double2(X1 * g2 - X2 * g1, X2 * g0 - X0 * g2));
+            row_store(dst + 1, make_double2(X0 * g1 - X1 * g0, g0));
+            row_store(dst + 2, make_double2(g1, g2));
+            if (FI) {
+                const int g = V.cam_group[c];
+                double2 ji[4];
+                load_ji<PK>(V, V.J2 + o, ji);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const double contrib = ji[k].x * tx + ji[k].y * ty;
+                    if (V.Ng > 1) red_add(atomic_out + yoff + 4 * g + k, contrib); else yi[k] += contrib;
+                }
+            }
+        }
     }
     if (FI && V.Ng == 1) tile_intr_store(S, M.sred, BarCta{}, tid, t, yi);
 }
@@ -390,21 +690,30 @@ __device__ __forceinline__ void gather_intrinsics(int Nc, int Ng, int nTiles, co
     }
 }
 
-// qdot = 0: y[c] = sum of rows (K4: the reduced right-hand side; multi-GPU NCCL path).
+// Entry j of G^T w (G row-major 6x6 in shared memory), fixed order.
+__device__ __forceinline__ double pose_factor_apply_t(const double* sG, const double* w, int j) {
+    return ((sG[j] * w[0] + sG[6 + j] * w[1]) + (sG[12 + j] * w[2] + sG[18 + j] * w[3])) + (sG[24 + j] * w[4] + sG[30 + j] * w[5]);
+}
+
+// qdot = 0: y[c] = sum of rows (K4: the reduced right-hand side; multi-GPU NCCL path).  G != nullptr: the rows are pose-factored
+// (k_schur_rows_f) and the sum is multiplied by G_c^T.
 // qdot = 1 (one GPU, PCG loop): q = y + Df2 p stored in y, and the CTA's share of p.q in dotp[blockIdx.x] — the PCG tail adds the
 //          Nc + 1 shares in index order (no ticket, no atomics).
 __global__ void __launch_bounds__(GATHER_WARPS * 32, BA_GATHER_MINB)
 k_camera_gather(int Nc, int Ng, int fi, int nTiles, RowSched S, const double* __restrict__ Df2, const double* __restrict__ p,
-                double* __restrict__ y, double* __restrict__ dotp, const PcgState2* __restrict__ st, int qdot) {
+                double* __restrict__ y, double* __restrict__ dotp, const PcgState2* __restrict__ st, int qdot, const double* __restrict__ G) {
     __shared__ double sw[6];
     __shared__ int sidx[GATHER_IDX_CAP];
     __shared__ double sdot[GATHER_WARPS];
+    __shared__ double sG[36];
     pdl_trigger();
     const int c = blockIdx.x;
     if (c < Nc) {
+        if (G && threadIdx.x < 36) sG[threadIdx.x] = __ldg(G + 36 * size_t(c) + threadIdx.x);   // static during the solve; visible after camera_row_sum's barriers
         if (!camera_row_sum(S, c, sw, sidx, st ? &st->done : nullptr)) return;
         if (threadIdx.x < 6) {
             double v = sw[threadIdx.x];
+            if (G) v = pose_factor_apply_t(sG, sw, threadIdx.x);   // pose-factored rows: y_c = G_c^T (sum of rows)
             const int j = 6 * c + threadIdx.x;
             double dot = 0.0;
             // p is the predecessor grid's output and this kernel's CTAs may share an SM with a successor's (the next K5a is launched while
