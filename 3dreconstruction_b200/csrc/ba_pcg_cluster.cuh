@@ -19,6 +19,10 @@
 
 namespace bak {
 
+#ifndef BA_TAIL_PREFETCH
+#define BA_TAIL_PREFETCH 1
+#endif
+__device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
 constexpr int TAIL_CL = 8;          // CTAs in the cluster (portable maximum)
 constexpr int TAIL_THREADS = 1024;
 
@@ -53,13 +57,32 @@ __global__ void __cluster_dims__(TAIL_CL, 1, 1) __launch_bounds__(TAIL_THREADS) 
     cg::cluster_group cl = cg::this_cluster();
     PcgState2* st = A.st;
     pdl_trigger();
-    pdl_wait();
-    if (st->done) return;                        // uniform over the cluster: nobody reaches a barrier
     const int Nc = A.Nc, nblk = Nc + (A.fi ? A.Ng : 0);
     const int per = ((nblk + TAIL_CL - 1) / TAIL_CL + 3) & ~3;          // diagonal blocks per CTA, whole warps of 8-lane groups
     const int b0 = int(cl.block_rank()) * per, b1 = min(nblk, b0 + per);
     const int sub = threadIdx.x & 7, grp = threadIdx.x >> 3;
     constexpr int NGRP = TAIL_THREADS / 8;
+#if BA_TAIL_PREFETCH
+    // Everything this CTA reads except the gather's output (y, dotp) was last written by the PREVIOUS tail or is static during the solve:
+    // pull those lines into this SM's L1 while the predecessor grid is still running, so that the dependent load phases after the wait
+    // (x, r, p, b, Df2 -> Minv rows -> z, p, G rows) are L1 hits.  The kernel is a chain of latencies, not of bytes.
+    for (int base = b0; base < b1; base += NGRP) {
+        const int blk = base + grp;
+        if (blk < b1) {
+            const bool cam = blk < Nc;
+            const int n = cam ? 6 : 4, off = cam ? 6 * blk : 6 * Nc + 4 * (blk - Nc);
+            if (sub < n) {
+                prefetch_l1(A.x + off + sub); prefetch_l1(A.r + off + sub); prefetch_l1(A.p + off + sub); prefetch_l1(A.b + off + sub);
+                if (A.mode != 0) prefetch_l1(A.Df2 + off + sub);
+                const double* M = cam ? A.Minv + 36 * size_t(blk) + n * sub : A.Minv + 36 * size_t(Nc) + 16 * size_t(blk - Nc) + n * sub;
+                prefetch_l1(M); prefetch_l1(M + n - 1);
+                if (A.vt && cam) { const double* Gr = A.G + 36 * size_t(blk) + 6 * sub; prefetch_l1(Gr); prefetch_l1(Gr + 5); }
+            }
+        }
+    }
+#endif
+    pdl_wait();
+    if (st->done) return;                        // uniform over the cluster: nobody reaches a barrier
     const double rho = st->rho;
     double alpha = st->alpha;
 

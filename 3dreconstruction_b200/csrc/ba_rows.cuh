@@ -23,8 +23,51 @@ constexpr int ROW_DOUBLES = BA_ROW_DOUBLES;    // 6: packed 48-byte rows; 8: 64-
 constexpr int GATHER_WARPS = 4;                // warps per CTA of the by-camera gather (K5b)
 constexpr int TILE_MAX_PTS = 64;               // points per tile (the streaming kernel reserves 48 bytes of Hinv per point in every stage)
 
+// L2 residency (BA_L2_HINTS): the partial rows of one PCG iteration (108 MB on the Venice shape) are written by K5a and read back by the
+// gather a few microseconds later, and overwritten by the next K5a; in between K5a streams 3-8x as many read-once bytes through the same
+// L2 (126 MB), which evicts the rows before the gather gets to them (ncu: 37 % L2 hit rate in the gather).  With a cache policy the rows
+// are kept (evict_last) and the read-once streams of the pose-factored K5a go first (evict_first).
+#ifndef BA_L2_HINTS
+#define BA_L2_HINTS 0          // bit 0: read-once streams evict_first, bit 1: row stores evict_last, bit 2: the gather's row loads evict_last
+#endif
+__device__ __forceinline__ uint64_t l2_policy_evict_first() { uint64_t p; asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p)); return p; }
+__device__ __forceinline__ uint64_t l2_policy_evict_last() { uint64_t p; asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p)); return p; }
 __device__ __forceinline__ void row_store(double2* p, double2 v) { __stcg(p, v); }
 __device__ __forceinline__ double2 row_load(const double2* p) { return __ldcg(p); }
+__device__ __forceinline__ void row_store_keep(double2* p, double2 v, uint64_t pol) {
+#if BA_L2_HINTS & 2
+    asm volatile("st.global.cg.L2::cache_hint.v2.f64 [%0], {%1, %2}, %3;" ::"l"(p), "d"(v.x), "d"(v.y), "l"(pol) : "memory");
+#else
+    __stcg(p, v);
+#endif
+}
+__device__ __forceinline__ double2 row_load_keep(const double2* p, uint64_t pol) {
+#if BA_L2_HINTS & 4
+    double2 v;
+    asm volatile("ld.global.cg.L2::cache_hint.v2.f64 {%0, %1}, [%2], %3;" : "=d"(v.x), "=d"(v.y) : "l"(p), "l"(pol) : "memory");
+    return v;
+#else
+    return __ldcg(p);
+#endif
+}
+__device__ __forceinline__ double2 ldg2_once(const double2* p, uint64_t pol) {      // read-once stream
+#if BA_L2_HINTS & 1
+    double2 v;
+    asm volatile("ld.global.nc.L2::cache_hint.v2.f64 {%0, %1}, [%2], %3;" : "=d"(v.x), "=d"(v.y) : "l"(p), "l"(pol));
+    return v;
+#else
+    return __ldg(p);
+#endif
+}
+__device__ __forceinline__ int4 ldg4_once(const int4* p, uint64_t pol) {
+#if BA_L2_HINTS & 1
+    int4 v;
+    asm volatile("ld.global.nc.L2::cache_hint.v4.s32 {%0, %1, %2, %3}, [%4], %5;" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p), "l"(pol));
+    return v;
+#else
+    return __ldg(p);
+#endif
+}
 
 struct RowSched {
     // One 16-byte record per tile position i = o0 + tid:
@@ -441,10 +484,14 @@ k_schur_rows_f(View V, RowSched S, const double* __restrict__ vt, const double* 
         }
         if (act) {
             const int o = o0 + tid;
-            tm = ldg4s(S.tmeta + o);
-            const double2* J = V.J2 + o;
-            load_jp<PK>(V, J, jp);
-            if (FI) load_ji<PK>(V, J, ji);
+            const uint64_t once = l2_policy_evict_first();
+            tm = ldg4_once(S.tmeta + o, once);
+            const double2* Jq = V.J2 + o + size_t(6 - (PK < 0 ? V.jpack : PK)) * V.ldo;
+            jp[0] = ldg2_once(Jq, once); jp[1] = ldg2_once(Jq + V.ldo, once); jp[2] = ldg2_once(Jq + 2 * size_t(V.ldo), once);
+            if (FI) {
+#pragma unroll
+                for (int k = 0; k < 4; ++k) ji[k] = ldg2_once(Jq + size_t(3 + k) * V.ldo, once);
+            }
 #if !BA_K5F_XSMEM
             const double* Xp = pt + 3 * size_t(pfirst + ((tm.y >> 24) & 0xff));
             X0 = __ldg(Xp); X1 = __ldg(Xp + 1); X2 = __ldg(Xp + 2);
@@ -551,7 +598,8 @@ k_schur_rows_f(View V, RowSched S, const double* __restrict__ vt, const double* 
             }
             if (tm.z >= 0) {
                 double2* dst = reinterpret_cast<double2*>(S.rows + size_t(ROW_DOUBLES) * (hbase + hrank));
-                row_store(dst, a); row_store(dst + 1, bq); row_store(dst + 2, cq);
+                const uint64_t keep = l2_policy_evict_last();
+                row_store_keep(dst, a, keep); row_store_keep(dst + 1, bq, keep); row_store_keep(dst + 2, cq, keep);
             }
         }
     } else {
@@ -646,17 +694,18 @@ __device__ __forceinline__ bool camera_row_sum(const RowSched& S, int c, double*
     const double2* R2 = reinterpret_cast<const double2*>(S.rows);
     double2 acc = make_double2(0.0, 0.0);
     if (sub < 3) {
+        const uint64_t keep = l2_policy_evict_last();
         int i = threadIdx.x >> 2;
         for (; i + (UNR - 1) * NG < staged; i += UNR * NG) {     // UNR rows per group and trip, all in flight
             double2 v[UNR];
 #pragma unroll
-            for (int k = 0; k < UNR; ++k) v[k] = row_load(R2 + size_t(ROW_DOUBLES / 2) * sidx[i + k * NG] + sub);
+            for (int k = 0; k < UNR; ++k) v[k] = row_load_keep(R2 + size_t(ROW_DOUBLES / 2) * sidx[i + k * NG] + sub, keep);
 #pragma unroll
             for (int k = 1; k < UNR; ++k) { v[0].x += v[k].x; v[0].y += v[k].y; }
             acc.x += v[0].x; acc.y += v[0].y;
         }
-        for (; i < staged; i += NG) { const double2 v = row_load(R2 + size_t(ROW_DOUBLES / 2) * sidx[i] + sub); acc.x += v.x; acc.y += v.y; }
-        for (; i < cnt; i += NG) { const double2 v = row_load(R2 + size_t(ROW_DOUBLES / 2) * __ldg(S.cam_rows + b + i) + sub); acc.x += v.x; acc.y += v.y; }
+        for (; i < staged; i += NG) { const double2 v = row_load_keep(R2 + size_t(ROW_DOUBLES / 2) * sidx[i] + sub, keep); acc.x += v.x; acc.y += v.y; }
+        for (; i < cnt; i += NG) { const double2 v = row_load_keep(R2 + size_t(ROW_DOUBLES / 2) * __ldg(S.cam_rows + b + i) + sub, keep); acc.x += v.x; acc.y += v.y; }
     }
     // the 8 groups of a warp (lanes with equal sub), fixed tree; then the warps in order
 #pragma unroll

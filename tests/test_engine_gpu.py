@@ -262,6 +262,41 @@ def test_multi_gpu_matches_single_gpu():
     assert "MISMATCH" not in r.stdout and "OK" in r.stdout
 
 
+@pytest.mark.parametrize("policy", [0, 1])
+@pytest.mark.parametrize("shape,fi,model", [("ladybug", 0, 0), ("ladybug", 1, 0), ("trafalgar", 0, 0), ("ladybug", 1, 1)])
+def test_pose_factored_matvec_matches_explicit(ba, monkeypatch, shape, fi, model, policy):
+    """K5a in its pose-factored form (Jc = Jp K(X) G_c: streams the point columns only) against the same engine with the
+    explicit pose columns (BA_POSE_FACTORED=0, read at ba_create): the same operator up to rounding, so with a tight PCG tolerance the two
+    Levenberg-Marquardt runs agree far inside the parity bar -- for both pose parametrisations (Ceres: angle-axis + t; g2o: left twist),
+    with constant cameras, free intrinsics and both camera models."""
+    if policy == 1 and (fi or model):
+        pytest.skip("g2o policy: pinhole model with constant intrinsics only")
+    if model == 1:
+        from test_snavely_bal import snavely_problem
+        P = snavely_problem(ba, shape, seed=2)
+    else:
+        P = ba.synth(shape)
+    P.cam_fixed[:] = 0
+    P.cam_fixed[[0, 3]] = 1
+    opts = dict(intrinsics_free=fi, model=model, lm_policy=policy, linear_solver=1, pcg_rel_tolerance=1e-12, pcg_max_iterations=3000, max_num_iterations=6)
+    out = []
+    for factored in (1, 0):
+        monkeypatch.setenv("BA_POSE_FACTORED", str(factored))
+        with ba.Engine(**opts) as eng:
+            eng.set_problem(P)
+            s = eng.solve()
+            out.append((s, eng.trajectory(), eng.get_state(), eng.execution_info()))
+    (sf, tf, xf, inf), (se, te, xe, ine) = out
+    assert inf["pose_factored"] == 1 and ine["pose_factored"] == 0 and inf["scatter_mode"] == ine["scatter_mode"] == 4
+    assert len(tf) == len(te) and sf.termination == se.termination
+    for a, b in zip(tf, te):
+        assert a.step_is_successful == b.step_is_successful
+        assert abs(a.cost - b.cost) <= 1e-9 * abs(b.cost), (a.iteration, a.cost, b.cost)
+        assert abs(a.pcg_iterations - b.pcg_iterations) <= max(8, 0.08 * b.pcg_iterations), (a.iteration, a.pcg_iterations, b.pcg_iterations)
+    assert rel_err(xf[0], xe[0]) <= 1e-8 and rel_err(xf[2], xe[2]) <= 1e-8 and rel_err(xf[1], xe[1]) <= 1e-8
+    assert np.array_equal(xf[0][[0, 3]], P.pose[[0, 3]])     # constant poses: G_c = 0, untouched
+
+
 @pytest.mark.parametrize("name", ["tiny", "ladybug", "trafalgar"])
 def test_g2o_policy_trajectory_parity(ba, oracle, name):
     """g2o policy (Levenberg lambda schedule, uniform damping, SE3 exp-map pose update): engine against the oracle in the same policy."""
