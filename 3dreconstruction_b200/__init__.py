@@ -254,10 +254,10 @@ class Handle:
     def execution_info(self):
         """dict(linear_solver, scatter_mode, allreduce (0 one GPU, 1 NCCL, 2 NVLink peer memory), host_syncs of the last solve, tiles, rows,
         pose_factored (1: the PCG matvec streams the point columns only, ba_rows.cuh k_schur_rows_f))."""
-        buf = (C.c_int64 * 7)()
+        buf = (C.c_int64 * 8)()
         n = C.c_int32(0)
-        self._check(self.lib.ba_get_execution_info(self.h, buf, 7, C.byref(n)), "ba_get_execution_info")
-        return dict(zip(("linear_solver", "scatter_mode", "allreduce", "host_syncs", "tiles", "rows", "pose_factored"), [int(v) for v in buf]))
+        self._check(self.lib.ba_get_execution_info(self.h, buf, 8, C.byref(n)), "ba_get_execution_info")
+        return dict(zip(("linear_solver", "scatter_mode", "allreduce", "host_syncs", "tiles", "rows", "pose_factored", "tail_cluster"), [int(v) for v in buf]))
 
     def set_profiling(self, mask, stride=1):
         """mask: False/0 off, True/1 every kernel, else a bit mask over kernel_stats() order; stride: time every n-th launch of

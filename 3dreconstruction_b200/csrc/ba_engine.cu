@@ -249,6 +249,7 @@ struct ba_engine {
     unsigned profiling = 0;           // bit k set: time kernel id k with CUDA events
     struct Stat { int64_t launches = 0; int64_t timed = 0; double ms = 0.0; double bytes = 0.0; } stats[KID_COUNT];
     int dbg_tail1 = 0;                // BA_TAIL_MODE1
+    int tail_cl = 8;                  // CTAs of the PCG tail's cluster for reduced systems of >= 32768 unknowns: 16 where the device can place such a cluster (BA_TAIL_CL=8 forces 8)
     int factored_opt = 1;             // BA_POSE_FACTORED (default 1): K5a streams Jp only (ba_rows.cuh: k_pose_factors); 0 = explicit Jc and Jp (bisecting / A-B)
     int factored = 0;                 // in effect for the current problem (partial rows, one CTA per tile, PCG)
     int p2p_wide = -1;                // peer-memory all-reduce: pull on many SMs in a kernel of its own (1) or inside the PCG tail's cluster (0); -1 (default): the
@@ -1191,7 +1192,8 @@ int solve_linear(ba_engine* e, double radius, double* rel_out, double lambda = 0
             }
             // q, alpha, x, r, z, rho, beta, stop test and the new search direction: one thread-block cluster (ba_pcg_cluster.cuh)
             LaunchTimer tt(e, KID_TAIL, sample, launched);
-            launch_chain(e, bak::k_pcg_tail, dim3(bak::TAIL_CL), dim3(bak::TAIL_THREADS), ta);
+            if (e->tail_cl == bak::TAIL_CL_WIDE && e->nf >= 32768) launch_chain(e, bak::k_pcg_tail<bak::TAIL_CL_WIDE>, dim3(bak::TAIL_CL_WIDE), dim3(bak::TAIL_THREADS), ta);
+            else launch_chain(e, bak::k_pcg_tail<bak::TAIL_CL>, dim3(bak::TAIL_CL), dim3(bak::TAIL_THREADS), ta);
         }
         read_scalars(e);
         if (e->h_scal->bad_lin & 8) throw BaFail{BA_ERR_NCCL, "peer-memory all-reduce timed out waiting for another rank"};
@@ -1505,6 +1507,26 @@ int ba_create(const ba_options* opt, ba_engine** out) {
         if (const char* v = std::getenv("BA_PDL")) e->pdl = std::atoi(v) ? 1 : 0;
         if (const char* v = std::getenv("BA_TAIL_MODE1")) e->dbg_tail1 = std::atoi(v) ? 1 : 0;
         if (const char* v = std::getenv("BA_POSE_FACTORED")) e->factored_opt = std::atoi(v) ? 1 : 0;
+        {   // a 16-CTA cluster is a non-portable size: opt in, then ask whether this device can co-schedule one
+            int want = bak::TAIL_CL_WIDE;
+            if (const char* v = std::getenv("BA_TAIL_CL")) want = std::atoi(v);
+            e->tail_cl = bak::TAIL_CL;
+            if (want == bak::TAIL_CL_WIDE && cudaFuncSetAttribute(bak::k_pcg_tail<bak::TAIL_CL_WIDE>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess) {
+                cudaLaunchConfig_t cfg{};
+                cfg.gridDim = dim3(bak::TAIL_CL_WIDE); cfg.blockDim = dim3(bak::TAIL_THREADS); cfg.dynamicSmemBytes = 0;
+                cudaLaunchAttribute at[1];
+                at[0].id = cudaLaunchAttributeClusterDimension; at[0].val.clusterDim.x = bak::TAIL_CL_WIDE; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+                cfg.attrs = at; cfg.numAttrs = 1;
+                int nclusters = 0;
+                if (cudaOccupancyMaxActiveClusters(&nclusters, bak::k_pcg_tail<bak::TAIL_CL_WIDE>, &cfg) != cudaSuccess) {   // the kernel carries __cluster_dims__: ask again without the attribute
+                    (void)cudaGetLastError();
+                    cfg.numAttrs = 0; nclusters = 0;
+                    if (cudaOccupancyMaxActiveClusters(&nclusters, bak::k_pcg_tail<bak::TAIL_CL_WIDE>, &cfg) != cudaSuccess) nclusters = 0;
+                }
+                if (nclusters >= 1) e->tail_cl = bak::TAIL_CL_WIDE;
+            }
+            (void)cudaGetLastError();   // a refusal above is not an error of this engine
+        }
         if (const char* v = std::getenv("BA_P2P_WIDE")) e->p2p_wide = std::atoi(v) ? 1 : 0;
         // sm_100a images are architecture-specific: they run on compute capability 10.0 only (not on 10.3 / 12.x); probe one kernel as well
         if (prop.major != 10 || prop.minor != 0)
@@ -1810,10 +1832,10 @@ int ba_nccl_unique_id(void* out128) {
 int ba_get_execution_info(ba_engine* e, int64_t* info, int32_t cap, int32_t* n) {
     if (!e || !n) return BA_ERR_INVALID_ARGUMENT;
     if (!e->has_problem) return fail(e, BA_ERR_NO_PROBLEM, "no problem set");
-    const int64_t v[7] = {e->dense ? BA_LINEAR_EXACT : BA_LINEAR_PCG, e->scatter_eff, e->opt.world_size > 1 ? (e->p2p.on ? 2 : 1) : 0, e->host_syncs, e->nTiles, e->RS.nRows,
-                          (e->factored && !e->dense) ? 1 : 0};
-    *n = 7;
-    if (info) for (int i = 0; i < std::min<int>(cap, 7); ++i) info[i] = v[i];
+    const int64_t v[8] = {e->dense ? BA_LINEAR_EXACT : BA_LINEAR_PCG, e->scatter_eff, e->opt.world_size > 1 ? (e->p2p.on ? 2 : 1) : 0, e->host_syncs, e->nTiles, e->RS.nRows,
+                          (e->factored && !e->dense) ? 1 : 0, (e->tail_cl == bak::TAIL_CL_WIDE && e->nf >= 32768) ? bak::TAIL_CL_WIDE : bak::TAIL_CL};
+    *n = 8;
+    if (info) for (int i = 0; i < std::min<int>(cap, 8); ++i) info[i] = v[i];
     return BA_OK;
 }
 

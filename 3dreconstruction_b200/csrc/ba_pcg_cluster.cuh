@@ -24,6 +24,7 @@ namespace bak {
 #endif
 __device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
 constexpr int TAIL_CL = 8;          // CTAs in the cluster (portable maximum)
+constexpr int TAIL_CL_WIDE = 16;    // non-portable cluster size (cudaFuncAttributeNonPortableClusterSizeAllowed): large reduced systems, when the device can place it
 constexpr int TAIL_THREADS = 1024;
 
 struct TailArgs {
@@ -40,17 +41,19 @@ struct TailArgs {
 
 // Sum of one double per CTA over the cluster, the same value (bit for bit) in every thread of every CTA.  `slot` is this CTA's own
 // shared-memory cell for THIS reduction (a different cell per reduction, so no second barrier is needed before reuse).
+template <int CL>
 __device__ __forceinline__ double cluster_total(cooperative_groups::cluster_group& cl, double v, double* slot, double* sred) {
     v = block_sum(v, sred);
     if (threadIdx.x == 0) *slot = v;
     cl.sync();
     double tot = 0.0;
 #pragma unroll
-    for (int k = 0; k < TAIL_CL; ++k) tot += *cl.map_shared_rank(slot, k);
+    for (int k = 0; k < CL; ++k) tot += *cl.map_shared_rank(slot, k);
     return tot;
 }
 
-__global__ void __cluster_dims__(TAIL_CL, 1, 1) __launch_bounds__(TAIL_THREADS) k_pcg_tail(TailArgs A) {
+template <int CL>
+__global__ void __cluster_dims__(CL, 1, 1) __launch_bounds__(TAIL_THREADS) k_pcg_tail(TailArgs A) {
     namespace cg = cooperative_groups;
     __shared__ double sred[32];
     __shared__ double cell[3];
@@ -58,7 +61,7 @@ __global__ void __cluster_dims__(TAIL_CL, 1, 1) __launch_bounds__(TAIL_THREADS) 
     PcgState2* st = A.st;
     pdl_trigger();
     const int Nc = A.Nc, nblk = Nc + (A.fi ? A.Ng : 0);
-    const int per = ((nblk + TAIL_CL - 1) / TAIL_CL + 3) & ~3;          // diagonal blocks per CTA, whole warps of 8-lane groups
+    const int per = ((nblk + CL - 1) / CL + 3) & ~3;          // diagonal blocks per CTA, whole warps of 8-lane groups
     const int b0 = int(cl.block_rank()) * per, b1 = min(nblk, b0 + per);
     const int sub = threadIdx.x & 7, grp = threadIdx.x >> 3;
     constexpr int NGRP = TAIL_THREADS / 8;
@@ -142,7 +145,7 @@ __global__ void __cluster_dims__(TAIL_CL, 1, 1) __launch_bounds__(TAIL_THREADS) 
                 }
             }
         }
-        const double pq = cluster_total(cl, acc, &cell[0], sred);
+        const double pq = cluster_total<CL>(cl, acc, &cell[0], sred);
         if (!(pq > 0.0) || !isfinite(pq)) {      // breakdown: every CTA sees the same pq
             if (cl.block_rank() == 0 && threadIdx.x == 0) { st->done = 3; st->alpha = 0.0; }
             cl.sync();                           // nobody leaves while its shared memory may still be read
@@ -196,7 +199,7 @@ __global__ void __cluster_dims__(TAIL_CL, 1, 1) __launch_bounds__(TAIL_THREADS) 
     cl.sync();
     double rho_new = 0.0, xb = 0.0;
 #pragma unroll
-    for (int k = 0; k < TAIL_CL; ++k) { const double* c = cl.map_shared_rank(&cell[0], k); rho_new += c[1]; xb += c[2]; }
+    for (int k = 0; k < CL; ++k) { const double* c = cl.map_shared_rank(&cell[0], k); rho_new += c[1]; xb += c[2]; }
 
     // ---- stop rules (identical in every thread; CTA 0 records them), then p = z + beta p -----------------------------------------
     const int k = st->k + 1;

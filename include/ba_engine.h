@@ -239,7 +239,10 @@ int  ba_get_kernel_stats(ba_engine* e, ba_kernel_stat* out, int32_t cap, int32_t
 int  ba_linear_solver_in_use(ba_engine* e, int32_t* solver);  /* after ba_set_problem: BA_LINEAR_EXACT or BA_LINEAR_PCG, what AUTO resolved to for this problem */
 /* Execution facts for reports (bench.py, tools): info[0] = linear solver in use (as ba_linear_solver_in_use), [1] = scatter mode in effect for
  * the current problem (1, 4 or 6), [2] = all-reduce of the PCG matvec (0: one GPU, 1: NCCL, 2: one-shot NVLink peer memory), [3] = host
- * synchronisations of the last ba_solve (Scalars read-backs), [4] = tiles and [5] = partial rows of this rank's shard.  The oracle reports zeros. */
+ * synchronisations of the last ba_solve (Scalars read-backs), [4] = tiles and [5] = partial rows of this rank's shard, [6] = 1 when the PCG
+ * matvec runs in its pose-factored form (streams the point columns only; BA_POSE_FACTORED=0 in the environment selects the explicit pose
+ * columns), [7] = CTAs of the PCG tail's thread-block cluster (8, or 16 for >= 32768 reduced unknowns where the device can place one).
+ * *n = entries the library has; at most cap are written.  The oracle reports zeros. */
 int  ba_get_execution_info(ba_engine* e, int64_t* info, int32_t cap, int32_t* n);
 int  ba_get_io_bytes(int64_t* h2d, int64_t* d2h);
 /* ba_cost_noalloc has NO counterpart in the reference: it was added for callers that cannot call

@@ -918,8 +918,8 @@ int ba_shard_points(int32_t, int32_t, const int32_t*, int32_t, int32_t*) { retur
 int ba_nccl_unique_id(void*) { return BA_ERR_UNSUPPORTED; }
 int ba_get_execution_info(ba_engine* e, int64_t* info, int32_t cap, int32_t* n) {
     if (!e || !n) return BA_ERR_INVALID_ARGUMENT;
-    *n = 6;
-    if (info) for (int i = 0; i < std::min<int>(cap, 6); ++i) info[i] = 0;
+    *n = 8;
+    if (info) for (int i = 0; i < std::min<int>(cap, 8); ++i) info[i] = 0;
     return BA_OK;
 }
 int ba_cost_noalloc(int32_t, void*, int32_t, int32_t, double, int32_t, int32_t, int32_t, int32_t, const double*, const double*, const int32_t*,
