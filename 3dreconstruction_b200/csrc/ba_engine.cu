@@ -894,6 +894,8 @@ void do_set_problem(ba_engine* e, const ba_problem* P, const DevState* dev = nul
         const double nr = e->RS.nRows;
         const double rb = 8.0 * bak::ROW_DOUBLES;   // bytes per partial row as stored
         e->stats[KID_K4].bytes = no * (jb + 16 + 16) + np * 24 + rb * nr + 16.0 * e->nTiles;
+        if (e->factored) e->stats[KID_K7].bytes = no * (48.0 + (e->fi ? 64.0 : 0.0) + 8 + 16) + np * (48 + 24 + 24 + 4 + 24) + (48 + 288 + 48) * nc;
+        if (e->factored) e->stats[KID_K4].bytes = no * (48.0 + (e->fi ? 64.0 : 0.0) + 16 + 16) + np * (24 + 24) + rb * nr + 16.0 * e->nTiles;
         e->stats[KID_K5].bytes = no * (jb + 16) + np * 48 + 48 * nc + rb * nr + 16.0 * e->nTiles;
         if (e->factored)   // pose-factored: Jp (48 B) [+ Ji 64 B] and the schedule record per observation, Hinv and the point per point, vt per camera
             e->stats[KID_K5].bytes = no * (48.0 + (e->fi ? 64.0 : 0.0) + 16) + np * (48 + 24) + 48 * nc + rb * nr + 16.0 * e->nTiles;
@@ -1016,6 +1018,19 @@ void launch_sweep(ba_engine* e, int kid, const double* xin, double* yout, const 
            else bak::k_schur_sweep<MODE, false, 0><<<e->nTiles, bak::TILE_OBS, 0, e->stream>>>(e->V, xin, yout, done, partial); }
 }
 
+// K7: back-substitution of the point steps and the model cost change, from the reduced solution in d_x.  Pose-factored form (streams Jp, r and
+// the index arrays; F y = Jp (v x X + tau) with (v, tau) = G_c y_c from k_pose_apply) whenever the factors exist, else the explicit sweep.
+void launch_backsub(ba_engine* e) {
+    if (!e->factored || e->nTiles == 0) { launch_sweep<bak::SWEEP_BACKSUB>(e, KID_K7, e->d_x.p, nullptr, nullptr, e->d_part0.p); return; }
+    LaunchTimer t(e, KID_K7);
+    KL(e), bak::k_pose_apply<<<cdiv(e->nf, 256), 256, 0, e->stream>>>(e->Nc, e->nf, e->d_G.p, e->d_x.p, e->d_vt.p);
+    KL(e);
+    if (e->fi) { if (e->jpack) bak::k_backsub_f<true, 1><<<e->nTiles, bak::TILE_OBS, 0, e->stream>>>(e->V, e->d_vt.p, e->d_pt.p, e->d_part0.p);
+                 else bak::k_backsub_f<true, 0><<<e->nTiles, bak::TILE_OBS, 0, e->stream>>>(e->V, e->d_vt.p, e->d_pt.p, e->d_part0.p); }
+    else { if (e->jpack) bak::k_backsub_f<false, 1><<<e->nTiles, bak::TILE_OBS, 0, e->stream>>>(e->V, e->d_vt.p, e->d_pt.p, e->d_part0.p);
+           else bak::k_backsub_f<false, 0><<<e->nTiles, bak::TILE_OBS, 0, e->stream>>>(e->V, e->d_vt.p, e->d_pt.p, e->d_part0.p); }
+}
+
 // K4 / K5a by the configured scatter: 1 = L2 atomics straight into `yout` (k_schur_sweep); 4 = partial rows, one CTA per
 // tile (k_schur_rows); 6 = partial rows, persistent streaming kernel (k_schur_stream).  4 and 6 leave the rows for the by-camera gather.
 #ifdef BA_WITH_STREAM
@@ -1065,10 +1080,13 @@ void launch_scatter(ba_engine* e, int kid, const double* xin, double* yout, cons
         return;
     }
 #endif
-    if (chain && e->factored) {   // K5a, pose-factored: gathers vt = G p (written by the PCG tail) instead of p, reads the points of the linearisation
-        auto gof = [&](auto kern) { launch_chain(e, kern, dim3(e->nTiles), dim3(bak::TILE_OBS), e->V, e->RS, e->d_vt.p, e->d_pt.p, yout, done); };
-        if (e->fi) { if (e->jpack) gof(bak::k_schur_rows_f<true, 1>); else gof(bak::k_schur_rows_f<true, 0>); }
-        else { if (e->jpack) gof(bak::k_schur_rows_f<false, 1>); else gof(bak::k_schur_rows_f<false, 0>); }
+    if (e->factored) {   // pose-factored rows.  K5a: gathers vt = G p (written by the PCG tail) instead of p; K4: no pose input.  Both read the points of the linearisation
+        auto gof = [&](auto kern) {
+            if (chain) launch_chain(e, kern, dim3(e->nTiles), dim3(bak::TILE_OBS), e->V, e->RS, e->d_vt.p, e->d_pt.p, yout, done);
+            else { KL(e); kern<<<e->nTiles, bak::TILE_OBS, 0, e->stream>>>(e->V, e->RS, nullptr, e->d_pt.p, yout, done); }
+        };
+        if (e->fi) { if (e->jpack) gof(bak::k_schur_rows_f<MODE, true, 1>); else gof(bak::k_schur_rows_f<MODE, true, 0>); }
+        else { if (e->jpack) gof(bak::k_schur_rows_f<MODE, false, 1>); else gof(bak::k_schur_rows_f<MODE, false, 0>); }
         return;
     }
     auto go = [&](auto kern) {
@@ -1102,7 +1120,7 @@ int solve_linear(ba_engine* e, double radius, double* rel_out, double lambda = 0
     if (!rowsm || e->nTiles == 0) e->d_b.zero(s);
     launch_scatter<bak::SWEEP_RHS>(e, KID_K4, nullptr, e->d_b.p, nullptr);
     if (rowsm && e->nTiles > 0) { LaunchTimer t(e, KID_GATHER);
-        KL(e), bak::k_camera_gather<<<gblocks, gthreads, 0, s>>>(e->Nc, e->Ng, e->fi, e->nTiles, e->RS, nullptr, nullptr, e->d_b.p, nullptr, nullptr, 0, nullptr); }
+        KL(e), bak::k_camera_gather<<<gblocks, gthreads, 0, s>>>(e->Nc, e->Ng, e->fi, e->nTiles, e->RS, nullptr, nullptr, e->d_b.p, nullptr, nullptr, 0, e->factored ? e->d_G.p : nullptr); }
     allreduce_sum(e, e->d_b.p, e->nf);
     if (e->dense) {   // direct solve (ba_dense.cuh): S formed densely, Cholesky with the right-hand side as an extra row, no host round trip
         const bak::DenseView& D = e->DV;
@@ -1130,7 +1148,7 @@ int solve_linear(ba_engine* e, double radius, double* rel_out, double lambda = 0
                 CU_TRY(cudaLaunchCooperativeKernel(reinterpret_cast<const void*>(bak::k_dense_chol), dim3(e->chol_grid), dim3(256), args, 0, s));
             }
         }
-        launch_sweep<bak::SWEEP_BACKSUB>(e, KID_K7, e->d_x.p, nullptr, nullptr, e->d_part0.p);
+        launch_backsub(e);
         { LaunchTimer t(e, KID_MISC);
           KL(e), bak::k_reduce_partials<<<1, 1024, 0, s>>>(e->d_part0.p, e->nTiles, &sc->mcc); }
         *rel_out = 0.0;
@@ -1215,7 +1233,7 @@ int solve_linear(ba_engine* e, double radius, double* rel_out, double lambda = 0
     *rel_out = e->h_scal->pcg.rel;
     if (e->h_scal->bad_lin || e->h_scal->pcg.done == 3) return -1;
     // back-substitution and model cost change
-    launch_sweep<bak::SWEEP_BACKSUB>(e, KID_K7, e->d_x.p, nullptr, nullptr, e->d_part0.p);
+    launch_backsub(e);
     { LaunchTimer t(e, KID_MISC);
       KL(e), bak::k_reduce_partials<<<1, 1024, 0, s>>>(e->d_part0.p, e->nTiles, &sc->mcc); }
     return e->h_scal->pcg.k;

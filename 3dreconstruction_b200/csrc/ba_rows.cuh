@@ -448,7 +448,8 @@ __device__ __forceinline__ void cp_async8(void* smem_dst, const void* gsrc) {
     asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(static_cast<uint32_t>(__cvta_generic_to_shared(smem_dst))), "l"(gsrc) : "memory");
 }
 
-template <bool FI, int PK>
+// MODE SWEEP_MATVEC: K5a as described.  MODE SWEEP_RHS: K4 in the same form, t = r - Jp vp (no per-point phase), rows (X x g ; g).
+template <int MODE, bool FI, int PK>
 __global__ void __launch_bounds__(TILE_OBS, BA_K5F_MINB)
 k_schur_rows_f(View V, RowSched S, const double* __restrict__ vt, const double* __restrict__ pt, double* __restrict__ atomic_out,
                const int* __restrict__ done_flag) {
@@ -470,7 +471,8 @@ k_schur_rows_f(View V, RowSched S, const double* __restrict__ vt, const double* 
         jp[0] = jp[1] = jp[2] = make_double2(0.0, 0.0);
         double X0 = 0.0, X1 = 0.0, X2 = 0.0;
         double2 h0 = make_double2(0.0, 0.0), h1 = h0, h2 = h0;
-        if (tid < npts) {   // this thread as a point thread (addressed from tile_info alone: no dependency on the schedule record)
+        double2 rr = make_double2(0.0, 0.0);
+        if (MODE == SWEEP_MATVEC && tid < npts) {   // this thread as a point thread (addressed from tile_info alone: no dependency on the schedule record)
             const double2* H = reinterpret_cast<const double2*>(V.Hinv + 6 * size_t(pfirst + tid));
 #if BA_K5F_HSMEM
             cp_async16(&M.sH[0][tid], H); cp_async16(&M.sH[1][tid], H + 1); cp_async16(&M.sH[2][tid], H + 2);
@@ -492,6 +494,7 @@ k_schur_rows_f(View V, RowSched S, const double* __restrict__ vt, const double* 
 #pragma unroll
                 for (int k = 0; k < 4; ++k) ji[k] = ldg2_once(Jq + size_t(3 + k) * V.ldo, once);
             }
+            if (MODE == SWEEP_RHS) rr = V.r2[o];
 #if !BA_K5F_XSMEM
             const double* Xp = pt + 3 * size_t(pfirst + ((tm.y >> 24) & 0xff));
             X0 = __ldg(Xp); X1 = __ldg(Xp + 1); X2 = __ldg(Xp + 2);
@@ -510,6 +513,8 @@ k_schur_rows_f(View V, RowSched S, const double* __restrict__ vt, const double* 
         const int g = (FI && act) ? V.cam_group[c] : 0;
         double2 u = make_double2(0.0, 0.0);
         double w0 = 0.0, w1 = 0.0, w2 = 0.0;
+        double tx = 0.0, ty = 0.0;
+      if (MODE == SWEEP_MATVEC) {
         if (act) {
             double x[8];                               // v = x[0..2], tau = x[3..5]
 #if BA_K5F_VT256
@@ -562,8 +567,15 @@ k_schur_rows_f(View V, RowSched S, const double* __restrict__ vt, const double* 
         __syncthreads();
         if (act) {
             const double* v = M.sV[lpt];
-            const double tx = u.x - (jp[0].x * v[0] + jp[1].x * v[1] + jp[2].x * v[2]);
-            const double ty = u.y - (jp[0].y * v[0] + jp[1].y * v[1] + jp[2].y * v[2]);
+            tx = u.x - (jp[0].x * v[0] + jp[1].x * v[1] + jp[2].x * v[2]);
+            ty = u.y - (jp[0].y * v[0] + jp[1].y * v[1] + jp[2].y * v[2]);
+        }
+      } else if (act) {   // SWEEP_RHS: t = r - E vp
+            const double* v = V.vp + 3 * size_t(pfirst + lpt);
+            tx = rr.x - (jp[0].x * v[0] + jp[1].x * v[1] + jp[2].x * v[2]);
+            ty = rr.y - (jp[0].y * v[0] + jp[1].y * v[1] + jp[2].y * v[2]);
+      }
+        if (act) {
             const double g0 = jp[0].x * tx + jp[0].y * ty, g1 = jp[1].x * tx + jp[1].y * ty, g2 = jp[2].x * tx + jp[2].y * ty;
 #if BA_K5F_XSMEM
             X0 = M.sX[lpt][0]; X1 = M.sX[lpt][1]; X2 = M.sX[lpt][2];
@@ -621,24 +633,27 @@ k_schur_rows_f(View V, RowSched S, const double* __restrict__ vt, const double* 
             }
             return u;
         };
-        double W[3] = {0, 0, 0};
-        for (int o = o0 + tid; o < o1; o += TILE_OBS) {
-            double2 jp[3];
-            load_jp<PK>(V, V.J2 + o, jp);
-            const double2 u = forward(o, V.obs_cam[o], jp);
+        double v0, v1, v2;
+        if (MODE == SWEEP_MATVEC) {
+            double W[3] = {0, 0, 0};
+            for (int o = o0 + tid; o < o1; o += TILE_OBS) {
+                double2 jp[3];
+                load_jp<PK>(V, V.J2 + o, jp);
+                const double2 u = forward(o, V.obs_cam[o], jp);
 #pragma unroll
-            for (int a = 0; a < 3; ++a) W[a] += jp[a].x * u.x + jp[a].y * u.y;
-        }
-        double w[3];
+                for (int a = 0; a < 3; ++a) W[a] += jp[a].x * u.x + jp[a].y * u.y;
+            }
+            double w[3];
 #pragma unroll
-        for (int a = 0; a < 3; ++a) w[a] = tile_sum(W[a], M.sred, BarCta{}, tid);
-        const double* H = V.Hinv + 6 * size_t(pfirst);
-        const double v0 = H[0] * w[0] + H[1] * w[1] + H[2] * w[2], v1 = H[1] * w[0] + H[3] * w[1] + H[4] * w[2], v2 = H[2] * w[0] + H[4] * w[1] + H[5] * w[2];
+            for (int a = 0; a < 3; ++a) w[a] = tile_sum(W[a], M.sred, BarCta{}, tid);
+            const double* H = V.Hinv + 6 * size_t(pfirst);
+            v0 = H[0] * w[0] + H[1] * w[1] + H[2] * w[2]; v1 = H[1] * w[0] + H[3] * w[1] + H[4] * w[2]; v2 = H[2] * w[0] + H[4] * w[1] + H[5] * w[2];
+        } else { v0 = V.vp[3 * size_t(pfirst)]; v1 = V.vp[3 * size_t(pfirst) + 1]; v2 = V.vp[3 * size_t(pfirst) + 2]; }
         for (int o = o0 + tid; o < o1; o += TILE_OBS) {
             const int c = V.obs_cam[o];
             double2 jp[3];
             load_jp<PK>(V, V.J2 + o, jp);
-            const double2 u = forward(o, c, jp);
+            const double2 u = MODE == SWEEP_MATVEC ? forward(o, c, jp) : V.r2[o];
             const double tx = u.x - (jp[0].x * v0 + jp[1].x * v1 + jp[2].x * v2), ty = u.y - (jp[0].y * v0 + jp[1].y * v1 + jp[2].y * v2);
             const double g0 = jp[0].x * tx + jp[0].y * ty, g1 = jp[1].x * tx + jp[1].y * ty, g2 = jp[2].x * tx + jp[2].y * ty;
             double2* dst = reinterpret_cast<double2*>(S.rows + size_t(ROW_DOUBLES) * (hbase + (o - o0)));
@@ -658,6 +673,123 @@ k_schur_rows_f(View V, RowSched S, const double* __restrict__ vt, const double* 
         }
     }
     if (FI && V.Ng == 1) tile_intr_store(S, M.sred, BarCta{}, tid, t, yi);
+}
+
+// vt = [G_c x_c | intrinsics entries of x] for an arbitrary reduced vector x (K7's input: the PCG solution).
+__global__ void k_pose_apply(int Nc, int nf, const double* __restrict__ G, const double* __restrict__ x, double* __restrict__ vt) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= nf) return;
+    if (j < 6 * Nc) {
+        const int c = j / 6, a = j - 6 * c;
+        const double* Gr = G + 36 * size_t(c) + 6 * a;
+        const double* xc = x + 6 * c;
+        double v = 0.0;
+#pragma unroll
+        for (int k = 0; k < 6; ++k) v += Gr[k] * xc[k];
+        vt[VT_STRIDE * size_t(c) + a] = v;
+    } else vt[j + (VT_STRIDE - 6) * Nc] = x[j];
+}
+
+// K7, pose-factored: yp = vp - Hinv E^T F y and the partial of sum m.(r + m/2), m = -(F y + E yp), with F y = Jp (v x X + tau) [+ Ji y_i],
+// (v, tau) = G_c y_c from k_pose_apply.  Same structure as k_schur_sweep<SWEEP_BACKSUB>; streams Jp, r and the index arrays only.
+template <bool FI, int PK>
+__global__ void __launch_bounds__(TILE_OBS)
+k_backsub_f(View V, const double* __restrict__ vt, const double* __restrict__ pt, double* __restrict__ partial) {
+    __shared__ double sW[TILE_OBS][3];
+    __shared__ double sV[TILE_OBS][3];
+    __shared__ double sred[32];
+    const int t = blockIdx.x;
+    const int o0 = V.tile_off[t], o1 = V.tile_off[t + 1];
+    const int ioff = VT_STRIDE * V.Nc;
+    double acc = 0.0;
+    auto forward = [&](int o, int c, const double* X, const double2 (&jp)[3]) {
+        const double2* xc = reinterpret_cast<const double2*>(vt + VT_STRIDE * size_t(c));
+        const double2 q0 = __ldg(xc), q1 = __ldg(xc + 1), q2 = __ldg(xc + 2);
+        const double d0 = q0.y * X[2] - q1.x * X[1] + q1.y, d1 = q1.x * X[0] - q0.x * X[2] + q2.x, d2 = q0.x * X[1] - q0.y * X[0] + q2.y;
+        double2 u = make_double2(jp[0].x * d0 + jp[1].x * d1 + jp[2].x * d2, jp[0].y * d0 + jp[1].y * d1 + jp[2].y * d2);
+        if (FI) {
+            const int g = V.cam_group[c];
+            double2 ji[4];
+            load_ji<PK>(V, V.J2 + o, ji);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) { const double xv = __ldg(vt + ioff + 4 * g + k); u.x += ji[k].x * xv; u.y += ji[k].y * xv; }
+        }
+        return u;
+    };
+    if (o1 - o0 <= TILE_OBS) {
+        const int o = o0 + threadIdx.x;
+        const bool act = o < o1;
+        double2 jp[3];
+        double2 u = make_double2(0.0, 0.0);
+        int p = 0;
+        if (act) {
+            const int c = V.obs_cam[o];
+            p = V.obs_pt[o];
+            load_jp<PK>(V, V.J2 + o, jp);
+            const double X[3] = {__ldg(pt + 3 * size_t(p)), __ldg(pt + 3 * size_t(p) + 1), __ldg(pt + 3 * size_t(p) + 2)};
+            u = forward(o, c, X, jp);
+#pragma unroll
+            for (int a = 0; a < 3; ++a) sW[threadIdx.x][a] = jp[a].x * u.x + jp[a].y * u.y;
+        }
+        __syncthreads();
+        const int pfirst = V.obs_pt[o0], plast = V.obs_pt[o1 - 1];
+        const int pj = pfirst + threadIdx.x;
+        if (pj <= plast) {
+            double W[3] = {0, 0, 0};
+            for (int i = V.pt_off[pj] - o0, e = V.pt_off[pj + 1] - o0; i < e; ++i) { W[0] += sW[i][0]; W[1] += sW[i][1]; W[2] += sW[i][2]; }
+            const double* H = V.Hinv + 6 * size_t(pj);
+            const double v0 = V.vp[3 * size_t(pj)] - (H[0] * W[0] + H[1] * W[1] + H[2] * W[2]);
+            const double v1 = V.vp[3 * size_t(pj) + 1] - (H[1] * W[0] + H[3] * W[1] + H[4] * W[2]);
+            const double v2 = V.vp[3 * size_t(pj) + 2] - (H[2] * W[0] + H[4] * W[1] + H[5] * W[2]);
+            V.yp[3 * size_t(pj)] = v0; V.yp[3 * size_t(pj) + 1] = v1; V.yp[3 * size_t(pj) + 2] = v2;
+            sV[threadIdx.x][0] = v0; sV[threadIdx.x][1] = v1; sV[threadIdx.x][2] = v2;
+        }
+        __syncthreads();
+        if (act) {
+            const double* v = sV[p - pfirst];
+            const double e0 = jp[0].x * v[0] + jp[1].x * v[1] + jp[2].x * v[2];
+            const double e1 = jp[0].y * v[0] + jp[1].y * v[1] + jp[2].y * v[2];
+            const double m0 = -(u.x + e0), m1 = -(u.y + e1);
+            const double2 r = V.r2[o];
+            acc += m0 * (r.x + 0.5 * m0) + m1 * (r.y + 0.5 * m1);
+        }
+    } else {   // one point with more than TILE_OBS observations
+        const int p = V.obs_pt[o0];
+        const double X[3] = {pt[3 * size_t(p)], pt[3 * size_t(p) + 1], pt[3 * size_t(p) + 2]};
+        double W[3] = {0, 0, 0};
+        for (int o = o0 + threadIdx.x; o < o1; o += TILE_OBS) {
+            double2 jp[3];
+            load_jp<PK>(V, V.J2 + o, jp);
+            const double2 u = forward(o, V.obs_cam[o], X, jp);
+#pragma unroll
+            for (int a = 0; a < 3; ++a) W[a] += jp[a].x * u.x + jp[a].y * u.y;
+        }
+#pragma unroll
+        for (int a = 0; a < 3; ++a) { const double s = block_sum(W[a], sred); if (threadIdx.x == 0) sV[0][a] = s; }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            const double* H = V.Hinv + 6 * size_t(p);
+            const double w0 = sV[0][0], w1 = sV[0][1], w2 = sV[0][2];
+            const double v0 = V.vp[3 * size_t(p)] - (H[0] * w0 + H[1] * w1 + H[2] * w2);
+            const double v1 = V.vp[3 * size_t(p) + 1] - (H[1] * w0 + H[3] * w1 + H[4] * w2);
+            const double v2 = V.vp[3 * size_t(p) + 2] - (H[2] * w0 + H[4] * w1 + H[5] * w2);
+            V.yp[3 * size_t(p)] = v0; V.yp[3 * size_t(p) + 1] = v1; V.yp[3 * size_t(p) + 2] = v2;
+            sV[1][0] = v0; sV[1][1] = v1; sV[1][2] = v2;
+        }
+        __syncthreads();
+        const double v0 = sV[1][0], v1 = sV[1][1], v2 = sV[1][2];
+        for (int o = o0 + threadIdx.x; o < o1; o += TILE_OBS) {
+            double2 jp[3];
+            load_jp<PK>(V, V.J2 + o, jp);
+            const double2 u = forward(o, V.obs_cam[o], X, jp);
+            const double e0 = jp[0].x * v0 + jp[1].x * v1 + jp[2].x * v2, e1 = jp[0].y * v0 + jp[1].y * v1 + jp[2].y * v2;
+            const double m0 = -(u.x + e0), m1 = -(u.y + e1);
+            const double2 r = V.r2[o];
+            acc += m0 * (r.x + 0.5 * m0) + m1 * (r.y + 0.5 * m1);
+        }
+    }
+    const double s = block_sum(acc, sred);
+    if (threadIdx.x == 0) partial[t] = s;
 }
 
 // ---------------------------------------------------------------------------------------------------------
