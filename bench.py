@@ -301,6 +301,12 @@ def run_ours(args, rank, world, local_rank):
                 traffic = json.load(f).get("dram_bytes_per_launch")
         allreduce = {0: "none (single GPU)", 1: "NCCL", 2: "one-shot NVLink peer-memory all-reduce fused into the gather and the PCG tail"}[info["allreduce"]]
         k5_kernel = {1: "k_schur_sweep (L2 atomics)", 4: "k_schur_rows (one CTA per tile)", 6: "k_schur_stream (persistent cp.async.bulk ring)"}[info["scatter_mode"]]
+        limiter = None
+        if info.get("pose_factored"):
+            k5_kernel = "k_schur_rows_f (one CTA per tile, pose-factored: streams the point columns only)"
+            # the contract's `bound` stays "hbm" (a byte-streaming FP64 kernel, no tensor-core work); what ncu shows saturated is stated beside it
+            limiter = ("load/store data pipe (ncu: l1tex__data_pipe_lsu_wavefronts ~90 % of peak, DRAM ~40 %): with 64 B per observation the per-observation "
+                       "gathers, the shared-memory camera sort and the shuffles of the fold cost more pipe cycles than the streams; see DESIGN.md 3.K5f")
         line = {
             "metric": METRIC, "value": lm_its / t_dev, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": 1e3 * t_dev / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
@@ -316,7 +322,7 @@ def run_ours(args, rank, world, local_rank):
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {"bound": "hbm", "kernel": f"K5_schur_matvec: {k5_kernel}, one PCG iteration's J sweep", "achieved": achieved, "peak": peak_gbs,
-                         "unit": "GB/s", "frac": achieved / peak_gbs, "traffic": traffic, "peak_source": peak_src,
+                         "unit": "GB/s", "frac": achieved / peak_gbs, "traffic": traffic, "peak_source": peak_src, "limiter": limiter,
                          "bytes_per_launch": k5["bytes_per_launch"], "launches": k5["launches"], "avg_us": k5_avg_s * 1e6,
                          "timed_launches": f"every {args.k5_stride}th of the timed region's K5 launches that did work is bracketed by CUDA events on the engine's stream"},
             "solve": {"lm_iterations_per_step": lm_its / args.steps, "pcg_iterations_per_step": pcg_its / args.steps, "ms_per_solve": 1e3 * t_dev / args.steps,
