@@ -855,7 +855,7 @@ void do_set_problem(ba_engine* e, const ba_problem* P, const DevState* dev = nul
     setup_p2p(e);
 
     bak::View& V = e->V;
-    V.Nc = Nc; V.Ng = Ng; V.Np = Np; V.No = No; V.ldo = e->ldo; V.nTiles = e->nTiles; V.fi = e->fi; V.left_twist = e->opt.lm_policy == BA_POLICY_G2O ? 1 : 0;
+    V.Nc = Nc; V.Ng = Ng; V.Np = Np; V.No = No; V.ldo = e->ldo; V.nTiles = e->nTiles; V.fi = e->fi; V.left_twist = e->opt.lm_policy == BA_POLICY_G2O ? 1 : 0; V.skip_jc = 0;
     V.tile_off = e->d_tile_off.p; V.obs_cam = e->d_obs_cam.p; V.obs_pt = e->d_obs_pt.p; V.obs_uv = e->d_obs_uv.p;
     V.pt_off = e->d_pt_off.p; V.cam_group = e->d_cam_group.p; V.cam_free = e->d_cam_free.p; V.grp_free = e->d_grp_free.p;
     V.perm_by_cam = e->d_perm.p; V.cam_off = e->d_cam_off.p;
@@ -878,7 +878,7 @@ void do_set_problem(ba_engine* e, const ba_problem* P, const DevState* dev = nul
     const double no = No, np = Np, nc = Nc, jb = (e->fi ? 208.0 : 144.0) - 16.0 * e->jpack;
     e->stats[KID_K0].bytes = (48 + 160) * nc;
     const double jca = e->fi ? 192.0 : 128.0;   // by-observation record for K2c
-    e->stats[KID_K1].bytes = no * (24 + jb + 16 + jca) + np * (24 + 72) + 160 * nc;
+    e->stats[KID_K1].bytes = no * (24 + jb + 16 + jca) + np * (24 + 72) + 160 * nc;   // (pose columns skipped: adjusted below, once `dense` and `factored` are known)
     e->stats[KID_K1C].bytes = no * 24 + np * 24 + 160 * nc;
     e->stats[KID_K2C].bytes = no * (jca + 4) + (288 + 48) * nc;
     e->stats[KID_K3P].bytes = np * (48 + 24 + 24 + 48 + 24);
@@ -895,6 +895,7 @@ void do_set_problem(ba_engine* e, const ba_problem* P, const DevState* dev = nul
         const double rb = 8.0 * bak::ROW_DOUBLES;   // bytes per partial row as stored
         e->stats[KID_K4].bytes = no * (jb + 16 + 16) + np * 24 + rb * nr + 16.0 * e->nTiles;
         if (e->factored) e->stats[KID_K7].bytes = no * (48.0 + (e->fi ? 64.0 : 0.0) + 8 + 16) + np * (48 + 24 + 24 + 4 + 24) + (48 + 288 + 48) * nc;
+        if (e->factored && !e->dense && e->opt.preconditioner != BA_PRECOND_SCHUR_JACOBI) e->stats[KID_K1].bytes -= no * (jb - 48.0 - (e->fi ? 64.0 : 0.0));   // the unread pose columns are not written
         if (e->factored) e->stats[KID_K4].bytes = no * (48.0 + (e->fi ? 64.0 : 0.0) + 16 + 16) + np * (24 + 24) + rb * nr + 16.0 * e->nTiles;
         e->stats[KID_K5].bytes = no * (jb + 16) + np * 48 + 48 * nc + rb * nr + 16.0 * e->nTiles;
         if (e->factored)   // pose-factored: Jp (48 B) [+ Ji 64 B] and the schedule record per observation, Hinv and the point per point, vt per camera
@@ -921,7 +922,7 @@ void read_scalars(ba_engine* e) {
 }
 
 // Evaluate residuals, Jacobian, cost and the block Hessian / gradient at the CURRENT parameters (K0, K1, K2c).
-void evaluate_full(ba_engine* e) {
+void evaluate_full(ba_engine* e, bool full_jacobian = false) {
     cudaStream_t s = e->stream;
     bak::Scalars* sc = e->d_scal.p;
     const bak::RobustParams rp{e->opt.robust_kind, e->opt.robust_a};
@@ -931,8 +932,12 @@ void evaluate_full(ba_engine* e) {
       if (e->factored) KL(e), bak::k_pose_factors<<<cdiv(e->Nc, 128), 128, 0, s>>>(e->Nc, e->d_camrec.p, e->d_cam_free.p, e->V.left_twist, e->d_G.p); }
     if (e->nTiles > 0) {
         LaunchTimer t(e, KID_K1);
-        if (e->opt.model == BA_MODEL_SNAVELY) KL(e), bak::k1_residual_jacobian<1><<<e->k1_grid, bak::TILE_OBS, 0, s>>>(e->V, e->d_camrec.p, e->d_intr.p, e->d_pt.p, rp, e->d_part0.p, &sc->bad_eval);
-        else KL(e), bak::k1_residual_jacobian<0><<<e->k1_grid, bak::TILE_OBS, 0, s>>>(e->V, e->d_camrec.p, e->d_intr.p, e->d_pt.p, rp, e->d_part0.p, &sc->bad_eval);
+        // the pose columns of J2 have no reader when K4/K5/K7 run pose-factored with the block-Jacobi preconditioner (K2c reads the by-observation
+        // records): K1 then skips those 80 / 96 bytes per observation -- except for ba_evaluate, which returns them
+        bak::View V1 = e->V;
+        V1.skip_jc = (!full_jacobian && e->factored && !e->dense && e->opt.preconditioner != BA_PRECOND_SCHUR_JACOBI) ? 1 : 0;
+        if (e->opt.model == BA_MODEL_SNAVELY) KL(e), bak::k1_residual_jacobian<1><<<e->k1_grid, bak::TILE_OBS, 0, s>>>(V1, e->d_camrec.p, e->d_intr.p, e->d_pt.p, rp, e->d_part0.p, &sc->bad_eval);
+        else KL(e), bak::k1_residual_jacobian<0><<<e->k1_grid, bak::TILE_OBS, 0, s>>>(V1, e->d_camrec.p, e->d_intr.p, e->d_pt.p, rp, e->d_part0.p, &sc->bad_eval);
     }
     { LaunchTimer t(e, KID_MISC);
       KL(e), bak::k_reduce_partials<<<1, 1024, 0, s>>>(e->d_part0.p, e->nTiles > 0 ? e->k1_grid : 0, &sc->cost); }
@@ -1759,7 +1764,7 @@ int ba_evaluate(ba_engine* e, double* cost, double* r, double* Jc, double* Jp, d
     int bad = 0;
     const int rc = guarded(e, [&] {
         CU_TRY(cudaSetDevice(e->device));
-        evaluate_full(e);
+        evaluate_full(e, true);
         read_scalars(e);
         bad = e->h_scal->bad_eval;
         if (cost) *cost = e->h_scal->cost;

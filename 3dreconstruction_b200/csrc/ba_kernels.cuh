@@ -33,6 +33,7 @@ struct View {
     int fi;                      // 1: intrinsics blocks are free (J2 has 13 column pairs)
     int jpack;                   // 1: pinhole model, columns 3 and 4 share one stored column (see load_jc): J2 has 8 (12) column pairs
     int left_twist;              // 1: pose columns are d/d(omega, upsilon) of T <- exp(omega, upsilon) T (g2o policy); 0: d/d(angle-axis, t)
+    int skip_jc;                 // K1 only: do not store the pose columns of J2 (nothing reads them when K4/K5/K7 run pose-factored; K2c reads JcA)
     const int* tile_off;         // [nTiles+1] first observation of each tile
     const int* obs_cam;          // [No]
     const int* obs_pt;           // [No] local point id, non-decreasing
@@ -426,13 +427,15 @@ k1_residual_jacobian(View V, const double* __restrict__ camrec, const double* __
             const double wc = V.cam_free[c] ? w : 0.0;   // constant pose: its Jacobian columns vanish (SetParameterBlockConstant, :105)
             double2* J = V.J2 + o;
             const size_t ld = V.ldo;
-            J[0 * ld] = make_double2(wc * Ja0[0], wc * Ja1[0]);
-            J[1 * ld] = make_double2(wc * Ja0[1], wc * Ja1[1]);
-            J[2 * ld] = make_double2(wc * Ja0[2], wc * Ja1[2]);
             const int pk = V.jpack;   // pinhole: A0[1] = A1[0] = 0, columns 3 and 4 share one stored column (load_jc)
-            if (pk) J[3 * ld] = make_double2(wc * A0[0], wc * A1[1]);
-            else { J[3 * ld] = make_double2(wc * A0[0], wc * A1[0]); J[4 * ld] = make_double2(wc * A0[1], wc * A1[1]); }
-            J[(5 - pk) * ld] = make_double2(wc * A0[2], wc * A1[2]);
+            if (!V.skip_jc) {
+                J[0 * ld] = make_double2(wc * Ja0[0], wc * Ja1[0]);
+                J[1 * ld] = make_double2(wc * Ja0[1], wc * Ja1[1]);
+                J[2 * ld] = make_double2(wc * Ja0[2], wc * Ja1[2]);
+                if (pk) J[3 * ld] = make_double2(wc * A0[0], wc * A1[1]);
+                else { J[3 * ld] = make_double2(wc * A0[0], wc * A1[0]); J[4 * ld] = make_double2(wc * A0[1], wc * A1[1]); }
+                J[(5 - pk) * ld] = make_double2(wc * A0[2], wc * A1[2]);
+            }
             const double p0[3] = {w * JX0[0], w * JX0[1], w * JX0[2]}, p1[3] = {w * JX1[0], w * JX1[1], w * JX1[2]};
             J[(6 - pk) * ld] = make_double2(p0[0], p1[0]);
             J[(7 - pk) * ld] = make_double2(p0[1], p1[1]);
