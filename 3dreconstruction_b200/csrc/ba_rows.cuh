@@ -728,15 +728,31 @@ k_backsub_f(View V, const double* __restrict__ vt, const double* __restrict__ pt
             load_jp<PK>(V, V.J2 + o, jp);
             const double X[3] = {__ldg(pt + 3 * size_t(p)), __ldg(pt + 3 * size_t(p) + 1), __ldg(pt + 3 * size_t(p) + 2)};
             u = forward(o, c, X, jp);
-#pragma unroll
-            for (int a = 0; a < 3; ++a) sW[threadIdx.x][a] = jp[a].x * u.x + jp[a].y * u.y;
+        }
+        {   // per-point sums: segmented shuffle reduction inside the warp (a point's observations are adjacent lanes), one shared-memory
+            // value per run; the point thread then adds one value per warp its point touches (as K5a does)
+            double w0 = 0.0, w1 = 0.0, w2 = 0.0;
+            if (act) { w0 = jp[0].x * u.x + jp[0].y * u.y; w1 = jp[1].x * u.x + jp[1].y * u.y; w2 = jp[2].x * u.x + jp[2].y * u.y; }
+            const unsigned same = __match_any_sync(0xffffffffu, act ? p : -1);
+            const int lane = threadIdx.x & 31;
+            const int segrem = __popc(same >> lane) - 1;
+            const int maxseg = __reduce_max_sync(0xffffffffu, segrem);
+            for (int d = 1; d <= maxseg; d <<= 1) {
+                const double a0 = __shfl_down_sync(0xffffffffu, w0, d), a1 = __shfl_down_sync(0xffffffffu, w1, d), a2 = __shfl_down_sync(0xffffffffu, w2, d);
+                if (d <= segrem) { w0 += a0; w1 += a1; w2 += a2; }
+            }
+            if (act && (same & ((1u << lane) - 1u)) == 0) { sW[threadIdx.x][0] = w0; sW[threadIdx.x][1] = w1; sW[threadIdx.x][2] = w2; }
         }
         __syncthreads();
         const int pfirst = V.obs_pt[o0], plast = V.obs_pt[o1 - 1];
         const int pj = pfirst + threadIdx.x;
         if (pj <= plast) {
+            const int i0 = V.pt_off[pj] - o0, i1 = V.pt_off[pj + 1] - o0;
             double W[3] = {0, 0, 0};
-            for (int i = V.pt_off[pj] - o0, e = V.pt_off[pj + 1] - o0; i < e; ++i) { W[0] += sW[i][0]; W[1] += sW[i][1]; W[2] += sW[i][2]; }
+            if (i1 > i0) {
+                W[0] = sW[i0][0]; W[1] = sW[i0][1]; W[2] = sW[i0][2];
+                for (int i = (i0 / 32 + 1) * 32; i < i1; i += 32) { W[0] += sW[i][0]; W[1] += sW[i][1]; W[2] += sW[i][2]; }
+            }
             const double* H = V.Hinv + 6 * size_t(pj);
             const double v0 = V.vp[3 * size_t(pj)] - (H[0] * W[0] + H[1] * W[1] + H[2] * W[2]);
             const double v1 = V.vp[3 * size_t(pj) + 1] - (H[1] * W[0] + H[3] * W[1] + H[4] * W[2]);
