@@ -188,6 +188,8 @@ struct ba_engine {
     vector<int32_t> h_shard_pt;   // [world+1] point range boundaries of every rank
     // device: static problem data
     DevBuf<int> d_tile_off, d_obs_cam, d_obs_pt, d_pt_off, d_cam_group, d_perm, d_cam_off;
+    DevBuf<int> d_pt_by_cam;          // local point of the i-th observation in camera order (pose-factored K2c)
+    bool lean = false;                // K1 writes neither the pose columns of J2 nor the by-observation records: K2c/K4/K5/K7 all run pose-factored (PCG, block-Jacobi)
     DevBuf<double2> d_obs_uv;
     DevBuf<unsigned char> d_cam_free, d_grp_free;
     // device: parameters (current, candidate, initial)
@@ -870,6 +872,11 @@ void do_set_problem(ba_engine* e, const ba_problem* P, const DevState* dev = nul
 
     pt_.tick("p2p, view");
     build_dense(e, P, pt_off);
+    e->lean = e->factored && !e->dense && e->opt.preconditioner != BA_PRECOND_SCHUR_JACOBI;
+    if (e->lean && No > 0) {
+        e->d_pt_by_cam.alloc(No);
+        KL(e), bak::k_points_by_camera<<<(No + 255) / 256, 256, 0, s>>>(No, e->d_perm.p, e->d_obs_pt.p, e->d_pt_by_cam.p);
+    }
     pt_.tick("dense setup");
     CU_TRY(cudaStreamSynchronize(s));   // the uploads read page-locked arrays this engine reuses in its next call
     pt_.tick("upload drain");
@@ -895,7 +902,10 @@ void do_set_problem(ba_engine* e, const ba_problem* P, const DevState* dev = nul
         const double rb = 8.0 * bak::ROW_DOUBLES;   // bytes per partial row as stored
         e->stats[KID_K4].bytes = no * (jb + 16 + 16) + np * 24 + rb * nr + 16.0 * e->nTiles;
         if (e->factored) e->stats[KID_K7].bytes = no * (48.0 + (e->fi ? 64.0 : 0.0) + 8 + 16) + np * (48 + 24 + 24 + 4 + 24) + (48 + 288 + 48) * nc;
-        if (e->factored && !e->dense && e->opt.preconditioner != BA_PRECOND_SCHUR_JACOBI) e->stats[KID_K1].bytes -= no * (jb - 48.0 - (e->fi ? 64.0 : 0.0));   // the unread pose columns are not written
+        if (e->lean) {   // neither the pose columns nor the by-observation records are written; K2c gathers Jp, r (4 [8] sectors per observation), two indices and the point
+            e->stats[KID_K1].bytes -= no * (jb - 48.0 - (e->fi ? 64.0 : 0.0) + jca) + 64 * nc;   // (and 96 of the record's 160 bytes)
+            e->stats[KID_K2C].bytes = no * (128.0 + (e->fi ? 128.0 : 0.0) + 8 + 24) + (288 + 288 + 48) * nc;
+        }
         if (e->factored) e->stats[KID_K4].bytes = no * (48.0 + (e->fi ? 64.0 : 0.0) + 16 + 16) + np * (24 + 24) + rb * nr + 16.0 * e->nTiles;
         e->stats[KID_K5].bytes = no * (jb + 16) + np * 48 + 48 * nc + rb * nr + 16.0 * e->nTiles;
         if (e->factored)   // pose-factored: Jp (48 B) [+ Ji 64 B] and the schedule record per observation, Hinv and the point per point, vt per camera
@@ -930,23 +940,31 @@ void evaluate_full(ba_engine* e, bool full_jacobian = false) {
     { LaunchTimer t(e, KID_K0);
       KL(e), bak::k0_camera_precompute<<<cdiv(e->Nc, 128), 128, 0, s>>>(e->Nc, e->d_pose.p, e->d_camrec.p, e->opt.taylor_rule);
       if (e->factored) KL(e), bak::k_pose_factors<<<cdiv(e->Nc, 128), 128, 0, s>>>(e->Nc, e->d_camrec.p, e->d_cam_free.p, e->V.left_twist, e->d_G.p); }
+    int k1_parts = 0;   // cost partials K1 writes (one per CTA of its persistent grid)
     if (e->nTiles > 0) {
         LaunchTimer t(e, KID_K1);
-        // the pose columns of J2 have no reader when K4/K5/K7 run pose-factored with the block-Jacobi preconditioner (K2c reads the by-observation
-        // records): K1 then skips those 80 / 96 bytes per observation -- except for ba_evaluate, which returns them
+        // neither the pose columns of J2 nor the by-observation records have a reader when K2c/K4/K5/K7 all run pose-factored (PCG with the
+        // block-Jacobi preconditioner): K1 then skips those 208 / 288 bytes per observation -- except for ba_evaluate, which returns the columns
         bak::View V1 = e->V;
-        V1.skip_jc = (!full_jacobian && e->factored && !e->dense && e->opt.preconditioner != BA_PRECOND_SCHUR_JACOBI) ? 1 : 0;
-        if (e->opt.model == BA_MODEL_SNAVELY) KL(e), bak::k1_residual_jacobian<1><<<e->k1_grid, bak::TILE_OBS, 0, s>>>(V1, e->d_camrec.p, e->d_intr.p, e->d_pt.p, rp, e->d_part0.p, &sc->bad_eval);
-        else KL(e), bak::k1_residual_jacobian<0><<<e->k1_grid, bak::TILE_OBS, 0, s>>>(V1, e->d_camrec.p, e->d_intr.p, e->d_pt.p, rp, e->d_part0.p, &sc->bad_eval);
+        V1.skip_jc = (!full_jacobian && e->lean) ? 1 : 0;
+        const int grid = V1.skip_jc ? std::max(1, std::min(e->nTiles, e->num_sms * K1_LEAN_CTAS_PER_SM)) : e->k1_grid;   // persistent: CTAs per SM x SMs
+        k1_parts = grid;
+        auto k1 = [&](auto kern) { KL(e); kern<<<grid, bak::TILE_OBS, 0, s>>>(V1, e->d_camrec.p, e->d_intr.p, e->d_pt.p, rp, e->d_part0.p, &sc->bad_eval); };
+        if (e->opt.model == BA_MODEL_SNAVELY) { if (V1.skip_jc) k1(bak::k1_residual_jacobian<1, true>); else k1(bak::k1_residual_jacobian<1, false>); }
+        else { if (V1.skip_jc) k1(bak::k1_residual_jacobian<0, true>); else k1(bak::k1_residual_jacobian<0, false>); }
     }
     { LaunchTimer t(e, KID_MISC);
-      KL(e), bak::k_reduce_partials<<<1, 1024, 0, s>>>(e->d_part0.p, e->nTiles > 0 ? e->k1_grid : 0, &sc->cost); }
+      KL(e), bak::k_reduce_partials<<<1, 1024, 0, s>>>(e->d_part0.p, k1_parts, &sc->cost); }
     if (e->Nc > 0) {
         LaunchTimer t(e, KID_K2C);
-        if (e->fi) {
-            KL(e), bak::k2c_camera_blocks<true><<<e->Nc, 128, 0, s>>>(e->V, e->Hcc(), e->gc(), e->d_ipart.p);
-            KL(e), bak::k_group_blocks<<<cdiv(e->Ng * 32, 128), 128, 0, s>>>(e->Ng, e->d_grp_off.p, e->d_grp_cams.p, e->d_ipart.p, e->Hii(), e->gi());
-        } else KL(e), bak::k2c_camera_blocks<false><<<e->Nc, 128, 0, s>>>(e->V, e->Hcc(), e->gc(), nullptr);
+        if (e->lean && e->No > 0) {   // pose-factored: from the SoA point columns, the residuals and the points (ba_rows.cuh)
+            if (e->fi) { if (e->jpack) KL(e), bak::k2c_camera_blocks_f<true, 1><<<e->Nc, 128, 0, s>>>(e->V, e->d_G.p, e->d_pt.p, e->d_pt_by_cam.p, e->Hcc(), e->gc(), e->d_ipart.p);
+                         else KL(e), bak::k2c_camera_blocks_f<true, 0><<<e->Nc, 128, 0, s>>>(e->V, e->d_G.p, e->d_pt.p, e->d_pt_by_cam.p, e->Hcc(), e->gc(), e->d_ipart.p); }
+            else { if (e->jpack) KL(e), bak::k2c_camera_blocks_f<false, 1><<<e->Nc, 128, 0, s>>>(e->V, e->d_G.p, e->d_pt.p, e->d_pt_by_cam.p, e->Hcc(), e->gc(), nullptr);
+                   else KL(e), bak::k2c_camera_blocks_f<false, 0><<<e->Nc, 128, 0, s>>>(e->V, e->d_G.p, e->d_pt.p, e->d_pt_by_cam.p, e->Hcc(), e->gc(), nullptr); }
+        } else if (e->fi) KL(e), bak::k2c_camera_blocks<true><<<e->Nc, 128, 0, s>>>(e->V, e->Hcc(), e->gc(), e->d_ipart.p);
+        else KL(e), bak::k2c_camera_blocks<false><<<e->Nc, 128, 0, s>>>(e->V, e->Hcc(), e->gc(), nullptr);
+        if (e->fi) KL(e), bak::k_group_blocks<<<cdiv(e->Ng * 32, 128), 128, 0, s>>>(e->Ng, e->d_grp_off.p, e->d_grp_cams.p, e->d_ipart.p, e->Hii(), e->gi());
     }
     if (e->opt.world_size > 1) {
         NCCL_TRY(g_nccl.GroupStart());

@@ -33,7 +33,7 @@ struct View {
     int fi;                      // 1: intrinsics blocks are free (J2 has 13 column pairs)
     int jpack;                   // 1: pinhole model, columns 3 and 4 share one stored column (see load_jc): J2 has 8 (12) column pairs
     int left_twist;              // 1: pose columns are d/d(omega, upsilon) of T <- exp(omega, upsilon) T (g2o policy); 0: d/d(angle-axis, t)
-    int skip_jc;                 // K1 only: do not store the pose columns of J2 (nothing reads them when K4/K5/K7 run pose-factored; K2c reads JcA)
+    int skip_jc;                 // K1 only: store neither the pose columns of J2 nor the by-observation records (nothing reads them when K2c/K4/K5/K7 run pose-factored)
     const int* tile_off;         // [nTiles+1] first observation of each tile
     const int* obs_cam;          // [No]
     const int* obs_pt;           // [No] local point id, non-decreasing
@@ -298,8 +298,13 @@ __device__ __forceinline__ void model_jacobian(const Proj& q, const double* __re
 #ifndef K1_CTAS_PER_SM
 #define K1_CTAS_PER_SM 4
 #endif
-template <int MODEL>
-__global__ void __launch_bounds__(TILE_OBS, K1_CTAS_PER_SM)
+// LEAN (engine: K2c/K4/K5/K7 all pose-factored): the pose columns and the by-observation records have no reader, so they are neither formed
+// nor stored, and only R and t of the camera record are fetched (96 of its 160 bytes: three 32-byte loads per observation instead of five).
+#ifndef K1_LEAN_CTAS_PER_SM
+#define K1_LEAN_CTAS_PER_SM 6   // 4: 240 us, 5: 235 us, 6: 220 us on the Venice shape (112 -> 85 registers, no spills that matter)
+#endif
+template <int MODEL, bool LEAN = false>
+__global__ void __launch_bounds__(TILE_OBS, LEAN ? K1_LEAN_CTAS_PER_SM : K1_CTAS_PER_SM)
 k1_residual_jacobian(View V, const double* __restrict__ camrec, const double* __restrict__ intr, const double* __restrict__ pt,
                      RobustParams rp, double* __restrict__ cost_partial, int* __restrict__ bad_flag) {
     __shared__ double sJp[TILE_OBS][9];   // per observation: Jp (2x3) , r (2)  [+1 pad: stride 9 is conflict-free]
@@ -376,7 +381,8 @@ k1_residual_jacobian(View V, const double* __restrict__ camrec, const double* __
 #pragma unroll
             for (int k = 0; k < CAMREC / 2; ++k) { int sl = k + rot12; if (sl >= 12) sl -= 12; const double2 v = sA[threadIdx.x * 12 + sl]; cr[2 * k] = v.x; cr[2 * k + 1] = v.y; }
 #else
-            load_camrec<CAMREC / 2>(camrec, c, cr);
+            if (LEAN) load_camrec<6>(camrec, c, cr);
+            else load_camrec<CAMREC / 2>(camrec, c, cr);
 #endif
             const double* in = intr + 4 * g;
             Proj q;
@@ -396,6 +402,8 @@ k1_residual_jacobian(View V, const double* __restrict__ camrec, const double* __
                 JX0[k] = A0[0] * cr[CR_R + k] + A0[1] * cr[CR_R + 3 + k] + A0[2] * cr[CR_R + 6 + k];
                 JX1[k] = A1[0] * cr[CR_R + k] + A1[1] * cr[CR_R + 3 + k] + A1[2] * cr[CR_R + 6 + k];
             }
+            double Ja0[3] = {0, 0, 0}, Ja1[3] = {0, 0, 0};
+            if (!LEAN) {
             // J_aa = A G, row i: (A_i.h) aa - a (A_i x X) + b (d A_i + (A_i.aa) X)
             const double ax = cr[CR_AA], ay = cr[CR_AA + 1], az = cr[CR_AA + 2];
             const double X0 = q.X[0], X1 = q.X[1], X2 = q.X[2];
@@ -403,7 +411,6 @@ k1_residual_jacobian(View V, const double* __restrict__ camrec, const double* __
             const double qx = ay * X2 - az * X1, qy = az * X0 - ax * X2, qz = ax * X1 - ay * X0;   // aa x X
             const double ca = cr[CR_A], cb = cr[CR_B], c1 = cr[CR_C1], c2 = cr[CR_C2], c3 = cr[CR_C3];
             const double hx = c1 * X0 + c2 * qx + c3 * d * ax, hy = c1 * X1 + c2 * qy + c3 * d * ay, hz = c1 * X2 + c2 * qz + c3 * d * az;
-            double Ja0[3], Ja1[3];
             if (V.left_twist) {   // g2o VertexSE3Expmap: dP/d(omega) = -[P]x  =>  row = P x A_i   (EdgeSE3ProjectXYZ::linearizeOplus)
                 const double P0 = q.P[0], P1 = q.P[1], P2 = q.P[2];
                 Ja0[0] = P1 * A0[2] - P2 * A0[1]; Ja0[1] = P2 * A0[0] - P0 * A0[2]; Ja0[2] = P0 * A0[1] - P1 * A0[0];
@@ -424,11 +431,12 @@ k1_residual_jacobian(View V, const double* __restrict__ camrec, const double* __
                 Ja1[2] = Ah * az - ca * cx2 + cb * (d * A1[2] + Aa * X2);
             }
             }
+            }
             const double wc = V.cam_free[c] ? w : 0.0;   // constant pose: its Jacobian columns vanish (SetParameterBlockConstant, :105)
             double2* J = V.J2 + o;
             const size_t ld = V.ldo;
             const int pk = V.jpack;   // pinhole: A0[1] = A1[0] = 0, columns 3 and 4 share one stored column (load_jc)
-            if (!V.skip_jc) {
+            if (!LEAN && !V.skip_jc) {
                 J[0 * ld] = make_double2(wc * Ja0[0], wc * Ja1[0]);
                 J[1 * ld] = make_double2(wc * Ja0[1], wc * Ja1[1]);
                 J[2 * ld] = make_double2(wc * Ja0[2], wc * Ja1[2]);
@@ -447,7 +455,7 @@ k1_residual_jacobian(View V, const double* __restrict__ camrec, const double* __
             }
             const double rr0 = w * q.r0, rr1 = w * q.r1;
             V.r2[o] = make_double2(rr0, rr1);
-            {   // by-observation record for K2c: whole sectors, so the by-camera gather fetches no byte it does not use
+            if (!LEAN && !V.skip_jc) {   // by-observation record for K2c: whole sectors, so the by-camera gather fetches no byte it does not use (not written when K2c runs pose-factored)
 #if BA_K1_JCA_SMEM
                 // staged in shared memory (12 slots of 16 bytes per thread, chunk k in slot (k + rot) % 12: conflict-free for the 16-byte
                 // accesses of 8 adjacent lanes) and written out after the barrier by consecutive lanes: whole lines per warp instruction.
@@ -477,7 +485,7 @@ k1_residual_jacobian(View V, const double* __restrict__ camrec, const double* __
         }
         __syncthreads();
 #if BA_K1_JCA_SMEM
-        {   // write the chunk's records out: consecutive lanes take consecutive 16-byte pieces of the records
+        if (!LEAN && !V.skip_jc) {   // write the chunk's records out: consecutive lanes take consecutive 16-byte pieces of the records
             const int st = V.jca_stride, nq = (lim - base) * st;
             double2* dst = V.JcA + size_t(base) * st;
             for (int q = threadIdx.x; q < nq; q += TILE_OBS) {

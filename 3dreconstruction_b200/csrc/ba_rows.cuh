@@ -675,6 +675,111 @@ k_schur_rows_f(View V, RowSched S, const double* __restrict__ vt, const double* 
     if (FI && V.Ng == 1) tile_intr_store(S, M.sred, BarCta{}, tid, t, yi);
 }
 
+// pt_by_cam[i] = local point of the i-th observation in camera order (static; built on the device once per ba_set_problem)
+__global__ void k_points_by_camera(int No, const int* __restrict__ perm_by_cam, const int* __restrict__ obs_pt, int* __restrict__ pt_by_cam) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < No) pt_by_cam[i] = obs_pt[perm_by_cam[i]];
+}
+
+// K2c, pose-factored: Hcc[c] = G^T N G and gc[c] = G^T n with  N = sum K(X)^T (Jp^T Jp) K(X),  n = sum K(X)^T Jp^T r  over the camera's
+// observations (camera order, fixed summation order => deterministic), K(X) = [-[X]x | I].  Reads the SoA point columns and residuals K1
+// writes for K4/K5/K7 anyway (four 16-byte pieces per observation) and the point, so K1 need not write the 128-byte by-observation
+// records (640 MB per evaluation on the Venice shape).  With free intrinsics also the camera's share of its group's 4x4 block and
+// gradient (ipart, as k2c_camera_blocks<true>).  N = [ -S M S   S M ; (S M)^T   M ],  S = [X]x,  M = Jp^T Jp.
+#ifndef BA_K2CF_MINB
+#define BA_K2CF_MINB 4
+#endif
+template <bool FI, int PK>
+__global__ void __launch_bounds__(128, FI ? 3 : BA_K2CF_MINB)
+k2c_camera_blocks_f(View V, const double* __restrict__ G, const double* __restrict__ pt, const int* __restrict__ pt_by_cam,
+                    double* __restrict__ Hcc, double* __restrict__ gc, double* __restrict__ ipart) {
+    constexpr int NV = FI ? (21 + 6 + 10 + 4) : (21 + 6);   // N_rr (6), S M (9), M (6), n (6), [Hii upper, gi]
+    __shared__ double sm[4][NV];
+    __shared__ double sN[36], sT[36], sG[36], sn[6];
+    const int c = blockIdx.x;
+    const int a0 = V.cam_off[c], a1 = V.cam_off[c + 1];
+    if (threadIdx.x < 36) sG[threadIdx.x] = G[36 * size_t(c) + threadIdx.x];
+    const size_t ld = V.ldo;
+    const int jp_col = 6 - (PK < 0 ? V.jpack : PK);
+    double acc[NV];
+#pragma unroll
+    for (int k = 0; k < NV; ++k) acc[k] = 0.0;
+    for (int i = a0 + threadIdx.x; i < a1; i += 128) {
+        const int o = __ldg(V.perm_by_cam + i), p = __ldg(pt_by_cam + i);
+        const double2* Jq = V.J2 + o + size_t(jp_col) * ld;
+        const double2 j0 = __ldg(Jq), j1 = __ldg(Jq + ld), j2 = __ldg(Jq + 2 * ld), r = __ldg(V.r2 + o);
+        const double X0 = __ldg(pt + 3 * size_t(p)), X1 = __ldg(pt + 3 * size_t(p) + 1), X2 = __ldg(pt + 3 * size_t(p) + 2);
+        const double M00 = j0.x * j0.x + j0.y * j0.y, M01 = j0.x * j1.x + j0.y * j1.y, M02 = j0.x * j2.x + j0.y * j2.y;
+        const double M11 = j1.x * j1.x + j1.y * j1.y, M12 = j1.x * j2.x + j1.y * j2.y, M22 = j2.x * j2.x + j2.y * j2.y;
+        // P = S M
+        const double P00 = X1 * M02 - X2 * M01, P01 = X1 * M12 - X2 * M11, P02 = X1 * M22 - X2 * M12;
+        const double P10 = X2 * M00 - X0 * M02, P11 = X2 * M01 - X0 * M12, P12 = X2 * M02 - X0 * M22;
+        const double P20 = X0 * M01 - X1 * M00, P21 = X0 * M11 - X1 * M01, P22 = X0 * M12 - X1 * M02;
+        // N_rr = -P S (symmetric): (P S)_i0 = P_i1 X2 - P_i2 X1, (P S)_i1 = P_i2 X0 - P_i0 X2, (P S)_i2 = P_i0 X1 - P_i1 X0
+        acc[0] += P02 * X1 - P01 * X2;  acc[1] += P00 * X2 - P02 * X0;  acc[2] += P01 * X0 - P00 * X1;
+        acc[3] += P10 * X2 - P12 * X0;  acc[4] += P11 * X0 - P10 * X1;  acc[5] += P21 * X0 - P20 * X1;
+        acc[6] += P00; acc[7] += P01; acc[8] += P02; acc[9] += P10; acc[10] += P11; acc[11] += P12; acc[12] += P20; acc[13] += P21; acc[14] += P22;
+        acc[15] += M00; acc[16] += M01; acc[17] += M02; acc[18] += M11; acc[19] += M12; acc[20] += M22;
+        const double g0 = j0.x * r.x + j0.y * r.y, g1 = j1.x * r.x + j1.y * r.y, g2 = j2.x * r.x + j2.y * r.y;
+        acc[21] += X1 * g2 - X2 * g1; acc[22] += X2 * g0 - X0 * g2; acc[23] += X0 * g1 - X1 * g0;
+        acc[24] += g0; acc[25] += g1; acc[26] += g2;
+        if (FI) {
+            double2 ji[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) ji[k] = __ldg(Jq + size_t(3 + k) * ld);
+            int n = 27;
+#pragma unroll
+            for (int a = 0; a < 4; ++a)
+#pragma unroll
+                for (int b = a; b < 4; ++b) acc[n++] += ji[a].x * ji[b].x + ji[a].y * ji[b].y;
+#pragma unroll
+            for (int a = 0; a < 4; ++a) acc[n++] += ji[a].x * r.x + ji[a].y * r.y;
+        }
+    }
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+#pragma unroll
+    for (int k = 0; k < NV; ++k) { const double s = warp_sum(acc[k]); if (lane == 0) sm[wid][k] = s; }
+    __syncthreads();
+    if (threadIdx.x < NV) {
+        const int k = threadIdx.x;
+        const double s = (sm[0][k] + sm[1][k]) + (sm[2][k] + sm[3][k]);
+        if (k < 6) {             // N_rr upper triangle: (0,0) (0,1) (0,2) (1,1) (1,2) (2,2)
+            const int a = k < 3 ? 0 : (k < 5 ? 1 : 2), b = k < 3 ? k : (k < 5 ? k - 2 : 2);
+            sN[6 * a + b] = s; sN[6 * b + a] = s;
+        } else if (k < 15) {     // N_rt = S M (3x3) and its transpose
+            const int a = (k - 6) / 3, b = (k - 6) % 3;
+            sN[6 * a + 3 + b] = s; sN[6 * (3 + b) + a] = s;
+        } else if (k < 21) {     // N_tt = M upper triangle
+            const int q = k - 15, a = q < 3 ? 0 : (q < 5 ? 1 : 2), b = q < 3 ? q : (q < 5 ? q - 2 : 2);
+            sN[6 * (3 + a) + 3 + b] = s; sN[6 * (3 + b) + 3 + a] = s;
+        } else if (k < 27) sn[k - 21] = s;
+        else if (FI) ipart[14 * size_t(c) + (k - 27)] = s;
+    }
+    __syncthreads();
+    if (threadIdx.x < 36) {      // T = N G
+        const int a = threadIdx.x / 6, b = threadIdx.x % 6;
+        double t = 0.0;
+#pragma unroll
+        for (int k = 0; k < 6; ++k) t += sN[6 * a + k] * sG[6 * k + b];
+        sT[threadIdx.x] = t;
+    }
+    __syncthreads();
+    if (threadIdx.x < 36) {      // Hcc = G^T T; the upper triangle is computed and mirrored so that the block is exactly symmetric
+        const int a = threadIdx.x / 6, b = threadIdx.x % 6;
+        const int lo = min(a, b), hi = max(a, b);
+        double h = 0.0;
+#pragma unroll
+        for (int k = 0; k < 6; ++k) h += sG[6 * k + lo] * sT[6 * k + hi];
+        Hcc[36 * size_t(c) + threadIdx.x] = h;
+    } else if (threadIdx.x < 42) {
+        const int a = threadIdx.x - 36;
+        double v = 0.0;
+#pragma unroll
+        for (int k = 0; k < 6; ++k) v += sG[6 * k + a] * sn[k];
+        gc[6 * size_t(c) + a] = v;
+    }
+}
+
 // vt = [G_c x_c | intrinsics entries of x] for an arbitrary reduced vector x (K7's input: the PCG solution).
 __global__ void k_pose_apply(int Nc, int nf, const double* __restrict__ G, const double* __restrict__ x, double* __restrict__ vt) {
     const int j = blockIdx.x * blockDim.x + threadIdx.x;
