@@ -6,6 +6,8 @@
 //     k_schur_stream (scatter_mode 6, ba_stream.cuh): persistent, warp-specialised, tiles streamed through a shared-memory ring with
 //                    cp.async.bulk + mbarrier.
 //   K5b  k_camera_gather: one CTA per camera adds that camera's rows in the fixed order of a static list.
+//   Pose-factored forms (the defaults, second half of this file): k_pose_factors (G_c per camera), k_schur_rows_f (K5a and
+//   K4 from the point columns only), k_backsub_f + k_pose_apply (K7), k2c_camera_blocks_f (K2c); the gather multiplies by G_c^T.
 //
 // Tile math: thread i = observation i of the tile.  u = Jc p[c] (+ Ji p[g]);  per point W = sum Jp^T u through shared memory (points
 // are contiguous, thread j sums point j), v = Hinv W;  t = u - Jp v;  the 6-vector Jc^T t is written to shared memory at the
