@@ -302,6 +302,13 @@ def run_ours(args, rank, world, local_rank):
         allreduce = {0: "none (single GPU)", 1: "NCCL", 2: "one-shot NVLink peer-memory all-reduce fused into the gather and the PCG tail"}[info["allreduce"]]
         k5_kernel = {1: "k_schur_sweep (L2 atomics)", 4: "k_schur_rows (one CTA per tile)", 6: "k_schur_stream (persistent cp.async.bulk ring)"}[info["scatter_mode"]]
         limiter = None
+        survey = None
+        if world == 1 and k5_avg_s > 0:
+            # SURVEY 8d's formula for one PCG iteration with a materialised Jacobian (152 No + 72 Np + 384 Nc): informational -- `achieved` and
+            # `frac` above use the bytes of THIS formulation (restated in BASELINE.md 5 / DESIGN.md 3), which are fewer
+            sb = 152.0 * P.sizes[3] + 72.0 * P.sizes[2] + 384.0 * P.sizes[0]
+            survey = {"bytes_per_launch": sb, "equivalent_gbs": sb / k5_avg_s / 1e9, "equivalent_frac": sb / k5_avg_s / 1e9 / peak_gbs,
+                      "note": "what the measured launch time would mean for the SURVEY's materialised-J formulation of K5; not the roofline claim"}
         if info.get("pose_factored"):
             k5_kernel = "k_schur_rows_f (one CTA per tile, pose-factored: streams the point columns only)"
             # the contract's `bound` stays "hbm" (a byte-streaming FP64 kernel, no tensor-core work); what ncu shows saturated is stated beside it
@@ -323,6 +330,7 @@ def run_ours(args, rank, world, local_rank):
             "clocks": clocks,
             "roofline": {"bound": "hbm", "kernel": f"K5_schur_matvec: {k5_kernel}, one PCG iteration's J sweep", "achieved": achieved, "peak": peak_gbs,
                          "unit": "GB/s", "frac": achieved / peak_gbs, "traffic": traffic, "peak_source": peak_src, "limiter": limiter,
+                         "survey_formula": survey,
                          "bytes_per_launch": k5["bytes_per_launch"], "launches": k5["launches"], "avg_us": k5_avg_s * 1e6,
                          "timed_launches": f"every {args.k5_stride}th of the timed region's K5 launches that did work is bracketed by CUDA events on the engine's stream"},
             "solve": {"lm_iterations_per_step": lm_its / args.steps, "pcg_iterations_per_step": pcg_its / args.steps, "ms_per_solve": 1e3 * t_dev / args.steps,
