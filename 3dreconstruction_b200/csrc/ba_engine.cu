@@ -251,6 +251,7 @@ struct ba_engine {
     unsigned profiling = 0;           // bit k set: time kernel id k with CUDA events
     struct Stat { int64_t launches = 0; int64_t timed = 0; double ms = 0.0; double bytes = 0.0; } stats[KID_COUNT];
     int dbg_tail1 = 0;                // BA_TAIL_MODE1
+    int tail_wide_min_nf = 32768;     // BA_TAIL_WIDE_MIN_NF: reduced unknowns from which the 16-CTA cluster is used
     int tail_cl = 8;                  // CTAs of the PCG tail's cluster for reduced systems of >= 32768 unknowns: 16 where the device can place such a cluster (BA_TAIL_CL=8 forces 8)
     int factored_opt = 1;             // BA_POSE_FACTORED (default 1): K5a streams Jp only (ba_rows.cuh: k_pose_factors); 0 = explicit Jc and Jp (bisecting / A-B)
     int factored = 0;                 // in effect for the current problem (partial rows, one CTA per tile, PCG)
@@ -1233,7 +1234,7 @@ int solve_linear(ba_engine* e, double radius, double* rel_out, double lambda = 0
             }
             // q, alpha, x, r, z, rho, beta, stop test and the new search direction: one thread-block cluster (ba_pcg_cluster.cuh)
             LaunchTimer tt(e, KID_TAIL, sample, launched);
-            if (e->tail_cl == bak::TAIL_CL_WIDE && e->nf >= 32768) launch_chain(e, bak::k_pcg_tail<bak::TAIL_CL_WIDE>, dim3(bak::TAIL_CL_WIDE), dim3(bak::TAIL_THREADS), ta);
+            if (e->tail_cl == bak::TAIL_CL_WIDE && e->nf >= e->tail_wide_min_nf) launch_chain(e, bak::k_pcg_tail<bak::TAIL_CL_WIDE>, dim3(bak::TAIL_CL_WIDE), dim3(bak::TAIL_THREADS), ta);
             else launch_chain(e, bak::k_pcg_tail<bak::TAIL_CL>, dim3(bak::TAIL_CL), dim3(bak::TAIL_THREADS), ta);
         }
         read_scalars(e);
@@ -1551,6 +1552,7 @@ int ba_create(const ba_options* opt, ba_engine** out) {
         {   // a 16-CTA cluster is a non-portable size: opt in, then ask whether this device can co-schedule one
             int want = bak::TAIL_CL_WIDE;
             if (const char* v = std::getenv("BA_TAIL_CL")) want = std::atoi(v);
+            if (const char* v = std::getenv("BA_TAIL_WIDE_MIN_NF")) e->tail_wide_min_nf = std::max(0, std::atoi(v));
             e->tail_cl = bak::TAIL_CL;
             if (want == bak::TAIL_CL_WIDE && cudaFuncSetAttribute(bak::k_pcg_tail<bak::TAIL_CL_WIDE>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess) {
                 cudaLaunchConfig_t cfg{};
@@ -1874,7 +1876,7 @@ int ba_get_execution_info(ba_engine* e, int64_t* info, int32_t cap, int32_t* n) 
     if (!e || !n) return BA_ERR_INVALID_ARGUMENT;
     if (!e->has_problem) return fail(e, BA_ERR_NO_PROBLEM, "no problem set");
     const int64_t v[8] = {e->dense ? BA_LINEAR_EXACT : BA_LINEAR_PCG, e->scatter_eff, e->opt.world_size > 1 ? (e->p2p.on ? 2 : 1) : 0, e->host_syncs, e->nTiles, e->RS.nRows,
-                          (e->factored && !e->dense) ? 1 : 0, (e->tail_cl == bak::TAIL_CL_WIDE && e->nf >= 32768) ? bak::TAIL_CL_WIDE : bak::TAIL_CL};
+                          (e->factored && !e->dense) ? 1 : 0, (e->tail_cl == bak::TAIL_CL_WIDE && e->nf >= e->tail_wide_min_nf) ? bak::TAIL_CL_WIDE : bak::TAIL_CL};
     *n = 8;
     if (info) for (int i = 0; i < std::min<int>(cap, 8); ++i) info[i] = v[i];
     return BA_OK;
