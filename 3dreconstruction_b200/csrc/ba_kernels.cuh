@@ -613,7 +613,6 @@ k_schur_sweep(View V, const double* __restrict__ xin, double* __restrict__ yout,
     if (done_flag && *done_flag) return;   // PCG already converged: batched launches become no-ops
     const int t = blockIdx.x;
     const int o0 = V.tile_off[t], o1 = V.tile_off[t + 1];
-    const size_t ld = V.ldo;
     const int ioff = 6 * V.Nc;
     double acc = 0.0;                      // BACKSUB: model-cost partial
     double yi[4] = {0, 0, 0, 0};           // FI: intrinsics-side scatter, reduced per CTA when there is one group
